@@ -1,0 +1,135 @@
+/*
+ * b200_wgridder.h -- C ABI of the B200-native visibility gridder / degridder.
+ *
+ * This is the drop-in boundary for the hot path of
+ *   ska_sdp_func_python.imaging.ng.invert_ng / predict_ng
+ * (/root/reference/src/ska_sdp_func_python/imaging/ng.py:146-294, :38-143).  In the
+ * reference all arithmetic of that path happens inside two calls into the third-party
+ * C++ module ducc0.wgridder:
+ *
+ *   ducc0.wgridder.ms2dirty(uvw, freq, ms, wgt, npix_x, npix_y, pixsize_x, pixsize_y,
+ *                           nu, nv, epsilon, do_wstacking, nthreads=, verbosity=,
+ *                           double_precision_accumulation=)     ng.py:240-256, :271-287
+ *   ducc0.wgridder.dirty2ms(uvw, freq, dirty, wgt, pixsize_x, pixsize_y, nu, nv,
+ *                           epsilon, do_wstacking, nthreads, verbosity)
+ *                                                               ng.py:99-112, :117-129
+ *
+ * The entry points below are what an FFI binding for those two calls binds instead
+ * (see INTEGRATION.md for the ctypes stub).  All functions return 0 on success and a
+ * non-zero status otherwise; b2g_last_error() returns a thread-local message.
+ *
+ * Conventions (identical to the ducc0 array-level convention, restated in
+ * oracle/dft_oracle.c):
+ *   uvw    [nrow][3]      float64, metres
+ *   freq   [nchan]        float64, Hz
+ *   ms     [nrow][nchan]  complex (interleaved re,im), float32 or float64 components
+ *   wgt    [nrow][nchan]  real, same component type as ms; may be NULL (all ones)
+ *   dirty  [npix_x][npix_y] real, float32 or float64
+ *   dirty[ix,iy] = (1/n) Re sum wgt*ms*exp(+2 pi i f/c (u x + v y - w (n-1)))
+ *   ms[row,chan] = wgt * sum dirty/n * exp(-2 pi i f/c (u x + v y - w (n-1)))
+ *   with x=(ix-npix_x/2) pixsize_x, y=(iy-npix_y/2) pixsize_y, n=sqrt(1-x^2-y^2);
+ *   do_wstacking=0 drops the w term and the 1/n factor.
+ *
+ * Pointers may be host or CUDA-device pointers, declared by the *_space arguments.
+ * There is no CPU fallback: every call needs a CUDA device and fails otherwise.
+ */
+#ifndef B200_WGRIDDER_H
+#define B200_WGRIDDER_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* component type codes */
+#define B2G_F32 0
+#define B2G_F64 1
+/* memory spaces */
+#define B2G_HOST 0
+#define B2G_DEVICE 1
+/* gridding kernel families */
+#define B2G_ALGO_AUTO (-1)
+#define B2G_ALGO_SIMPLE 0   /* one thread per visibility, global atomics (validation path) */
+#define B2G_ALGO_WARPRUN 1  /* sorted runs, register window, warp per run (fast path)      */
+
+typedef struct b2g_plan b2g_plan;
+
+/* Thread-local description of the last failure in this thread ("" if none). */
+const char *b2g_last_error(void);
+
+/* Library version string. */
+const char *b2g_version(void);
+
+/*
+ * Plan: everything that depends only on (uvw, freq, image geometry, epsilon):
+ * kernel/oversampling choice, w-plane layout, gridding-correction tables and the
+ * (uv-cell, w-plane)-sorted visibility index.  Replaces the per-call scan/bucket pass
+ * ducc0 repeats on every ms2dirty/dirty2ms call (the reference wrapper calls it once per
+ * polarisation and channel with identical uvw: ng.py:235-289).
+ *
+ *   precision : B2G_F32 / B2G_F64 arithmetic of the kernels
+ *   uvw_space : B2G_HOST / B2G_DEVICE for uvw and freq
+ *   nu, nv    : padded grid size, 0 = choose
+ *   algo      : B2G_ALGO_*
+ *   stream    : cudaStream_t (NULL = default stream); all work of the plan is ordered on it
+ */
+int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, const double *uvw,
+                    const double *freq, int uvw_space, int64_t npix_x, int64_t npix_y,
+                    double pixsize_x, double pixsize_y, int64_t nu, int64_t nv,
+                    double epsilon, int do_wstacking, int precision, int algo,
+                    int verbosity, void *stream);
+
+void b2g_plan_destroy(b2g_plan *plan);
+
+/* ms2dirty on a plan.  ms/wgt: component type vis_dtype in vis_space;
+ * dirty: dirty_dtype in dirty_space (written, not accumulated). */
+int b2g_plan_invert(b2g_plan *plan, const void *ms, const void *wgt, int vis_dtype,
+                    int vis_space, void *dirty, int dirty_dtype, int dirty_space);
+
+/* dirty2ms on a plan.  ms_out: component type vis_dtype in vis_space (overwritten). */
+int b2g_plan_predict(b2g_plan *plan, const void *dirty, int dirty_dtype, int dirty_space,
+                     const void *wgt, void *ms_out, int vis_dtype, int vis_space);
+
+/* Plan introspection: fills up to n entries of
+ *   iinfo = {W, nu, nv, nplanes, nslabs, planes_per_slab, algo_used, poly_degree,
+ *            nvis_sorted, key_bits, launches_last_call}
+ *   dinfo = {sigma, eps_kernel, dw, wmin, wmax, beta, e0, t_plan_ms, t_last_ms} */
+int b2g_plan_info(const b2g_plan *plan, int64_t *iinfo, int ni, double *dinfo, int nd);
+
+/* Per-stage device times (ms, CUDA events on the plan's stream) of the last invert or
+ * predict call: {h2d, prep, grid_or_degrid, fft, screen, correct, d2h, total}. */
+int b2g_plan_timings(const b2g_plan *plan, double *ms_out, int n);
+
+/* One-shot equivalents of the two ducc0 calls (plan + execute + destroy). */
+int b2g_ms2dirty(int64_t nrow, int64_t nchan, const double *uvw, const double *freq,
+                 const void *ms, const void *wgt, int vis_dtype, int space,
+                 int64_t npix_x, int64_t npix_y, double pixsize_x, double pixsize_y,
+                 int64_t nu, int64_t nv, double epsilon, int do_wstacking, int precision,
+                 void *dirty, int dirty_dtype, void *stream);
+
+int b2g_dirty2ms(int64_t nrow, int64_t nchan, const double *uvw, const double *freq,
+                 const void *dirty, int dirty_dtype, const void *wgt, int vis_dtype,
+                 int space, int64_t npix_x, int64_t npix_y, double pixsize_x,
+                 double pixsize_y, int64_t nu, int64_t nv, double epsilon,
+                 int do_wstacking, int precision, void *ms_out, void *stream);
+
+/* Deterministic fp64 sum of n weights (fixed reduction tree; exact for 0/1 weights).
+ * Mirrors numpy.sum(wgt) at ng.py:258, :289. */
+int b2g_sumwt(const void *wgt, int dtype, int space, int64_t n, double *out, void *stream);
+
+/* Host-side kernel mathematics, exported so that tests can check them without a GPU.
+ * b2g_kernel_select: choose (W, sigma) for epsilon; returns 0 and fills
+ *   out = {W, sigma, beta, e0, eps_kernel}.
+ * b2g_kernel_eval:  evaluate the piecewise-polynomial kernel of (W, beta, e0) at n
+ *   points t in [-1,1].
+ * b2g_kernel_corr:  Fourier transform psi-hat of that kernel at n points x (cycles/cell). */
+int b2g_kernel_select(double epsilon, int do_wstacking, int precision, int64_t npix_x,
+                      int64_t npix_y, double nvis, double *out5);
+int b2g_kernel_eval(int W, double beta, double e0, const double *t, int n, double *out);
+int b2g_kernel_corr(int W, double beta, double e0, const double *x, int n, double *out);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B200_WGRIDDER_H */

@@ -1,0 +1,139 @@
+"""Direct-DFT oracle (fp64) for ms2dirty / dirty2ms -- TEST INFRASTRUCTURE ONLY.
+
+Restates the measurement equation the reference evaluates through ducc0.wgridder
+(call sites /root/reference/src/ska_sdp_func_python/imaging/ng.py:99-112, :240-256);
+formula and provenance in oracle/dft_oracle.c.  Parity status: the sign/axis convention
+is pinned to the reference's own dft_cpu_looped
+(/root/reference/src/ska_sdp_func_python/imaging/dft.py:265-285) via tests/golden/;
+it is unpinned against ducc0 output itself (ducc0 is not installable here).
+"""
+import ctypes
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+_LIB = None
+C_M_S = 299792458.0
+
+
+def build(force=False):
+    """Compile liboracle.so with gcc (recipe: oracle/Makefile)."""
+    so = os.path.join(_HERE, "liboracle.so")
+    srcs = [os.path.join(_HERE, f) for f in ("dft_oracle.c", "wgridder_cpu.c")]
+    if (not force and os.path.exists(so)
+            and all(os.path.getmtime(so) >= os.path.getmtime(s) for s in srcs)):
+        return so
+    subprocess.check_call(["make", "-s", "-C", _HERE, "-B", "liboracle.so"])
+    return so
+
+
+def lib():
+    global _LIB
+    if _LIB is None:
+        _LIB = ctypes.CDLL(build())
+    return _LIB
+
+
+def _p(a, t=ctypes.c_double):
+    return None if a is None else a.ctypes.data_as(ctypes.POINTER(t))
+
+
+def ms2dirty_points(uvw, freq, ms, wgt, npix_x, npix_y, pixsize_x, pixsize_y,
+                    do_wstacking, px, py):
+    """dirty[px[k], py[k]] by direct summation (ducc0 array convention)."""
+    uvw = np.ascontiguousarray(uvw, dtype=np.float64)
+    freq = np.ascontiguousarray(freq, dtype=np.float64)
+    ms = np.ascontiguousarray(ms, dtype=np.complex128)
+    wgt = None if wgt is None else np.ascontiguousarray(wgt, dtype=np.float64)
+    px = np.ascontiguousarray(px, dtype=np.int64)
+    py = np.ascontiguousarray(py, dtype=np.int64)
+    out = np.zeros(px.shape[0], dtype=np.float64)
+    nrow, nchan = ms.shape
+    lib().oracle_ms2dirty_points(
+        ctypes.c_int64(nrow), ctypes.c_int64(nchan), _p(uvw), _p(freq), _p(ms), _p(wgt),
+        ctypes.c_int64(npix_x), ctypes.c_int64(npix_y), ctypes.c_double(pixsize_x),
+        ctypes.c_double(pixsize_y), ctypes.c_int(int(do_wstacking)),
+        ctypes.c_int64(px.shape[0]), _p(px, ctypes.c_int64), _p(py, ctypes.c_int64), _p(out))
+    return out
+
+
+def ms2dirty(uvw, freq, ms, wgt, npix_x, npix_y, pixsize_x, pixsize_y, do_wstacking):
+    """Full dirty image [npix_x, npix_y] by direct summation."""
+    ix, iy = np.meshgrid(np.arange(npix_x), np.arange(npix_y), indexing="ij")
+    out = ms2dirty_points(uvw, freq, ms, wgt, npix_x, npix_y, pixsize_x, pixsize_y,
+                          do_wstacking, ix.ravel(), iy.ravel())
+    return out.reshape(npix_x, npix_y)
+
+
+def dirty2ms_samples(uvw, freq, dirty, wgt, pixsize_x, pixsize_y, do_wstacking, rows, chans):
+    """ms[rows[k], chans[k]] by direct summation."""
+    uvw = np.ascontiguousarray(uvw, dtype=np.float64)
+    freq = np.ascontiguousarray(freq, dtype=np.float64)
+    dirty = np.ascontiguousarray(dirty, dtype=np.float64)
+    wgt = None if wgt is None else np.ascontiguousarray(wgt, dtype=np.float64)
+    rows = np.ascontiguousarray(rows, dtype=np.int64)
+    chans = np.ascontiguousarray(chans, dtype=np.int64)
+    out = np.zeros(rows.shape[0], dtype=np.complex128)
+    lib().oracle_dirty2ms_samples(
+        ctypes.c_int64(freq.shape[0]), _p(uvw), _p(freq), _p(dirty), _p(wgt),
+        ctypes.c_int64(dirty.shape[0]), ctypes.c_int64(dirty.shape[1]),
+        ctypes.c_double(pixsize_x), ctypes.c_double(pixsize_y),
+        ctypes.c_int(int(do_wstacking)), ctypes.c_int64(rows.shape[0]),
+        _p(rows, ctypes.c_int64), _p(chans, ctypes.c_int64), _p(out))
+    return out
+
+
+def dirty2ms(uvw, freq, dirty, wgt, pixsize_x, pixsize_y, do_wstacking):
+    """Full ms [nrow, nchan] by direct summation."""
+    nrow, nchan = uvw.shape[0], np.asarray(freq).shape[0]
+    r, c = np.meshgrid(np.arange(nrow), np.arange(nchan), indexing="ij")
+    out = dirty2ms_samples(uvw, freq, dirty, wgt, pixsize_x, pixsize_y, do_wstacking,
+                           r.ravel(), c.ravel())
+    return out.reshape(nrow, nchan)
+
+
+# ---- pure-numpy statement of the same sums (small cases; cross-checks the C) ----------
+
+def ms2dirty_numpy(uvw, freq, ms, wgt, npix_x, npix_y, pixsize_x, pixsize_y, do_wstacking):
+    x = (np.arange(npix_x) - npix_x // 2) * pixsize_x
+    y = (np.arange(npix_y) - npix_y // 2) * pixsize_y
+    xx, yy = np.meshgrid(x, y, indexing="ij")
+    r2 = xx * xx + yy * yy
+    if do_wstacking:
+        nm1 = -r2 / (np.sqrt(1.0 - r2) + 1.0)
+        n = nm1 + 1.0
+    else:
+        nm1 = np.zeros_like(r2)
+        n = np.ones_like(r2)
+    res = np.zeros((npix_x, npix_y))
+    v = ms if wgt is None else ms * wgt
+    for r in range(uvw.shape[0]):
+        for c in range(len(freq)):
+            if v[r, c] == 0:
+                continue
+            ph = freq[c] / C_M_S * (xx * uvw[r, 0] + yy * uvw[r, 1] - uvw[r, 2] * nm1)
+            res += (v[r, c] * np.exp(2j * np.pi * ph)).real
+    return res / n
+
+
+def dirty2ms_numpy(uvw, freq, dirty, wgt, pixsize_x, pixsize_y, do_wstacking):
+    npix_x, npix_y = dirty.shape
+    x = (np.arange(npix_x) - npix_x // 2) * pixsize_x
+    y = (np.arange(npix_y) - npix_y // 2) * pixsize_y
+    xx, yy = np.meshgrid(x, y, indexing="ij")
+    r2 = xx * xx + yy * yy
+    if do_wstacking:
+        nm1 = -r2 / (np.sqrt(1.0 - r2) + 1.0)
+        n = nm1 + 1.0
+    else:
+        nm1 = np.zeros_like(r2)
+        n = np.ones_like(r2)
+    out = np.zeros((uvw.shape[0], len(freq)), dtype=np.complex128)
+    dn = dirty / n
+    for r in range(uvw.shape[0]):
+        for c in range(len(freq)):
+            ph = freq[c] / C_M_S * (xx * uvw[r, 0] + yy * uvw[r, 1] - uvw[r, 2] * nm1)
+            out[r, c] = np.sum(dn * np.exp(-2j * np.pi * ph))
+    return out if wgt is None else out * wgt

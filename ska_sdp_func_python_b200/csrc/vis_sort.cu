@@ -1,0 +1,275 @@
+// vis_sort.cu -- the uv-cell / w-plane sort ("bucket") pass.
+//
+// Every visibility gets the key  ((slab*nu + iu0)*nv + iv0)*gs + (p0 - slab*gs)  where
+// (iu0, iv0, p0) is the lower corner of its kernel footprint, and the (key, index) pairs
+// are radix-sorted.  This is the B200 counterpart of the scan/bucket pass at the start
+// of ducc0.wgridder.ms2dirty / dirty2ms (call sites
+// /root/reference/src/ska_sdp_func_python/imaging/ng.py:240-256, :99-112): ducc0 buckets
+// (row, channel-range) runs per 16x16 tile and w-plane on the host; here the sort is
+// per visibility and exact, because the gridding kernels accumulate runs of identical
+// origins in registers.
+//
+// LSD radix sort, 8 bits per pass, three kernels per pass:
+//   1. per-tile digit histogram (shared-memory counters, one tile = 4096 pairs per block)
+//   2. exclusive scan of the [digit][tile] table (single cooperative-free two-level scan)
+//   3. stable scatter: each warp ranks its 128-pair strip with match.any, strips are
+//      combined through a shared-memory digit table.
+#include "kernels.h"
+
+namespace b2g {
+
+namespace {
+
+__global__ void __launch_bounds__(256)
+keygen_kernel(VisGeo g, int W, long long nvis, uint64_t *__restrict__ keys,
+              uint32_t *__restrict__ idx, unsigned long long *__restrict__ slab_counts,
+              int nslabs)
+{
+    extern __shared__ unsigned int sh_cnt[];  // [nslabs] when nslabs <= 1024
+    const bool use_sh = nslabs <= 1024;
+    if (use_sh) {
+        for (int i = threadIdx.x; i < nslabs; i += blockDim.x) sh_cnt[i] = 0;
+        __syncthreads();
+    }
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < nvis) {
+        const uint32_t row = (uint32_t)(i / g.nchan), chan = (uint32_t)(i - (long long)row * g.nchan);
+        const Located L = locate(g, W, row, chan);
+        const int slab = L.p0 / g.gs;
+        const int prel = L.p0 - slab * g.gs;
+        uint64_t key = (uint64_t)slab * (uint64_t)g.nu + (uint64_t)L.iu0;
+        key = key * (uint64_t)g.nv + (uint64_t)L.iv0;
+        key = key * (uint64_t)g.gs + (uint64_t)prel;
+        keys[i] = key;
+        idx[i] = (uint32_t)i;
+        if (use_sh) atomicAdd(&sh_cnt[slab], 1u);
+        else atomicAdd(&slab_counts[slab], 1ull);
+    }
+    if (use_sh) {
+        __syncthreads();
+        for (int s = threadIdx.x; s < nslabs; s += blockDim.x)
+            if (sh_cnt[s]) atomicAdd(&slab_counts[s], (unsigned long long)sh_cnt[s]);
+    }
+}
+
+constexpr int kRadixBits = 8;
+constexpr int kRadix = 1 << kRadixBits;
+constexpr int kSortThreads = 256;
+constexpr int kItems = 16;                          // pairs per thread
+constexpr int kTile = kSortThreads * kItems;        // 4096 pairs per block
+
+__global__ void __launch_bounds__(kSortThreads)
+radix_hist_kernel(const uint64_t *__restrict__ keys, long long n, int shift, int ntiles,
+                  uint32_t *__restrict__ table /* [kRadix][ntiles] */)
+{
+    __shared__ unsigned int cnt[kRadix];
+    cnt[threadIdx.x] = 0;  // kSortThreads == kRadix
+    __syncthreads();
+    const long long base = (long long)blockIdx.x * kTile;
+#pragma unroll
+    for (int it = 0; it < kItems; ++it) {
+        const long long i = base + (long long)it * kSortThreads + threadIdx.x;
+        const bool live = i < n;
+        const unsigned livemask = __ballot_sync(0xffffffffu, live);
+        if (live) {
+            const unsigned d = (unsigned)(keys[i] >> shift) & (kRadix - 1);
+            // warp-aggregated increment: consecutive visibilities mostly share the digit
+            const unsigned peers = __match_any_sync(livemask, d);
+            if ((int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&cnt[d], __popc(peers));
+        }
+    }
+    __syncthreads();
+    table[(size_t)threadIdx.x * ntiles + blockIdx.x] = cnt[threadIdx.x];
+}
+
+// Exclusive scan over the table in (digit-major, tile-minor) order.  Two levels:
+// scan_partial sums blocks of 1024 entries, scan_finish scans the block sums (single
+// block) and scan_apply writes the exclusive prefix back.
+__global__ void __launch_bounds__(256)
+scan_partial_kernel(const uint32_t *__restrict__ in, long long n, uint64_t *__restrict__ bsum)
+{
+    __shared__ unsigned long long sh[256];
+    const long long base = (long long)blockIdx.x * 1024;
+    unsigned long long s = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const long long i = base + threadIdx.x * 4 + k;
+        if (i < n) s += in[i];
+    }
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int w = 128; w > 0; w >>= 1) {
+        if ((int)threadIdx.x < w) sh[threadIdx.x] += sh[threadIdx.x + w];
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) bsum[blockIdx.x] = sh[0];
+}
+__global__ void __launch_bounds__(1024)
+scan_finish_kernel(uint64_t *__restrict__ bsum, long long nb)
+{
+    // single block: sequential over chunks of 1024 with a running carry
+    __shared__ unsigned long long sh[1024];
+    __shared__ unsigned long long carry;
+    if (threadIdx.x == 0) carry = 0;
+    __syncthreads();
+    for (long long base = 0; base < nb; base += 1024) {
+        const long long i = base + threadIdx.x;
+        const unsigned long long v = (i < nb) ? bsum[i] : 0ull;
+        sh[threadIdx.x] = v;
+        __syncthreads();
+        for (int off = 1; off < 1024; off <<= 1) {
+            unsigned long long t = 0;
+            if ((int)threadIdx.x >= off) t = sh[threadIdx.x - off];
+            __syncthreads();
+            sh[threadIdx.x] += t;
+            __syncthreads();
+        }
+        const unsigned long long incl = sh[threadIdx.x];
+        if (i < nb) bsum[i] = carry + incl - v;  // exclusive
+        __syncthreads();
+        if (threadIdx.x == 1023) carry += incl;
+        __syncthreads();
+    }
+}
+__global__ void __launch_bounds__(256)
+scan_apply_kernel(const uint32_t *__restrict__ in, long long n, const uint64_t *__restrict__ bsum,
+                  uint64_t *__restrict__ out)
+{
+    __shared__ unsigned long long sh[256];
+    const long long base = (long long)blockIdx.x * 1024;
+    unsigned int v[4];
+    unsigned long long s = 0;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const long long i = base + threadIdx.x * 4 + k;
+        v[k] = (i < n) ? in[i] : 0u;
+        s += v[k];
+    }
+    sh[threadIdx.x] = s;
+    __syncthreads();
+    for (int off = 1; off < 256; off <<= 1) {
+        unsigned long long t = 0;
+        if ((int)threadIdx.x >= off) t = sh[threadIdx.x - off];
+        __syncthreads();
+        sh[threadIdx.x] += t;
+        __syncthreads();
+    }
+    unsigned long long run = bsum[blockIdx.x] + sh[threadIdx.x] - s;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const long long i = base + threadIdx.x * 4 + k;
+        if (i < n) out[i] = run;
+        run += v[k];
+    }
+}
+
+// Stable scatter.  Block = one tile of kTile pairs, processed in kItems rounds of 256
+// pairs in input order.  Within a round: warp-level ranks by match.any, cross-warp
+// offsets through warp_cnt[warp][digit]; running per-digit offsets carry across rounds.
+__global__ void __launch_bounds__(kSortThreads)
+radix_scatter_kernel(const uint64_t *__restrict__ keys_in, const uint32_t *__restrict__ idx_in,
+                     uint64_t *__restrict__ keys_out, uint32_t *__restrict__ idx_out, long long n,
+                     int shift, int ntiles, const uint64_t *__restrict__ offs /* [kRadix][ntiles] */)
+{
+    constexpr int NW = kSortThreads / 32;
+    __shared__ unsigned long long dig_base[kRadix];   // global position of next pair of digit d
+    __shared__ unsigned int warp_cnt[NW][kRadix];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    dig_base[threadIdx.x] = offs[(size_t)threadIdx.x * ntiles + blockIdx.x];
+    const long long base = (long long)blockIdx.x * kTile;
+    for (int it = 0; it < kItems; ++it) {
+        for (int w = 0; w < NW; ++w) warp_cnt[w][threadIdx.x] = 0;
+        __syncthreads();
+        const long long i = base + (long long)it * kSortThreads + threadIdx.x;
+        const bool live = i < n;
+        uint64_t key = 0;
+        uint32_t id = 0;
+        unsigned d = 0, rank_in_warp = 0;
+        if (live) {
+            key = keys_in[i];
+            id = idx_in[i];
+            d = (unsigned)(key >> shift) & (kRadix - 1);
+        }
+        const unsigned livemask = __ballot_sync(0xffffffffu, live);
+        if (live) {
+            const unsigned peers = __match_any_sync(livemask, d);
+            rank_in_warp = __popc(peers & ((1u << lane) - 1u));
+            if (rank_in_warp == 0) warp_cnt[warp][d] = __popc(peers);
+        }
+        __syncthreads();
+        unsigned long long pos = 0;
+        if (live) {
+            unsigned before = 0;
+            for (int w = 0; w < warp; ++w) before += warp_cnt[w][d];
+            pos = dig_base[d] + before + rank_in_warp;
+        }
+        __syncthreads();
+        {   // advance the running offsets (thread t handles digit t)
+            unsigned tot = 0;
+#pragma unroll
+            for (int w = 0; w < NW; ++w) tot += warp_cnt[w][threadIdx.x];
+            dig_base[threadIdx.x] += tot;
+        }
+        if (live) {
+            keys_out[pos] = key;
+            idx_out[pos] = id;
+        }
+        __syncthreads();
+    }
+}
+
+}  // namespace
+
+int launch_keygen(const VisGeo &geo, int W, long long nvis, uint64_t *keys, uint32_t *idx,
+                  unsigned long long *slab_counts, int nslabs, cudaStream_t stream)
+{
+    if (nvis <= 0) return 0;
+    cudaMemsetAsync(slab_counts, 0, sizeof(unsigned long long) * nslabs, stream);
+    const unsigned blocks = (unsigned)((nvis + 255) / 256);
+    const size_t sh = nslabs <= 1024 ? sizeof(unsigned int) * nslabs : 0;
+    keygen_kernel<<<blocks, 256, sh, stream>>>(geo, W, nvis, keys, idx, slab_counts, nslabs);
+    return (int)cudaGetLastError();
+}
+
+// Scratch is allocated per call with the stream-ordered allocator.
+int sort_pairs(uint64_t *keys_in, uint64_t *keys_out, uint32_t *idx_in, uint32_t *idx_out,
+               long long n, int key_bits, cudaStream_t stream)
+{
+    if (n <= 0) return 0;
+    const int ntiles = (int)((n + kTile - 1) / kTile);
+    const long long tab_n = (long long)kRadix * ntiles;
+    const long long nb = (tab_n + 1023) / 1024;
+    uint32_t *table = nullptr;
+    uint64_t *offs = nullptr, *bsum = nullptr;
+    cudaError_t e;
+    if ((e = cudaMallocAsync(&table, sizeof(uint32_t) * tab_n, stream)) != cudaSuccess) return (int)e;
+    if ((e = cudaMallocAsync(&offs, sizeof(uint64_t) * tab_n, stream)) != cudaSuccess) return (int)e;
+    if ((e = cudaMallocAsync(&bsum, sizeof(uint64_t) * nb, stream)) != cudaSuccess) return (int)e;
+    // ping-pong: pass 0 reads *_in and writes *_out, pass 1 the other way round, ...
+    uint64_t *ka = keys_in, *kb = keys_out;
+    uint32_t *ia = idx_in, *ib = idx_out;
+    int npass = (key_bits + kRadixBits - 1) / kRadixBits;
+    if (npass < 1) npass = 1;
+    for (int p = 0; p < npass; ++p) {
+        const int shift = p * kRadixBits;
+        radix_hist_kernel<<<ntiles, kSortThreads, 0, stream>>>(ka, n, shift, ntiles, table);
+        scan_partial_kernel<<<(unsigned)nb, 256, 0, stream>>>(table, tab_n, bsum);
+        scan_finish_kernel<<<1, 1024, 0, stream>>>(bsum, nb);
+        scan_apply_kernel<<<(unsigned)nb, 256, 0, stream>>>(table, tab_n, bsum, offs);
+        radix_scatter_kernel<<<ntiles, kSortThreads, 0, stream>>>(ka, ia, kb, ib, n, shift, ntiles,
+                                                                 offs);
+        uint64_t *tk = ka; ka = kb; kb = tk;
+        uint32_t *ti = ia; ia = ib; ib = ti;
+    }
+    // result is in (ka, ia); make sure it ends in the *_out buffers
+    if (ka != keys_out) {
+        cudaMemcpyAsync(keys_out, ka, sizeof(uint64_t) * n, cudaMemcpyDeviceToDevice, stream);
+        cudaMemcpyAsync(idx_out, ia, sizeof(uint32_t) * n, cudaMemcpyDeviceToDevice, stream);
+    }
+    cudaFreeAsync(table, stream);
+    cudaFreeAsync(offs, stream);
+    cudaFreeAsync(bsum, stream);
+    return (int)cudaGetLastError();
+}
+
+}  // namespace b2g
