@@ -1,0 +1,80 @@
+"""ctypes binding of the C ABI in include/b200_wgridder.h (libb200wgridder.so).
+
+The shared library is built in-tree by ``__graft_entry__.build()`` (nvcc, sm_100a).  There
+is deliberately no fallback: if the library is missing, or no CUDA device is present when a
+compute entry point is called, an exception is raised.
+"""
+import ctypes
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libb200wgridder.so")
+
+F32, F64 = 0, 1
+HOST, DEVICE = 0, 1
+ALGO_AUTO, ALGO_SIMPLE, ALGO_WARPRUN = -1, 0, 1
+
+EXPORTS = (
+    "b2g_last_error", "b2g_version", "b2g_plan_create", "b2g_plan_destroy",
+    "b2g_plan_invert", "b2g_plan_predict", "b2g_plan_info", "b2g_plan_timings",
+    "b2g_ms2dirty", "b2g_dirty2ms", "b2g_sumwt", "b2g_kernel_select", "b2g_kernel_eval",
+    "b2g_kernel_corr",
+)
+
+_lib = None
+
+
+class WgridderError(RuntimeError):
+    """Raised when a C-ABI call returns a non-zero status."""
+
+
+def lib():
+    """Load (once) and return the ctypes handle of libb200wgridder.so."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; "
+            "g.build()'` (needs nvcc); there is no CPU fallback")
+    L = ctypes.CDLL(LIB_PATH)
+    i64, dbl, vp, ci = ctypes.c_int64, ctypes.c_double, ctypes.c_void_p, ctypes.c_int
+    pd = ctypes.POINTER(ctypes.c_double)
+    L.b2g_last_error.restype = ctypes.c_char_p
+    L.b2g_last_error.argtypes = []
+    L.b2g_version.restype = ctypes.c_char_p
+    L.b2g_version.argtypes = []
+    L.b2g_plan_create.restype = ci
+    L.b2g_plan_create.argtypes = [ctypes.POINTER(vp), i64, i64, vp, vp, ci, i64, i64, dbl, dbl,
+                                  i64, i64, dbl, ci, ci, ci, ci, vp]
+    L.b2g_plan_destroy.restype = None
+    L.b2g_plan_destroy.argtypes = [vp]
+    L.b2g_plan_invert.restype = ci
+    L.b2g_plan_invert.argtypes = [vp, vp, vp, ci, ci, vp, ci, ci]
+    L.b2g_plan_predict.restype = ci
+    L.b2g_plan_predict.argtypes = [vp, vp, ci, ci, vp, vp, ci, ci]
+    L.b2g_plan_info.restype = ci
+    L.b2g_plan_info.argtypes = [vp, ctypes.POINTER(i64), ci, pd, ci]
+    L.b2g_plan_timings.restype = ci
+    L.b2g_plan_timings.argtypes = [vp, pd, ci]
+    L.b2g_ms2dirty.restype = ci
+    L.b2g_ms2dirty.argtypes = [i64, i64, vp, vp, vp, vp, ci, ci, i64, i64, dbl, dbl, i64, i64,
+                               dbl, ci, ci, vp, ci, vp]
+    L.b2g_dirty2ms.restype = ci
+    L.b2g_dirty2ms.argtypes = [i64, i64, vp, vp, vp, ci, vp, ci, ci, i64, i64, dbl, dbl, i64,
+                               i64, dbl, ci, ci, vp, vp]
+    L.b2g_sumwt.restype = ci
+    L.b2g_sumwt.argtypes = [vp, ci, ci, i64, pd, vp]
+    L.b2g_kernel_select.restype = ci
+    L.b2g_kernel_select.argtypes = [dbl, ci, ci, i64, i64, dbl, pd]
+    L.b2g_kernel_eval.restype = ci
+    L.b2g_kernel_eval.argtypes = [ci, dbl, dbl, pd, ci, pd]
+    L.b2g_kernel_corr.restype = ci
+    L.b2g_kernel_corr.argtypes = [ci, dbl, dbl, pd, ci, pd]
+    _lib = L
+    return L
+
+
+def check(rc):
+    if rc != 0:
+        raise WgridderError(lib().b2g_last_error().decode("utf-8", "replace"))

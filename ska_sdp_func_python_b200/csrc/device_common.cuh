@@ -6,8 +6,9 @@
 //   fscale   [nchan]     f64   f/c
 //   ms       [nrow][nchan] complex<T> ; wgt [nrow][nchan] T
 //   sidx     [nvis]      u32   visibility index (row*nchan+chan) sorted by
-//                              (slab, iu0, iv0, p0) = the cell/plane of the footprint origin
-//   slab     [planes][nu][nv] complex<T>   a group of consecutive w-planes of the uv-grid
+//                              (p0, iu0, iv0) = the w-plane / cell of the footprint origin
+//   ring     [nslots][nu][nv] complex<T>   ring buffer of w-planes of the uv-grid;
+//                              plane P lives in slot P mod nslots, nslots = gs + W - 1
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
@@ -15,10 +16,6 @@
 namespace b2g {
 
 template <typename T> struct cplx { T re, im; };
-
-template <typename T> struct VecOf;
-template <> struct VecOf<float> { using type = float2; };
-template <> struct VecOf<double> { using type = double2; };
 
 // Piecewise-polynomial kernel table, passed BY VALUE as a kernel argument so that the
 // Horner FMAs take their coefficient operand straight from the constant bank.
@@ -33,18 +30,18 @@ struct VisGeo {
     uint32_t nchan;
     int nu, nv;           // padded grid
     int nplanes;          // total w-planes (1 without w-stacking)
-    int gs;               // origin planes per slab
+    int nslots;           // ring slots
     int wstack;
     double su, sv;        // pixsize_x, pixsize_y  (cycles per pixel per wavelength)
-    double sw, w0s;       // wg = |w_lambda| * sw - w0s
+    double sw, w0s;       // plane coordinate of a sample: |w_lambda| * sw - w0s
     long long plane_stride;  // nu*nv
 };
 
 // Footprint origin + sub-cell offsets of one visibility.
 struct Located {
     int iu0, iv0;        // wrapped to [0,nu), [0,nv)
-    int p0;              // global plane of the first w-plane touched
-    double du, dv, dw;   // in [0,1]: distance (cells) from the footprint's lower edge
+    int p0;              // first w-plane touched
+    double du, dv, dw;   // in [0,1): distance (cells) from the footprint's lower edge
     bool flip;           // (u,v,w) -> -(u,v,w), vis -> conj(vis)
 };
 
@@ -57,8 +54,8 @@ __device__ __forceinline__ void locate_axis(double cyc, int n, double halfW, int
     double c = ceil(s);
     delta = c - s;
     int i0 = (int)c;
-    i0 %= n;
     if (i0 < 0) i0 += n;
+    if (i0 >= n) i0 -= n;
     i0w = i0;
 }
 

@@ -168,32 +168,41 @@ inline int64_t good_size_even(int64_t n)
 
 inline int cols_per_lane(int W) { return (W * W + 31) / 32; }
 
-// Relative cost (arbitrary units ~ warp-instructions) used to pick (W, sigma).
-// nvis: number of samples; nplanes_per_unit_sigma: (wmax-wmin)*2*|nm1min| (so that
-// nplanes = that*sigma + W); fp64 doubles everything so it cancels.
+// Estimated run time (seconds, B200) used to pick (W, sigma): the visibility-side kernels
+// are issue-bound (packed FMAs on register-resident cells plus ~W*pw cell flushes per
+// visibility where the uv-plane is sparsely filled), the image side (FFT passes, screens)
+// streams the padded grid through HBM about six times per w-plane.
+//   planes_per_sigma = (wmax-wmin)*2*|nm1min|  (so that nplanes = that*sigma + W)
+//   csize            = bytes per complex grid cell (8 fp32 / 16 fp64)
 inline double cost_model(int W, double sigma, bool wstack, double nvis, int64_t npix_x,
-                         int64_t npix_y, double planes_per_sigma)
+                         int64_t npix_y, double planes_per_sigma, int csize)
 {
-    int64_t nu = good_size_even((int64_t)std::ceil(sigma * npix_x));
-    int64_t nv = good_size_even((int64_t)std::ceil(sigma * npix_y));
-    int pw = wstack ? W : 1;
-    double cvis = nvis * (24.0 + cols_per_lane(W) * (5.0 + 2.0 * pw));
-    double nplanes = wstack ? std::ceil(planes_per_sigma * sigma) + W : 1.0;
-    double cimg = nplanes * (double(nu) * double(nv) * 10.0 + double(npix_x) * npix_y * 3.0);
-    return cvis + cimg;
+    const int64_t nu = good_size_even((int64_t)std::ceil(sigma * npix_x));
+    const int64_t nv = good_size_even((int64_t)std::ceil(sigma * npix_y));
+    const int pw = wstack ? W : 1;
+    const double nplanes = wstack ? std::ceil(planes_per_sigma * sigma) + W : 1.0;
+    const double fp = csize == 8 ? 1.0 : 2.5;
+    const double instr = 30.0 + cols_per_lane(W) * (8.0 + 2.5 * pw);
+    double t_vis = nvis * instr * fp / 4.0e11;
+    const double density = nvis / (double(nu) * double(nv) * std::max(1.0, nplanes - W + 1));
+    const double flushes = std::min(1.0, 1.0 / std::max(density, 1e-30)) * W * pw;
+    t_vis += nvis * flushes * 1.3 * fp / (148.0 * 1.5e9);
+    const double t_img = nplanes * (double(nu) * double(nv) * 6.0 * csize +
+                                    double(npix_x) * npix_y * 3.0 * (csize / 2)) / 5.0e12;
+    return t_vis + t_img;
 }
 
 // Pick the cheapest table row whose error meets eps_dim (per-dimension target).
 // Returns index into kKernelDB or -1.
 inline int select_kernel(double eps_dim, bool wstack, int maxW, double nvis, int64_t npix_x,
-                         int64_t npix_y, double planes_per_sigma)
+                         int64_t npix_y, double planes_per_sigma, int csize)
 {
     int best = -1;
     double bestc = 0;
     for (int i = 0; i < kKernelDBSize; ++i) {
         const KernelRow &r = kKernelDB[i];
         if (r.W > maxW || r.eps > eps_dim) continue;
-        double c = cost_model(r.W, r.sigma, wstack, nvis, npix_x, npix_y, planes_per_sigma);
+        double c = cost_model(r.W, r.sigma, wstack, nvis, npix_x, npix_y, planes_per_sigma, csize);
         if (best < 0 || c < bestc) {
             best = i;
             bestc = c;

@@ -42,7 +42,7 @@ __device__ __forceinline__ double corr_factor(const ImgGeo &g, int a, int b)
         const double nm1 = nm1_of(r2);
         // nm1 in [nm1min, 0] -> z in [-1, 1]
         const double z = (g.nm1min < 0.0) ? fma(2.0 / g.nm1min, nm1, -1.0) : 0.0;
-        f *= cheb_eval(g.cheb, g.ncheb, z);
+        f *= cheb_eval(g.cheb, g.ncheb, z) / (nm1 + 1.0);  // 1/(psi-hat_w * n)
     }
     return f;
 }
@@ -60,7 +60,7 @@ __device__ __forceinline__ void phase_sincos(double ph, double &s, double &c)
 
 template <typename T>
 __global__ void __launch_bounds__(256)
-screen_accumulate_kernel(ImgGeo g, const cplx<T> *__restrict__ slab, int pfirst, int np,
+screen_accumulate_kernel(ImgGeo g, const cplx<T> *__restrict__ ring, int pfirst, int np,
                          T *__restrict__ acc, bool first)
 {
     const int b = blockIdx.x * blockDim.x + threadIdx.x;
@@ -74,19 +74,21 @@ screen_accumulate_kernel(ImgGeo g, const cplx<T> *__restrict__ slab, int pfirst,
     const long long stride = (long long)g.nu * g.nv;
     T sum = T(0);
     if (!g.wstack) {
-        sum = slab[cell].re;
+        sum = ring[cell].re;
     } else {
         const double x = (double)(a - g.npix_x / 2) * g.pixsize_x;
         const double y = (double)(b - g.npix_y / 2) * g.pixsize_y;
         const double r2 = x * x + y * y;
         if (r2 < 1.0) {
             const double nm1 = nm1_of(r2);
+            int slot = pfirst % g.nslots;
             for (int p = 0; p < np; ++p) {
                 const double w = fma((double)(pfirst + p), g.dw, g.w0);
                 T s, c;
                 phase_sincos(-w * nm1, s, c);
-                const cplx<T> v = slab[(long long)p * stride + cell];
+                const cplx<T> v = ring[(long long)slot * stride + cell];
                 sum += v.re * c - v.im * s;
+                slot = (slot + 1 == g.nslots) ? 0 : slot + 1;
             }
         }
     }
@@ -119,7 +121,7 @@ precorrect_kernel(ImgGeo g, const Tin *__restrict__ dirty, T *__restrict__ pre)
 // One thread per grid cell (iu, iv); writes that cell of every plane of the slab.
 template <typename T>
 __global__ void __launch_bounds__(256)
-screen_apply_kernel(ImgGeo g, const T *__restrict__ pre, cplx<T> *__restrict__ slab, int pfirst,
+screen_apply_kernel(ImgGeo g, const T *__restrict__ pre, cplx<T> *__restrict__ ring, int pfirst,
                     int np)
 {
     const int iv = blockIdx.x * blockDim.x + threadIdx.x;
@@ -148,19 +150,24 @@ screen_apply_kernel(ImgGeo g, const T *__restrict__ pre, cplx<T> *__restrict__ s
         }
         live = (val != T(0));
     }
+    int slot = pfirst % g.nslots;
     if (!live) {
-        for (int p = 0; p < np; ++p) slab[(long long)p * stride + cell] = cplx<T>{T(0), T(0)};
+        for (int p = 0; p < np; ++p) {
+            ring[(long long)slot * stride + cell] = cplx<T>{T(0), T(0)};
+            slot = (slot + 1 == g.nslots) ? 0 : slot + 1;
+        }
         return;
     }
     if (!g.wstack) {
-        slab[cell] = cplx<T>{val, T(0)};
+        ring[cell] = cplx<T>{val, T(0)};
         return;
     }
     for (int p = 0; p < np; ++p) {
         const double w = fma((double)(pfirst + p), g.dw, g.w0);
         T s, c;
         phase_sincos(w * nm1, s, c);
-        slab[(long long)p * stride + cell] = cplx<T>{val * c, val * s};
+        ring[(long long)slot * stride + cell] = cplx<T>{val * c, val * s};
+        slot = (slot + 1 == g.nslots) ? 0 : slot + 1;
     }
 }
 
@@ -247,10 +254,10 @@ inline dim3 img_grid(int nfast, int nslow) { return dim3((unsigned)((nfast + 255
 }  // namespace
 
 template <typename T>
-int launch_screen_accumulate(const ImgGeo &g, const cplx<T> *slab, int pfirst, int np, T *acc,
+int launch_screen_accumulate(const ImgGeo &g, const cplx<T> *ring, int pfirst, int np, T *acc,
                              bool first, cudaStream_t s)
 {
-    screen_accumulate_kernel<T><<<img_grid(g.npix_y, g.npix_x), 256, 0, s>>>(g, slab, pfirst, np,
+    screen_accumulate_kernel<T><<<img_grid(g.npix_y, g.npix_x), 256, 0, s>>>(g, ring, pfirst, np,
                                                                             acc, first);
     return (int)cudaGetLastError();
 }
@@ -267,10 +274,10 @@ int launch_precorrect(const ImgGeo &g, const Tin *dirty, T *pre, cudaStream_t s)
     return (int)cudaGetLastError();
 }
 template <typename T>
-int launch_screen_apply(const ImgGeo &g, const T *pre, cplx<T> *slab, int pfirst, int np,
+int launch_screen_apply(const ImgGeo &g, const T *pre, cplx<T> *ring, int pfirst, int np,
                         cudaStream_t s)
 {
-    screen_apply_kernel<T><<<img_grid(g.nv, g.nu), 256, 0, s>>>(g, pre, slab, pfirst, np);
+    screen_apply_kernel<T><<<img_grid(g.nv, g.nu), 256, 0, s>>>(g, pre, ring, pfirst, np);
     return (int)cudaGetLastError();
 }
 template <typename Tin, typename Tout>

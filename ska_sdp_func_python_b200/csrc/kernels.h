@@ -7,7 +7,8 @@
 
 namespace b2g {
 
-// One gridding / degridding launch over the sorted visibilities [begin, end) of a slab.
+// One gridding / degridding launch over the sorted visibilities [begin, end) of a slab
+// (= the samples whose first w-plane p0 lies in [plane0, plane0 + gs)).
 template <typename T> struct VisLaunch {
     VisGeo geo;
     int W;
@@ -15,11 +16,12 @@ template <typename T> struct VisLaunch {
     const double *coef;     // host, [W][W+4], highest power first
     const uint32_t *sidx;   // device, sorted visibility indices
     long long begin, end;   // range in sidx
-    int slab;               // slab number (origin planes [slab*gs, (slab+1)*gs))
+    int plane0;             // first origin plane of the slab
+    int slot0;              // ring slot of plane0 (= plane0 mod nslots)
     const cplx<T> *ms;      // gridding input  [nrow][nchan]
     const T *wgt;           // optional weights [nrow][nchan]
     cplx<T> *ms_out;        // degridding output [nrow][nchan]
-    cplx<T> *slabbuf;       // [gs+W-1][nu][nv]
+    cplx<T> *ring;          // [nslots][nu][nv]
     cudaStream_t stream;
 };
 
@@ -30,11 +32,12 @@ template <typename T> bool warprun_supported(int W, bool wstack);
 template <typename T> int launch_grid_warprun(const VisLaunch<T> &L);
 template <typename T> int launch_degrid_warprun(const VisLaunch<T> &L);
 
-// Sort keys: key = ((slab*nu + iu0)*nv + iv0)*gs + (p0 - slab*gs); also counts per slab.
+// Sort keys: key = (p0*nu + iu0)*nv + iv0; also a histogram of p0 (plane_counts[nplanes]).
 int launch_keygen(const VisGeo &geo, int W, long long nvis, uint64_t *keys, uint32_t *idx,
-                  unsigned long long *slab_counts, int nslabs, cudaStream_t stream);
+                  unsigned long long *plane_counts, cudaStream_t stream);
 
 // Radix sort of (key, idx) pairs on the lowest key_bits bits; result in keys_out/idx_out.
+// Returns 0 or a cudaError_t.
 int sort_pairs(uint64_t *keys_in, uint64_t *keys_out, uint32_t *idx_in, uint32_t *idx_out,
                long long n, int key_bits, cudaStream_t stream);
 
@@ -46,17 +49,18 @@ struct ImgGeo {
     int npix_x, npix_y, nu, nv;
     double pixsize_x, pixsize_y;
     int wstack;
+    int nslots;
     double w0, dw;          // plane p sits at w = w0 + p*dw (wavelengths)
     const double *cu;       // [npix_x] 1/psi-hat_u
     const double *cv;       // [npix_y] 1/psi-hat_v
-    const double *cheb;     // Chebyshev coefficients of 1/(psi-hat_w(nm1*dw)*(nm1+1)) in nm1
+    const double *cheb;     // Chebyshev coefficients of 1/psi-hat_w(nm1*dw) in nm1 on [nm1min,0]
     int ncheb;
     double nm1min;          // most negative n-1 over the image (<= 0)
 };
 
-// acc[a][b] += sum_{p<np} Re( slab[p][a'][b'] * exp(-2 pi i (w0+(pfirst+p)dw) nm1) )
+// acc[a][b] (+)= sum_{p<np} Re( ring[slot(pfirst+p)][a'][b'] * exp(-2 pi i (w0+(pfirst+p)dw) nm1) )
 template <typename T>
-int launch_screen_accumulate(const ImgGeo &g, const cplx<T> *slab, int pfirst, int np, T *acc,
+int launch_screen_accumulate(const ImgGeo &g, const cplx<T> *ring, int pfirst, int np, T *acc,
                              bool first, cudaStream_t s);
 // out[a][b] = acc[a][b] * cu[a]*cv[b]*gw(nm1)          (Tout = float or double)
 template <typename T, typename Tout>
@@ -64,15 +68,16 @@ int launch_correct(const ImgGeo &g, const T *acc, Tout *out, cudaStream_t s);
 // pre[a][b] = dirty[a][b] * cu[a]*cv[b]*gw(nm1)
 template <typename T, typename Tin>
 int launch_precorrect(const ImgGeo &g, const Tin *dirty, T *pre, cudaStream_t s);
-// slab[p][iu][iv] = pre[a][b]*exp(+2 pi i (w0+(pfirst+p)dw) nm1) on the image footprint, 0 elsewhere
+// ring[slot(pfirst+p)][iu][iv] = pre[a][b]*exp(+2 pi i (w0+(pfirst+p)dw) nm1) on the image
+// footprint, 0 elsewhere
 template <typename T>
-int launch_screen_apply(const ImgGeo &g, const T *pre, cplx<T> *slab, int pfirst, int np,
+int launch_screen_apply(const ImgGeo &g, const T *pre, cplx<T> *ring, int pfirst, int np,
                         cudaStream_t s);
 
 // dtype conversion helpers (n real elements)
 template <typename Tin, typename Tout>
 int launch_convert(const Tin *in, Tout *out, long long n, cudaStream_t s);
-// deterministic fp64 sum
+// deterministic fp64 sum; scratch holds nscratch doubles
 template <typename Tin>
 int launch_sum(const Tin *in, long long n, double *out_dev, double *scratch, int nscratch,
                cudaStream_t s);

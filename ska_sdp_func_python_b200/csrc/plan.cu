@@ -1,0 +1,1020 @@
+// plan.cu -- host side of the B200 gridder: plan construction (kernel choice, w-plane
+// layout, correction tables, visibility sort), the invert / predict drivers and the C ABI
+// declared in include/b200_wgridder.h.
+//
+// Replaces what happens inside ducc0.wgridder.ms2dirty / dirty2ms, which the reference
+// calls at /root/reference/src/ska_sdp_func_python/imaging/ng.py:240-256, :271-287
+// (ms2dirty) and :99-112, :117-129 (dirty2ms).  There is no CPU fallback in this file:
+// every entry point needs a CUDA device.
+#include <cuda_runtime.h>
+#include <cufft.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/b200_wgridder.h"
+#include "es_kernel.h"
+#include "kernels.h"
+
+using namespace b2g;
+
+namespace {
+
+constexpr double kSpeedOfLight = 299792458.0;
+
+thread_local std::string g_err;
+
+int fail(const char *fmt, ...)
+{
+    char buf[1024];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_err = buf;
+    return 1;
+}
+
+#define CUDA_OK(expr)                                                                     \
+    do {                                                                                  \
+        cudaError_t e_ = (expr);                                                          \
+        if (e_ != cudaSuccess)                                                            \
+            return fail("%s:%d: %s -> %s", __FILE__, __LINE__, #expr, cudaGetErrorString(e_)); \
+    } while (0)
+#define FFT_OK(expr)                                                                      \
+    do {                                                                                  \
+        cufftResult r_ = (expr);                                                          \
+        if (r_ != CUFFT_SUCCESS)                                                          \
+            return fail("%s:%d: %s -> cufft error %d", __FILE__, __LINE__, #expr, (int)r_); \
+    } while (0)
+#define KERNEL_OK(expr)                                                                   \
+    do {                                                                                  \
+        int k_ = (expr);                                                                  \
+        if (k_ != 0)                                                                      \
+            return fail("%s:%d: %s -> %s", __FILE__, __LINE__, #expr,                     \
+                        k_ < 0 ? "unsupported kernel configuration"                       \
+                               : cudaGetErrorString((cudaError_t)k_));                    \
+    } while (0)
+#define B2G_OK(expr)               \
+    do {                           \
+        int b_ = (expr);           \
+        if (b_ != 0) return b_;    \
+    } while (0)
+
+enum Stage { S_H2D = 0, S_PREP, S_VIS, S_FFT, S_SCREEN, S_CORRECT, S_D2H, S_TOTAL, S_COUNT };
+
+// CUDA-event stage timer: begin/end pairs are summed per stage after one synchronise.
+struct StageTimer {
+    cudaStream_t stream = nullptr;
+    bool enabled = true;
+    struct Span { int stage; cudaEvent_t a, b; };
+    std::vector<Span> spans;
+    std::vector<cudaEvent_t> pool;
+    cudaEvent_t get()
+    {
+        if (!pool.empty()) {
+            cudaEvent_t e = pool.back();
+            pool.pop_back();
+            return e;
+        }
+        cudaEvent_t e;
+        cudaEventCreate(&e);
+        return e;
+    }
+    void begin(int stage)
+    {
+        if (!enabled) return;
+        Span s{stage, get(), get()};
+        cudaEventRecord(s.a, stream);
+        spans.push_back(s);
+    }
+    void end()
+    {
+        if (!enabled || spans.empty()) return;
+        cudaEventRecord(spans.back().b, stream);
+    }
+    // drop spans left behind by a call that failed half-way
+    void reset()
+    {
+        for (auto &s : spans) {
+            pool.push_back(s.a);
+            pool.push_back(s.b);
+        }
+        spans.clear();
+        (void)cudaGetLastError();
+    }
+    // call after the stream has been synchronised
+    void collect(double *out)
+    {
+        for (int i = 0; i < S_COUNT; ++i) out[i] = 0.0;
+        for (auto &s : spans) {
+            float ms = 0.f;
+            if (cudaEventElapsedTime(&ms, s.a, s.b) == cudaSuccess) out[s.stage] += ms;
+            pool.push_back(s.a);
+            pool.push_back(s.b);
+        }
+        spans.clear();
+    }
+    ~StageTimer()
+    {
+        for (auto &s : spans) {
+            cudaEventDestroy(s.a);
+            cudaEventDestroy(s.b);
+        }
+        for (auto e : pool) cudaEventDestroy(e);
+    }
+};
+
+size_t real_size(int dtype) { return dtype == B2G_F64 ? 8 : 4; }
+
+}  // namespace
+
+struct b2g_plan {
+    int64_t nrow = 0, nchan = 0, nvis = 0, npix_x = 0, npix_y = 0, nu = 0, nv = 0;
+    double psx = 0, psy = 0, epsilon = 0;
+    int wstack = 0, precision = B2G_F32, algo = B2G_ALGO_AUTO, verbosity = 0;
+    cudaStream_t stream = nullptr;
+    int device = 0;
+    // kernel
+    int W = 0;
+    double sigma = 0, beta = 0, e0 = 0, eps_kernel = 0;
+    PolyKernel pk;
+    // w-planes
+    int nplanes = 1, gs = 1, nslabs = 1, nslots = 1;
+    double dw = 0, w0 = 0, wmin = 0, wmax = 0, nm1min = 0;
+    // device buffers
+    double *d_uvw = nullptr;
+    bool own_uvw = false;
+    double *d_fscale = nullptr;
+    double *d_cu = nullptr, *d_cv = nullptr, *d_cheb = nullptr;
+    int ncheb = 0;
+    uint32_t *d_sidx = nullptr;
+    std::vector<long long> slab_begin;
+    void *d_ring = nullptr;
+    size_t plane_bytes = 0;
+    void *d_acc = nullptr;
+    double *d_scratch = nullptr;  // small scratch (sums)
+    cufftHandle fft = 0;
+    bool fft_ok = false;
+    void *d_fftwork = nullptr;
+    int key_bits = 0;
+    double t_plan_ms = 0, t_last_ms = 0;
+    double timings[S_COUNT] = {0};
+    long long launches_last = 0;
+    StageTimer timer;
+
+    VisGeo vis_geo() const
+    {
+        VisGeo g;
+        g.uvw = d_uvw;
+        g.fscale = d_fscale;
+        g.nchan = (uint32_t)nchan;
+        g.nu = (int)nu;
+        g.nv = (int)nv;
+        g.nplanes = nplanes;
+        g.nslots = nslots;
+        g.wstack = wstack;
+        g.su = psx;
+        g.sv = psy;
+        g.sw = wstack ? 1.0 / dw : 0.0;
+        g.w0s = wstack ? w0 / dw : 0.0;
+        g.plane_stride = (long long)nu * nv;
+        return g;
+    }
+    ImgGeo img_geo() const
+    {
+        ImgGeo g;
+        g.npix_x = (int)npix_x;
+        g.npix_y = (int)npix_y;
+        g.nu = (int)nu;
+        g.nv = (int)nv;
+        g.pixsize_x = psx;
+        g.pixsize_y = psy;
+        g.wstack = wstack;
+        g.nslots = nslots;
+        g.w0 = w0;
+        g.dw = dw;
+        g.cu = d_cu;
+        g.cv = d_cv;
+        g.cheb = d_cheb;
+        g.ncheb = ncheb;
+        g.nm1min = nm1min;
+        return g;
+    }
+    void release()
+    {
+        if (own_uvw && d_uvw) cudaFree(d_uvw);
+        if (d_fscale) cudaFree(d_fscale);
+        if (d_cu) cudaFree(d_cu);
+        if (d_cv) cudaFree(d_cv);
+        if (d_cheb) cudaFree(d_cheb);
+        if (d_sidx) cudaFree(d_sidx);
+        if (d_ring) cudaFree(d_ring);
+        if (d_acc) cudaFree(d_acc);
+        if (d_scratch) cudaFree(d_scratch);
+        if (d_fftwork) cudaFree(d_fftwork);
+        if (fft_ok) cufftDestroy(fft);
+        d_uvw = d_fscale = d_cu = d_cv = d_cheb = d_scratch = nullptr;
+        d_sidx = nullptr;
+        d_ring = d_acc = d_fftwork = nullptr;
+        fft_ok = false;
+    }
+};
+
+namespace {
+
+// (W, sigma, ...) for the request; honours an explicit padded grid (nu, nv) if given.
+int choose_kernel(double epsilon, bool wstack, int precision, int64_t npix_x, int64_t npix_y,
+                  int64_t nu_req, int64_t nv_req, double nvis, double planes_per_sigma,
+                  KernelRow *out)
+{
+    if (!(epsilon > 0.0)) return fail("epsilon must be positive (got %g)", epsilon);
+    const double eps_dim = epsilon / (wstack ? 3.0 : 2.0);
+    const int maxW = precision == B2G_F32 ? 8 : kMaxW;
+    const int csize = precision == B2G_F32 ? 8 : 16;
+    if (precision == B2G_F32 && epsilon < 5e-7)
+        return fail("epsilon=%g is below what single precision supports (>= 5e-7); use "
+                    "double precision", epsilon);
+    int best = -1;
+    if (nu_req > 0 && nv_req > 0) {
+        const double smax = std::min(double(nu_req) / npix_x, double(nv_req) / npix_y);
+        if (smax < 1.15)
+            return fail("requested grid %lldx%lld is less than 1.15x the image", (long long)nu_req,
+                        (long long)nv_req);
+        for (int i = 0; i < kKernelDBSize; ++i) {
+            const KernelRow &r = kKernelDB[i];
+            if (r.W > maxW || r.eps > eps_dim || r.sigma > smax + 1e-9) continue;
+            if (best < 0 || r.W < kKernelDB[best].W ||
+                (r.W == kKernelDB[best].W && r.sigma > kKernelDB[best].sigma))
+                best = i;
+        }
+    } else {
+        best = select_kernel(eps_dim, wstack, maxW, nvis, npix_x, npix_y, planes_per_sigma, csize);
+    }
+    if (best < 0)
+        return fail("no gridding kernel reaches epsilon=%g in %s precision", epsilon,
+                    precision == B2G_F32 ? "single" : "double");
+    *out = kKernelDB[best];
+    return 0;
+}
+
+int build_tables(b2g_plan *p)
+{
+    // 1/psi-hat along u and v at the image pixels (x in cycles per grid cell)
+    std::vector<double> cu(p->npix_x), cv(p->npix_y);
+    for (int64_t a = 0; a < p->npix_x; ++a)
+        cu[a] = 1.0 / p->pk.corr(double(a - p->npix_x / 2) / double(p->nu));
+    for (int64_t b = 0; b < p->npix_y; ++b)
+        cv[b] = 1.0 / p->pk.corr(double(b - p->npix_y / 2) / double(p->nv));
+    CUDA_OK(cudaMalloc(&p->d_cu, sizeof(double) * p->npix_x));
+    CUDA_OK(cudaMalloc(&p->d_cv, sizeof(double) * p->npix_y));
+    CUDA_OK(cudaMemcpyAsync(p->d_cu, cu.data(), sizeof(double) * p->npix_x,
+                            cudaMemcpyHostToDevice, p->stream));
+    CUDA_OK(cudaMemcpyAsync(p->d_cv, cv.data(), sizeof(double) * p->npix_y,
+                            cudaMemcpyHostToDevice, p->stream));
+    // 1/psi-hat_w(nm1*dw) as a Chebyshev series in nm1 on [nm1min, 0]
+    std::vector<double> cheb(1, 1.0);
+    if (p->wstack) {
+        const PolyKernel &pk = p->pk;
+        const double dw = p->dw;
+        cheb = cheb_fit([&](double nm1) { return 1.0 / pk.corr(nm1 * dw); }, p->nm1min, 0.0,
+                        1e-16);
+    }
+    p->ncheb = (int)cheb.size();
+    CUDA_OK(cudaMalloc(&p->d_cheb, sizeof(double) * cheb.size()));
+    CUDA_OK(cudaMemcpyAsync(p->d_cheb, cheb.data(), sizeof(double) * cheb.size(),
+                            cudaMemcpyHostToDevice, p->stream));
+    CUDA_OK(cudaStreamSynchronize(p->stream));  // host vectors go out of scope
+    return 0;
+}
+
+int build_sort(b2g_plan *p)
+{
+    const long long n = p->nvis;
+    p->slab_begin.assign(p->nslabs + 1, 0);
+    if (n == 0) return 0;
+    if (n >= (1ll << 32)) return fail("more than 2^32 samples per plan (%lld)", n);
+    uint64_t *keys_a = nullptr, *keys_b = nullptr;
+    uint32_t *idx_a = nullptr;
+    unsigned long long *counts = nullptr;
+    CUDA_OK(cudaMalloc(&p->d_sidx, sizeof(uint32_t) * n));
+    CUDA_OK(cudaMalloc(&keys_a, sizeof(uint64_t) * n));
+    CUDA_OK(cudaMalloc(&keys_b, sizeof(uint64_t) * n));
+    CUDA_OK(cudaMalloc(&idx_a, sizeof(uint32_t) * n));
+    CUDA_OK(cudaMalloc(&counts, sizeof(unsigned long long) * p->nplanes));
+    const VisGeo g = p->vis_geo();
+    int rc = launch_keygen(g, p->W, n, keys_a, idx_a, counts, p->stream);
+    if (rc == 0) {
+        const double kmax = double(p->nplanes) * double(p->nu) * double(p->nv);
+        p->key_bits = std::max(1, (int)std::ceil(std::log2(kmax + 1.0)));
+        rc = sort_pairs(keys_a, keys_b, idx_a, p->d_sidx, n, p->key_bits, p->stream);
+    }
+    std::vector<unsigned long long> h(p->nplanes, 0);
+    cudaError_t e = cudaMemcpyAsync(h.data(), counts, sizeof(unsigned long long) * p->nplanes,
+                                    cudaMemcpyDeviceToHost, p->stream);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
+    cudaFree(keys_a);
+    cudaFree(keys_b);
+    cudaFree(idx_a);
+    cudaFree(counts);
+    KERNEL_OK(rc);
+    CUDA_OK(e);
+    // slab s = origin planes [s*gs, (s+1)*gs)
+    long long run = 0;
+    for (int s = 0; s < p->nslabs; ++s) {
+        p->slab_begin[s] = run;
+        for (int q = s * p->gs; q < std::min((s + 1) * p->gs, p->nplanes); ++q) run += (long long)h[q];
+    }
+    p->slab_begin[p->nslabs] = run;
+    if (run != n) {
+        // origin planes beyond nplanes-W cannot occur (locate() clamps); count them anyway
+        for (int q = p->nslabs * p->gs; q < p->nplanes; ++q) run += (long long)h[q];
+        if (run != n) return fail("internal: plane histogram covers %lld of %lld samples", run, n);
+        p->slab_begin[p->nslabs] = run;
+    }
+    return 0;
+}
+
+}  // namespace
+
+extern "C" const char *b2g_last_error(void) { return g_err.c_str(); }
+extern "C" const char *b2g_version(void) { return "b200-wgridder 0.1.0 (sm_100a)"; }
+
+extern "C" int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, const double *uvw,
+                               const double *freq, int uvw_space, int64_t npix_x, int64_t npix_y,
+                               double pixsize_x, double pixsize_y, int64_t nu, int64_t nv,
+                               double epsilon, int do_wstacking, int precision, int algo,
+                               int verbosity, void *stream)
+{
+    g_err.clear();
+    if (!plan) return fail("plan pointer is NULL");
+    *plan = nullptr;
+    if (nrow < 0 || nchan < 1) return fail("bad shape nrow=%lld nchan=%lld", (long long)nrow, (long long)nchan);
+    if (npix_x < 2 || npix_y < 2 || (npix_x & 1) || (npix_y & 1))
+        return fail("image dimensions must be even and >= 2 (got %lld x %lld)", (long long)npix_x,
+                    (long long)npix_y);
+    if (!(pixsize_x > 0.0) || !(pixsize_y > 0.0)) return fail("pixel sizes must be positive");
+    if (precision != B2G_F32 && precision != B2G_F64) return fail("bad precision code %d", precision);
+    if (nrow > 0 && !uvw) return fail("uvw is NULL");
+    if (!freq) return fail("freq is NULL");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return fail("no CUDA device available (this library has no CPU path)");
+
+    b2g_plan *p = new b2g_plan();
+    struct Guard {
+        b2g_plan *p;
+        ~Guard() { if (p) { p->release(); delete p; } }
+    } guard{p};
+    cudaEvent_t ev0, ev1;
+    p->stream = (cudaStream_t)stream;
+    p->timer.stream = p->stream;
+    CUDA_OK(cudaGetDevice(&p->device));
+    CUDA_OK(cudaEventCreate(&ev0));
+    CUDA_OK(cudaEventCreate(&ev1));
+    CUDA_OK(cudaEventRecord(ev0, p->stream));
+    p->nrow = nrow;
+    p->nchan = nchan;
+    p->nvis = nrow * nchan;
+    p->npix_x = npix_x;
+    p->npix_y = npix_y;
+    p->psx = pixsize_x;
+    p->psy = pixsize_y;
+    p->epsilon = epsilon;
+    p->wstack = do_wstacking ? 1 : 0;
+    p->precision = precision;
+    p->verbosity = verbosity;
+
+    // frequencies -> f/c on the device
+    std::vector<double> fs(nchan);
+    if (uvw_space == B2G_DEVICE) {
+        CUDA_OK(cudaMemcpy(fs.data(), freq, sizeof(double) * nchan, cudaMemcpyDeviceToHost));
+    } else {
+        std::memcpy(fs.data(), freq, sizeof(double) * nchan);
+    }
+    double fsmin = 1e300, fsmax = 0.0;
+    for (auto &f : fs) {
+        if (!(f > 0.0)) return fail("frequencies must be positive");
+        f /= kSpeedOfLight;
+        fsmin = std::min(fsmin, f);
+        fsmax = std::max(fsmax, f);
+    }
+    CUDA_OK(cudaMalloc(&p->d_fscale, sizeof(double) * nchan));
+    CUDA_OK(cudaMemcpy(p->d_fscale, fs.data(), sizeof(double) * nchan, cudaMemcpyHostToDevice));
+    // uvw
+    if (uvw_space == B2G_DEVICE) {
+        p->d_uvw = const_cast<double *>(uvw);
+        p->own_uvw = false;
+    } else {
+        CUDA_OK(cudaMalloc(&p->d_uvw, sizeof(double) * 3 * std::max<int64_t>(nrow, 1)));
+        p->own_uvw = true;
+        if (nrow > 0)
+            CUDA_OK(cudaMemcpyAsync(p->d_uvw, uvw, sizeof(double) * 3 * nrow,
+                                    cudaMemcpyHostToDevice, p->stream));
+    }
+    CUDA_OK(cudaMalloc(&p->d_scratch, sizeof(double) * 2048));
+    double st[4] = {0, 0, 0, 0};
+    if (nrow > 0) {
+        KERNEL_OK(launch_uvw_stats(p->d_uvw, nrow, p->d_scratch, p->stream));
+        CUDA_OK(cudaMemcpyAsync(st, p->d_scratch, sizeof(st), cudaMemcpyDeviceToHost, p->stream));
+        CUDA_OK(cudaStreamSynchronize(p->stream));
+    }
+    if (!(st[1] == st[1]) || !(st[2] == st[2]) || !(st[3] == st[3]) || st[1] > 1e300)
+        return fail("uvw contains NaN or Inf");
+    p->wmin = st[0] * fsmin;
+    p->wmax = st[1] * fsmax;
+    if (nrow == 0) p->wmin = p->wmax = 0.0;
+
+    // field of view -> most negative n-1
+    {
+        const double xm = pixsize_x * double(npix_x / 2), ym = pixsize_y * double(npix_y / 2);
+        const double r2 = xm * xm + ym * ym;
+        p->nm1min = r2 >= 1.0 ? -1.0 : -r2 / (std::sqrt(1.0 - r2) + 1.0);
+    }
+    const double planes_per_sigma = p->wstack ? (p->wmax - p->wmin) * 2.0 * std::fabs(p->nm1min) : 0.0;
+    KernelRow kr;
+    B2G_OK(choose_kernel(epsilon, p->wstack, precision, npix_x, npix_y, nu, nv, double(p->nvis),
+                         planes_per_sigma, &kr));
+    p->W = kr.W;
+    p->sigma = kr.sigma;
+    p->beta = kr.beta;
+    p->e0 = kr.e0;
+    p->eps_kernel = kr.eps;
+    p->pk.build(kr.W, kr.beta, kr.e0);
+    if (nu > 0 && nv > 0) {
+        if ((nu & 1) || (nv & 1)) return fail("nu and nv must be even");
+        p->nu = nu;
+        p->nv = nv;
+    } else {
+        p->nu = std::max<int64_t>(good_size_even((int64_t)std::ceil(kr.sigma * npix_x)), 32);
+        p->nv = std::max<int64_t>(good_size_even((int64_t)std::ceil(kr.sigma * npix_y)), 32);
+    }
+    if (p->nu > 32768 || p->nv > 32768) return fail("padded grid %lldx%lld too large", (long long)p->nu, (long long)p->nv);
+
+    // w-planes
+    const size_t csize = 2 * real_size(precision);
+    p->plane_bytes = size_t(p->nu) * size_t(p->nv) * csize;
+    if (p->wstack) {
+        p->dw = 0.5 / (kr.sigma * std::max(std::fabs(p->nm1min), 1e-12));
+        const double span = (p->wmax - p->wmin) / p->dw;
+        if (span > 60000.0) return fail("w range needs %g planes", span);
+        p->nplanes = (int)std::ceil(span) + p->W;
+        p->w0 = 0.5 * (p->wmin + p->wmax) - 0.5 * double(p->nplanes - 1) * p->dw;
+        size_t free_b = 0, total_b = 0;
+        CUDA_OK(cudaMemGetInfo(&free_b, &total_b));
+        // working set besides the ring: sorted index (4 B/sample) + sort scratch
+        // (20 B/sample, released after the sort) + caller's visibilities
+        const double avail = 0.35 * double(free_b);
+        int gs = (int)(avail / double(p->plane_bytes)) - (p->W - 1);
+        gs = std::max(1, std::min(gs, 8));
+        gs = std::min(gs, p->nplanes - p->W + 1);
+        p->gs = gs;
+        p->nslots = gs + p->W - 1;
+        p->nslabs = (p->nplanes - p->W + 1 + gs - 1) / gs;
+    } else {
+        p->dw = 0.0;
+        p->w0 = 0.0;
+        p->nplanes = 1;
+        p->gs = 1;
+        p->nslots = 1;
+        p->nslabs = 1;
+    }
+
+    // gridding kernel family
+    bool fast_ok = precision == B2G_F32 ? warprun_supported<float>(p->W, p->wstack)
+                                        : warprun_supported<double>(p->W, p->wstack);
+    if (algo == B2G_ALGO_AUTO) algo = fast_ok ? B2G_ALGO_WARPRUN : B2G_ALGO_SIMPLE;
+    if (algo == B2G_ALGO_WARPRUN && !fast_ok)
+        return fail("warp-run kernels do not support W=%d (%s, wstacking=%d)", p->W,
+                    precision == B2G_F32 ? "f32" : "f64", p->wstack);
+    if (algo != B2G_ALGO_SIMPLE && algo != B2G_ALGO_WARPRUN) return fail("bad algo code %d", algo);
+    p->algo = algo;
+
+    B2G_OK(build_tables(p));
+    B2G_OK(build_sort(p));
+
+    // FFT plan (own work area so that memory use is explicit)
+    FFT_OK(cufftCreate(&p->fft));
+    p->fft_ok = true;
+    FFT_OK(cufftSetAutoAllocation(p->fft, 0));
+    size_t work = 0;
+    FFT_OK(cufftMakePlan2d(p->fft, (int)p->nu, (int)p->nv,
+                           precision == B2G_F32 ? CUFFT_C2C : CUFFT_Z2Z, &work));
+    if (work > 0) CUDA_OK(cudaMalloc(&p->d_fftwork, work));
+    FFT_OK(cufftSetWorkArea(p->fft, p->d_fftwork));
+    FFT_OK(cufftSetStream(p->fft, p->stream));
+
+    CUDA_OK(cudaMalloc(&p->d_ring, p->plane_bytes * size_t(p->nslots)));
+    CUDA_OK(cudaMalloc(&p->d_acc, size_t(npix_x) * size_t(npix_y) * real_size(precision)));
+
+    CUDA_OK(cudaEventRecord(ev1, p->stream));
+    CUDA_OK(cudaEventSynchronize(ev1));
+    float ms = 0.f;
+    cudaEventElapsedTime(&ms, ev0, ev1);
+    cudaEventDestroy(ev0);
+    cudaEventDestroy(ev1);
+    p->t_plan_ms = ms;
+    if (verbosity > 0)
+        fprintf(stderr,
+                "[b2g] plan: nvis=%lld W=%d sigma=%.2f grid=%lldx%lld planes=%d (gs=%d, slabs=%d) "
+                "dw=%g w=[%g,%g] algo=%d key_bits=%d work=%.1f MB plan=%.2f ms\n",
+                (long long)p->nvis, p->W, p->sigma, (long long)p->nu, (long long)p->nv, p->nplanes,
+                p->gs, p->nslabs, p->dw, p->wmin, p->wmax, p->algo, p->key_bits, work / 1048576.0,
+                p->t_plan_ms);
+    guard.p = nullptr;
+    *plan = p;
+    return 0;
+}
+
+extern "C" void b2g_plan_destroy(b2g_plan *plan)
+{
+    if (!plan) return;
+    cudaStreamSynchronize(plan->stream);
+    plan->release();
+    delete plan;
+}
+
+namespace {
+
+// A device view of caller data in the plan's precision; owns a staging copy if the caller's
+// data is on the host or has the other component type.
+template <typename T> struct Staged {
+    T *ptr = nullptr;
+    bool owned = false;
+    cudaStream_t stream = nullptr;
+    ~Staged()
+    {
+        if (owned && ptr) cudaFreeAsync(ptr, stream);
+    }
+};
+
+constexpr long long kChunkReals = 1ll << 26;  // staging chunk (reals) for converting copies
+
+// src (n reals of `dtype` in `space`) -> device array of T
+template <typename T>
+int stage_in(const void *src, int dtype, int space, long long n, cudaStream_t s, Staged<T> *out)
+{
+    out->stream = s;
+    const int want = sizeof(T) == 8 ? B2G_F64 : B2G_F32;
+    if (n == 0 || src == nullptr) return 0;
+    if (space == B2G_DEVICE && dtype == want) {
+        out->ptr = const_cast<T *>(static_cast<const T *>(src));
+        return 0;
+    }
+    CUDA_OK(cudaMallocAsync(&out->ptr, sizeof(T) * n, s));
+    out->owned = true;
+    if (dtype == want) {
+        CUDA_OK(cudaMemcpyAsync(out->ptr, src, sizeof(T) * n, cudaMemcpyHostToDevice, s));
+        return 0;
+    }
+    // other component type: convert on the device, chunk by chunk
+    if (dtype == B2G_F64) {
+        const double *sp = static_cast<const double *>(src);
+        if (space == B2G_DEVICE) {
+            KERNEL_OK((launch_convert<double, float>(sp, reinterpret_cast<float *>(out->ptr), n, s)));
+            return 0;
+        }
+        const long long cn = std::min(n, kChunkReals);
+        double *tmp = nullptr;
+        CUDA_OK(cudaMallocAsync(&tmp, sizeof(double) * cn, s));
+        for (long long o = 0; o < n; o += cn) {
+            const long long m = std::min(cn, n - o);
+            CUDA_OK(cudaMemcpyAsync(tmp, sp + o, sizeof(double) * m, cudaMemcpyHostToDevice, s));
+            KERNEL_OK((launch_convert<double, float>(tmp, reinterpret_cast<float *>(out->ptr) + o, m, s)));
+        }
+        CUDA_OK(cudaFreeAsync(tmp, s));
+    } else {
+        const float *sp = static_cast<const float *>(src);
+        if (space == B2G_DEVICE) {
+            KERNEL_OK((launch_convert<float, double>(sp, reinterpret_cast<double *>(out->ptr), n, s)));
+            return 0;
+        }
+        const long long cn = std::min(n, kChunkReals);
+        float *tmp = nullptr;
+        CUDA_OK(cudaMallocAsync(&tmp, sizeof(float) * cn, s));
+        for (long long o = 0; o < n; o += cn) {
+            const long long m = std::min(cn, n - o);
+            CUDA_OK(cudaMemcpyAsync(tmp, sp + o, sizeof(float) * m, cudaMemcpyHostToDevice, s));
+            KERNEL_OK((launch_convert<float, double>(tmp, reinterpret_cast<double *>(out->ptr) + o, m, s)));
+        }
+        CUDA_OK(cudaFreeAsync(tmp, s));
+    }
+    return 0;
+}
+
+// device array of T (n reals) -> dst (`dtype` in `space`); no-op if dst aliases src
+template <typename T>
+int stage_out(const T *src, void *dst, int dtype, int space, long long n, cudaStream_t s)
+{
+    const int have = sizeof(T) == 8 ? B2G_F64 : B2G_F32;
+    if (n == 0 || static_cast<const void *>(src) == dst) return 0;
+    if (dtype == have) {
+        CUDA_OK(cudaMemcpyAsync(dst, src, sizeof(T) * n,
+                                space == B2G_DEVICE ? cudaMemcpyDeviceToDevice : cudaMemcpyDeviceToHost, s));
+        return 0;
+    }
+    if (dtype == B2G_F64) {  // T == float
+        double *dp = static_cast<double *>(dst);
+        const float *sp = reinterpret_cast<const float *>(src);
+        if (space == B2G_DEVICE) {
+            KERNEL_OK((launch_convert<float, double>(sp, dp, n, s)));
+            return 0;
+        }
+        const long long cn = std::min(n, kChunkReals);
+        double *tmp = nullptr;
+        CUDA_OK(cudaMallocAsync(&tmp, sizeof(double) * cn, s));
+        for (long long o = 0; o < n; o += cn) {
+            const long long m = std::min(cn, n - o);
+            KERNEL_OK((launch_convert<float, double>(sp + o, tmp, m, s)));
+            CUDA_OK(cudaMemcpyAsync(dp + o, tmp, sizeof(double) * m, cudaMemcpyDeviceToHost, s));
+        }
+        CUDA_OK(cudaFreeAsync(tmp, s));
+    } else {  // T == double, dst float
+        float *dp = static_cast<float *>(dst);
+        const double *sp = reinterpret_cast<const double *>(src);
+        if (space == B2G_DEVICE) {
+            KERNEL_OK((launch_convert<double, float>(sp, dp, n, s)));
+            return 0;
+        }
+        const long long cn = std::min(n, kChunkReals);
+        float *tmp = nullptr;
+        CUDA_OK(cudaMallocAsync(&tmp, sizeof(float) * cn, s));
+        for (long long o = 0; o < n; o += cn) {
+            const long long m = std::min(cn, n - o);
+            KERNEL_OK((launch_convert<double, float>(sp + o, tmp, m, s)));
+            CUDA_OK(cudaMemcpyAsync(dp + o, tmp, sizeof(float) * m, cudaMemcpyDeviceToHost, s));
+        }
+        CUDA_OK(cudaFreeAsync(tmp, s));
+    }
+    return 0;
+}
+
+template <typename T> VisLaunch<T> make_launch(b2g_plan *p, int slab)
+{
+    VisLaunch<T> L;
+    L.geo = p->vis_geo();
+    L.W = p->W;
+    L.wstack = p->wstack != 0;
+    L.coef = p->pk.c.data();
+    L.sidx = p->d_sidx;
+    L.begin = p->slab_begin[slab];
+    L.end = p->slab_begin[slab + 1];
+    L.plane0 = slab * p->gs;
+    L.slot0 = L.plane0 % p->nslots;
+    L.ms = nullptr;
+    L.wgt = nullptr;
+    L.ms_out = nullptr;
+    L.ring = static_cast<cplx<T> *>(p->d_ring);
+    L.stream = p->stream;
+    return L;
+}
+
+template <typename T> cplx<T> *slot_ptr(b2g_plan *p, int plane)
+{
+    return static_cast<cplx<T> *>(p->d_ring) + (size_t)(plane % p->nslots) * size_t(p->nu) * size_t(p->nv);
+}
+
+template <typename T> int fft_plane(b2g_plan *p, int plane, int direction)
+{
+    cplx<T> *d = slot_ptr<T>(p, plane);
+    if (sizeof(T) == 4)
+        FFT_OK(cufftExecC2C(p->fft, reinterpret_cast<cufftComplex *>(d),
+                            reinterpret_cast<cufftComplex *>(d), direction));
+    else
+        FFT_OK(cufftExecZ2Z(p->fft, reinterpret_cast<cufftDoubleComplex *>(d),
+                            reinterpret_cast<cufftDoubleComplex *>(d), direction));
+    return 0;
+}
+
+// planes finished by slab s (invert) : [first, first+count)
+void slab_planes_done(const b2g_plan *p, int s, int *first, int *count)
+{
+    *first = s * p->gs;
+    *count = (s == p->nslabs - 1) ? p->nplanes - *first : p->gs;
+}
+// planes that must be produced before slab s can be degridded (predict)
+void slab_planes_new(const b2g_plan *p, int s, int *first, int *count)
+{
+    if (s == 0) {
+        *first = 0;
+        *count = std::min(p->nslots, p->nplanes);
+    } else {
+        *first = s * p->gs + p->W - 1;
+        *count = std::min(p->gs, p->nplanes - *first);
+        if (*count < 0) *count = 0;
+    }
+}
+
+template <typename T>
+int invert_impl(b2g_plan *p, const void *ms, const void *wgt, int vis_dtype, int vis_space,
+                void *dirty, int dirty_dtype, int dirty_space)
+{
+    StageTimer &tm = p->timer;
+    cudaStream_t s = p->stream;
+    const long long n = p->nvis;
+    p->launches_last = 0;
+    tm.reset();
+    tm.begin(S_TOTAL);
+    const size_t tot_idx = tm.spans.size() - 1;
+
+    tm.begin(S_H2D);
+    Staged<T> d_ms, d_wgt;
+    B2G_OK(stage_in<T>(ms, vis_dtype, vis_space, 2 * n, s, &d_ms));
+    B2G_OK(stage_in<T>(wgt, vis_dtype, vis_space, n, s, &d_wgt));
+    tm.end();
+
+    tm.begin(S_PREP);
+    CUDA_OK(cudaMemsetAsync(p->d_ring, 0, p->plane_bytes * size_t(p->nslots), s));
+    tm.end();
+
+    const ImgGeo ig = p->img_geo();
+    for (int sl = 0; sl < p->nslabs; ++sl) {
+        VisLaunch<T> L = make_launch<T>(p, sl);
+        L.ms = reinterpret_cast<const cplx<T> *>(d_ms.ptr);
+        L.wgt = d_wgt.ptr;
+        tm.begin(S_VIS);
+        if (L.end > L.begin) {
+            if (p->algo == B2G_ALGO_WARPRUN) KERNEL_OK(launch_grid_warprun<T>(L));
+            else KERNEL_OK(launch_grid_simple<T>(L));
+            p->launches_last++;
+        }
+        tm.end();
+        int first, count;
+        slab_planes_done(p, sl, &first, &count);
+        tm.begin(S_FFT);
+        for (int q = 0; q < count; ++q) B2G_OK(fft_plane<T>(p, first + q, CUFFT_INVERSE));
+        tm.end();
+        tm.begin(S_SCREEN);
+        KERNEL_OK(launch_screen_accumulate<T>(ig, static_cast<const cplx<T> *>(p->d_ring), first,
+                                              count, static_cast<T *>(p->d_acc), sl == 0, s));
+        p->launches_last++;
+        tm.end();
+        if (sl + 1 < p->nslabs) {
+            tm.begin(S_PREP);
+            for (int q = 0; q < count; ++q)
+                CUDA_OK(cudaMemsetAsync(slot_ptr<T>(p, first + q), 0, p->plane_bytes, s));
+            tm.end();
+        }
+    }
+
+    tm.begin(S_CORRECT);
+    void *d_out = dirty;
+    const long long npx = p->npix_x * p->npix_y;
+    if (dirty_space != B2G_DEVICE) CUDA_OK(cudaMallocAsync(&d_out, real_size(dirty_dtype) * npx, s));
+    if (dirty_dtype == B2G_F64)
+        KERNEL_OK((launch_correct<T, double>(ig, static_cast<const T *>(p->d_acc), static_cast<double *>(d_out), s)));
+    else
+        KERNEL_OK((launch_correct<T, float>(ig, static_cast<const T *>(p->d_acc), static_cast<float *>(d_out), s)));
+    p->launches_last++;
+    tm.end();
+    if (dirty_space != B2G_DEVICE) {
+        tm.begin(S_D2H);
+        CUDA_OK(cudaMemcpyAsync(dirty, d_out, real_size(dirty_dtype) * npx, cudaMemcpyDeviceToHost, s));
+        CUDA_OK(cudaFreeAsync(d_out, s));
+        tm.end();
+    }
+    if (tm.enabled) cudaEventRecord(tm.spans[tot_idx].b, s);
+    CUDA_OK(cudaStreamSynchronize(s));
+    tm.collect(p->timings);
+    p->t_last_ms = p->timings[S_TOTAL];
+    return 0;
+}
+
+template <typename T>
+int predict_impl(b2g_plan *p, const void *dirty, int dirty_dtype, int dirty_space,
+                 const void *wgt, void *ms_out, int vis_dtype, int vis_space)
+{
+    StageTimer &tm = p->timer;
+    cudaStream_t s = p->stream;
+    const long long n = p->nvis;
+    const int want = sizeof(T) == 8 ? B2G_F64 : B2G_F32;
+    p->launches_last = 0;
+    tm.reset();
+    tm.begin(S_TOTAL);
+    const size_t tot_idx = tm.spans.size() - 1;
+    const long long npx = p->npix_x * p->npix_y;
+    const ImgGeo ig = p->img_geo();
+
+    tm.begin(S_H2D);
+    const void *d_dirty = dirty;
+    void *d_dirty_tmp = nullptr;
+    if (dirty_space != B2G_DEVICE) {
+        CUDA_OK(cudaMallocAsync(&d_dirty_tmp, real_size(dirty_dtype) * npx, s));
+        CUDA_OK(cudaMemcpyAsync(d_dirty_tmp, dirty, real_size(dirty_dtype) * npx, cudaMemcpyHostToDevice, s));
+        d_dirty = d_dirty_tmp;
+    }
+    Staged<T> d_wgt;
+    B2G_OK(stage_in<T>(wgt, vis_dtype, vis_space, n, s, &d_wgt));
+    tm.end();
+
+    tm.begin(S_CORRECT);
+    if (dirty_dtype == B2G_F64)
+        KERNEL_OK((launch_precorrect<T, double>(ig, static_cast<const double *>(d_dirty), static_cast<T *>(p->d_acc), s)));
+    else
+        KERNEL_OK((launch_precorrect<T, float>(ig, static_cast<const float *>(d_dirty), static_cast<T *>(p->d_acc), s)));
+    p->launches_last++;
+    if (d_dirty_tmp) CUDA_OK(cudaFreeAsync(d_dirty_tmp, s));
+    tm.end();
+
+    cplx<T> *d_out = static_cast<cplx<T> *>(ms_out);
+    bool own_out = false;
+    if (n > 0 && !(vis_space == B2G_DEVICE && vis_dtype == want)) {
+        CUDA_OK(cudaMallocAsync(&d_out, sizeof(cplx<T>) * n, s));
+        own_out = true;
+    }
+
+    for (int sl = 0; sl < p->nslabs; ++sl) {
+        int first, count;
+        slab_planes_new(p, sl, &first, &count);
+        if (count > 0) {
+            tm.begin(S_SCREEN);
+            KERNEL_OK(launch_screen_apply<T>(ig, static_cast<const T *>(p->d_acc),
+                                             static_cast<cplx<T> *>(p->d_ring), first, count, s));
+            p->launches_last++;
+            tm.end();
+            tm.begin(S_FFT);
+            for (int q = 0; q < count; ++q) B2G_OK(fft_plane<T>(p, first + q, CUFFT_FORWARD));
+            tm.end();
+        }
+        VisLaunch<T> L = make_launch<T>(p, sl);
+        L.wgt = d_wgt.ptr;
+        L.ms_out = d_out;
+        tm.begin(S_VIS);
+        if (L.end > L.begin) {
+            if (p->algo == B2G_ALGO_WARPRUN) KERNEL_OK(launch_degrid_warprun<T>(L));
+            else KERNEL_OK(launch_degrid_simple<T>(L));
+            p->launches_last++;
+        }
+        tm.end();
+    }
+    if (own_out) {
+        tm.begin(S_D2H);
+        B2G_OK(stage_out<T>(reinterpret_cast<const T *>(d_out), ms_out, vis_dtype, vis_space, 2 * n, s));
+        CUDA_OK(cudaFreeAsync(d_out, s));
+        tm.end();
+    }
+    if (tm.enabled) cudaEventRecord(tm.spans[tot_idx].b, s);
+    CUDA_OK(cudaStreamSynchronize(s));
+    tm.collect(p->timings);
+    p->t_last_ms = p->timings[S_TOTAL];
+    return 0;
+}
+
+}  // namespace
+
+static int check_codes(int dtype, int space, const char *what)
+{
+    if (dtype != B2G_F32 && dtype != B2G_F64) return fail("bad %s dtype code %d", what, dtype);
+    if (space != B2G_HOST && space != B2G_DEVICE) return fail("bad %s memory-space code %d", what, space);
+    return 0;
+}
+
+extern "C" int b2g_plan_invert(b2g_plan *plan, const void *ms, const void *wgt, int vis_dtype,
+                               int vis_space, void *dirty, int dirty_dtype, int dirty_space)
+{
+    g_err.clear();
+    if (!plan) return fail("plan is NULL");
+    if (!dirty) return fail("dirty is NULL");
+    if (plan->nvis > 0 && !ms) return fail("ms is NULL");
+    B2G_OK(check_codes(vis_dtype, vis_space, "visibility"));
+    B2G_OK(check_codes(dirty_dtype, dirty_space, "image"));
+    CUDA_OK(cudaSetDevice(plan->device));
+    return plan->precision == B2G_F32
+               ? invert_impl<float>(plan, ms, wgt, vis_dtype, vis_space, dirty, dirty_dtype, dirty_space)
+               : invert_impl<double>(plan, ms, wgt, vis_dtype, vis_space, dirty, dirty_dtype, dirty_space);
+}
+
+extern "C" int b2g_plan_predict(b2g_plan *plan, const void *dirty, int dirty_dtype, int dirty_space,
+                                const void *wgt, void *ms_out, int vis_dtype, int vis_space)
+{
+    g_err.clear();
+    if (!plan) return fail("plan is NULL");
+    if (!dirty) return fail("dirty is NULL");
+    if (plan->nvis > 0 && !ms_out) return fail("ms_out is NULL");
+    B2G_OK(check_codes(vis_dtype, vis_space, "visibility"));
+    B2G_OK(check_codes(dirty_dtype, dirty_space, "image"));
+    CUDA_OK(cudaSetDevice(plan->device));
+    return plan->precision == B2G_F32
+               ? predict_impl<float>(plan, dirty, dirty_dtype, dirty_space, wgt, ms_out, vis_dtype, vis_space)
+               : predict_impl<double>(plan, dirty, dirty_dtype, dirty_space, wgt, ms_out, vis_dtype, vis_space);
+}
+
+extern "C" int b2g_plan_info(const b2g_plan *p, int64_t *iinfo, int ni, double *dinfo, int nd)
+{
+    g_err.clear();
+    if (!p) return fail("plan is NULL");
+    const int64_t iv[11] = {p->W, p->nu, p->nv, p->nplanes, p->nslabs, p->gs, p->algo,
+                            poly_degree(p->W), p->nvis, p->key_bits, p->launches_last};
+    const double dv[9] = {p->sigma, p->eps_kernel, p->dw, p->wmin, p->wmax, p->beta, p->e0,
+                          p->t_plan_ms, p->t_last_ms};
+    for (int i = 0; i < ni && i < 11; ++i) iinfo[i] = iv[i];
+    for (int i = 0; i < nd && i < 9; ++i) dinfo[i] = dv[i];
+    return 0;
+}
+
+extern "C" int b2g_plan_timings(const b2g_plan *p, double *ms_out, int n)
+{
+    g_err.clear();
+    if (!p) return fail("plan is NULL");
+    for (int i = 0; i < n && i < S_COUNT; ++i) ms_out[i] = p->timings[i];
+    return 0;
+}
+
+extern "C" int b2g_ms2dirty(int64_t nrow, int64_t nchan, const double *uvw, const double *freq,
+                            const void *ms, const void *wgt, int vis_dtype, int space,
+                            int64_t npix_x, int64_t npix_y, double pixsize_x, double pixsize_y,
+                            int64_t nu, int64_t nv, double epsilon, int do_wstacking, int precision,
+                            void *dirty, int dirty_dtype, void *stream)
+{
+    b2g_plan *p = nullptr;
+    B2G_OK(b2g_plan_create(&p, nrow, nchan, uvw, freq, space, npix_x, npix_y, pixsize_x, pixsize_y,
+                           nu, nv, epsilon, do_wstacking, precision, B2G_ALGO_AUTO, 0, stream));
+    int rc = b2g_plan_invert(p, ms, wgt, vis_dtype, space, dirty, dirty_dtype, space);
+    b2g_plan_destroy(p);
+    return rc;
+}
+
+extern "C" int b2g_dirty2ms(int64_t nrow, int64_t nchan, const double *uvw, const double *freq,
+                            const void *dirty, int dirty_dtype, const void *wgt, int vis_dtype,
+                            int space, int64_t npix_x, int64_t npix_y, double pixsize_x,
+                            double pixsize_y, int64_t nu, int64_t nv, double epsilon,
+                            int do_wstacking, int precision, void *ms_out, void *stream)
+{
+    b2g_plan *p = nullptr;
+    B2G_OK(b2g_plan_create(&p, nrow, nchan, uvw, freq, space, npix_x, npix_y, pixsize_x, pixsize_y,
+                           nu, nv, epsilon, do_wstacking, precision, B2G_ALGO_AUTO, 0, stream));
+    int rc = b2g_plan_predict(p, dirty, dirty_dtype, space, wgt, ms_out, vis_dtype, space);
+    b2g_plan_destroy(p);
+    return rc;
+}
+
+extern "C" int b2g_sumwt(const void *wgt, int dtype, int space, int64_t n, double *out, void *stream)
+{
+    g_err.clear();
+    if (!out) return fail("out is NULL");
+    B2G_OK(check_codes(dtype, space, "weight"));
+    *out = 0.0;
+    if (n <= 0) return 0;
+    if (!wgt) return fail("wgt is NULL");
+    cudaStream_t s = (cudaStream_t)stream;
+    constexpr int kParts = 1024;
+    double *scratch = nullptr;
+    CUDA_OK(cudaMallocAsync(&scratch, sizeof(double) * (kParts + 1), s));
+    int rc = 0;
+    if (dtype == B2G_F64) {
+        Staged<double> w;
+        rc = stage_in<double>(wgt, dtype, space, n, s, &w);
+        if (!rc) rc = launch_sum<double>(w.ptr, n, scratch + kParts, scratch, kParts, s) ? fail("sum kernel launch failed") : 0;
+        if (!rc && cudaMemcpyAsync(out, scratch + kParts, sizeof(double), cudaMemcpyDeviceToHost, s) != cudaSuccess)
+            rc = fail("sumwt copy failed");
+        if (!rc && cudaStreamSynchronize(s) != cudaSuccess) rc = fail("sumwt sync failed");
+    } else {
+        Staged<float> w;
+        rc = stage_in<float>(wgt, dtype, space, n, s, &w);
+        if (!rc) rc = launch_sum<float>(w.ptr, n, scratch + kParts, scratch, kParts, s) ? fail("sum kernel launch failed") : 0;
+        if (!rc && cudaMemcpyAsync(out, scratch + kParts, sizeof(double), cudaMemcpyDeviceToHost, s) != cudaSuccess)
+            rc = fail("sumwt copy failed");
+        if (!rc && cudaStreamSynchronize(s) != cudaSuccess) rc = fail("sumwt sync failed");
+    }
+    cudaFreeAsync(scratch, s);
+    return rc;
+}
+
+extern "C" int b2g_kernel_select(double epsilon, int do_wstacking, int precision, int64_t npix_x,
+                                 int64_t npix_y, double nvis, double *out5)
+{
+    g_err.clear();
+    KernelRow kr;
+    B2G_OK(choose_kernel(epsilon, do_wstacking != 0, precision, npix_x, npix_y, 0, 0, nvis, 0.0, &kr));
+    out5[0] = kr.W;
+    out5[1] = kr.sigma;
+    out5[2] = kr.beta;
+    out5[3] = kr.e0;
+    out5[4] = kr.eps;
+    return 0;
+}
+
+extern "C" int b2g_kernel_eval(int W, double beta, double e0, const double *t, int n, double *out)
+{
+    g_err.clear();
+    if (W < kMinW || W > kMaxW) return fail("W=%d out of range", W);
+    PolyKernel pk;
+    pk.build(W, beta, e0);
+    for (int i = 0; i < n; ++i) out[i] = pk.eval(t[i]);
+    return 0;
+}
+
+extern "C" int b2g_kernel_corr(int W, double beta, double e0, const double *x, int n, double *out)
+{
+    g_err.clear();
+    if (W < kMinW || W > kMaxW) return fail("W=%d out of range", W);
+    PolyKernel pk;
+    pk.build(W, beta, e0);
+    for (int i = 0; i < n; ++i) out[i] = pk.corr(x[i]);
+    return 0;
+}

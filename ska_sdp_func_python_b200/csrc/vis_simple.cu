@@ -12,8 +12,9 @@ namespace b2g {
 template <typename T, int W, bool WS>
 __global__ void __launch_bounds__(128)
 grid_simple_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ sidx,
-                   long long begin, long long end, int slab, const cplx<T> *__restrict__ ms,
-                   const T *__restrict__ wgt, cplx<T> *__restrict__ slabbuf)
+                   long long begin, long long end, int plane0, int slot0,
+                   const cplx<T> *__restrict__ ms, const T *__restrict__ wgt,
+                   cplx<T> *__restrict__ ring)
 {
     constexpr int PW = WS ? W : 1;
     long long i = begin + (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -33,10 +34,10 @@ grid_simple_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ s
     kernel_values<T, W>(tab, (T)L.du, ku);
     kernel_values<T, W>(tab, (T)L.dv, kv);
     if (WS) kernel_values<T, W>(tab, (T)L.dw, kw);
-    const int pbase = L.p0 - slab * g.gs;
+    const int sbase = L.p0 - plane0 + slot0;
 #pragma unroll 1
     for (int q = 0; q < PW; ++q) {
-        cplx<T> *plane = slabbuf + (long long)(pbase + q) * g.plane_stride;
+        cplx<T> *plane = ring + (long long)wrap_inc(sbase + q, g.nslots) * g.plane_stride;
         const T fq = WS ? kw[q] : T(1);
 #pragma unroll 1
         for (int a = 0; a < W; ++a) {
@@ -55,8 +56,9 @@ grid_simple_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ s
 template <typename T, int W, bool WS>
 __global__ void __launch_bounds__(128)
 degrid_simple_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ sidx,
-                     long long begin, long long end, int slab, const T *__restrict__ wgt,
-                     cplx<T> *__restrict__ out, const cplx<T> *__restrict__ slabbuf)
+                     long long begin, long long end, int plane0, int slot0,
+                     const T *__restrict__ wgt, cplx<T> *__restrict__ out,
+                     const cplx<T> *__restrict__ ring)
 {
     constexpr int PW = WS ? W : 1;
     long long i = begin + (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -76,11 +78,11 @@ degrid_simple_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__
     kernel_values<T, W>(tab, (T)L.du, ku);
     kernel_values<T, W>(tab, (T)L.dv, kv);
     if (WS) kernel_values<T, W>(tab, (T)L.dw, kw);
-    const int pbase = L.p0 - slab * g.gs;
+    const int sbase = L.p0 - plane0 + slot0;
     T sre = T(0), sim = T(0);
 #pragma unroll 1
     for (int q = 0; q < PW; ++q) {
-        const cplx<T> *plane = slabbuf + (long long)(pbase + q) * g.plane_stride;
+        const cplx<T> *plane = ring + (long long)wrap_inc(sbase + q, g.nslots) * g.plane_stride;
         T pre = T(0), pim = T(0);
 #pragma unroll 1
         for (int a = 0; a < W; ++a) {
@@ -118,7 +120,7 @@ template <typename T, int W, bool WS> static int grid_simple_inst(const VisLaunc
     if (n <= 0) return 0;
     unsigned blocks = (unsigned)((n + 127) / 128);
     grid_simple_kernel<T, W, WS><<<blocks, 128, 0, L.stream>>>(
-        L.geo, make_tab<T, W>(L.coef), L.sidx, L.begin, L.end, L.slab, L.ms, L.wgt, L.slabbuf);
+        L.geo, make_tab<T, W>(L.coef), L.sidx, L.begin, L.end, L.plane0, L.slot0, L.ms, L.wgt, L.ring);
     return (int)cudaGetLastError();
 }
 template <typename T, int W, bool WS> static int degrid_simple_inst(const VisLaunch<T> &L)
@@ -127,8 +129,8 @@ template <typename T, int W, bool WS> static int degrid_simple_inst(const VisLau
     if (n <= 0) return 0;
     unsigned blocks = (unsigned)((n + 127) / 128);
     degrid_simple_kernel<T, W, WS><<<blocks, 128, 0, L.stream>>>(
-        L.geo, make_tab<T, W>(L.coef), L.sidx, L.begin, L.end, L.slab, L.wgt, L.ms_out,
-        L.slabbuf);
+        L.geo, make_tab<T, W>(L.coef), L.sidx, L.begin, L.end, L.plane0, L.slot0, L.wgt, L.ms_out,
+        L.ring);
     return (int)cudaGetLastError();
 }
 

@@ -1,8 +1,8 @@
 // vis_sort.cu -- the uv-cell / w-plane sort ("bucket") pass.
 //
-// Every visibility gets the key  ((slab*nu + iu0)*nv + iv0)*gs + (p0 - slab*gs)  where
-// (iu0, iv0, p0) is the lower corner of its kernel footprint, and the (key, index) pairs
-// are radix-sorted.  This is the B200 counterpart of the scan/bucket pass at the start
+// Every visibility gets the key  (p0*nu + iu0)*nv + iv0  where (iu0, iv0, p0) is the
+// lower corner of its kernel footprint (first cell in u and v, first w-plane), and the
+// (key, index) pairs are radix-sorted; a histogram of p0 gives the slab boundaries.  This is the B200 counterpart of the scan/bucket pass at the start
 // of ducc0.wgridder.ms2dirty / dirty2ms (call sites
 // /root/reference/src/ska_sdp_func_python/imaging/ng.py:240-256, :99-112): ducc0 buckets
 // (row, channel-range) runs per 16x16 tile and w-plane on the host; here the sort is
@@ -22,33 +22,30 @@ namespace {
 
 __global__ void __launch_bounds__(256)
 keygen_kernel(VisGeo g, int W, long long nvis, uint64_t *__restrict__ keys,
-              uint32_t *__restrict__ idx, unsigned long long *__restrict__ slab_counts,
-              int nslabs)
+              uint32_t *__restrict__ idx, unsigned long long *__restrict__ plane_counts)
 {
-    extern __shared__ unsigned int sh_cnt[];  // [nslabs] when nslabs <= 1024
-    const bool use_sh = nslabs <= 1024;
+    extern __shared__ unsigned int sh_cnt[];  // [nplanes] when nplanes <= 4096
+    const int np = g.nplanes;
+    const bool use_sh = np <= 4096;
     if (use_sh) {
-        for (int i = threadIdx.x; i < nslabs; i += blockDim.x) sh_cnt[i] = 0;
+        for (int i = threadIdx.x; i < np; i += blockDim.x) sh_cnt[i] = 0;
         __syncthreads();
     }
     long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i < nvis) {
         const uint32_t row = (uint32_t)(i / g.nchan), chan = (uint32_t)(i - (long long)row * g.nchan);
         const Located L = locate(g, W, row, chan);
-        const int slab = L.p0 / g.gs;
-        const int prel = L.p0 - slab * g.gs;
-        uint64_t key = (uint64_t)slab * (uint64_t)g.nu + (uint64_t)L.iu0;
+        uint64_t key = (uint64_t)L.p0 * (uint64_t)g.nu + (uint64_t)L.iu0;
         key = key * (uint64_t)g.nv + (uint64_t)L.iv0;
-        key = key * (uint64_t)g.gs + (uint64_t)prel;
         keys[i] = key;
         idx[i] = (uint32_t)i;
-        if (use_sh) atomicAdd(&sh_cnt[slab], 1u);
-        else atomicAdd(&slab_counts[slab], 1ull);
+        if (use_sh) atomicAdd(&sh_cnt[L.p0], 1u);
+        else atomicAdd(&plane_counts[L.p0], 1ull);
     }
     if (use_sh) {
         __syncthreads();
-        for (int s = threadIdx.x; s < nslabs; s += blockDim.x)
-            if (sh_cnt[s]) atomicAdd(&slab_counts[s], (unsigned long long)sh_cnt[s]);
+        for (int s = threadIdx.x; s < np; s += blockDim.x)
+            if (sh_cnt[s]) atomicAdd(&plane_counts[s], (unsigned long long)sh_cnt[s]);
     }
 }
 
@@ -221,13 +218,13 @@ radix_scatter_kernel(const uint64_t *__restrict__ keys_in, const uint32_t *__res
 }  // namespace
 
 int launch_keygen(const VisGeo &geo, int W, long long nvis, uint64_t *keys, uint32_t *idx,
-                  unsigned long long *slab_counts, int nslabs, cudaStream_t stream)
+                  unsigned long long *plane_counts, cudaStream_t stream)
 {
+    cudaMemsetAsync(plane_counts, 0, sizeof(unsigned long long) * geo.nplanes, stream);
     if (nvis <= 0) return 0;
-    cudaMemsetAsync(slab_counts, 0, sizeof(unsigned long long) * nslabs, stream);
     const unsigned blocks = (unsigned)((nvis + 255) / 256);
-    const size_t sh = nslabs <= 1024 ? sizeof(unsigned int) * nslabs : 0;
-    keygen_kernel<<<blocks, 256, sh, stream>>>(geo, W, nvis, keys, idx, slab_counts, nslabs);
+    const size_t sh = geo.nplanes <= 4096 ? sizeof(unsigned int) * geo.nplanes : 0;
+    keygen_kernel<<<blocks, 256, sh, stream>>>(geo, W, nvis, keys, idx, plane_counts);
     return (int)cudaGetLastError();
 }
 

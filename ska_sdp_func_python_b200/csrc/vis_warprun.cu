@@ -4,29 +4,27 @@
 // dirty2ms (call sites /root/reference/src/ska_sdp_func_python/imaging/ng.py:240-256,
 // :99-112) with a B200-first design:
 //
-//  * Visibilities arrive sorted by (iu0, iv0, p0) = the grid cell and w-plane of the
-//    lower corner of their W x W x W footprint, so consecutive visibilities touch the
-//    same cells.
-//  * One warp owns a contiguous chunk of the sorted list.  Its 32 lanes own the W*W
-//    uv-cells of the current footprint (CPL = ceil(W*W/32) cells per lane, consecutive
-//    lanes = consecutive v cells, so every global access is a run of 8-byte cells), and
-//    every lane keeps all W planes of its cells in REGISTERS ("register window").
-//    Plane P lives in register slot P mod W, so when the footprint origin moves up in w
-//    the window rolls: only the planes that fell out of the window are flushed
-//    (gridding) or fetched (degridding).
+//  * Visibilities arrive sorted by (p0, iu0, iv0) = the first w-plane and the first grid
+//    cell of their W x W x W footprint, so consecutive visibilities touch the same planes
+//    and overlapping cells.
+//  * One warp owns a contiguous chunk of the sorted list.  Its lanes own the W*W residue
+//    classes (i, j) of uv-cell indices modulo W (CPL = ceil(W*W/32) classes per lane).
+//    Any W x W footprint contains exactly one cell of every class, so for every
+//    visibility each lane has exactly one cell per class to update, and it keeps the W
+//    w-planes of that cell in REGISTERS.  When the footprint moves by one cell only the
+//    W lanes whose cell left the footprint flush (gridding) or reload (degridding) their
+//    registers; everything else stays put.  Dense uv regions therefore cost ~2W packed
+//    FMAs per lane and visibility and almost no memory traffic, sparse regions cost about
+//    W*W_w cell flushes per visibility instead of W*W*W_w.
 //  * Per 32 visibilities: a lane-parallel preparation phase (one visibility per lane:
 //    fp64 coordinates -> cell/plane origin + sub-cell offsets, 3*W Horner evaluations of
-//    the kernel polynomial with coefficients taken from the constant bank, staging in
-//    shared memory), then a visibility-serial accumulation phase in which each lane does
-//    CPL*(3 + 2W) FMAs per visibility on its register window and touches no memory but
-//    a few broadcast shared-memory loads.
+//    the kernel polynomial with coefficients taken from the constant bank, staged in
+//    shared memory), then a visibility-serial accumulation phase on the register cells.
 //  * Gridding flushes with vectorised red.global.add.v2.f32 (one complex cell per
-//    instruction-lane, no return value, no CAS loop); degridding reduces the 32 lane
-//    partials of 32 visibilities through a padded shared-memory transpose.
-//
-// Per visibility this is ~60 issued warp-instructions for W=8 (vs 512 read-modify-writes
-// for a scatter gridder); the flush traffic is amortised over all visibilities sharing a
-// (iu0, iv0) origin.
+//    lane-op, no return value, no CAS loop); degridding reduces the 32 lane partials of
+//    32 visibilities through a padded shared-memory transpose.
+//  * fp32 arithmetic uses the packed FFMA2 (fma.rn.f32x2) of sm_100: (re, im) of a cell
+//    is one 64-bit register pair.
 #include "kernels.h"
 
 namespace b2g {
@@ -34,26 +32,43 @@ namespace b2g {
 namespace {
 
 constexpr int kWarps = 4;        // warps per block
-constexpr int kChunk = 512;      // visibilities per warp (multiple of 32)
+constexpr int kChunk = 256;      // visibilities per warp (multiple of 32)
+
+template <typename T> struct V2;
+template <> struct V2<float> { using type = float2; };
+template <> struct V2<double> { using type = double2; };
+
+__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
+__device__ __forceinline__ double2 fma2(double2 a, double2 b, double2 c)
+{
+    return make_double2(fma(a.x, b.x, c.x), fma(a.y, b.y, c.y));
+}
+__device__ __forceinline__ float2 mk2(float a, float b) { return make_float2(a, b); }
+__device__ __forceinline__ double2 mk2(double a, double b) { return make_double2(a, b); }
+
+// row stride of the duplicated w-kernel table, in (k,k) pairs: even (16-byte rows for
+// float) and == 2 mod 4 (spreads the lane-parallel stores over the banks)
+constexpr int kw_stride(int pw) { return ((pw + 1) / 4) * 4 + 2; }
 
 template <typename T, int W, bool WS> struct Stage {
+    using P = typename V2<T>::type;
     static constexpr int PW = WS ? W : 1;
     static constexpr int KS = W | 1;                 // odd row stride: conflict-free STS
-    static constexpr int KWS = (PW + 3) / 4 * 4;     // 16-byte aligned rows
-    alignas(16) T kw[32 * KWS];
-    alignas(16) cplx<T> val[32];
-    alignas(16) int4 org[32];                        // iu0, iv0, prel, active
+    static constexpr int KWS = kw_stride(PW);
+    alignas(16) P kw2[32 * KWS];                     // (kw, kw) pairs, plane p0+q at [q]
+    alignas(16) P val[32];
+    alignas(16) int4 org[32];                        // iu0, iv0, p0, ru | rv<<8 | active<<16
     T ku[32 * KS];
     T kv[32 * KS];
 };
 
 template <typename T> struct Partials {
-    cplx<T> p[32 * 33];
+    typename V2<T>::type p[32 * 33];
 };
 
 // Lane-parallel preparation of one visibility (lane `lane` of the warp).
 template <typename T, int W, bool WS>
-__device__ __forceinline__ void prepare(const VisGeo &g, const KernelTab<T, W> &tab, int slab,
+__device__ __forceinline__ void prepare(const VisGeo &g, const KernelTab<T, W> &tab,
                                         uint32_t idx, int lane, Stage<T, W, WS> &st,
                                         bool &flip)
 {
@@ -61,8 +76,7 @@ __device__ __forceinline__ void prepare(const VisGeo &g, const KernelTab<T, W> &
     const uint32_t row = idx / g.nchan, chan = idx - row * g.nchan;
     const Located L = locate(g, W, row, chan);
     flip = L.flip;
-    const int prel = L.p0 - slab * g.gs;
-    st.org[lane] = make_int4(L.iu0, L.iv0, prel, 1);
+    st.org[lane] = make_int4(L.iu0, L.iv0, L.p0, (L.iu0 % W) | ((L.iv0 % W) << 8) | (1 << 16));
     T k[W];
     kernel_values<T, W>(tab, (T)L.du, k);
 #pragma unroll
@@ -72,12 +86,8 @@ __device__ __forceinline__ void prepare(const VisGeo &g, const KernelTab<T, W> &
     for (int s = 0; s < W; ++s) st.kv[lane * S::KS + s] = k[s];
     if (WS) {
         kernel_values<T, W>(tab, (T)L.dw, k);
-        int slot = prel % W;  // plane P = prel+s lives in slot P mod W
 #pragma unroll
-        for (int s = 0; s < W; ++s) {
-            st.kw[lane * S::KWS + slot] = k[s];
-            slot = (slot + 1 == W) ? 0 : slot + 1;
-        }
+        for (int s = 0; s < W; ++s) st.kw2[lane * S::KWS + s] = mk2(k[s], k[s]);
     }
 }
 
@@ -89,11 +99,12 @@ __device__ __forceinline__ void prepare(const VisGeo &g, const KernelTab<T, W> &
 template <typename T, int W, bool WS>
 __global__ void __launch_bounds__(32 * kWarps)
 grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ sidx,
-                    long long begin, long long end, int slab,
+                    long long begin, long long end, int plane0, int slot0,
                     const cplx<T> *__restrict__ ms, const T *__restrict__ wgt,
-                    cplx<T> *__restrict__ slabbuf)
+                    cplx<T> *__restrict__ ring)
 {
     using S = Stage<T, W, WS>;
+    using P = typename V2<T>::type;
     constexpr int PW = S::PW;
     constexpr int CPL = (W * W + 31) / 32;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -106,48 +117,34 @@ grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ 
     if (cbeg >= end) return;
     const long long cend = (cbeg + kChunk < end) ? cbeg + kChunk : end;
 
-    // cells owned by this lane: c = lane + 32k -> (a, b) = (c / W, c % W), a along u
-    int ca[CPL], cb[CPL];
+    // residue classes owned by this lane: c = lane + 32k -> (i, j) = (c / W, c % W)
+    int ri[CPL], rj[CPL];
     bool valid[CPL];
 #pragma unroll
     for (int k = 0; k < CPL; ++k) {
         int c = lane + 32 * k;
         valid[k] = c < W * W;
         if (!valid[k]) c = 0;
-        ca[k] = c / W;
-        cb[k] = c - ca[k] * W;
+        ri[k] = c / W;
+        rj[k] = c - ri[k] * W;
     }
-    T are[CPL][PW], aim[CPL][PW];
-#pragma unroll
-    for (int k = 0; k < CPL; ++k)
-#pragma unroll
-        for (int q = 0; q < PW; ++q) are[k][q] = aim[k][q] = T(0);
+    P acc[CPL][PW];
     int coff[CPL];
 #pragma unroll
-    for (int k = 0; k < CPL; ++k) coff[k] = 0;
-    int cur_iu = -1, cur_iv = -1, cur_p = 0, r0 = 0;
-
-    // plane held in slot q of a window whose lowest plane is cur_p (r0 = cur_p % W)
-    auto plane_of = [&](int q) { return cur_p + q - r0 + (q < r0 ? W : 0); };
-
-    auto flush_slot = [&](int q, int P) {
-        cplx<T> *base = slabbuf + (long long)P * g.plane_stride;
+    for (int k = 0; k < CPL; ++k) {
+        coff[k] = -1;
 #pragma unroll
-        for (int k = 0; k < CPL; ++k) {
-            if (valid[k]) red_add(base + coff[k], are[k][q], aim[k][q]);
-            are[k][q] = T(0);
-            aim[k][q] = T(0);
-        }
-    };
-    auto flush_all = [&]() {
-#pragma unroll
-        for (int q = 0; q < PW; ++q) flush_slot(q, WS ? plane_of(q) : 0);
-    };
-    auto flush_below = [&](int pnew) {  // planes [cur_p, pnew) leave the window
+        for (int q = 0; q < PW; ++q) acc[k][q] = mk2(T(0), T(0));
+    }
+    int cur_p = 0;
+
+    auto flush_k = [&](int k) {
+        const int sbase = cur_p - plane0 + slot0;
 #pragma unroll
         for (int q = 0; q < PW; ++q) {
-            const int P = plane_of(q);
-            if (P < pnew) flush_slot(q, P);
+            cplx<T> *base = ring + (long long)wrap_inc(sbase + q, g.nslots) * g.plane_stride;
+            red_add(base + coff[k], acc[k][q].x, acc[k][q].y);
+            acc[k][q] = mk2(T(0), T(0));
         }
     };
 
@@ -165,55 +162,57 @@ grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ 
                 st.org[lane] = make_int4(0, 0, 0, 0);  // inactive: skipped below
             } else {
                 bool flip;
-                prepare<T, W, WS>(g, tab, slab, idx, lane, st, flip);
+                prepare<T, W, WS>(g, tab, idx, lane, st, flip);
                 if (flip) val.im = -val.im;
-                st.val[lane] = val;
+                st.val[lane] = mk2(val.re, val.im);
             }
         }
         __syncwarp();
         for (int v = 0; v < n; ++v) {
             const int4 o = st.org[v];
-            if (o.w == 0) continue;
-            if (o.x != cur_iu || o.y != cur_iv) {
-                if (cur_iu >= 0) flush_all();
-                cur_iu = o.x;
-                cur_iv = o.y;
-                cur_p = o.z;
-                r0 = WS ? cur_p % W : 0;
+            if ((o.w >> 16) == 0) continue;
+            if (WS && o.z != cur_p) {
 #pragma unroll
                 for (int k = 0; k < CPL; ++k)
-                    coff[k] = wrap_inc(cur_iu + ca[k], g.nu) * g.nv + wrap_inc(cur_iv + cb[k], g.nv);
-            } else if (WS && o.z != cur_p) {
-                if (o.z < cur_p || o.z >= cur_p + W) flush_all();
-                else flush_below(o.z);
+                    if (valid[k] && coff[k] >= 0) flush_k(k);
                 cur_p = o.z;
-                r0 = cur_p % W;
             }
-            const cplx<T> val = st.val[v];
-            T kwv[PW];
+            const int ru = o.w & 0xff, rv = (o.w >> 8) & 0xff;
+            const P val = st.val[v];
+            P kw2[PW];
             if (WS) {
 #pragma unroll
-                for (int q = 0; q < PW; ++q) kwv[q] = st.kw[v * S::KWS + q];
+                for (int q = 0; q < PW; ++q) kw2[q] = st.kw2[v * S::KWS + q];
             }
 #pragma unroll
             for (int k = 0; k < CPL; ++k) {
-                const T kk = st.ku[v * S::KS + ca[k]] * st.kv[v * S::KS + cb[k]];
-                const T pr = kk * val.re, pi = kk * val.im;
+                if (!valid[k]) continue;
+                int a = ri[k] - ru;
+                a += (a < 0) ? W : 0;
+                int b = rj[k] - rv;
+                b += (b < 0) ? W : 0;
+                const int cu = wrap_inc(o.x + a, g.nu), cv = wrap_inc(o.y + b, g.nv);
+                const int off = cu * g.nv + cv;
+                if (off != coff[k]) {
+                    if (coff[k] >= 0) flush_k(k);
+                    coff[k] = off;
+                }
+                const T kk = st.ku[v * S::KS + a] * st.kv[v * S::KS + b];
+                const P pv = mk2(kk * val.x, kk * val.y);
                 if (WS) {
 #pragma unroll
-                    for (int q = 0; q < PW; ++q) {
-                        are[k][q] = fma(pr, kwv[q], are[k][q]);
-                        aim[k][q] = fma(pi, kwv[q], aim[k][q]);
-                    }
+                    for (int q = 0; q < PW; ++q) acc[k][q] = fma2(pv, kw2[q], acc[k][q]);
                 } else {
-                    are[k][0] += pr;
-                    aim[k][0] += pi;
+                    acc[k][0].x += pv.x;
+                    acc[k][0].y += pv.y;
                 }
             }
         }
         __syncwarp();
     }
-    if (cur_iu >= 0) flush_all();
+#pragma unroll
+    for (int k = 0; k < CPL; ++k)
+        if (valid[k] && coff[k] >= 0) flush_k(k);
 }
 
 // ------------------------------------------------------------------------------------
@@ -222,10 +221,12 @@ grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ 
 template <typename T, int W, bool WS>
 __global__ void __launch_bounds__(32 * kWarps)
 degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ sidx,
-                      long long begin, long long end, int slab, const T *__restrict__ wgt,
-                      cplx<T> *__restrict__ out, const cplx<T> *__restrict__ slabbuf)
+                      long long begin, long long end, int plane0, int slot0,
+                      const T *__restrict__ wgt, cplx<T> *__restrict__ out,
+                      const cplx<T> *__restrict__ ring)
 {
     using S = Stage<T, W, WS>;
+    using P = typename V2<T>::type;
     constexpr int PW = S::PW;
     constexpr int CPL = (W * W + 31) / 32;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -235,45 +236,39 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
     const int lane = threadIdx.x & 31;
     const int warp = threadIdx.x >> 5;
     S &st = stage_all[warp];
-    cplx<T> *part = part_all[warp].p;
+    P *part = part_all[warp].p;
     const long long cbeg = begin + ((long long)blockIdx.x * kWarps + warp) * kChunk;
     if (cbeg >= end) return;
     const long long cend = (cbeg + kChunk < end) ? cbeg + kChunk : end;
 
-    int ca[CPL], cb[CPL];
+    int ri[CPL], rj[CPL];
     bool valid[CPL];
 #pragma unroll
     for (int k = 0; k < CPL; ++k) {
         int c = lane + 32 * k;
         valid[k] = c < W * W;
         if (!valid[k]) c = 0;
-        ca[k] = c / W;
-        cb[k] = c - ca[k] * W;
+        ri[k] = c / W;
+        rj[k] = c - ri[k] * W;
     }
-    T gre[CPL][PW], gim[CPL][PW];
-#pragma unroll
-    for (int k = 0; k < CPL; ++k)
-#pragma unroll
-        for (int q = 0; q < PW; ++q) gre[k][q] = gim[k][q] = T(0);
+    P gv[CPL][PW];
     int coff[CPL];
 #pragma unroll
-    for (int k = 0; k < CPL; ++k) coff[k] = 0;
-    int cur_iu = -1, cur_iv = -1, cur_p = 0, r0 = 0;
+    for (int k = 0; k < CPL; ++k) {
+        coff[k] = -1;
+#pragma unroll
+        for (int q = 0; q < PW; ++q) gv[k][q] = mk2(T(0), T(0));
+    }
+    int cur_p = -1;
 
-    auto plane_of = [&](int q) { return cur_p + q - r0 + (q < r0 ? W : 0); };
-    auto load_slot = [&](int q, int P) {
-        const cplx<T> *base = slabbuf + (long long)P * g.plane_stride;
+    auto load_k = [&](int k) {
+        const int sbase = cur_p - plane0 + slot0;
 #pragma unroll
-        for (int k = 0; k < CPL; ++k) {
-            cplx<T> c{T(0), T(0)};
-            if (valid[k]) c = base[coff[k]];
-            gre[k][q] = c.re;
-            gim[k][q] = c.im;
+        for (int q = 0; q < PW; ++q) {
+            const cplx<T> *base = ring + (long long)wrap_inc(sbase + q, g.nslots) * g.plane_stride;
+            const cplx<T> c = base[coff[k]];
+            gv[k][q] = mk2(c.re, c.im);
         }
-    };
-    auto load_all = [&]() {
-#pragma unroll
-        for (int q = 0; q < PW; ++q) load_slot(q, WS ? plane_of(q) : 0);
     };
 
     for (long long b0 = cbeg; b0 < cend; b0 += 32) {
@@ -287,65 +282,45 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
             if (my_w == T(0)) {
                 st.org[lane] = make_int4(0, 0, 0, 0);
             } else {
-                prepare<T, W, WS>(g, tab, slab, my_idx, lane, st, my_flip);
+                prepare<T, W, WS>(g, tab, my_idx, lane, st, my_flip);
             }
         }
         __syncwarp();
         for (int v = 0; v < n; ++v) {
             const int4 o = st.org[v];
-            cplx<T> s{T(0), T(0)};
-            if (o.w != 0) {
-                if (o.x != cur_iu || o.y != cur_iv) {
-                    cur_iu = o.x;
-                    cur_iv = o.y;
-                    cur_p = o.z;
-                    r0 = WS ? cur_p % W : 0;
-#pragma unroll
-                    for (int k = 0; k < CPL; ++k)
-                        coff[k] = wrap_inc(cur_iu + ca[k], g.nu) * g.nv +
-                                  wrap_inc(cur_iv + cb[k], g.nv);
-                    load_all();
-                } else if (WS && o.z != cur_p) {
-                    if (o.z < cur_p || o.z >= cur_p + W) {
-                        cur_p = o.z;
-                        r0 = cur_p % W;
-                        load_all();
-                    } else {
-                        // slots whose plane dropped below the new origin take the plane W above
-                        const int pnew = o.z;
-                        bool need[PW];
-#pragma unroll
-                        for (int q = 0; q < PW; ++q) need[q] = plane_of(q) < pnew;
-                        cur_p = pnew;
-                        r0 = cur_p % W;
-#pragma unroll
-                        for (int q = 0; q < PW; ++q)
-                            if (need[q]) load_slot(q, plane_of(q));
-                    }
-                }
-                T kwv[PW];
+            P s = mk2(T(0), T(0));
+            if ((o.w >> 16) != 0) {
+                const bool newplane = (o.z != cur_p);
+                cur_p = o.z;
+                const int ru = o.w & 0xff, rv = (o.w >> 8) & 0xff;
+                P kw2[PW];
                 if (WS) {
 #pragma unroll
-                    for (int q = 0; q < PW; ++q) kwv[q] = st.kw[v * S::KWS + q];
+                    for (int q = 0; q < PW; ++q) kw2[q] = st.kw2[v * S::KWS + q];
                 }
 #pragma unroll
                 for (int k = 0; k < CPL; ++k) {
-                    const T kk = st.ku[v * S::KS + ca[k]] * st.kv[v * S::KS + cb[k]];
-                    T tre, tim;
-                    if (WS) {
-                        tre = gre[k][0] * kwv[0];
-                        tim = gim[k][0] * kwv[0];
-#pragma unroll
-                        for (int q = 1; q < PW; ++q) {
-                            tre = fma(gre[k][q], kwv[q], tre);
-                            tim = fma(gim[k][q], kwv[q], tim);
-                        }
-                    } else {
-                        tre = gre[k][0];
-                        tim = gim[k][0];
+                    if (!valid[k]) continue;
+                    int a = ri[k] - ru;
+                    a += (a < 0) ? W : 0;
+                    int b = rj[k] - rv;
+                    b += (b < 0) ? W : 0;
+                    const int cu = wrap_inc(o.x + a, g.nu), cv = wrap_inc(o.y + b, g.nv);
+                    const int off = cu * g.nv + cv;
+                    if (newplane || off != coff[k]) {
+                        coff[k] = off;
+                        load_k(k);
                     }
-                    s.re = fma(kk, tre, s.re);
-                    s.im = fma(kk, tim, s.im);
+                    const T kk = st.ku[v * S::KS + a] * st.kv[v * S::KS + b];
+                    P t;
+                    if (WS) {
+                        t = mk2(gv[k][0].x * kw2[0].x, gv[k][0].y * kw2[0].y);
+#pragma unroll
+                        for (int q = 1; q < PW; ++q) t = fma2(gv[k][q], kw2[q], t);
+                    } else {
+                        t = gv[k][0];
+                    }
+                    s = fma2(mk2(kk, kk), t, s);
                 }
             }
             part[v * 33 + lane] = s;
@@ -355,9 +330,9 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
             T sre = T(0), sim = T(0);
 #pragma unroll 8
             for (int l = 0; l < 32; ++l) {
-                const cplx<T> c = part[lane * 33 + l];
-                sre += c.re;
-                sim += c.im;
+                const P c = part[lane * 33 + l];
+                sre += c.x;
+                sim += c.y;
             }
             if (my_flip) sim = -sim;
             out[my_idx] = cplx<T>{sre * my_w, sim * my_w};
@@ -388,14 +363,12 @@ template <typename T, int W, bool WS> static int grid_inst(const VisLaunch<T> &L
     const long long n = L.end - L.begin;
     if (n <= 0) return 0;
     const size_t smem = kWarps * sizeof(Stage<T, W, WS>);
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(grid_warprun_kernel<T, W, WS>,
-                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        attr_set = true;
-    }
+    cudaError_t e = cudaFuncSetAttribute(grid_warprun_kernel<T, W, WS>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
     grid_warprun_kernel<T, W, WS><<<nblocks_for(n), 32 * kWarps, smem, L.stream>>>(
-        L.geo, make_tab<T, W>(L.coef), L.sidx, L.begin, L.end, L.slab, L.ms, L.wgt, L.slabbuf);
+        L.geo, make_tab<T, W>(L.coef), L.sidx, L.begin, L.end, L.plane0, L.slot0, L.ms, L.wgt,
+        L.ring);
     return (int)cudaGetLastError();
 }
 template <typename T, int W, bool WS> static int degrid_inst(const VisLaunch<T> &L)
@@ -403,15 +376,12 @@ template <typename T, int W, bool WS> static int degrid_inst(const VisLaunch<T> 
     const long long n = L.end - L.begin;
     if (n <= 0) return 0;
     const size_t smem = kWarps * (sizeof(Stage<T, W, WS>) + sizeof(Partials<T>));
-    static bool attr_set = false;
-    if (!attr_set) {
-        cudaFuncSetAttribute(degrid_warprun_kernel<T, W, WS>,
-                             cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        attr_set = true;
-    }
+    cudaError_t e = cudaFuncSetAttribute(degrid_warprun_kernel<T, W, WS>,
+                                         cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return (int)e;
     degrid_warprun_kernel<T, W, WS><<<nblocks_for(n), 32 * kWarps, smem, L.stream>>>(
-        L.geo, make_tab<T, W>(L.coef), L.sidx, L.begin, L.end, L.slab, L.wgt, L.ms_out,
-        L.slabbuf);
+        L.geo, make_tab<T, W>(L.coef), L.sidx, L.begin, L.end, L.plane0, L.slot0, L.wgt,
+        L.ms_out, L.ring);
     return (int)cudaGetLastError();
 }
 
