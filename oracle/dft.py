@@ -7,6 +7,7 @@ is pinned to the reference's own dft_cpu_looped
 (/root/reference/src/ska_sdp_func_python/imaging/dft.py:265-285) via tests/golden/;
 it is unpinned against ducc0 output itself (ducc0 is not installable here).
 """
+import concurrent.futures
 import ctypes
 import os
 import subprocess
@@ -21,7 +22,7 @@ C_M_S = 299792458.0
 def build(force=False):
     """Compile liboracle.so with gcc (recipe: oracle/Makefile)."""
     so = os.path.join(_HERE, "liboracle.so")
-    srcs = [os.path.join(_HERE, f) for f in ("dft_oracle.c", "wgridder_cpu.c")]
+    srcs = [os.path.join(_HERE, f) for f in ("dft_oracle.c",)]
     if (not force and os.path.exists(so)
             and all(os.path.getmtime(so) >= os.path.getmtime(s) for s in srcs)):
         return so
@@ -34,6 +35,17 @@ def lib():
     if _LIB is None:
         _LIB = ctypes.CDLL(build())
     return _LIB
+
+
+def _threaded(work, n, nthreads=None):
+    """Run work(lo, hi) over [0, n) in chunks on a thread pool (ctypes drops the GIL)."""
+    nthreads = nthreads or os.cpu_count() or 1
+    if n <= 0:
+        return
+    nchunk = min(n, nthreads * 4)
+    edges = [n * i // nchunk for i in range(nchunk + 1)]
+    with concurrent.futures.ThreadPoolExecutor(max_workers=nthreads) as ex:
+        list(ex.map(lambda i: work(edges[i], edges[i + 1]), range(nchunk)))
 
 
 def _p(a, t=ctypes.c_double):
@@ -51,11 +63,17 @@ def ms2dirty_points(uvw, freq, ms, wgt, npix_x, npix_y, pixsize_x, pixsize_y,
     py = np.ascontiguousarray(py, dtype=np.int64)
     out = np.zeros(px.shape[0], dtype=np.float64)
     nrow, nchan = ms.shape
-    lib().oracle_ms2dirty_points(
-        ctypes.c_int64(nrow), ctypes.c_int64(nchan), _p(uvw), _p(freq), _p(ms), _p(wgt),
-        ctypes.c_int64(npix_x), ctypes.c_int64(npix_y), ctypes.c_double(pixsize_x),
-        ctypes.c_double(pixsize_y), ctypes.c_int(int(do_wstacking)),
-        ctypes.c_int64(px.shape[0]), _p(px, ctypes.c_int64), _p(py, ctypes.c_int64), _p(out))
+    L = lib()
+
+    def work(lo, hi):
+        L.oracle_ms2dirty_points(
+            ctypes.c_int64(nrow), ctypes.c_int64(nchan), _p(uvw), _p(freq), _p(ms), _p(wgt),
+            ctypes.c_int64(npix_x), ctypes.c_int64(npix_y), ctypes.c_double(pixsize_x),
+            ctypes.c_double(pixsize_y), ctypes.c_int(int(do_wstacking)),
+            ctypes.c_int64(hi - lo), _p(px[lo:hi], ctypes.c_int64), _p(py[lo:hi], ctypes.c_int64),
+            _p(out[lo:hi]))
+
+    _threaded(work, px.shape[0])
     return out
 
 
@@ -76,12 +94,17 @@ def dirty2ms_samples(uvw, freq, dirty, wgt, pixsize_x, pixsize_y, do_wstacking, 
     rows = np.ascontiguousarray(rows, dtype=np.int64)
     chans = np.ascontiguousarray(chans, dtype=np.int64)
     out = np.zeros(rows.shape[0], dtype=np.complex128)
-    lib().oracle_dirty2ms_samples(
-        ctypes.c_int64(freq.shape[0]), _p(uvw), _p(freq), _p(dirty), _p(wgt),
-        ctypes.c_int64(dirty.shape[0]), ctypes.c_int64(dirty.shape[1]),
-        ctypes.c_double(pixsize_x), ctypes.c_double(pixsize_y),
-        ctypes.c_int(int(do_wstacking)), ctypes.c_int64(rows.shape[0]),
-        _p(rows, ctypes.c_int64), _p(chans, ctypes.c_int64), _p(out))
+    L = lib()
+
+    def work(lo, hi):
+        L.oracle_dirty2ms_samples(
+            ctypes.c_int64(freq.shape[0]), _p(uvw), _p(freq), _p(dirty), _p(wgt),
+            ctypes.c_int64(dirty.shape[0]), ctypes.c_int64(dirty.shape[1]),
+            ctypes.c_double(pixsize_x), ctypes.c_double(pixsize_y),
+            ctypes.c_int(int(do_wstacking)), ctypes.c_int64(hi - lo),
+            _p(rows[lo:hi], ctypes.c_int64), _p(chans[lo:hi], ctypes.c_int64), _p(out[lo:hi]))
+
+    _threaded(work, rows.shape[0])
     return out
 
 

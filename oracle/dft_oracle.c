@@ -24,6 +24,7 @@
  * Both entry points work on an explicit list of output pixels / samples so that large
  * configurations can be spot-checked.
  */
+#define _GNU_SOURCE
 #include <math.h>
 #include <stddef.h>
 #include <stdint.h>

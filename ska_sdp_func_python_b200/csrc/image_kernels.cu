@@ -40,8 +40,8 @@ __device__ __forceinline__ double corr_factor(const ImgGeo &g, int a, int b)
         const double r2 = x * x + y * y;
         if (r2 >= 1.0) return 0.0;
         const double nm1 = nm1_of(r2);
-        // nm1 in [nm1min, 0] -> z in [-1, 1]
-        const double z = (g.nm1min < 0.0) ? fma(2.0 / g.nm1min, nm1, -1.0) : 0.0;
+        // nm1 in [nm1min, 0] -> z in [-1, 1]  (same map as cheb_fit(f, nm1min, 0) in es_kernel.h)
+        const double z = (g.nm1min < 0.0) ? fma(-2.0 / g.nm1min, nm1, 1.0) : 0.0;
         f *= cheb_eval(g.cheb, g.ncheb, z) / (nm1 + 1.0);  // 1/(psi-hat_w * n)
     }
     return f;

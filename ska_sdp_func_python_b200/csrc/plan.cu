@@ -234,12 +234,19 @@ int choose_kernel(double epsilon, bool wstack, int precision, int64_t npix_x, in
                   KernelRow *out)
 {
     if (!(epsilon > 0.0)) return fail("epsilon must be positive (got %g)", epsilon);
-    const double eps_dim = epsilon / (wstack ? 3.0 : 2.0);
+    // Error budget: the aliasing errors of the 2 (3) separable dimensions add in quadrature;
+    // 1.5x head-room covers the polynomial fit and the difference between the tabulated
+    // mean over |x| <= 1/(2 sigma) and the actual image; `floor` is the rounding noise of
+    // the arithmetic type, which no kernel can remove.
+    const double floor = precision == B2G_F32 ? 6e-7 : 3e-13;
+    const double eps_dim = (epsilon - floor) / (1.5 * std::sqrt(wstack ? 3.0 : 2.0));
     const int maxW = precision == B2G_F32 ? 8 : kMaxW;
     const int csize = precision == B2G_F32 ? 8 : 16;
-    if (precision == B2G_F32 && epsilon < 5e-7)
-        return fail("epsilon=%g is below what single precision supports (>= 5e-7); use "
+    if (precision == B2G_F32 && epsilon < 2e-6)
+        return fail("epsilon=%g is below what single precision supports (>= 2e-6); use "
                     "double precision", epsilon);
+    if (epsilon < 4e-13)
+        return fail("epsilon=%g is below what double precision supports (>= 4e-13)", epsilon);
     int best = -1;
     if (nu_req > 0 && nv_req > 0) {
         const double smax = std::min(double(nu_req) / npix_x, double(nv_req) / npix_y);
