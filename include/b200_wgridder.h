@@ -48,6 +48,12 @@ extern "C" {
 /* memory spaces */
 #define B2G_HOST 0
 #define B2G_DEVICE 1
+/* integer / real types accepted for the flags cube of b2g_vis_prepare */
+#define B2G_FLAG_NONE 0
+#define B2G_FLAG_U8 1
+#define B2G_FLAG_I32 2
+#define B2G_FLAG_I64 3
+#define B2G_FLAG_F64 4
 /* gridding kernel families */
 #define B2G_ALGO_AUTO (-1)
 #define B2G_ALGO_SIMPLE 0   /* one thread per visibility, global atomics (validation path) */
@@ -128,6 +134,38 @@ int b2g_kernel_select(double epsilon, int do_wstacking, int precision, int64_t n
                       int64_t npix_y, double nvis, double *out5);
 int b2g_kernel_eval(int W, double beta, double e0, const double *t, int n, double *out);
 int b2g_kernel_corr(int W, double beta, double e0, const double *x, int n, double *out);
+
+/*
+ * Marshalling of the Visibility cube around the gridder, one streaming kernel per direction.
+ * ALL pointers except polmat and lmn are DEVICE pointers; polmat / lmn are small host arrays.
+ *
+ * b2g_vis_prepare replaces the numpy passes of invert_ng before the ducc0 call
+ * (ng.py:182-204, :231-233: phase rotation to the image centre [shift_vis_to_image,
+ * imaging/base.py:48-92 -> visibility/base.py:27-45, :60-96], flagged_vis, flagged_imaging_weight,
+ * convert_pol_frame, astype, transposes):
+ *   vis     [nrow][nchan][npol_in] complex (vis_dtype), a chunk of rows starting at row0
+ *   flags   same shape, type flag_dtype (B2G_FLAG_*), may be NULL;  factor = 1 - flags
+ *   weight  same shape, real (wgt_dtype), may be NULL (all ones)
+ *   polmat  [npol_out][npol_in] complex double (host): visibility frame -> image frame
+ *   lmn     NULL (no rotation) or host {l, m, n-1} of the image centre relative to the
+ *           visibility phase centre, signed for the uvw array passed here
+ *   uvw     [nrow_total][3] metres, fscale [nchan] = f/c  (only read if lmn != NULL)
+ *   ms_out  [npol_out][nrow_total][nchan] complex (out_dtype);  wgt_out same, real, may be NULL
+ *   dopsf   pol 0 = 1, other pols = 0 (ng.py:231-233)
+ *
+ * b2g_vis_finish is the tail of predict_ng (ng.py:131-143): convert_pol_frame image frame ->
+ * visibility frame, interleave to [nrow][nchan][npol_vis], inverse phase rotation.
+ */
+int b2g_vis_prepare(int64_t nrow, int64_t nchan, int npol_in, int npol_out, const void *vis,
+                    int vis_dtype, const void *flags, int flag_dtype, const void *weight,
+                    int wgt_dtype, const double *polmat, const double *lmn, const double *uvw,
+                    const double *fscale, int64_t row0, int64_t nrow_total, int dopsf,
+                    void *ms_out, void *wgt_out, int out_dtype, void *stream);
+
+int b2g_vis_finish(int64_t nrow, int64_t nchan, int npol_img, int npol_vis, const void *ms,
+                   int ms_dtype, const double *polmat, const double *lmn, const double *uvw,
+                   const double *fscale, int64_t row0, int64_t nrow_total, void *vis_out,
+                   int vis_dtype, void *stream);
 
 #ifdef __cplusplus
 }

@@ -59,6 +59,8 @@ def lib():
         L.wg_screen_accumulate.restype = None
         L.wg_screen_apply.argtypes = [vp, vp, i64, i64, dbl, vp, ci]
         L.wg_screen_apply.restype = None
+        L.wg_correction.argtypes = [vp, i64, i64, vp, vp, vp, ci, dbl, vp, ci]
+        L.wg_correction.restype = None
         _LIB = L
     return _LIB
 
@@ -191,17 +193,17 @@ class CpuPlan:
             return self._corr
         cu = 1.0 / kernel_ft(self.coef, (np.arange(self.npix_x) - self.npix_x // 2) / self.nu)
         cv = 1.0 / kernel_ft(self.coef, (np.arange(self.npix_y) - self.npix_y // 2) / self.nv)
-        corr = np.outer(cu, cv)
+        corr = np.empty((self.npix_x, self.npix_y))
+        lo = min(self.nm1min, -1e-12)
         if self.wstack:
-            x = (np.arange(self.npix_x) - self.npix_x // 2) * self.psx
-            y = (np.arange(self.npix_y) - self.npix_y // 2) * self.psy
-            r2 = x[:, None] ** 2 + y[None, :] ** 2
-            ok = r2 < 1.0
-            nm1 = np.where(ok, -r2 / (np.sqrt(np.where(ok, 1.0 - r2, 1.0)) + 1.0), 0.0)
             fit = np.polynomial.chebyshev.Chebyshev.interpolate(
-                lambda t: 1.0 / kernel_ft(self.coef, t * self.dw), 64,
-                domain=[min(self.nm1min, -1e-12), 0.0])
-            corr = np.where(ok, corr * fit(nm1) / (nm1 + 1.0), 0.0)
+                lambda t: 1.0 / kernel_ft(self.coef, t * self.dw), 64, domain=[lo, 0.0])
+            cheb = np.ascontiguousarray(fit.coef)
+        else:
+            cheb = np.ones(1)
+        cu, cv = np.ascontiguousarray(cu), np.ascontiguousarray(cv)
+        self.L.wg_correction(self.ctx, self.npix_x, self.npix_y, cu.ctypes.data, cv.ctypes.data,
+                             cheb.ctypes.data, len(cheb), lo, corr.ctypes.data, self.nthreads)
         self._corr = corr
         return corr
 
@@ -216,7 +218,7 @@ class CpuPlan:
         for p in range(self.nplanes):
             self.L.wg_grid_plane(self.ctx, p, ms.ctypes.data,
                                  None if wgt is None else wgt.ctypes.data, grid.ctypes.data, nt)
-            f = scipy.fft.ifft2(grid, norm="forward", workers=nt)
+            f = scipy.fft.ifft2(grid, norm="forward", workers=nt, overwrite_x=True)
             self.L.wg_screen_accumulate(self.ctx, f.ctypes.data, self.npix_x, self.npix_y,
                                         self.w0 + p * self.dw, acc.ctypes.data, nt)
         return acc * self.correction()
@@ -232,7 +234,7 @@ class CpuPlan:
         for p in range(self.nplanes):
             self.L.wg_screen_apply(self.ctx, pre.ctypes.data, self.npix_x, self.npix_y,
                                    self.w0 + p * self.dw, grid.ctypes.data, nt)
-            f = scipy.fft.fft2(grid, norm="backward", workers=nt)
+            f = scipy.fft.fft2(grid, norm="backward", workers=nt, overwrite_x=True)
             self.L.wg_degrid_plane(self.ctx, p, f.ctypes.data, out.ctypes.data, nt)
         self.L.wg_finish_ms(self.ctx, None if wgt is None else wgt.ctypes.data, out.ctypes.data, nt)
         return out

@@ -18,8 +18,9 @@ EXPORTS = (
     "b2g_last_error", "b2g_version", "b2g_plan_create", "b2g_plan_destroy",
     "b2g_plan_invert", "b2g_plan_predict", "b2g_plan_info", "b2g_plan_timings",
     "b2g_ms2dirty", "b2g_dirty2ms", "b2g_sumwt", "b2g_kernel_select", "b2g_kernel_eval",
-    "b2g_kernel_corr",
+    "b2g_kernel_corr", "b2g_vis_prepare", "b2g_vis_finish",
 )
+FLAG_NONE, FLAG_U8, FLAG_I32, FLAG_I64, FLAG_F64 = 0, 1, 2, 3, 4
 
 _lib = None
 
@@ -71,6 +72,11 @@ def lib():
     L.b2g_kernel_eval.argtypes = [ci, dbl, dbl, pd, ci, pd]
     L.b2g_kernel_corr.restype = ci
     L.b2g_kernel_corr.argtypes = [ci, dbl, dbl, pd, ci, pd]
+    L.b2g_vis_prepare.restype = ci
+    L.b2g_vis_prepare.argtypes = [i64, i64, ci, ci, vp, ci, vp, ci, vp, ci, pd, pd, vp, vp, i64,
+                                  i64, ci, vp, vp, ci, vp]
+    L.b2g_vis_finish.restype = ci
+    L.b2g_vis_finish.argtypes = [i64, i64, ci, ci, vp, ci, pd, pd, vp, vp, i64, i64, vp, ci, vp]
     _lib = L
     return L
 

@@ -349,6 +349,10 @@ int build_sort(b2g_plan *p)
 
 }  // namespace
 
+namespace b2g {
+int wrapper_fail(const char *msg) { return fail("%s", msg); }
+}  // namespace b2g
+
 extern "C" const char *b2g_last_error(void) { return g_err.c_str(); }
 extern "C" const char *b2g_version(void) { return "b200-wgridder 0.1.0 (sm_100a)"; }
 
