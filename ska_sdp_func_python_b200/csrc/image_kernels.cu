@@ -10,6 +10,8 @@
 // axis of both the image [npix_x][npix_y] and the grid planes [nu][nv]); each thread
 // computes n-1 once in fp64 and loops over the planes of the slab, so the image is read
 // and written once per slab instead of once per plane.
+#include <math_constants.h>
+
 #include "kernels.h"
 
 namespace b2g {
@@ -212,7 +214,7 @@ __global__ void __launch_bounds__(256) sum_stage2(const double *__restrict__ par
     if (threadIdx.x == 0) *out = sh[0];
 }
 
-// min|w|, max|w|, max|u|, max|v| over rows (NaN-free input assumed)
+// min|w|, max|w|, max|u|, max|v| over rows; any non-finite coordinate makes max|w| = +inf
 __global__ void __launch_bounds__(256)
 uvw_stats_kernel(const double *__restrict__ uvw, long long nrow, double *__restrict__ out4)
 {
@@ -221,6 +223,10 @@ uvw_stats_kernel(const double *__restrict__ uvw, long long nrow, double *__restr
     for (long long r = (long long)blockIdx.x * 256 + threadIdx.x; r < nrow;
          r += (long long)gridDim.x * 256) {
         const double u = fabs(uvw[3 * r]), v = fabs(uvw[3 * r + 1]), w = fabs(uvw[3 * r + 2]);
+        if (!(isfinite(u) && isfinite(v) && isfinite(w))) {  // reported as max|w| = inf
+            wmax = CUDART_INF;
+            continue;
+        }
         wmin = fmin(wmin, w);
         wmax = fmax(wmax, w);
         umax = fmax(umax, u);

@@ -1,0 +1,135 @@
+"""Edge cases and size-independent properties of the CUDA path (through the C ABI)."""
+import numpy as np
+import pytest
+
+from conftest import C_M_S, make_case, rel_l2, rel_max
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def wg(built):
+    import torch
+    assert torch.cuda.is_available()
+    from ska_sdp_func_python_b200 import wgridder
+    return wgridder
+
+
+def test_empty_input(wg):
+    """nrow = 0: dirty image is zero, predicted array is empty."""
+    uvw = np.zeros((0, 3))
+    freq = np.array([1e8, 1.1e8])
+    d = wg.ms2dirty(uvw, freq, np.zeros((0, 2), complex), None, 64, 64, 1e-3, 1e-3, 0, 0, 1e-6, True)
+    assert d.shape == (64, 64) and np.all(d == 0)
+    v = wg.dirty2ms(uvw, freq, np.ones((64, 64)), None, 1e-3, 1e-3, 0, 0, 1e-6, True)
+    assert v.shape == (0, 2)
+
+
+def test_all_weights_zero_and_single_sample(wg):
+    from oracle import dft as odft
+    uvw, freq, ms, wgt = make_case(31, 200, 2, 64, 64, 1e-3, 1e-3, 0.1)
+    d = wg.ms2dirty(uvw, freq, ms, np.zeros_like(wgt), 64, 64, 1e-3, 1e-3, 0, 0, 1e-8, True)
+    assert np.all(d == 0)
+    v = wg.dirty2ms(uvw, freq, np.ones((64, 64)), np.zeros_like(wgt), 1e-3, 1e-3, 0, 0, 1e-8, True)
+    assert np.all(v == 0)
+    d1 = wg.ms2dirty(uvw[:1], freq[:1], ms[:1, :1], None, 64, 64, 1e-3, 1e-3, 0, 0, 1e-8, True)
+    r1 = odft.ms2dirty(uvw[:1], freq[:1], ms[:1, :1], None, 64, 64, 1e-3, 1e-3, True)
+    assert rel_l2(d1, r1) < 1e-8
+
+
+def test_w_all_zero_with_wstacking(wg):
+    """The reference warns that 'nifty gridder doesn't like all w = 0 with do_wstacking=True'
+    (ng.py:9-11); this implementation handles it (one plane set) and matches the DFT."""
+    from oracle import dft as odft
+    uvw, freq, ms, wgt = make_case(32, 300, 2, 64, 48, 1e-3, 1.2e-3, 0.0)
+    d = wg.ms2dirty(uvw, freq, ms, wgt, 64, 48, 1e-3, 1.2e-3, 0, 0, 1e-9, True)
+    assert rel_l2(d, odft.ms2dirty(uvw, freq, ms, wgt, 64, 48, 1e-3, 1.2e-3, True)) < 1e-9
+
+
+def test_negative_w_conjugate_symmetry(wg):
+    """(u,v,w,V) and (-u,-v,-w,conj V) are the same measurement: identical dirty images."""
+    uvw, freq, ms, wgt = make_case(33, 400, 3, 96, 96, 8e-4, 8e-4, 0.2)
+    a = wg.ms2dirty(uvw, freq, ms, wgt, 96, 96, 8e-4, 8e-4, 0, 0, 1e-10, True)
+    b = wg.ms2dirty(-uvw, freq, np.conj(ms), wgt, 96, 96, 8e-4, 8e-4, 0, 0, 1e-10, True)
+    assert rel_max(a, b) < 1e-12
+
+
+def test_linearity_and_mask(wg):
+    uvw, freq, ms, wgt = make_case(34, 500, 2, 64, 64, 1e-3, 1e-3, 0.1)
+    ms2 = np.roll(ms, 7, axis=0)
+    with wg.Plan(uvw, freq, 64, 64, 1e-3, 1e-3, 1e-10, True) as p:
+        a, b, c = p.invert(ms, wgt), p.invert(ms2, wgt), p.invert(2 * ms - 3 * ms2, wgt)
+    assert rel_max(c, 2 * a - 3 * b) < 1e-12
+    mask = (np.arange(ms.size).reshape(ms.shape) % 3 != 0).astype(np.uint8)
+    dm = wg.ms2dirty(uvw, freq, ms, wgt, 64, 64, 1e-3, 1e-3, 0, 0, 1e-10, True, mask=mask)
+    dw = wg.ms2dirty(uvw, freq, ms, wgt * mask, 64, 64, 1e-3, 1e-3, 0, 0, 1e-10, True)
+    assert rel_max(dm, dw) < 1e-13
+
+
+def test_explicit_grid_size_and_rejections(wg):
+    from oracle import dft as odft
+    uvw, freq, ms, wgt = make_case(35, 300, 1, 64, 64, 1e-3, 1e-3, 0.1)
+    d = wg.ms2dirty(uvw, freq, ms, wgt, 64, 64, 1e-3, 1e-3, 128, 128, 1e-6, True)
+    assert rel_l2(d, odft.ms2dirty(uvw, freq, ms, wgt, 64, 64, 1e-3, 1e-3, True)) < 1e-6
+    with pytest.raises(wg.WgridderError):
+        wg.ms2dirty(uvw, freq, ms, wgt, 64, 64, 1e-3, 1e-3, 66, 66, 1e-6, True)  # < 1.15 x image
+    with pytest.raises(wg.WgridderError):
+        wg.ms2dirty(uvw, freq, ms.astype(np.complex64), None, 64, 64, 1e-3, 1e-3, 0, 0, 1e-9, True)
+    bad = uvw.copy()
+    bad[3, 1] = np.nan
+    with pytest.raises(wg.WgridderError):
+        wg.ms2dirty(bad, freq, ms, wgt, 64, 64, 1e-3, 1e-3, 0, 0, 1e-6, True)
+
+
+def test_sumwt_bit_exact(wg):
+    """0/1 weights (the reference fixtures: weight 1, autocorrelations 0) sum exactly; host and
+    device pointers agree bit for bit with numpy.sum."""
+    import torch
+    rng = np.random.default_rng(5)
+    w = (rng.uniform(size=(4000, 37)) < 0.9).astype(np.float64)
+    assert wg.sumwt(w) == float(np.sum(w))
+    assert wg.sumwt(w.astype(np.float32)) == float(np.sum(w))
+    assert wg.sumwt(torch.as_tensor(w, device="cuda:0")) == float(np.sum(w))
+    w2 = w * 0.25 + 0.5 * (rng.uniform(size=w.shape) < 0.5)   # multiples of 1/4: still exact
+    assert wg.sumwt(w2) == float(np.sum(w2))
+
+
+def test_psf_peak_is_one_with_natural_weights(wg):
+    """dopsf semantics at array level: unit visibilities, natural weights -> PSF peak = sumwt."""
+    uvw, freq, _, wgt = make_case(36, 2000, 2, 128, 128, 5e-4, 5e-4, 0.1)
+    psf = wg.ms2dirty(uvw, freq, np.ones(wgt.shape, complex), wgt, 128, 128, 5e-4, 5e-4, 0, 0,
+                      1e-10, True)
+    assert abs(psf[64, 64] / wgt.sum() - 1.0) < 1e-9
+    assert psf.max() == psf[64, 64]
+
+
+@pytest.mark.parametrize("config,nchan", [("C2", 8)])
+def test_full_geometry_sampled_dft(wg, config, nchan):
+    """A slice of the benchmark workload (SKA-LOW full array, npixel=2048, fp32, eps=1e-5):
+    point sources with exact visibilities -> dirty image checked at sampled pixels, predicted
+    visibilities checked at sampled (row, channel) against the direct DFT."""
+    import torch
+    from oracle import dft as odft
+    from ska_sdp_func_python_b200 import simulate
+    obs = simulate.observation(config, nchan=nchan, ntimes=4)
+    uvw = simulate.flip_for_gridder(obs["uvw"])
+    freq, npix, cell = obs["freq"], obs["npix"], obs["cellsize"]
+    ms, model = simulate.point_source_vis(uvw, freq, npix, cell, nsrc=8)
+    wgt = np.ones(ms.shape, dtype=np.float32)
+    wgt[obs["auto"]] = 0
+    eps = 1e-5
+    with wg.Plan(uvw, freq, npix, npix, cell, cell, eps, True, precision="single") as p:
+        d = p.invert(ms.astype(np.complex64), wgt)
+        v = p.predict(model.astype(np.float32))
+    rng = np.random.default_rng(9)
+    src = np.argwhere(model > 0)
+    px = np.concatenate([src[:, 0], rng.integers(0, npix, 56), [0, npix - 1]])
+    py = np.concatenate([src[:, 1], rng.integers(0, npix, 56), [0, npix - 1]])
+    dref = odft.ms2dirty_points(uvw, freq, ms, wgt.astype(np.float64), npix, npix, cell, cell, True, px, py)
+    peak = np.abs(dref).max()
+    assert np.abs(d[px, py] - dref).max() < 10 * eps * peak
+    rows = rng.integers(0, uvw.shape[0], 300)
+    chans = rng.integers(0, nchan, 300)
+    vref = odft.dirty2ms_samples(uvw, freq, model, None, cell, cell, True, rows, chans)
+    assert np.abs(v[rows, chans] - vref).max() < 10 * eps * np.abs(vref).max()
+    assert rel_l2(v[rows, chans], ms[rows, chans]) < 10 * eps  # predict(model) == the exact vis

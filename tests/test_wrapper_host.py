@@ -1,0 +1,112 @@
+"""Host-side logic of the invert_ng / predict_ng drop-in that needs no GPU: geometry helpers
+against the stand-in SkyCoord / WCS (which the reference's own shift_vis_to_image ran on when the
+goldens were made), polarisation matrices, error behaviour (ng.py:52-56, :78, :172-173)."""
+import numpy as np
+import pytest
+
+from conftest import load_ng_case
+
+from ska_sdp_func_python_b200 import imaging, minimal_models as mm, polarisation
+
+
+def test_image_centre_and_lmn_match_standins():
+    pc = mm.SkyCoord.from_deg(180.0, -35.0)
+    ipc = mm.SkyCoord.from_deg(181.0, -34.5)
+    im = mm.create_image(48, 1.5e-3, ipc, [1e8])
+    ra, dec = imaging.image_centre_radec(im)
+    sc = mm.pixel_to_skycoord(48 // 2 + 1, 48 // 2 + 1, im.image_acc.wcs, origin=1)
+    assert abs(ra - sc.ra.rad) < 1e-15 and abs(dec - sc.dec.rad) < 1e-15
+    assert abs(imaging.separation(pc.ra.rad, pc.dec.rad, ra, dec) - pc.separation(sc).rad) < 1e-16
+    l, m, nm1 = imaging.skycoord_to_lmn(ra, dec, pc.ra.rad, pc.dec.rad)
+    dc = sc.transform_to(pc.skyoffset_frame()).represent_as(None)
+    assert np.allclose((l, m, nm1), (dc.y.value, dc.z.value, dc.x.value - 1), rtol=0, atol=1e-15)
+
+
+def test_image_centre_off_reference_pixel():
+    """crpix away from the FFT centre: SIN deprojection equals the stand-in WCS."""
+    pc = mm.SkyCoord.from_deg(10.0, -60.0)
+    im = mm.create_image(64, 1e-3, pc, [1e8])
+    im.attrs["wcs"].wcs.crpix[:2] = [20.0, 40.0]
+    ra, dec = imaging.image_centre_radec(im)
+    sc = mm.pixel_to_skycoord(33, 33, im.image_acc.wcs, origin=1)
+    assert abs(ra - sc.ra.rad) < 1e-15 and abs(dec - sc.dec.rad) < 1e-15
+    assert pc.separation(sc).rad > 1e-3
+
+
+def test_shift_vector_noop_when_centres_coincide():
+    g, vis, im = load_ng_case("ng_case_a.npz")
+    assert imaging._shift_vector(vis, im) == (None, False)
+    g, vis, im = load_ng_case("ng_case_b.npz")
+    shift, update = imaging._shift_vector(vis, im)
+    assert update and shift is not None and abs(shift[0]) > 1e-3
+
+
+@pytest.mark.parametrize("a,b", [("linear", "stokesIQUV"), ("circular", "stokesIQUV"),
+                                 ("linearnp", "stokesIQ"), ("circularnp", "stokesIV")])
+def test_pol_matrices_invert_each_other(a, b):
+    fa, fb = mm.PolarisationFrame(a), mm.PolarisationFrame(b)
+    M, Mi = polarisation.pol_matrix(fa, fb), polarisation.pol_matrix(fb, fa)
+    assert np.allclose(M @ Mi, np.eye(fa.npol), atol=1e-15)
+
+
+def test_pol_matrix_linear_convention():
+    """XX = I + Q, XY = U + iV, YX = U - iV, YY = I - Q."""
+    M = polarisation.pol_matrix(mm.PolarisationFrame("stokesIQUV"), mm.PolarisationFrame("linear"))
+    iquv = np.array([1.0, 0.2, 0.3, 0.4])
+    assert np.allclose(M @ iquv, [1.2, 0.3 + 0.4j, 0.3 - 0.4j, 0.8])
+    assert np.array_equal(polarisation.pol_matrix(mm.PolarisationFrame("stokesI"),
+                                                  mm.PolarisationFrame("stokesI")), np.eye(1))
+    with pytest.raises(ValueError):
+        polarisation.pol_matrix(mm.PolarisationFrame("linear"), mm.PolarisationFrame("stokesIV"))
+
+
+def test_vis_to_im_mapping():
+    g, vis, im = load_ng_case("ng_case_b.npz")
+    assert list(imaging._vis_to_im(im, vis.frequency.data)) == [0, 0, 1, 1]
+
+
+def test_error_behaviour_matches_reference():
+    g, vis, im = load_ng_case("ng_case_a.npz")
+    assert imaging.predict_ng(vis, None) is vis                      # ng.py:52-53
+    with pytest.raises(AssertionError):
+        imaging.invert_ng(vis, "not an image")                       # ng.py:172
+    with pytest.raises(AssertionError):
+        imaging.predict_ng(vis, object())                            # ng.py:55
+    bad = im.copy(deep=True)
+    bad.attrs["wcs"].wcs.ctype[0] = "RA---TAN"
+    with pytest.raises(AssertionError):
+        imaging.invert_ng(vis, bad)                                  # ng.py:173 is_canonical
+    with pytest.raises(ValueError):
+        imaging.invert_visibility(vis, im, context="nonsense")       # imaging.py:105
+    with pytest.raises(ValueError):
+        imaging.predict_visibility(vis, im, context="nonsense")      # imaging.py:55
+
+
+def test_npol_mismatch_asserts():
+    g, vis, im = load_ng_case("ng_case_a.npz")
+    im4 = mm.create_image(64, 1e-3, vis.phasecentre, [1e8],
+                          polarisation_frame=mm.PolarisationFrame("stokesIQUV"))
+    with pytest.raises((AssertionError, Exception)) as exc:
+        imaging.predict_ng(vis, im4)                                 # ng.py:78
+    assert exc.type is AssertionError or "CUDA" in str(exc.value)
+
+
+def test_no_cpu_fallback_in_wrapper():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("a GPU is present")
+    from ska_sdp_func_python_b200.wgridder import WgridderError
+    g, vis, im = load_ng_case("ng_case_a.npz")
+    with pytest.raises(WgridderError):
+        imaging.invert_ng(vis, im)
+    with pytest.raises(WgridderError):
+        imaging.predict_ng(vis, im)
+
+
+def test_inputs_are_not_mutated_by_standin_copy():
+    g, vis, im = load_ng_case("ng_case_a.npz")
+    c = vis.copy(deep=True, zero=True)
+    assert np.all(c["vis"].data == 0) and np.any(vis["vis"].data != 0)
+    assert np.array_equal(c["uvw"].data, vis["uvw"].data)
+    c["uvw"].data[...] = 0
+    assert np.any(vis["uvw"].data != 0)
