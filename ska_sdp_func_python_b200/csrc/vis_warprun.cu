@@ -55,8 +55,8 @@ template <typename T, int W, bool WS> struct Stage {
     static constexpr int PW = WS ? W : 1;
     static constexpr int KS = W | 1;                 // odd row stride: conflict-free STS
     static constexpr int KWS = kw_stride(PW);
-    alignas(16) P kw2[32 * KWS];                     // (kw, kw) pairs, plane p0+q at [q]
-    alignas(16) P val[32];
+    alignas(16) P kwv[32 * KWS];                     // gridding: (kw*re, kw*im) of plane p0+q at [q]
+                                                     // degridding: (kw, kw)
     alignas(16) int4 org[32];                        // iu0, iv0, p0, ru | rv<<8 | active<<16
     T ku[32 * KS];
     T kv[32 * KS];
@@ -66,11 +66,13 @@ template <typename T> struct Partials {
     typename V2<T>::type p[32 * 33];
 };
 
-// Lane-parallel preparation of one visibility (lane `lane` of the warp).
-template <typename T, int W, bool WS>
+// Lane-parallel preparation of one visibility (lane `lane` of the warp).  `val` is the
+// (weighted, conjugated if flipped) visibility for gridding; for degridding pass (1, 1) so that
+// kwv holds the duplicated w-kernel values.
+template <typename T, int W, bool WS, bool GRID>
 __device__ __forceinline__ void prepare(const VisGeo &g, const KernelTab<T, W> &tab,
                                         uint32_t idx, int lane, Stage<T, W, WS> &st,
-                                        bool &flip)
+                                        cplx<T> val, bool &flip)
 {
     using S = Stage<T, W, WS>;
     const uint32_t row = idx / g.nchan, chan = idx - row * g.nchan;
@@ -84,10 +86,14 @@ __device__ __forceinline__ void prepare(const VisGeo &g, const KernelTab<T, W> &
     kernel_values<T, W>(tab, (T)L.dv, k);
 #pragma unroll
     for (int s = 0; s < W; ++s) st.kv[lane * S::KS + s] = k[s];
+    if (GRID && flip) val.im = -val.im;
     if (WS) {
         kernel_values<T, W>(tab, (T)L.dw, k);
 #pragma unroll
-        for (int s = 0; s < W; ++s) st.kw2[lane * S::KWS + s] = mk2(k[s], k[s]);
+        for (int s = 0; s < W; ++s)
+            st.kwv[lane * S::KWS + s] = GRID ? mk2(k[s] * val.re, k[s] * val.im) : mk2(k[s], k[s]);
+    } else if (GRID) {
+        st.kwv[lane * S::KWS] = mk2(val.re, val.im);
     }
 }
 
@@ -129,14 +135,17 @@ grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ 
         rj[k] = c - ri[k] * W;
     }
     P acc[CPL][PW];
-    int coff[CPL];
+    int coff[CPL];       // grid cell (iu*nv + iv) the accumulators of class k belong to, -1 = none
+    int aoff[CPL], boff[CPL];   // position of that cell inside the current footprint
 #pragma unroll
     for (int k = 0; k < CPL; ++k) {
         coff[k] = -1;
+        aoff[k] = boff[k] = 0;
 #pragma unroll
         for (int q = 0; q < PW; ++q) acc[k][q] = mk2(T(0), T(0));
     }
     int cur_p = 0;
+    int pox = -1, poy = -1, poz = -1;   // footprint origin of the previous sample
 
     auto flush_k = [&](int k) {
         const int sbase = cur_p - plane0 + slot0;
@@ -162,50 +171,56 @@ grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ 
                 st.org[lane] = make_int4(0, 0, 0, 0);  // inactive: skipped below
             } else {
                 bool flip;
-                prepare<T, W, WS>(g, tab, idx, lane, st, flip);
-                if (flip) val.im = -val.im;
-                st.val[lane] = mk2(val.re, val.im);
+                prepare<T, W, WS, true>(g, tab, idx, lane, st, val, flip);
             }
         }
         __syncwarp();
         for (int v = 0; v < n; ++v) {
             const int4 o = st.org[v];
             if ((o.w >> 16) == 0) continue;
-            if (WS && o.z != cur_p) {
+            if (o.x != pox || o.y != poy || o.z != poz) {
+                // the footprint moved: re-derive which cell of it every class owns
+                if (WS && o.z != cur_p) {
 #pragma unroll
-                for (int k = 0; k < CPL; ++k)
-                    if (valid[k] && coff[k] >= 0) flush_k(k);
-                cur_p = o.z;
-            }
-            const int ru = o.w & 0xff, rv = (o.w >> 8) & 0xff;
-            const P val = st.val[v];
-            P kw2[PW];
-            if (WS) {
+                    for (int k = 0; k < CPL; ++k)
+                        if (valid[k] && coff[k] >= 0) {
+                            flush_k(k);
+                            coff[k] = -1;
+                        }
+                    cur_p = o.z;
+                }
+                const int ru = o.w & 0xff, rv = (o.w >> 8) & 0xff;
 #pragma unroll
-                for (int q = 0; q < PW; ++q) kw2[q] = st.kw2[v * S::KWS + q];
+                for (int k = 0; k < CPL; ++k) {
+                    if (!valid[k]) continue;
+                    int a = ri[k] - ru;
+                    a += (a < 0) ? W : 0;
+                    int b = rj[k] - rv;
+                    b += (b < 0) ? W : 0;
+                    const int cu = wrap_inc(o.x + a, g.nu), cv = wrap_inc(o.y + b, g.nv);
+                    const int off = cu * g.nv + cv;
+                    if (off != coff[k]) {
+                        if (coff[k] >= 0) flush_k(k);
+                        coff[k] = off;
+                    }
+                    aoff[k] = a;
+                    boff[k] = b;
+                }
+                pox = o.x;
+                poy = o.y;
+                poz = o.z;
             }
+            P kwv[PW];
+#pragma unroll
+            for (int q = 0; q < PW; ++q) kwv[q] = st.kwv[v * S::KWS + q];
+            const T *kur = st.ku + v * S::KS, *kvr = st.kv + v * S::KS;
 #pragma unroll
             for (int k = 0; k < CPL; ++k) {
-                if (!valid[k]) continue;
-                int a = ri[k] - ru;
-                a += (a < 0) ? W : 0;
-                int b = rj[k] - rv;
-                b += (b < 0) ? W : 0;
-                const int cu = wrap_inc(o.x + a, g.nu), cv = wrap_inc(o.y + b, g.nv);
-                const int off = cu * g.nv + cv;
-                if (off != coff[k]) {
-                    if (coff[k] >= 0) flush_k(k);
-                    coff[k] = off;
-                }
-                const T kk = st.ku[v * S::KS + a] * st.kv[v * S::KS + b];
-                const P pv = mk2(kk * val.x, kk * val.y);
-                if (WS) {
+                // classes beyond W*W accumulate into registers that are never flushed
+                const T kk = kur[aoff[k]] * kvr[boff[k]];
+                const P kk2 = mk2(kk, kk);
 #pragma unroll
-                    for (int q = 0; q < PW; ++q) acc[k][q] = fma2(pv, kw2[q], acc[k][q]);
-                } else {
-                    acc[k][0].x += pv.x;
-                    acc[k][0].y += pv.y;
-                }
+                for (int q = 0; q < PW; ++q) acc[k][q] = fma2(kk2, kwv[q], acc[k][q]);
             }
         }
         __syncwarp();
@@ -251,15 +266,17 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
         ri[k] = c / W;
         rj[k] = c - ri[k] * W;
     }
-    P gv[CPL][PW];
-    int coff[CPL];
+    P gv[CPL][PW];       // grid values of the cell of class k, planes cur_p .. cur_p+PW-1
+    int coff[CPL], aoff[CPL], boff[CPL];
 #pragma unroll
     for (int k = 0; k < CPL; ++k) {
         coff[k] = -1;
+        aoff[k] = boff[k] = 0;
 #pragma unroll
         for (int q = 0; q < PW; ++q) gv[k][q] = mk2(T(0), T(0));
     }
     int cur_p = -1;
+    int pox = -1, poy = -1, poz = -1;
 
     auto load_k = [&](int k) {
         const int sbase = cur_p - plane0 + slot0;
@@ -282,7 +299,7 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
             if (my_w == T(0)) {
                 st.org[lane] = make_int4(0, 0, 0, 0);
             } else {
-                prepare<T, W, WS>(g, tab, my_idx, lane, st, my_flip);
+                prepare<T, W, WS, false>(g, tab, my_idx, lane, st, cplx<T>{T(1), T(1)}, my_flip);
             }
         }
         __syncwarp();
@@ -290,28 +307,40 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
             const int4 o = st.org[v];
             P s = mk2(T(0), T(0));
             if ((o.w >> 16) != 0) {
-                const bool newplane = (o.z != cur_p);
-                cur_p = o.z;
-                const int ru = o.w & 0xff, rv = (o.w >> 8) & 0xff;
+                if (o.x != pox || o.y != poy || o.z != poz) {
+                    const bool newplane = (o.z != cur_p);
+                    cur_p = o.z;
+                    const int ru = o.w & 0xff, rv = (o.w >> 8) & 0xff;
+#pragma unroll
+                    for (int k = 0; k < CPL; ++k) {
+                        if (!valid[k]) continue;
+                        int a = ri[k] - ru;
+                        a += (a < 0) ? W : 0;
+                        int b = rj[k] - rv;
+                        b += (b < 0) ? W : 0;
+                        const int cu = wrap_inc(o.x + a, g.nu), cv = wrap_inc(o.y + b, g.nv);
+                        const int off = cu * g.nv + cv;
+                        if (newplane || off != coff[k]) {
+                            coff[k] = off;
+                            load_k(k);
+                        }
+                        aoff[k] = a;
+                        boff[k] = b;
+                    }
+                    pox = o.x;
+                    poy = o.y;
+                    poz = o.z;
+                }
                 P kw2[PW];
                 if (WS) {
 #pragma unroll
-                    for (int q = 0; q < PW; ++q) kw2[q] = st.kw2[v * S::KWS + q];
+                    for (int q = 0; q < PW; ++q) kw2[q] = st.kwv[v * S::KWS + q];
                 }
+                const T *kur = st.ku + v * S::KS, *kvr = st.kv + v * S::KS;
 #pragma unroll
                 for (int k = 0; k < CPL; ++k) {
-                    if (!valid[k]) continue;
-                    int a = ri[k] - ru;
-                    a += (a < 0) ? W : 0;
-                    int b = rj[k] - rv;
-                    b += (b < 0) ? W : 0;
-                    const int cu = wrap_inc(o.x + a, g.nu), cv = wrap_inc(o.y + b, g.nv);
-                    const int off = cu * g.nv + cv;
-                    if (newplane || off != coff[k]) {
-                        coff[k] = off;
-                        load_k(k);
-                    }
-                    const T kk = st.ku[v * S::KS + a] * st.kv[v * S::KS + b];
+                    // classes beyond W*W hold zeros in gv and contribute nothing
+                    const T kk = kur[aoff[k]] * kvr[boff[k]];
                     P t;
                     if (WS) {
                         t = mk2(gv[k][0].x * kw2[0].x, gv[k][0].y * kw2[0].y);
