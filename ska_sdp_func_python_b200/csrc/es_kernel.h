@@ -116,6 +116,20 @@ struct PolyKernel {
             }
             for (int d = 0; d < n; ++d) c[size_t(s) * n + d] = (double)mono[D - d];
         }
+        // The kernel is even: piece W-1-s is piece s mirrored (xi -> -xi).  Make the table
+        // exactly so, because the device evaluates mirrored pairs from one set of even / odd
+        // coefficients (device_common.cuh: KernelTab) and the correction factors below must
+        // describe the very same polynomial.
+        for (int s = 0; s <= W - 1 - s; ++s) {
+            const int m = W - 1 - s;
+            for (int d = 0; d < n; ++d) {
+                const double sign = ((D - d) & 1) ? -1.0 : 1.0;
+                const double a = c[size_t(s) * n + d], b = sign * c[size_t(m) * n + d];
+                const double mean = (s == m && sign < 0) ? 0.0 : 0.5 * (a + b);
+                c[size_t(s) * n + d] = mean;
+                c[size_t(m) * n + d] = sign * mean;
+            }
+        }
     }
 
     double eval_piece(int s, double xi) const

@@ -25,6 +25,25 @@ template <typename T> struct VisLaunch {
     cudaStream_t stream;
 };
 
+// host table [W][W+4] (highest power first, exactly mirror-symmetric: es_kernel.h) -> the
+// even / odd half-tap table the device evaluates
+template <typename T, int W> inline KernelTab<T, W> make_tab(const double *coef)
+{
+    using K = KernelTab<T, W>;
+    K t;
+    for (int h = 0; h < K::NH2; ++h) {
+        for (int k = 0; k < K::NE; ++k) {
+            const int power = 2 * (K::NE - 1 - k);
+            t.e[k][h] = h < K::NH ? (T)coef[h * (K::D + 1) + (K::D - power)] : T(0);
+        }
+        for (int k = 0; k < K::NO; ++k) {
+            const int power = 2 * (K::NO - 1 - k) + 1;
+            t.o[k][h] = h < K::NH ? (T)coef[h * (K::D + 1) + (K::D - power)] : T(0);
+        }
+    }
+    return t;
+}
+
 template <typename T> int launch_grid_simple(const VisLaunch<T> &L);
 template <typename T> int launch_degrid_simple(const VisLaunch<T> &L);
 

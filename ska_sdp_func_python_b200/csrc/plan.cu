@@ -173,7 +173,7 @@ struct b2g_plan {
         VisGeo g;
         g.uvw = d_uvw;
         g.fscale = d_fscale;
-        g.nchan = (uint32_t)nchan;
+        g.set_nchan((uint32_t)nchan);
         g.nu = (int)nu;
         g.nv = (int)nv;
         g.nplanes = nplanes;

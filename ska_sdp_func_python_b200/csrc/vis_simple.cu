@@ -20,7 +20,8 @@ grid_simple_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ s
     long long i = begin + (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= end) return;
     const uint32_t idx = sidx[i];
-    const uint32_t row = idx / g.nchan, chan = idx - row * g.nchan;
+    uint32_t row, chan;
+    g.split(idx, row, chan);
     const Located L = locate(g, W, row, chan);
     cplx<T> val = ms[idx];
     if (wgt) {
@@ -64,7 +65,8 @@ degrid_simple_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__
     long long i = begin + (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= end) return;
     const uint32_t idx = sidx[i];
-    const uint32_t row = idx / g.nchan, chan = idx - row * g.nchan;
+    uint32_t row, chan;
+    g.split(idx, row, chan);
     T wv = T(1);
     if (wgt) {
         wv = wgt[idx];
@@ -106,13 +108,6 @@ degrid_simple_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__
     out[idx] = cplx<T>{sre * wv, sim * wv};
 }
 
-template <typename T, int W> static KernelTab<T, W> make_tab(const double *coef)
-{
-    KernelTab<T, W> t;
-    for (int s = 0; s < W; ++s)
-        for (int d = 0; d < W + 4; ++d) t.c[s][d] = (T)coef[s * (W + 4) + d];
-    return t;
-}
 
 template <typename T, int W, bool WS> static int grid_simple_inst(const VisLaunch<T> &L)
 {

@@ -4,27 +4,28 @@
 // dirty2ms (call sites /root/reference/src/ska_sdp_func_python/imaging/ng.py:240-256,
 // :99-112) with a B200-first design:
 //
-//  * Visibilities arrive sorted by (p0, iu0, iv0) = the first w-plane and the first grid
-//    cell of their W x W x W footprint, so consecutive visibilities touch the same planes
-//    and overlapping cells.
-//  * One warp owns a contiguous chunk of the sorted list.  Its lanes own the W*W residue
-//    classes (i, j) of uv-cell indices modulo W (CPL = ceil(W*W/32) classes per lane).
-//    Any W x W footprint contains exactly one cell of every class, so for every
-//    visibility each lane has exactly one cell per class to update, and it keeps the W
-//    w-planes of that cell in REGISTERS.  When the footprint moves by one cell only the
-//    W lanes whose cell left the footprint flush (gridding) or reload (degridding) their
-//    registers; everything else stays put.  Dense uv regions therefore cost ~2W packed
-//    FMAs per lane and visibility and almost no memory traffic, sparse regions cost about
-//    W*W_w cell flushes per visibility instead of W*W*W_w.
-//  * Per 32 visibilities: a lane-parallel preparation phase (one visibility per lane:
-//    fp64 coordinates -> cell/plane origin + sub-cell offsets, 3*W Horner evaluations of
-//    the kernel polynomial with coefficients taken from the constant bank, staged in
-//    shared memory), then a visibility-serial accumulation phase on the register cells.
-//  * Gridding flushes with vectorised red.global.add.v2.f32 (one complex cell per
-//    lane-op, no return value, no CAS loop); degridding reduces the 32 lane partials of
-//    32 visibilities through a padded shared-memory transpose.
-//  * fp32 arithmetic uses the packed FFMA2 (fma.rn.f32x2) of sm_100: (re, im) of a cell
-//    is one 64-bit register pair.
+//  * Samples arrive sorted by (p0, iu0, iv0) = the first w-plane and the first grid cell of
+//    their W x W x W footprint, so consecutive samples touch the same planes and mostly the
+//    same cells (on the C2 benchmark 99.3 % of the samples have the origin of their
+//    predecessor).
+//  * One warp owns a contiguous run of the sorted list.  Its lanes own the W*W residue
+//    classes (i, j) of uv-cell indices modulo W: lane = (ig, j) owns column class j and the
+//    IPL row classes ig*IPL .. ig*IPL+IPL-1.  Any W x W footprint contains exactly one cell
+//    of every class, so for every sample each lane has exactly one cell per class to update,
+//    and it keeps the W w-planes of that cell in REGISTERS.  When the footprint moves only
+//    the lanes whose cell left it flush (gridding) or reload (degridding).
+//  * Per 32 samples a lane-parallel preparation phase (one sample per lane: fp64 coordinates
+//    -> origin + sub-cell offsets, the 3 W kernel values from the even/odd half-tap
+//    polynomials with packed FMAs) stages the kernel values in shared memory ROTATED by the
+//    origin's residue, so that in the sample-serial accumulation phase every lane reads its
+//    operands at lane-constant addresses: per sample and lane 4 LDS.128 + 2 LDS + IPL FMUL +
+//    IPL*W FFMA2, no index arithmetic.  "Did the footprint move" is one bit per sample in a
+//    warp-uniform mask computed during preparation.
+//  * Gridding flushes with vectorised red.global.add.v2.f32 (one complex cell per lane-op);
+//    degridding reduces the 32 lane partials of 16 samples at a time through a padded
+//    shared-memory transpose.
+//  * fp32 arithmetic uses the packed FFMA2 (fma.rn.f32x2) of sm_100: (re, im) of a cell is
+//    one 64-bit register pair.
 #include "kernels.h"
 
 namespace b2g {
@@ -32,69 +33,148 @@ namespace b2g {
 namespace {
 
 constexpr int kWarps = 4;        // warps per block
-constexpr int kChunk = 256;      // visibilities per warp (multiple of 32)
+constexpr int kChunk = 256;      // samples per warp (multiple of 32)
+constexpr unsigned kFull = 0xffffffffu;
 
-template <typename T> struct V2;
-template <> struct V2<float> { using type = float2; };
-template <> struct V2<double> { using type = double2; };
+template <typename T> struct Vec16;
+template <> struct Vec16<float> { using type = float4; };
+template <> struct Vec16<double> { using type = double2; };
 
-__device__ __forceinline__ float2 fma2(float2 a, float2 b, float2 c) { return __ffma2_rn(a, b, c); }
-__device__ __forceinline__ double2 fma2(double2 a, double2 b, double2 c)
-{
-    return make_double2(fma(a.x, b.x, c.x), fma(a.y, b.y, c.y));
-}
-__device__ __forceinline__ float2 mk2(float a, float b) { return make_float2(a, b); }
-__device__ __forceinline__ double2 mk2(double a, double b) { return make_double2(a, b); }
-
-// row stride of the duplicated w-kernel table, in (k,k) pairs: even (16-byte rows for
-// float) and == 2 mod 4 (spreads the lane-parallel stores over the banks)
-constexpr int kw_stride(int pw) { return ((pw + 1) / 4) * 4 + 2; }
-
-template <typename T, int W, bool WS> struct Stage {
-    using P = typename V2<T>::type;
+template <typename T, int W, bool WS, bool GRID> struct Cfg {
     static constexpr int PW = WS ? W : 1;
-    static constexpr int KS = W | 1;                 // odd row stride: conflict-free STS
-    static constexpr int KWS = kw_stride(PW);
-    alignas(16) P kwv[32 * KWS];                     // gridding: (kw*re, kw*im) of plane p0+q at [q]
-                                                     // degridding: (kw, kw)
-    alignas(16) int4 org[32];                        // iu0, iv0, p0, ru | rv<<8 | active<<16
-    T ku[32 * KS];
-    T kv[32 * KS];
+    static constexpr int JL = W <= 5 ? W : (W <= 8 ? 8 : 16);   // lanes along v (column classes)
+    static constexpr int IG = 32 / JL;                          // complete lane groups along u
+    static constexpr int NG = 31 / JL + 1;                      // incl. a partial last group
+    static constexpr int IPL = (W + IG - 1) / IG;               // row classes per lane
+    static constexpr int KU_N = NG * IPL;                       // ku entries a row must hold
+    static constexpr bool KU_VEC = IPL == 2;                    // read as one (T, T) vector
+    static constexpr int KUS = KU_VEC ? KU_N + 2 : (KU_N | 1);  // row strides, in T
+    static constexpr int KVS = (JL + 1) | 1;
+    // w-kernel row: gridding (kw*re, kw*im) per plane, degridding kw per plane
+    static constexpr int KW_T = GRID ? 2 * PW : PW;
+    static constexpr int KW_V = 16 / (int)sizeof(T);            // T per 16-byte vector
+    static constexpr int KW_N16 = (KW_T + KW_V - 1) / KW_V;     // vectors read per row
+    static constexpr int KW_S16 = KW_N16 | 1;                   // odd stride: conflict-free STS.128
+};
+
+template <typename T, int W, bool WS, bool GRID> struct Stage {
+    using C = Cfg<T, W, WS, GRID>;
+    alignas(16) T kw[32 * C::KW_S16 * C::KW_V];
+    alignas(16) int4 org[32];     // iu0, iv0, p0, ru | rv << 8   (read when the footprint moved)
+    alignas(16) T ku[32 * C::KUS];  // ku[(s + ru) mod W] = kernel value of footprint row s
+    T kv[32 * C::KVS];
 };
 
 template <typename T> struct Partials {
-    typename V2<T>::type p[32 * 33];
+    typename V2<T>::type p[16 * 33];
 };
 
-// Lane-parallel preparation of one visibility (lane `lane` of the warp).  `val` is the
-// (weighted, conjugated if flipped) visibility for gridding; for degridding pass (1, 1) so that
-// kwv holds the duplicated w-kernel values.
+// Lane-parallel preparation of one sample (lane `lane` of the warp).  `val` is the (weighted)
+// visibility for gridding.  Returns the packed origin (iu0 << 16 | iv0, p0).
 template <typename T, int W, bool WS, bool GRID>
-__device__ __forceinline__ void prepare(const VisGeo &g, const KernelTab<T, W> &tab,
-                                        uint32_t idx, int lane, Stage<T, W, WS> &st,
-                                        cplx<T> val, bool &flip)
+__device__ __forceinline__ void prepare(const VisGeo &g, const KernelTab<T, W> &tab, uint32_t idx,
+                                        int lane, Stage<T, W, WS, GRID> &st, cplx<T> val,
+                                        bool &flip, int &oxy, int &oz)
 {
-    using S = Stage<T, W, WS>;
-    const uint32_t row = idx / g.nchan, chan = idx - row * g.nchan;
+    using C = Cfg<T, W, WS, GRID>;
+    uint32_t row, chan;
+    g.split(idx, row, chan);
     const Located L = locate(g, W, row, chan);
     flip = L.flip;
-    st.org[lane] = make_int4(L.iu0, L.iv0, L.p0, (L.iu0 % W) | ((L.iv0 % W) << 8) | (1 << 16));
+    oxy = (L.iu0 << 16) | L.iv0;
+    oz = L.p0;
+    const int ru = L.iu0 % W, rv = L.iv0 % W;
+    st.org[lane] = make_int4(L.iu0, L.iv0, L.p0, ru | (rv << 8));
     T k[W];
     kernel_values<T, W>(tab, (T)L.du, k);
 #pragma unroll
-    for (int s = 0; s < W; ++s) st.ku[lane * S::KS + s] = k[s];
+    for (int s = 0; s < W; ++s) {
+        int pos = s + ru;
+        pos -= pos >= W ? W : 0;
+        st.ku[lane * C::KUS + pos] = k[s];
+    }
     kernel_values<T, W>(tab, (T)L.dv, k);
 #pragma unroll
-    for (int s = 0; s < W; ++s) st.kv[lane * S::KS + s] = k[s];
-    if (GRID && flip) val.im = -val.im;
-    if (WS) {
-        kernel_values<T, W>(tab, (T)L.dw, k);
-#pragma unroll
-        for (int s = 0; s < W; ++s)
-            st.kwv[lane * S::KWS + s] = GRID ? mk2(k[s] * val.re, k[s] * val.im) : mk2(k[s], k[s]);
-    } else if (GRID) {
-        st.kwv[lane * S::KWS] = mk2(val.re, val.im);
+    for (int s = 0; s < W; ++s) {
+        int pos = s + rv;
+        pos -= pos >= W ? W : 0;
+        st.kv[lane * C::KVS + pos] = k[s];
     }
+    if (GRID && flip) val.im = -val.im;
+    if (WS || GRID) {
+        T row_[C::KW_N16 * C::KW_V];
+#pragma unroll
+        for (int i = 0; i < C::KW_N16 * C::KW_V; ++i) row_[i] = T(0);
+        if (WS) {
+            kernel_values<T, W>(tab, (T)L.dw, k);
+#pragma unroll
+            for (int s = 0; s < W; ++s) {
+                if (GRID) {
+                    row_[2 * s] = k[s] * val.re;
+                    row_[2 * s + 1] = k[s] * val.im;
+                } else {
+                    row_[s] = k[s];
+                }
+            }
+        } else {
+            row_[0] = val.re;
+            row_[1] = val.im;
+        }
+        using V = typename Vec16<T>::type;
+        V *dst = reinterpret_cast<V *>(st.kw) + lane * C::KW_S16;
+#pragma unroll
+        for (int n = 0; n < C::KW_N16; ++n) dst[n] = *reinterpret_cast<const V *>(row_ + n * C::KW_V);
+    }
+}
+
+// the w-kernel row of sample v, as C::KW_T values of T
+template <typename T, int W, bool WS, bool GRID>
+__device__ __forceinline__ void load_kw(const Stage<T, W, WS, GRID> &st, int v,
+                                        T (&out)[Cfg<T, W, WS, GRID>::KW_N16 * Cfg<T, W, WS, GRID>::KW_V])
+{
+    using C = Cfg<T, W, WS, GRID>;
+    using V = typename Vec16<T>::type;
+    const V *src = reinterpret_cast<const V *>(st.kw) + v * C::KW_S16;
+#pragma unroll
+    for (int n = 0; n < C::KW_N16; ++n) *reinterpret_cast<V *>(out + n * C::KW_V) = src[n];
+}
+
+// ku values of this lane's IPL row classes (lane-constant offset i0) and its kv value
+template <typename T, int W, bool WS, bool GRID>
+__device__ __forceinline__ void load_kuv(const Stage<T, W, WS, GRID> &st, int v, int i0, int j,
+                                         T (&ku)[Cfg<T, W, WS, GRID>::IPL], T &kv)
+{
+    using C = Cfg<T, W, WS, GRID>;
+    using P = typename V2<T>::type;
+    if (C::KU_VEC) {
+        const P t = *reinterpret_cast<const P *>(st.ku + v * C::KUS + i0);
+        ku[0] = t.x;
+        ku[C::IPL - 1] = t.y;
+    } else {
+#pragma unroll
+        for (int k = 0; k < C::IPL; ++k) ku[k] = st.ku[v * C::KUS + i0 + k];
+    }
+    kv = st.kv[v * C::KVS + j];
+}
+
+// previous active sample's origin for every lane -> "moved" flags; updates the carry
+__device__ __forceinline__ unsigned moved_mask(bool active, int oxy, int oz, int lane, unsigned act,
+                                               int &carry_xy, int &carry_z)
+{
+    const unsigned below = act & ((1u << lane) - 1u);
+    const int src = below ? 31 - __clz(below) : 0;
+    int pxy = __shfl_sync(kFull, oxy, src), pz = __shfl_sync(kFull, oz, src);
+    if (!below) {
+        pxy = carry_xy;
+        pz = carry_z;
+    }
+    const unsigned mov = __ballot_sync(kFull, active && (oxy != pxy || oz != pz));
+    if (act) {
+        const int last = 31 - __clz(act);
+        carry_xy = __shfl_sync(kFull, oxy, last);
+        carry_z = __shfl_sync(kFull, oz, last);
+    }
+    return mov;
 }
 
 }  // namespace
@@ -109,10 +189,10 @@ grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ 
                     const cplx<T> *__restrict__ ms, const T *__restrict__ wgt,
                     cplx<T> *__restrict__ ring)
 {
-    using S = Stage<T, W, WS>;
+    using C = Cfg<T, W, WS, true>;
+    using S = Stage<T, W, WS, true>;
     using P = typename V2<T>::type;
-    constexpr int PW = S::PW;
-    constexpr int CPL = (W * W + 31) / 32;
+    constexpr int PW = C::PW, IPL = C::IPL;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     S *stage_all = reinterpret_cast<S *>(smem_raw);
 
@@ -123,29 +203,20 @@ grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ 
     if (cbeg >= end) return;
     const long long cend = (cbeg + kChunk < end) ? cbeg + kChunk : end;
 
-    // residue classes owned by this lane: c = lane + 32k -> (i, j) = (c / W, c % W)
-    int ri[CPL], rj[CPL];
-    bool valid[CPL];
+    const int j = lane % C::JL, i0 = (lane / C::JL) * IPL;
+    bool valid[IPL];
 #pragma unroll
-    for (int k = 0; k < CPL; ++k) {
-        int c = lane + 32 * k;
-        valid[k] = c < W * W;
-        if (!valid[k]) c = 0;
-        ri[k] = c / W;
-        rj[k] = c - ri[k] * W;
-    }
-    P acc[CPL][PW];
-    int coff[CPL];       // grid cell (iu*nv + iv) the accumulators of class k belong to, -1 = none
-    int aoff[CPL], boff[CPL];   // position of that cell inside the current footprint
+    for (int k = 0; k < IPL; ++k) valid[k] = j < W && i0 + k < W;
+    P acc[IPL][PW];
+    int coff[IPL];       // grid cell (iu*nv + iv) the accumulators of class k belong to, -1 = none
 #pragma unroll
-    for (int k = 0; k < CPL; ++k) {
+    for (int k = 0; k < IPL; ++k) {
         coff[k] = -1;
-        aoff[k] = boff[k] = 0;
 #pragma unroll
         for (int q = 0; q < PW; ++q) acc[k][q] = mk2(T(0), T(0));
     }
     int cur_p = 0;
-    int pox = -1, poy = -1, poz = -1;   // footprint origin of the previous sample
+    int carry_xy = -1, carry_z = -1;
 
     auto flush_k = [&](int k) {
         const int sbase = cur_p - plane0 + slot0;
@@ -157,76 +228,101 @@ grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ 
         }
     };
 
+    // software pipeline: the next batch's index / sample / weight are in flight while the
+    // current batch is accumulated
+    uint32_t nidx = 0;
+    cplx<T> nval{T(0), T(0)};
+    if (cbeg + lane < cend) {
+        nidx = sidx[cbeg + lane];
+        nval = ms[nidx];
+        if (wgt) {
+            const T w = wgt[nidx];
+            nval.re *= w;
+            nval.im *= w;
+        }
+    }
+
     for (long long b0 = cbeg; b0 < cend; b0 += 32) {
         const int n = (int)((cend - b0 < 32) ? cend - b0 : 32);
-        if (lane < n) {
-            const uint32_t idx = sidx[b0 + lane];
-            cplx<T> val = ms[idx];
+        const uint32_t idx = nidx;
+        const cplx<T> val = nval;
+        if (b0 + 32 + lane < cend) {
+            nidx = sidx[b0 + 32 + lane];
+            nval = ms[nidx];
             if (wgt) {
-                const T w = wgt[idx];
-                val.re *= w;
-                val.im *= w;
-            }
-            if (val.re == T(0) && val.im == T(0)) {
-                st.org[lane] = make_int4(0, 0, 0, 0);  // inactive: skipped below
-            } else {
-                bool flip;
-                prepare<T, W, WS, true>(g, tab, idx, lane, st, val, flip);
+                const T w = wgt[nidx];
+                nval.re *= w;
+                nval.im *= w;
             }
         }
+        const bool active = lane < n && (val.re != T(0) || val.im != T(0));
+        int oxy = 0, oz = 0;
+        if (active) {
+            bool flip;
+            prepare<T, W, WS, true>(g, tab, idx, lane, st, val, flip, oxy, oz);
+        }
+        const unsigned act = __ballot_sync(kFull, active);
+        const unsigned mov = moved_mask(active, oxy, oz, lane, act, carry_xy, carry_z);
         __syncwarp();
-        for (int v = 0; v < n; ++v) {
-            const int4 o = st.org[v];
-            if ((o.w >> 16) == 0) continue;
-            if (o.x != pox || o.y != poy || o.z != poz) {
+        // samples that need more than the plain accumulation: footprint moved, or inactive
+        const unsigned stop = (mov | ~act) & (n == 32 ? kFull : ((1u << n) - 1u));
+        int v = 0;
+        while (v < n) {
+            if ((stop >> v) & 1u) {
+                if (!((act >> v) & 1u)) {
+                    ++v;
+                    continue;
+                }
                 // the footprint moved: re-derive which cell of it every class owns
+                const int4 o = st.org[v];
                 if (WS && o.z != cur_p) {
 #pragma unroll
-                    for (int k = 0; k < CPL; ++k)
+                    for (int k = 0; k < IPL; ++k)
                         if (valid[k] && coff[k] >= 0) {
                             flush_k(k);
                             coff[k] = -1;
                         }
                     cur_p = o.z;
                 }
-                const int ru = o.w & 0xff, rv = (o.w >> 8) & 0xff;
+                const int ru = o.w & 0xff, rv = o.w >> 8;
+                int b = j - rv;
+                b += (b < 0) ? W : 0;
+                const int cv = wrap_inc(o.y + b, g.nv);
 #pragma unroll
-                for (int k = 0; k < CPL; ++k) {
+                for (int k = 0; k < IPL; ++k) {
                     if (!valid[k]) continue;
-                    int a = ri[k] - ru;
+                    int a = i0 + k - ru;
                     a += (a < 0) ? W : 0;
-                    int b = rj[k] - rv;
-                    b += (b < 0) ? W : 0;
-                    const int cu = wrap_inc(o.x + a, g.nu), cv = wrap_inc(o.y + b, g.nv);
-                    const int off = cu * g.nv + cv;
+                    const int off = wrap_inc(o.x + a, g.nu) * g.nv + cv;
                     if (off != coff[k]) {
                         if (coff[k] >= 0) flush_k(k);
                         coff[k] = off;
                     }
-                    aoff[k] = a;
-                    boff[k] = b;
                 }
-                pox = o.x;
-                poy = o.y;
-                poz = o.z;
             }
-            P kwv[PW];
+            // this sample and the run of plain samples behind it
+            const unsigned rest = v < 31 ? stop >> (v + 1) : 0u;
+            const int vend = rest ? v + __ffs(rest) : n;
+#pragma unroll 4
+            for (; v < vend; ++v) {
+                T kwr[C::KW_N16 * C::KW_V], kur[IPL], kvr;
+                load_kw<T, W, WS, true>(st, v, kwr);
+                load_kuv<T, W, WS, true>(st, v, i0, j, kur, kvr);
 #pragma unroll
-            for (int q = 0; q < PW; ++q) kwv[q] = st.kwv[v * S::KWS + q];
-            const T *kur = st.ku + v * S::KS, *kvr = st.kv + v * S::KS;
+                for (int k = 0; k < IPL; ++k) {
+                    // classes outside the footprint accumulate into registers never flushed
+                    const T kk = kur[k] * kvr;
+                    const P kk2 = mk2(kk, kk);
 #pragma unroll
-            for (int k = 0; k < CPL; ++k) {
-                // classes beyond W*W accumulate into registers that are never flushed
-                const T kk = kur[aoff[k]] * kvr[boff[k]];
-                const P kk2 = mk2(kk, kk);
-#pragma unroll
-                for (int q = 0; q < PW; ++q) acc[k][q] = fma2(kk2, kwv[q], acc[k][q]);
+                    for (int q = 0; q < PW; ++q)
+                        acc[k][q] = fma2(kk2, mk2(kwr[2 * q], kwr[2 * q + 1]), acc[k][q]);
+                }
             }
         }
         __syncwarp();
     }
 #pragma unroll
-    for (int k = 0; k < CPL; ++k)
+    for (int k = 0; k < IPL; ++k)
         if (valid[k] && coff[k] >= 0) flush_k(k);
 }
 
@@ -240,10 +336,10 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
                       const T *__restrict__ wgt, cplx<T> *__restrict__ out,
                       const cplx<T> *__restrict__ ring)
 {
-    using S = Stage<T, W, WS>;
+    using C = Cfg<T, W, WS, false>;
+    using S = Stage<T, W, WS, false>;
     using P = typename V2<T>::type;
-    constexpr int PW = S::PW;
-    constexpr int CPL = (W * W + 31) / 32;
+    constexpr int PW = C::PW, IPL = C::IPL;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     S *stage_all = reinterpret_cast<S *>(smem_raw);
     Partials<T> *part_all = reinterpret_cast<Partials<T> *>(smem_raw + kWarps * sizeof(S));
@@ -256,27 +352,27 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
     if (cbeg >= end) return;
     const long long cend = (cbeg + kChunk < end) ? cbeg + kChunk : end;
 
-    int ri[CPL], rj[CPL];
-    bool valid[CPL];
+    // rows / columns of ku, kv that no sample writes must read as zero: the classes outside
+    // the footprint multiply them with their (zero) grid registers
+    for (int i = lane; i < 32 * C::KUS; i += 32) st.ku[i] = T(0);
+    for (int i = lane; i < 32 * C::KVS; i += 32) st.kv[i] = T(0);
+    for (int i = lane; i < 16 * 33; i += 32) part[i] = mk2(T(0), T(0));
+    __syncwarp();
+
+    const int j = lane % C::JL, i0 = (lane / C::JL) * IPL;
+    bool valid[IPL];
 #pragma unroll
-    for (int k = 0; k < CPL; ++k) {
-        int c = lane + 32 * k;
-        valid[k] = c < W * W;
-        if (!valid[k]) c = 0;
-        ri[k] = c / W;
-        rj[k] = c - ri[k] * W;
-    }
-    P gv[CPL][PW];       // grid values of the cell of class k, planes cur_p .. cur_p+PW-1
-    int coff[CPL], aoff[CPL], boff[CPL];
+    for (int k = 0; k < IPL; ++k) valid[k] = j < W && i0 + k < W;
+    P gv[IPL][PW];       // grid values of the cell of class k, planes cur_p .. cur_p+PW-1
+    int coff[IPL];
 #pragma unroll
-    for (int k = 0; k < CPL; ++k) {
+    for (int k = 0; k < IPL; ++k) {
         coff[k] = -1;
-        aoff[k] = boff[k] = 0;
 #pragma unroll
         for (int q = 0; q < PW; ++q) gv[k][q] = mk2(T(0), T(0));
     }
     int cur_p = -1;
-    int pox = -1, poy = -1, poz = -1;
+    int carry_xy = -1, carry_z = -1;
 
     auto load_k = [&](int k) {
         const int sbase = cur_p - plane0 + slot0;
@@ -288,83 +384,101 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
         }
     };
 
+    uint32_t nidx = 0;
+    T nw = T(1);
+    if (cbeg + lane < cend) {
+        nidx = sidx[cbeg + lane];
+        if (wgt) nw = wgt[nidx];
+    }
+
     for (long long b0 = cbeg; b0 < cend; b0 += 32) {
         const int n = (int)((cend - b0 < 32) ? cend - b0 : 32);
-        uint32_t my_idx = 0;
-        T my_w = T(1);
-        bool my_flip = false;
-        if (lane < n) {
-            my_idx = sidx[b0 + lane];
-            if (wgt) my_w = wgt[my_idx];
-            if (my_w == T(0)) {
-                st.org[lane] = make_int4(0, 0, 0, 0);
-            } else {
-                prepare<T, W, WS, false>(g, tab, my_idx, lane, st, cplx<T>{T(1), T(1)}, my_flip);
-            }
+        const uint32_t my_idx = nidx;
+        const T my_w = nw;
+        if (b0 + 32 + lane < cend) {
+            nidx = sidx[b0 + 32 + lane];
+            if (wgt) nw = wgt[nidx];
         }
+        const bool active = lane < n && my_w != T(0);
+        bool my_flip = false;
+        int oxy = 0, oz = 0;
+        if (active)
+            prepare<T, W, WS, false>(g, tab, my_idx, lane, st, cplx<T>{T(1), T(1)}, my_flip, oxy, oz);
+        const unsigned act = __ballot_sync(kFull, active);
+        const unsigned mov = moved_mask(active, oxy, oz, lane, act, carry_xy, carry_z);
         __syncwarp();
-        for (int v = 0; v < n; ++v) {
-            const int4 o = st.org[v];
-            P s = mk2(T(0), T(0));
-            if ((o.w >> 16) != 0) {
-                if (o.x != pox || o.y != poy || o.z != poz) {
+        P res = mk2(T(0), T(0));
+        const unsigned stop = (mov | ~act) & (n == 32 ? kFull : ((1u << n) - 1u));
+        for (int h0 = 0; h0 < n; h0 += 16) {
+            const int hn = n < h0 + 16 ? n : h0 + 16;
+            int v = h0;
+            while (v < hn) {
+                if ((stop >> v) & 1u) {
+                    if (!((act >> v) & 1u)) {
+                        part[(v & 15) * 33 + lane] = mk2(T(0), T(0));
+                        ++v;
+                        continue;
+                    }
+                    // the footprint moved: reload the cells that entered it
+                    const int4 o = st.org[v];
                     const bool newplane = (o.z != cur_p);
                     cur_p = o.z;
-                    const int ru = o.w & 0xff, rv = (o.w >> 8) & 0xff;
+                    const int ru = o.w & 0xff, rv = o.w >> 8;
+                    int b = j - rv;
+                    b += (b < 0) ? W : 0;
+                    const int cv = wrap_inc(o.y + b, g.nv);
 #pragma unroll
-                    for (int k = 0; k < CPL; ++k) {
+                    for (int k = 0; k < IPL; ++k) {
                         if (!valid[k]) continue;
-                        int a = ri[k] - ru;
+                        int a = i0 + k - ru;
                         a += (a < 0) ? W : 0;
-                        int b = rj[k] - rv;
-                        b += (b < 0) ? W : 0;
-                        const int cu = wrap_inc(o.x + a, g.nu), cv = wrap_inc(o.y + b, g.nv);
-                        const int off = cu * g.nv + cv;
+                        const int off = wrap_inc(o.x + a, g.nu) * g.nv + cv;
                         if (newplane || off != coff[k]) {
                             coff[k] = off;
                             load_k(k);
                         }
-                        aoff[k] = a;
-                        boff[k] = b;
                     }
-                    pox = o.x;
-                    poy = o.y;
-                    poz = o.z;
                 }
-                P kw2[PW];
-                if (WS) {
+                const unsigned rest = v < 31 ? stop >> (v + 1) : 0u;
+                int vend = rest ? v + __ffs(rest) : hn;
+                vend = vend < hn ? vend : hn;
+#pragma unroll 4
+                for (; v < vend; ++v) {
+                    T kwr[C::KW_N16 * C::KW_V], kur[IPL], kvr;
+                    if (WS) load_kw<T, W, WS, false>(st, v, kwr);
+                    load_kuv<T, W, WS, false>(st, v, i0, j, kur, kvr);
+                    P s = mk2(T(0), T(0));
 #pragma unroll
-                    for (int q = 0; q < PW; ++q) kw2[q] = st.kwv[v * S::KWS + q];
-                }
-                const T *kur = st.ku + v * S::KS, *kvr = st.kv + v * S::KS;
+                    for (int k = 0; k < IPL; ++k) {
+                        // classes outside the footprint hold zeros in gv and contribute nothing
+                        const T kk = kur[k] * kvr;
+                        P t;
+                        if (WS) {
+                            t = mul2(gv[k][0], mk2(kwr[0], kwr[0]));
 #pragma unroll
-                for (int k = 0; k < CPL; ++k) {
-                    // classes beyond W*W hold zeros in gv and contribute nothing
-                    const T kk = kur[aoff[k]] * kvr[boff[k]];
-                    P t;
-                    if (WS) {
-                        t = mk2(gv[k][0].x * kw2[0].x, gv[k][0].y * kw2[0].y);
-#pragma unroll
-                        for (int q = 1; q < PW; ++q) t = fma2(gv[k][q], kw2[q], t);
-                    } else {
-                        t = gv[k][0];
+                            for (int q = 1; q < PW; ++q) t = fma2(gv[k][q], mk2(kwr[q], kwr[q]), t);
+                        } else {
+                            t = gv[k][0];
+                        }
+                        s = fma2(mk2(kk, kk), t, s);
                     }
-                    s = fma2(mk2(kk, kk), t, s);
+                    part[(v & 15) * 33 + lane] = s;
                 }
             }
-            part[v * 33 + lane] = s;
+            // the 32 lane partials of (up to) 16 samples: lane = (sample r, half h)
+            __syncwarp();
+            const P *src = part + (lane & 15) * 33 + (lane >> 4) * 16;
+            P t = src[0];
+#pragma unroll
+            for (int i = 1; i < 16; ++i) t = add2(t, src[i]);
+            t.x += __shfl_xor_sync(kFull, t.x, 16);
+            t.y += __shfl_xor_sync(kFull, t.y, 16);
+            if ((lane >> 4) == (h0 >> 4)) res = t;
+            __syncwarp();
         }
-        __syncwarp();
         if (lane < n) {
-            T sre = T(0), sim = T(0);
-#pragma unroll 8
-            for (int l = 0; l < 32; ++l) {
-                const P c = part[lane * 33 + l];
-                sre += c.x;
-                sim += c.y;
-            }
-            if (my_flip) sim = -sim;
-            out[my_idx] = cplx<T>{sre * my_w, sim * my_w};
+            if (my_flip) res.y = -res.y;
+            out[my_idx] = cplx<T>{res.x * my_w, res.y * my_w};
         }
         __syncwarp();
     }
@@ -373,14 +487,6 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
 // ------------------------------------------------------------------------------------
 // Launchers
 // ------------------------------------------------------------------------------------
-template <typename T, int W> static KernelTab<T, W> make_tab(const double *coef)
-{
-    KernelTab<T, W> t;
-    for (int s = 0; s < W; ++s)
-        for (int d = 0; d < W + 4; ++d) t.c[s][d] = (T)coef[s * (W + 4) + d];
-    return t;
-}
-
 static unsigned nblocks_for(long long n)
 {
     const long long per_block = (long long)kWarps * kChunk;
@@ -391,7 +497,7 @@ template <typename T, int W, bool WS> static int grid_inst(const VisLaunch<T> &L
 {
     const long long n = L.end - L.begin;
     if (n <= 0) return 0;
-    const size_t smem = kWarps * sizeof(Stage<T, W, WS>);
+    const size_t smem = kWarps * sizeof(Stage<T, W, WS, true>);
     cudaError_t e = cudaFuncSetAttribute(grid_warprun_kernel<T, W, WS>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
@@ -404,7 +510,7 @@ template <typename T, int W, bool WS> static int degrid_inst(const VisLaunch<T> 
 {
     const long long n = L.end - L.begin;
     if (n <= 0) return 0;
-    const size_t smem = kWarps * (sizeof(Stage<T, W, WS>) + sizeof(Partials<T>));
+    const size_t smem = kWarps * (sizeof(Stage<T, W, WS, false>) + sizeof(Partials<T>));
     cudaError_t e = cudaFuncSetAttribute(degrid_warprun_kernel<T, W, WS>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
