@@ -124,6 +124,12 @@ int b2g_dirty2ms(int64_t nrow, int64_t nchan, const double *uvw, const double *f
  * Mirrors numpy.sum(wgt) at ng.py:258, :289. */
 int b2g_sumwt(const void *wgt, int dtype, int space, int64_t n, double *out, void *stream);
 
+/* Plans created from HOST uvw stream the visibility arrays of b2g_plan_invert /
+ * b2g_plan_predict over PCIe in row chunks of about `nsamples` samples, overlapped with
+ * gridding / degridding (what a caller of ducc0.wgridder with host arrays gets, ng.py:240-256).
+ * Default 2^24; 0 disables chunking.  Process-wide setting, applies to plans created later. */
+int b2g_set_host_chunk_samples(int64_t nsamples);
+
 /* Host-side kernel mathematics, exported so that tests can check them without a GPU.
  * b2g_kernel_select: choose (W, sigma) for epsilon; returns 0 and fills
  *   out = {W, sigma, beta, e0, eps_kernel}.

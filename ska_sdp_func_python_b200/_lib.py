@@ -18,7 +18,7 @@ EXPORTS = (
     "b2g_last_error", "b2g_version", "b2g_plan_create", "b2g_plan_destroy",
     "b2g_plan_invert", "b2g_plan_predict", "b2g_plan_info", "b2g_plan_timings",
     "b2g_ms2dirty", "b2g_dirty2ms", "b2g_sumwt", "b2g_kernel_select", "b2g_kernel_eval",
-    "b2g_kernel_corr", "b2g_vis_prepare", "b2g_vis_finish",
+    "b2g_kernel_corr", "b2g_vis_prepare", "b2g_vis_finish", "b2g_set_host_chunk_samples",
 )
 FLAG_NONE, FLAG_U8, FLAG_I32, FLAG_I64, FLAG_F64 = 0, 1, 2, 3, 4
 
@@ -66,6 +66,8 @@ def lib():
                                i64, dbl, ci, ci, vp, vp]
     L.b2g_sumwt.restype = ci
     L.b2g_sumwt.argtypes = [vp, ci, ci, i64, pd, vp]
+    L.b2g_set_host_chunk_samples.restype = ci
+    L.b2g_set_host_chunk_samples.argtypes = [i64]
     L.b2g_kernel_select.restype = ci
     L.b2g_kernel_select.argtypes = [dbl, ci, ci, i64, i64, dbl, pd]
     L.b2g_kernel_eval.restype = ci

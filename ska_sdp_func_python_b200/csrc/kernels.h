@@ -51,9 +51,11 @@ template <typename T> bool warprun_supported(int W, bool wstack);
 template <typename T> int launch_grid_warprun(const VisLaunch<T> &L);
 template <typename T> int launch_degrid_warprun(const VisLaunch<T> &L);
 
-// Sort keys: key = (p0*nu + iu0)*nv + iv0; also a histogram of p0 (plane_counts[nplanes]).
-int launch_keygen(const VisGeo &geo, int W, long long nvis, uint64_t *keys, uint32_t *idx,
-                  unsigned long long *plane_counts, cudaStream_t stream);
+// Sort keys: key = ((chunk*nplanes + p0)*nu + iu0)*nv + iv0, chunk = row / rows_per_chunk (0 if
+// rows_per_chunk == 0); also a histogram of p0 (plane_counts[nplanes]).
+int launch_keygen(const VisGeo &geo, int W, long long nvis, uint32_t rows_per_chunk,
+                  uint64_t *keys, uint32_t *idx, unsigned long long *plane_counts,
+                  cudaStream_t stream);
 
 // Radix sort of (key, idx) pairs on the lowest key_bits bits; result in keys_out/idx_out.
 // Returns 0 or a cudaError_t.

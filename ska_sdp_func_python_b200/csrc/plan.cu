@@ -10,6 +10,7 @@
 #include <cufft.h>
 
 #include <algorithm>
+#include <atomic>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -28,6 +29,11 @@ namespace {
 constexpr double kSpeedOfLight = 299792458.0;
 
 thread_local std::string g_err;
+
+// Plans built from HOST uvw stream the visibilities of invert / predict over PCIe in row chunks
+// of about this many samples, overlapped with gridding / degridding (0 disables chunking).
+std::atomic<long long> g_host_chunk_samples{1ll << 24};
+constexpr int kMaxChunks = 32;
 
 int fail(const char *fmt, ...)
 {
@@ -155,6 +161,13 @@ struct b2g_plan {
     int ncheb = 0;
     uint32_t *d_sidx = nullptr;
     std::vector<long long> slab_begin;
+    // host-streaming plans (nslabs == 1): sorted by (row chunk, p0, iu0, iv0); chunk c holds
+    // rows [c*rows_per_chunk, (c+1)*rows_per_chunk)
+    int nchunks = 1;
+    long long rows_per_chunk = 0;
+    cudaStream_t copy_stream = nullptr;
+    std::vector<cudaEvent_t> chunk_ev;
+    cudaEvent_t ev_a = nullptr, ev_b = nullptr;
     void *d_ring = nullptr;
     size_t plane_bytes = 0;
     void *d_acc = nullptr;
@@ -208,17 +221,25 @@ struct b2g_plan {
     }
     void release()
     {
-        if (own_uvw && d_uvw) cudaFree(d_uvw);
-        if (d_fscale) cudaFree(d_fscale);
-        if (d_cu) cudaFree(d_cu);
-        if (d_cv) cudaFree(d_cv);
-        if (d_cheb) cudaFree(d_cheb);
-        if (d_sidx) cudaFree(d_sidx);
-        if (d_ring) cudaFree(d_ring);
-        if (d_acc) cudaFree(d_acc);
-        if (d_scratch) cudaFree(d_scratch);
-        if (d_fftwork) cudaFree(d_fftwork);
+        // all plan buffers come from the stream-ordered pool (see pool_setup)
+        if (own_uvw && d_uvw) cudaFreeAsync(d_uvw, stream);
+        if (d_fscale) cudaFreeAsync(d_fscale, stream);
+        if (d_cu) cudaFreeAsync(d_cu, stream);
+        if (d_cv) cudaFreeAsync(d_cv, stream);
+        if (d_cheb) cudaFreeAsync(d_cheb, stream);
+        if (d_sidx) cudaFreeAsync(d_sidx, stream);
+        if (d_ring) cudaFreeAsync(d_ring, stream);
+        if (d_acc) cudaFreeAsync(d_acc, stream);
+        if (d_scratch) cudaFreeAsync(d_scratch, stream);
+        if (d_fftwork) cudaFreeAsync(d_fftwork, stream);
         if (fft_ok) cufftDestroy(fft);
+        for (auto e : chunk_ev) cudaEventDestroy(e);
+        chunk_ev.clear();
+        if (ev_a) cudaEventDestroy(ev_a);
+        if (ev_b) cudaEventDestroy(ev_b);
+        if (copy_stream) cudaStreamDestroy(copy_stream);
+        ev_a = ev_b = nullptr;
+        copy_stream = nullptr;
         d_uvw = d_fscale = d_cu = d_cv = d_cheb = d_scratch = nullptr;
         d_sidx = nullptr;
         d_ring = d_acc = d_fftwork = nullptr;
@@ -278,8 +299,8 @@ int build_tables(b2g_plan *p)
         cu[a] = 1.0 / p->pk.corr(double(a - p->npix_x / 2) / double(p->nu));
     for (int64_t b = 0; b < p->npix_y; ++b)
         cv[b] = 1.0 / p->pk.corr(double(b - p->npix_y / 2) / double(p->nv));
-    CUDA_OK(cudaMalloc(&p->d_cu, sizeof(double) * p->npix_x));
-    CUDA_OK(cudaMalloc(&p->d_cv, sizeof(double) * p->npix_y));
+    CUDA_OK(cudaMallocAsync(&p->d_cu, sizeof(double) * p->npix_x, p->stream));
+    CUDA_OK(cudaMallocAsync(&p->d_cv, sizeof(double) * p->npix_y, p->stream));
     CUDA_OK(cudaMemcpyAsync(p->d_cu, cu.data(), sizeof(double) * p->npix_x,
                             cudaMemcpyHostToDevice, p->stream));
     CUDA_OK(cudaMemcpyAsync(p->d_cv, cv.data(), sizeof(double) * p->npix_y,
@@ -293,7 +314,7 @@ int build_tables(b2g_plan *p)
                         1e-16);
     }
     p->ncheb = (int)cheb.size();
-    CUDA_OK(cudaMalloc(&p->d_cheb, sizeof(double) * cheb.size()));
+    CUDA_OK(cudaMallocAsync(&p->d_cheb, sizeof(double) * cheb.size(), p->stream));
     CUDA_OK(cudaMemcpyAsync(p->d_cheb, cheb.data(), sizeof(double) * cheb.size(),
                             cudaMemcpyHostToDevice, p->stream));
     CUDA_OK(cudaStreamSynchronize(p->stream));  // host vectors go out of scope
@@ -306,36 +327,38 @@ int build_sort(b2g_plan *p)
     p->slab_begin.assign(p->nslabs + 1, 0);
     if (n == 0) return 0;
     if (n >= (1ll << 32)) return fail("more than 2^32 samples per plan (%lld)", n);
+    cudaStream_t s = p->stream;
     uint64_t *keys_a = nullptr, *keys_b = nullptr;
     uint32_t *idx_a = nullptr;
     unsigned long long *counts = nullptr;
-    CUDA_OK(cudaMalloc(&p->d_sidx, sizeof(uint32_t) * n));
-    CUDA_OK(cudaMalloc(&keys_a, sizeof(uint64_t) * n));
-    CUDA_OK(cudaMalloc(&keys_b, sizeof(uint64_t) * n));
-    CUDA_OK(cudaMalloc(&idx_a, sizeof(uint32_t) * n));
-    CUDA_OK(cudaMalloc(&counts, sizeof(unsigned long long) * p->nplanes));
+    CUDA_OK(cudaMallocAsync(&p->d_sidx, sizeof(uint32_t) * n, s));
+    CUDA_OK(cudaMallocAsync(&keys_a, sizeof(uint64_t) * n, s));
+    CUDA_OK(cudaMallocAsync(&keys_b, sizeof(uint64_t) * n, s));
+    CUDA_OK(cudaMallocAsync(&idx_a, sizeof(uint32_t) * n, s));
+    CUDA_OK(cudaMallocAsync(&counts, sizeof(unsigned long long) * p->nplanes, s));
     const VisGeo g = p->vis_geo();
-    int rc = launch_keygen(g, p->W, n, keys_a, idx_a, counts, p->stream);
+    int rc = launch_keygen(g, p->W, n, p->nchunks > 1 ? (uint32_t)p->rows_per_chunk : 0u, keys_a,
+                           idx_a, counts, s);
     if (rc == 0) {
-        const double kmax = double(p->nplanes) * double(p->nu) * double(p->nv);
+        const double kmax = double(p->nchunks) * double(p->nplanes) * double(p->nu) * double(p->nv);
         p->key_bits = std::max(1, (int)std::ceil(std::log2(kmax + 1.0)));
-        rc = sort_pairs(keys_a, keys_b, idx_a, p->d_sidx, n, p->key_bits, p->stream);
+        rc = sort_pairs(keys_a, keys_b, idx_a, p->d_sidx, n, p->key_bits, s);
     }
     std::vector<unsigned long long> h(p->nplanes, 0);
     cudaError_t e = cudaMemcpyAsync(h.data(), counts, sizeof(unsigned long long) * p->nplanes,
-                                    cudaMemcpyDeviceToHost, p->stream);
-    if (e == cudaSuccess) e = cudaStreamSynchronize(p->stream);
-    cudaFree(keys_a);
-    cudaFree(keys_b);
-    cudaFree(idx_a);
-    cudaFree(counts);
+                                    cudaMemcpyDeviceToHost, s);
+    cudaFreeAsync(keys_a, s);
+    cudaFreeAsync(keys_b, s);
+    cudaFreeAsync(idx_a, s);
+    cudaFreeAsync(counts, s);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(s);
     KERNEL_OK(rc);
     CUDA_OK(e);
-    // slab s = origin planes [s*gs, (s+1)*gs)
+    // slab sl = origin planes [sl*gs, (sl+1)*gs)
     long long run = 0;
-    for (int s = 0; s < p->nslabs; ++s) {
-        p->slab_begin[s] = run;
-        for (int q = s * p->gs; q < std::min((s + 1) * p->gs, p->nplanes); ++q) run += (long long)h[q];
+    for (int sl = 0; sl < p->nslabs; ++sl) {
+        p->slab_begin[sl] = run;
+        for (int q = sl * p->gs; q < std::min((sl + 1) * p->gs, p->nplanes); ++q) run += (long long)h[q];
     }
     p->slab_begin[p->nslabs] = run;
     if (run != n) {
@@ -344,6 +367,23 @@ int build_sort(b2g_plan *p)
         if (run != n) return fail("internal: plane histogram covers %lld of %lld samples", run, n);
         p->slab_begin[p->nslabs] = run;
     }
+    return 0;
+}
+
+// The stream-ordered pool keeps freed blocks instead of returning them to the driver at every
+// synchronisation: plan creation / destruction per call (the one-shot ms2dirty / dirty2ms
+// pattern of the reference) then costs no cudaMalloc / cudaFree round trips after the first.
+int pool_setup(int device)
+{
+    static std::atomic<unsigned> done{0};
+    if (device < 0 || device >= 32 || (done.load() & (1u << device))) return 0;
+    cudaMemPool_t pool;
+    CUDA_OK(cudaDeviceGetDefaultMemPool(&pool, device));
+    size_t free_b = 0, total_b = 0;
+    CUDA_OK(cudaMemGetInfo(&free_b, &total_b));
+    unsigned long long keep = (unsigned long long)(total_b / 4);
+    CUDA_OK(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    done.fetch_or(1u << device);
     return 0;
 }
 
@@ -386,6 +426,7 @@ extern "C" int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, con
     p->stream = (cudaStream_t)stream;
     p->timer.stream = p->stream;
     CUDA_OK(cudaGetDevice(&p->device));
+    B2G_OK(pool_setup(p->device));
     CUDA_OK(cudaEventCreate(&ev0));
     CUDA_OK(cudaEventCreate(&ev1));
     CUDA_OK(cudaEventRecord(ev0, p->stream));
@@ -415,26 +456,27 @@ extern "C" int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, con
         fsmin = std::min(fsmin, f);
         fsmax = std::max(fsmax, f);
     }
-    CUDA_OK(cudaMalloc(&p->d_fscale, sizeof(double) * nchan));
-    CUDA_OK(cudaMemcpy(p->d_fscale, fs.data(), sizeof(double) * nchan, cudaMemcpyHostToDevice));
+    CUDA_OK(cudaMallocAsync(&p->d_fscale, sizeof(double) * nchan, p->stream));
+    CUDA_OK(cudaMemcpyAsync(p->d_fscale, fs.data(), sizeof(double) * nchan, cudaMemcpyHostToDevice,
+                            p->stream));
     // uvw
     if (uvw_space == B2G_DEVICE) {
         p->d_uvw = const_cast<double *>(uvw);
         p->own_uvw = false;
     } else {
-        CUDA_OK(cudaMalloc(&p->d_uvw, sizeof(double) * 3 * std::max<int64_t>(nrow, 1)));
+        CUDA_OK(cudaMallocAsync(&p->d_uvw, sizeof(double) * 3 * std::max<int64_t>(nrow, 1), p->stream));
         p->own_uvw = true;
         if (nrow > 0)
             CUDA_OK(cudaMemcpyAsync(p->d_uvw, uvw, sizeof(double) * 3 * nrow,
                                     cudaMemcpyHostToDevice, p->stream));
     }
-    CUDA_OK(cudaMalloc(&p->d_scratch, sizeof(double) * 2048));
+    CUDA_OK(cudaMallocAsync(&p->d_scratch, sizeof(double) * 2048, p->stream));
     double st[4] = {0, 0, 0, 0};
     if (nrow > 0) {
         KERNEL_OK(launch_uvw_stats(p->d_uvw, nrow, p->d_scratch, p->stream));
         CUDA_OK(cudaMemcpyAsync(st, p->d_scratch, sizeof(st), cudaMemcpyDeviceToHost, p->stream));
-        CUDA_OK(cudaStreamSynchronize(p->stream));
     }
+    CUDA_OK(cudaStreamSynchronize(p->stream));  // also: fs (host vector) has been consumed
     if (!(st[1] == st[1]) || !(st[2] == st[2]) || !(st[3] == st[3]) || st[1] > 1e300)
         return fail("uvw contains NaN or Inf");
     p->wmin = st[0] * fsmin;
@@ -482,8 +524,10 @@ extern "C" int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, con
         // (20 B/sample, released after the sort) + caller's visibilities
         const double avail = 0.35 * double(free_b);
         int gs = (int)(avail / double(p->plane_bytes)) - (p->W - 1);
-        gs = std::max(1, std::min(gs, 8));
-        gs = std::min(gs, p->nplanes - p->W + 1);
+        // all origin planes in one slab when that is cheap (enables host streaming), else <= 8
+        const int all = p->nplanes - p->W + 1;
+        gs = (all <= 24 && gs >= all) ? all : std::max(1, std::min(gs, 8));
+        gs = std::min(gs, all);
         p->gs = gs;
         p->nslots = gs + p->W - 1;
         p->nslabs = (p->nplanes - p->W + 1 + gs - 1) / gs;
@@ -494,6 +538,23 @@ extern "C" int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, con
         p->gs = 1;
         p->nslots = 1;
         p->nslabs = 1;
+    }
+
+    // host-streaming plans: row chunks as the outermost sort component (all planes resident)
+    {
+        const long long per = g_host_chunk_samples.load();
+        if (uvw_space == B2G_HOST && p->nslabs == 1 && per > 0 && p->nvis >= 2 * per) {
+            int nc = (int)std::min<long long>(kMaxChunks, p->nvis / per);
+            p->rows_per_chunk = (nrow + nc - 1) / nc;
+            p->nchunks = (int)((nrow + p->rows_per_chunk - 1) / p->rows_per_chunk);
+        }
+        if (p->nchunks > 1) {
+            CUDA_OK(cudaStreamCreateWithFlags(&p->copy_stream, cudaStreamNonBlocking));
+            p->chunk_ev.resize(p->nchunks);
+            for (auto &e : p->chunk_ev) CUDA_OK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            CUDA_OK(cudaEventCreateWithFlags(&p->ev_a, cudaEventDisableTiming));
+            CUDA_OK(cudaEventCreateWithFlags(&p->ev_b, cudaEventDisableTiming));
+        }
     }
 
     // gridding kernel family
@@ -516,12 +577,12 @@ extern "C" int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, con
     size_t work = 0;
     FFT_OK(cufftMakePlan2d(p->fft, (int)p->nu, (int)p->nv,
                            precision == B2G_F32 ? CUFFT_C2C : CUFFT_Z2Z, &work));
-    if (work > 0) CUDA_OK(cudaMalloc(&p->d_fftwork, work));
+    if (work > 0) CUDA_OK(cudaMallocAsync(&p->d_fftwork, work, p->stream));
     FFT_OK(cufftSetWorkArea(p->fft, p->d_fftwork));
     FFT_OK(cufftSetStream(p->fft, p->stream));
 
-    CUDA_OK(cudaMalloc(&p->d_ring, p->plane_bytes * size_t(p->nslots)));
-    CUDA_OK(cudaMalloc(&p->d_acc, size_t(npix_x) * size_t(npix_y) * real_size(precision)));
+    CUDA_OK(cudaMallocAsync(&p->d_ring, p->plane_bytes * size_t(p->nslots), p->stream));
+    CUDA_OK(cudaMallocAsync(&p->d_acc, size_t(npix_x) * size_t(npix_y) * real_size(precision), p->stream));
 
     CUDA_OK(cudaEventRecord(ev1, p->stream));
     CUDA_OK(cudaEventSynchronize(ev1));
@@ -533,10 +594,10 @@ extern "C" int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, con
     if (verbosity > 0)
         fprintf(stderr,
                 "[b2g] plan: nvis=%lld W=%d sigma=%.2f grid=%lldx%lld planes=%d (gs=%d, slabs=%d) "
-                "dw=%g w=[%g,%g] algo=%d key_bits=%d work=%.1f MB plan=%.2f ms\n",
+                "dw=%g w=[%g,%g] algo=%d key_bits=%d host_chunks=%d work=%.1f MB plan=%.2f ms\n",
                 (long long)p->nvis, p->W, p->sigma, (long long)p->nu, (long long)p->nv, p->nplanes,
-                p->gs, p->nslabs, p->dw, p->wmin, p->wmax, p->algo, p->key_bits, work / 1048576.0,
-                p->t_plan_ms);
+                p->gs, p->nslabs, p->dw, p->wmin, p->wmax, p->algo, p->key_bits, p->nchunks,
+                work / 1048576.0, p->t_plan_ms);
     guard.p = nullptr;
     *plan = p;
     return 0;
@@ -558,9 +619,13 @@ template <typename T> struct Staged {
     T *ptr = nullptr;
     bool owned = false;
     cudaStream_t stream = nullptr;
+    cudaStream_t filler = nullptr;  // second stream that writes into the buffer, if any
     ~Staged()
     {
-        if (owned && ptr) cudaFreeAsync(ptr, stream);
+        if (owned && ptr) {
+            if (filler) cudaStreamSynchronize(filler);
+            cudaFreeAsync(ptr, stream);
+        }
     }
 };
 
@@ -673,8 +738,8 @@ template <typename T> VisLaunch<T> make_launch(b2g_plan *p, int slab)
     L.wstack = p->wstack != 0;
     L.coef = p->pk.c.data();
     L.sidx = p->d_sidx;
-    L.begin = p->slab_begin[slab];
-    L.end = p->slab_begin[slab + 1];
+    L.begin = p->slab_begin.empty() ? 0 : p->slab_begin[slab];
+    L.end = p->slab_begin.empty() ? 0 : p->slab_begin[slab + 1];
     L.plane0 = slab * p->gs;
     L.slot0 = L.plane0 % p->nslots;
     L.ms = nullptr;
@@ -733,11 +798,38 @@ int invert_impl(b2g_plan *p, const void *ms, const void *wgt, int vis_dtype, int
     tm.begin(S_TOTAL);
     const size_t tot_idx = tm.spans.size() - 1;
 
-    tm.begin(S_H2D);
+    const int want = sizeof(T) == 8 ? B2G_F64 : B2G_F32;
+    // host arrays of the plan's own type are streamed chunk by chunk, overlapped with gridding
+    const bool stream_in = p->nchunks > 1 && vis_space == B2G_HOST && vis_dtype == want && n > 0;
     Staged<T> d_ms, d_wgt;
-    B2G_OK(stage_in<T>(ms, vis_dtype, vis_space, 2 * n, s, &d_ms));
-    B2G_OK(stage_in<T>(wgt, vis_dtype, vis_space, n, s, &d_wgt));
-    tm.end();
+    if (stream_in) {
+        d_ms.stream = d_wgt.stream = s;
+        d_ms.filler = d_wgt.filler = p->copy_stream;
+        CUDA_OK(cudaMallocAsync(&d_ms.ptr, sizeof(T) * 2 * n, s));
+        d_ms.owned = true;
+        if (wgt) {
+            CUDA_OK(cudaMallocAsync(&d_wgt.ptr, sizeof(T) * n, s));
+            d_wgt.owned = true;
+        }
+        CUDA_OK(cudaEventRecord(p->ev_a, s));
+        CUDA_OK(cudaStreamWaitEvent(p->copy_stream, p->ev_a, 0));
+        for (int c = 0; c < p->nchunks; ++c) {
+            const long long r0 = std::min<long long>(p->nrow, c * p->rows_per_chunk);
+            const long long r1 = std::min<long long>(p->nrow, (c + 1) * p->rows_per_chunk);
+            const long long o = r0 * p->nchan, m = (r1 - r0) * p->nchan;
+            CUDA_OK(cudaMemcpyAsync(d_ms.ptr + 2 * o, static_cast<const T *>(ms) + 2 * o,
+                                    sizeof(T) * 2 * m, cudaMemcpyHostToDevice, p->copy_stream));
+            if (wgt)
+                CUDA_OK(cudaMemcpyAsync(d_wgt.ptr + o, static_cast<const T *>(wgt) + o, sizeof(T) * m,
+                                        cudaMemcpyHostToDevice, p->copy_stream));
+            CUDA_OK(cudaEventRecord(p->chunk_ev[c], p->copy_stream));
+        }
+    } else {
+        tm.begin(S_H2D);
+        B2G_OK(stage_in<T>(ms, vis_dtype, vis_space, 2 * n, s, &d_ms));
+        B2G_OK(stage_in<T>(wgt, vis_dtype, vis_space, n, s, &d_wgt));
+        tm.end();
+    }
 
     tm.begin(S_PREP);
     CUDA_OK(cudaMemsetAsync(p->d_ring, 0, p->plane_bytes * size_t(p->nslots), s));
@@ -749,10 +841,18 @@ int invert_impl(b2g_plan *p, const void *ms, const void *wgt, int vis_dtype, int
         L.ms = reinterpret_cast<const cplx<T> *>(d_ms.ptr);
         L.wgt = d_wgt.ptr;
         tm.begin(S_VIS);
-        if (L.end > L.begin) {
-            if (p->algo == B2G_ALGO_WARPRUN) KERNEL_OK(launch_grid_warprun<T>(L));
-            else KERNEL_OK(launch_grid_simple<T>(L));
-            p->launches_last++;
+        // one launch per row chunk (nslabs == 1), each behind its own H2D copy when streaming
+        for (int c = 0; c < p->nchunks; ++c) {
+            if (p->nchunks > 1) {
+                L.begin = std::min<long long>(p->nrow, c * p->rows_per_chunk) * p->nchan;
+                L.end = std::min<long long>(p->nrow, (c + 1) * p->rows_per_chunk) * p->nchan;
+                if (stream_in) CUDA_OK(cudaStreamWaitEvent(s, p->chunk_ev[c], 0));
+            }
+            if (L.end > L.begin) {
+                if (p->algo == B2G_ALGO_WARPRUN) KERNEL_OK(launch_grid_warprun<T>(L));
+                else KERNEL_OK(launch_grid_simple<T>(L));
+                p->launches_last++;
+            }
         }
         tm.end();
         int first, count;
@@ -838,6 +938,8 @@ int predict_impl(b2g_plan *p, const void *dirty, int dirty_dtype, int dirty_spac
         CUDA_OK(cudaMallocAsync(&d_out, sizeof(cplx<T>) * n, s));
         own_out = true;
     }
+    // host output of the plan's own type: each row chunk goes back while the next is degridded
+    const bool stream_out = own_out && p->nchunks > 1 && vis_space == B2G_HOST && vis_dtype == want;
 
     for (int sl = 0; sl < p->nslabs; ++sl) {
         int first, count;
@@ -856,14 +958,31 @@ int predict_impl(b2g_plan *p, const void *dirty, int dirty_dtype, int dirty_spac
         L.wgt = d_wgt.ptr;
         L.ms_out = d_out;
         tm.begin(S_VIS);
-        if (L.end > L.begin) {
-            if (p->algo == B2G_ALGO_WARPRUN) KERNEL_OK(launch_degrid_warprun<T>(L));
-            else KERNEL_OK(launch_degrid_simple<T>(L));
-            p->launches_last++;
+        for (int c = 0; c < p->nchunks; ++c) {
+            if (p->nchunks > 1) {
+                L.begin = std::min<long long>(p->nrow, c * p->rows_per_chunk) * p->nchan;
+                L.end = std::min<long long>(p->nrow, (c + 1) * p->rows_per_chunk) * p->nchan;
+            }
+            if (L.end > L.begin) {
+                if (p->algo == B2G_ALGO_WARPRUN) KERNEL_OK(launch_degrid_warprun<T>(L));
+                else KERNEL_OK(launch_degrid_simple<T>(L));
+                p->launches_last++;
+            }
+            if (stream_out && L.end > L.begin) {
+                CUDA_OK(cudaEventRecord(p->chunk_ev[c], s));
+                CUDA_OK(cudaStreamWaitEvent(p->copy_stream, p->chunk_ev[c], 0));
+                CUDA_OK(cudaMemcpyAsync(static_cast<cplx<T> *>(ms_out) + L.begin, d_out + L.begin,
+                                        sizeof(cplx<T>) * (L.end - L.begin), cudaMemcpyDeviceToHost,
+                                        p->copy_stream));
+            }
         }
         tm.end();
     }
-    if (own_out) {
+    if (stream_out) {
+        CUDA_OK(cudaEventRecord(p->ev_b, p->copy_stream));
+        CUDA_OK(cudaStreamWaitEvent(s, p->ev_b, 0));
+        CUDA_OK(cudaFreeAsync(d_out, s));
+    } else if (own_out) {
         tm.begin(S_D2H);
         B2G_OK(stage_out<T>(reinterpret_cast<const T *>(d_out), ms_out, vis_dtype, vis_space, 2 * n, s));
         CUDA_OK(cudaFreeAsync(d_out, s));
@@ -994,6 +1113,13 @@ extern "C" int b2g_sumwt(const void *wgt, int dtype, int space, int64_t n, doubl
     }
     cudaFreeAsync(scratch, s);
     return rc;
+}
+
+extern "C" int b2g_set_host_chunk_samples(int64_t nsamples)
+{
+    g_err.clear();
+    g_host_chunk_samples.store(nsamples > 0 ? (long long)nsamples : 0ll);
+    return 0;
 }
 
 extern "C" int b2g_kernel_select(double epsilon, int do_wstacking, int precision, int64_t npix_x,

@@ -1,6 +1,7 @@
 // vis_sort.cu -- the uv-cell / w-plane sort ("bucket") pass.
 //
-// Every visibility gets the key  (p0*nu + iu0)*nv + iv0  where (iu0, iv0, p0) is the
+// Every visibility gets the key  ((chunk*nplanes + p0)*nu + iu0)*nv + iv0  where chunk is the
+// row chunk of a host-streaming plan (0 otherwise) and (iu0, iv0, p0) is the
 // lower corner of its kernel footprint (first cell in u and v, first w-plane), and the
 // (key, index) pairs are radix-sorted; a histogram of p0 gives the slab boundaries.  This is the B200 counterpart of the scan/bucket pass at the start
 // of ducc0.wgridder.ms2dirty / dirty2ms (call sites
@@ -21,8 +22,9 @@ namespace b2g {
 namespace {
 
 __global__ void __launch_bounds__(256)
-keygen_kernel(VisGeo g, int W, long long nvis, uint64_t *__restrict__ keys,
-              uint32_t *__restrict__ idx, unsigned long long *__restrict__ plane_counts)
+keygen_kernel(VisGeo g, int W, long long nvis, uint32_t rows_per_chunk,
+              uint64_t *__restrict__ keys, uint32_t *__restrict__ idx,
+              unsigned long long *__restrict__ plane_counts)
 {
     extern __shared__ unsigned int sh_cnt[];  // [nplanes] when nplanes <= 4096
     const int np = g.nplanes;
@@ -35,7 +37,9 @@ keygen_kernel(VisGeo g, int W, long long nvis, uint64_t *__restrict__ keys,
     if (i < nvis) {
         const uint32_t row = (uint32_t)(i / g.nchan), chan = (uint32_t)(i - (long long)row * g.nchan);
         const Located L = locate(g, W, row, chan);
-        uint64_t key = (uint64_t)L.p0 * (uint64_t)g.nu + (uint64_t)L.iu0;
+        // row chunks (host-streaming plans) are the most significant key component
+        uint64_t key = rows_per_chunk ? (uint64_t)(row / rows_per_chunk) * (uint64_t)g.nplanes : 0ull;
+        key = (key + (uint64_t)L.p0) * (uint64_t)g.nu + (uint64_t)L.iu0;
         key = key * (uint64_t)g.nv + (uint64_t)L.iv0;
         keys[i] = key;
         idx[i] = (uint32_t)i;
@@ -217,14 +221,15 @@ radix_scatter_kernel(const uint64_t *__restrict__ keys_in, const uint32_t *__res
 
 }  // namespace
 
-int launch_keygen(const VisGeo &geo, int W, long long nvis, uint64_t *keys, uint32_t *idx,
-                  unsigned long long *plane_counts, cudaStream_t stream)
+int launch_keygen(const VisGeo &geo, int W, long long nvis, uint32_t rows_per_chunk,
+                  uint64_t *keys, uint32_t *idx, unsigned long long *plane_counts,
+                  cudaStream_t stream)
 {
     cudaMemsetAsync(plane_counts, 0, sizeof(unsigned long long) * geo.nplanes, stream);
     if (nvis <= 0) return 0;
     const unsigned blocks = (unsigned)((nvis + 255) / 256);
     const size_t sh = geo.nplanes <= 4096 ? sizeof(unsigned int) * geo.nplanes : 0;
-    keygen_kernel<<<blocks, 256, sh, stream>>>(geo, W, nvis, keys, idx, plane_counts);
+    keygen_kernel<<<blocks, 256, sh, stream>>>(geo, W, nvis, rows_per_chunk, keys, idx, plane_counts);
     return (int)cudaGetLastError();
 }
 

@@ -135,3 +135,31 @@ def test_mixed_dtypes_through_the_abi(wg):
         v = p.predict(model, wgt, out_dtype=np.complex128)
     assert d.dtype == np.float64 and v.dtype == np.complex128
     assert rel_l2(d, dref) < 1e-5 and rel_l2(v, vref) < 1e-5
+
+
+@pytest.mark.parametrize("prec,eps", [("single", 1e-5), ("double", 1e-9)])
+@pytest.mark.parametrize("ws", [False, True])
+def test_host_streaming_chunks(wg, built, prec, eps, ws):
+    """Plans built from host uvw stream the sample arrays in row chunks (sort key carries the
+    chunk); the result must match the DFT oracle and the unchunked plan."""
+    uvw, freq, ms, wgt, model, dref, vref = _oracle("narrow", ws)
+    nrow, nchan, npx, npy, psx, psy, _ = GEOS["narrow"]
+    cdt, rdt = (np.complex128, np.float64) if prec == "double" else (np.complex64, np.float32)
+    msc, wc, mc = ms.astype(cdt), wgt.astype(rdt), model.astype(rdt)
+    try:
+        built.b2g_set_host_chunk_samples(1700)  # 12000 samples -> 7 chunks, ragged last one
+        with wg.Plan(uvw, freq, npx, npy, psx, psy, eps, ws, precision=prec) as plan:
+            assert plan.info()["key_bits"] > 0
+            d1, v1 = plan.invert(msc, wc), plan.predict(mc)
+            d1b = plan.invert(msc, None)
+        built.b2g_set_host_chunk_samples(0)
+        with wg.Plan(uvw, freq, npx, npy, psx, psy, eps, ws, precision=prec) as plan:
+            d0, v0 = plan.invert(msc, wc), plan.predict(mc)
+            d0b = plan.invert(msc, None)
+    finally:
+        built.b2g_set_host_chunk_samples(1 << 24)
+    assert rel_l2(d1, dref) < eps
+    tol = 1e-5 if prec == "single" else 1e-12
+    assert rel_max(d1, d0) < tol and rel_max(v1, v0) < tol and rel_max(d1b, d0b) < tol
+    # predict without weights covers every sample, also the zero-weight rows of `wgt`
+    assert np.all(np.isfinite(v1)) and rel_l2(v1[wgt != 0], (vref / np.where(wgt == 0, 1, wgt))[wgt != 0]) < eps
