@@ -154,7 +154,8 @@ struct PolyKernel {
     double corr(double x) const
     {
         static thread_local std::vector<double> gx, gw;
-        if (gx.empty()) gauss_legendre(40, gx, gw);
+        // 24 nodes integrate (degree <= 19 polynomial) x cos(<= pi/2 t + phase) to < 1e-17
+        if (gx.empty()) gauss_legendre(24, gx, gw);
         const double twopi = 6.283185307179586476925286766559;
         double sum = 0.0;
         for (int s = 0; s < W; ++s) {

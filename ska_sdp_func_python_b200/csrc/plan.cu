@@ -11,6 +11,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -168,6 +169,7 @@ struct b2g_plan {
     cudaStream_t copy_stream = nullptr;
     std::vector<cudaEvent_t> chunk_ev;
     cudaEvent_t ev_a = nullptr, ev_b = nullptr;
+    cudaEvent_t ev_plan0 = nullptr, ev_plan1 = nullptr;  // plan creation on the stream
     void *d_ring = nullptr;
     size_t plane_bytes = 0;
     void *d_acc = nullptr;
@@ -176,7 +178,19 @@ struct b2g_plan {
     bool fft_ok = false;
     void *d_fftwork = nullptr;
     int key_bits = 0;
-    double t_plan_ms = 0, t_last_ms = 0;
+    double t_plan_ms = -1, t_last_ms = 0;
+    // device time of plan creation; the sort of a single-slab plan is left running on the
+    // stream when b2g_plan_create returns, so this may have to wait for it
+    double plan_ms()
+    {
+        if (t_plan_ms < 0 && ev_plan0 && ev_plan1) {
+            float ms = 0.f;
+            if (cudaEventSynchronize(ev_plan1) == cudaSuccess &&
+                cudaEventElapsedTime(&ms, ev_plan0, ev_plan1) == cudaSuccess)
+                t_plan_ms = ms;
+        }
+        return t_plan_ms < 0 ? 0.0 : t_plan_ms;
+    }
     double timings[S_COUNT] = {0};
     long long launches_last = 0;
     StageTimer timer;
@@ -237,6 +251,9 @@ struct b2g_plan {
         chunk_ev.clear();
         if (ev_a) cudaEventDestroy(ev_a);
         if (ev_b) cudaEventDestroy(ev_b);
+        if (ev_plan0) cudaEventDestroy(ev_plan0);
+        if (ev_plan1) cudaEventDestroy(ev_plan1);
+        ev_plan0 = ev_plan1 = nullptr;
         if (copy_stream) cudaStreamDestroy(copy_stream);
         ev_a = ev_b = nullptr;
         copy_stream = nullptr;
@@ -294,11 +311,20 @@ int choose_kernel(double epsilon, bool wstack, int precision, int64_t npix_x, in
 int build_tables(b2g_plan *p)
 {
     // 1/psi-hat along u and v at the image pixels (x in cycles per grid cell)
-    std::vector<double> cu(p->npix_x), cv(p->npix_y);
-    for (int64_t a = 0; a < p->npix_x; ++a)
-        cu[a] = 1.0 / p->pk.corr(double(a - p->npix_x / 2) / double(p->nu));
-    for (int64_t b = 0; b < p->npix_y; ++b)
-        cv[b] = 1.0 / p->pk.corr(double(b - p->npix_y / 2) / double(p->nv));
+    // psi-hat is even: evaluate one half, mirror the other; reuse u for v on square grids
+    auto table = [&](int64_t npix, int64_t n, std::vector<double> &out) {
+        out.resize(npix);
+        const int64_t h = npix / 2;
+        for (int64_t k = 0; k <= h; ++k) {
+            const double c = 1.0 / p->pk.corr(double(k) / double(n));
+            out[h - k] = c;                    // pixel h-k sits at -k
+            if (h + k < npix) out[h + k] = c;  // pixel h+k at +k
+        }
+    };
+    std::vector<double> cu, cv;
+    table(p->npix_x, p->nu, cu);
+    if (p->npix_y == p->npix_x && p->nv == p->nu) cv = cu;
+    else table(p->npix_y, p->nv, cv);
     CUDA_OK(cudaMallocAsync(&p->d_cu, sizeof(double) * p->npix_x, p->stream));
     CUDA_OK(cudaMallocAsync(&p->d_cv, sizeof(double) * p->npix_y, p->stream));
     CUDA_OK(cudaMemcpyAsync(p->d_cu, cu.data(), sizeof(double) * p->npix_x,
@@ -343,6 +369,16 @@ int build_sort(b2g_plan *p)
         const double kmax = double(p->nchunks) * double(p->nplanes) * double(p->nu) * double(p->nv);
         p->key_bits = std::max(1, (int)std::ceil(std::log2(kmax + 1.0)));
         rc = sort_pairs(keys_a, keys_b, idx_a, p->d_sidx, n, p->key_bits, s);
+    }
+    if (p->nslabs == 1) {
+        // one slab holds every sample: no histogram needed, the sort stays in flight
+        cudaFreeAsync(keys_a, s);
+        cudaFreeAsync(keys_b, s);
+        cudaFreeAsync(idx_a, s);
+        cudaFreeAsync(counts, s);
+        KERNEL_OK(rc);
+        p->slab_begin[1] = n;
+        return 0;
     }
     std::vector<unsigned long long> h(p->nplanes, 0);
     cudaError_t e = cudaMemcpyAsync(h.data(), counts, sizeof(unsigned long long) * p->nplanes,
@@ -417,19 +453,26 @@ extern "C" int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, con
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
         return fail("no CUDA device available (this library has no CPU path)");
 
+    auto wall0 = std::chrono::steady_clock::now();
+    auto lap = [&](const char *what) {
+        if (verbosity < 2) return;
+        auto now = std::chrono::steady_clock::now();
+        fprintf(stderr, "[b2g] plan_create %-14s %8.3f ms\n", what,
+                std::chrono::duration<double, std::milli>(now - wall0).count());
+        wall0 = now;
+    };
     b2g_plan *p = new b2g_plan();
     struct Guard {
         b2g_plan *p;
         ~Guard() { if (p) { p->release(); delete p; } }
     } guard{p};
-    cudaEvent_t ev0, ev1;
     p->stream = (cudaStream_t)stream;
     p->timer.stream = p->stream;
     CUDA_OK(cudaGetDevice(&p->device));
     B2G_OK(pool_setup(p->device));
-    CUDA_OK(cudaEventCreate(&ev0));
-    CUDA_OK(cudaEventCreate(&ev1));
-    CUDA_OK(cudaEventRecord(ev0, p->stream));
+    CUDA_OK(cudaEventCreate(&p->ev_plan0));
+    CUDA_OK(cudaEventCreate(&p->ev_plan1));
+    CUDA_OK(cudaEventRecord(p->ev_plan0, p->stream));
     p->nrow = nrow;
     p->nchan = nchan;
     p->nvis = nrow * nchan;
@@ -477,6 +520,7 @@ extern "C" int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, con
         CUDA_OK(cudaMemcpyAsync(st, p->d_scratch, sizeof(st), cudaMemcpyDeviceToHost, p->stream));
     }
     CUDA_OK(cudaStreamSynchronize(p->stream));  // also: fs (host vector) has been consumed
+    lap("uvw+stats");
     if (!(st[1] == st[1]) || !(st[2] == st[2]) || !(st[3] == st[3]) || st[1] > 1e300)
         return fail("uvw contains NaN or Inf");
     p->wmin = st[0] * fsmin;
@@ -567,8 +611,9 @@ extern "C" int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, con
     if (algo != B2G_ALGO_SIMPLE && algo != B2G_ALGO_WARPRUN) return fail("bad algo code %d", algo);
     p->algo = algo;
 
+    lap("setup");
     B2G_OK(build_tables(p));
-    B2G_OK(build_sort(p));
+    lap("tables");
 
     // FFT plan (own work area so that memory use is explicit)
     FFT_OK(cufftCreate(&p->fft));
@@ -577,27 +622,25 @@ extern "C" int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, con
     size_t work = 0;
     FFT_OK(cufftMakePlan2d(p->fft, (int)p->nu, (int)p->nv,
                            precision == B2G_F32 ? CUFFT_C2C : CUFFT_Z2Z, &work));
+    FFT_OK(cufftSetStream(p->fft, p->stream));
+    lap("cufft plan");
+
+    // the sort goes last: for a single-slab plan it is still running when this call returns,
+    // so the caller's next call (e.g. the H2D copies of b2g_plan_invert) overlaps with it
+    B2G_OK(build_sort(p));
     if (work > 0) CUDA_OK(cudaMallocAsync(&p->d_fftwork, work, p->stream));
     FFT_OK(cufftSetWorkArea(p->fft, p->d_fftwork));
-    FFT_OK(cufftSetStream(p->fft, p->stream));
-
     CUDA_OK(cudaMallocAsync(&p->d_ring, p->plane_bytes * size_t(p->nslots), p->stream));
     CUDA_OK(cudaMallocAsync(&p->d_acc, size_t(npix_x) * size_t(npix_y) * real_size(precision), p->stream));
-
-    CUDA_OK(cudaEventRecord(ev1, p->stream));
-    CUDA_OK(cudaEventSynchronize(ev1));
-    float ms = 0.f;
-    cudaEventElapsedTime(&ms, ev0, ev1);
-    cudaEventDestroy(ev0);
-    cudaEventDestroy(ev1);
-    p->t_plan_ms = ms;
+    CUDA_OK(cudaEventRecord(p->ev_plan1, p->stream));
+    lap("sort+alloc");
     if (verbosity > 0)
         fprintf(stderr,
                 "[b2g] plan: nvis=%lld W=%d sigma=%.2f grid=%lldx%lld planes=%d (gs=%d, slabs=%d) "
                 "dw=%g w=[%g,%g] algo=%d key_bits=%d host_chunks=%d work=%.1f MB plan=%.2f ms\n",
                 (long long)p->nvis, p->W, p->sigma, (long long)p->nu, (long long)p->nv, p->nplanes,
                 p->gs, p->nslabs, p->dw, p->wmin, p->wmax, p->algo, p->key_bits, p->nchunks,
-                work / 1048576.0, p->t_plan_ms);
+                work / 1048576.0, p->plan_ms());
     guard.p = nullptr;
     *plan = p;
     return 0;
@@ -805,14 +848,15 @@ int invert_impl(b2g_plan *p, const void *ms, const void *wgt, int vis_dtype, int
     if (stream_in) {
         d_ms.stream = d_wgt.stream = s;
         d_ms.filler = d_wgt.filler = p->copy_stream;
-        CUDA_OK(cudaMallocAsync(&d_ms.ptr, sizeof(T) * 2 * n, s));
+        // allocated on the copy stream: the copies must not wait for what is still queued on
+        // the compute stream (the plan's sort); the gridding launches order themselves behind
+        // the copies through the chunk events
+        CUDA_OK(cudaMallocAsync(&d_ms.ptr, sizeof(T) * 2 * n, p->copy_stream));
         d_ms.owned = true;
         if (wgt) {
-            CUDA_OK(cudaMallocAsync(&d_wgt.ptr, sizeof(T) * n, s));
+            CUDA_OK(cudaMallocAsync(&d_wgt.ptr, sizeof(T) * n, p->copy_stream));
             d_wgt.owned = true;
         }
-        CUDA_OK(cudaEventRecord(p->ev_a, s));
-        CUDA_OK(cudaStreamWaitEvent(p->copy_stream, p->ev_a, 0));
         for (int c = 0; c < p->nchunks; ++c) {
             const long long r0 = std::min<long long>(p->nrow, c * p->rows_per_chunk);
             const long long r1 = std::min<long long>(p->nrow, (c + 1) * p->rows_per_chunk);
@@ -1038,6 +1082,7 @@ extern "C" int b2g_plan_info(const b2g_plan *p, int64_t *iinfo, int ni, double *
 {
     g_err.clear();
     if (!p) return fail("plan is NULL");
+    const_cast<b2g_plan *>(p)->plan_ms();
     const int64_t iv[11] = {p->W, p->nu, p->nv, p->nplanes, p->nslabs, p->gs, p->algo,
                             poly_degree(p->W), p->nvis, p->key_bits, p->launches_last};
     const double dv[9] = {p->sigma, p->eps_kernel, p->dw, p->wmin, p->wmax, p->beta, p->e0,
