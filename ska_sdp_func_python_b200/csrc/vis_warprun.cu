@@ -40,8 +40,10 @@ template <typename T> struct Vec16;
 template <> struct Vec16<float> { using type = float4; };
 template <> struct Vec16<double> { using type = double2; };
 
-template <typename T, int W, bool WS, bool GRID> struct Cfg {
-    static constexpr int PW = WS ? W : 1;
+// PWB: w-planes of a sample's support handled per pass (0 = no w-stacking, W = all in one pass)
+template <typename T, int W, int PWB, bool GRID> struct Cfg {
+    static constexpr bool WS = PWB > 0;
+    static constexpr int PW = WS ? PWB : 1;
     static constexpr int JL = W <= 5 ? W : (W <= 8 ? 8 : 16);   // lanes along v (column classes)
     static constexpr int IG = 32 / JL;                          // complete lane groups along u
     static constexpr int NG = 31 / JL + 1;                      // incl. a partial last group
@@ -57,8 +59,8 @@ template <typename T, int W, bool WS, bool GRID> struct Cfg {
     static constexpr int KW_S16 = KW_N16 | 1;                   // odd stride: conflict-free STS.128
 };
 
-template <typename T, int W, bool WS, bool GRID> struct Stage {
-    using C = Cfg<T, W, WS, GRID>;
+template <typename T, int W, int PWB, bool GRID> struct Stage {
+    using C = Cfg<T, W, PWB, GRID>;
     alignas(16) T kw[32 * C::KW_S16 * C::KW_V];
     alignas(16) int4 org[32];     // iu0, iv0, p0, ru | rv << 8   (read when the footprint moved)
     alignas(16) T ku[32 * C::KUS];  // ku[(s + ru) mod W] = kernel value of footprint row s
@@ -71,12 +73,13 @@ template <typename T> struct Partials {
 
 // Lane-parallel preparation of one sample (lane `lane` of the warp).  `val` is the (weighted)
 // visibility for gridding.  Returns the packed origin (iu0 << 16 | iv0, p0).
-template <typename T, int W, bool WS, bool GRID>
+template <typename T, int W, int PWB, bool GRID>
 __device__ __forceinline__ void prepare(const VisGeo &g, const KernelTab<T, W> &tab, uint32_t idx,
-                                        int lane, Stage<T, W, WS, GRID> &st, cplx<T> val,
+                                        int lane, Stage<T, W, PWB, GRID> &st, cplx<T> val, int q0,
                                         bool &flip, int &oxy, int &oz)
 {
-    using C = Cfg<T, W, WS, GRID>;
+    using C = Cfg<T, W, PWB, GRID>;
+    constexpr bool WS = C::WS;
     uint32_t row, chan;
     g.split(idx, row, chan);
     const Located L = locate(g, W, row, chan);
@@ -107,13 +110,20 @@ __device__ __forceinline__ void prepare(const VisGeo &g, const KernelTab<T, W> &
         for (int i = 0; i < C::KW_N16 * C::KW_V; ++i) row_[i] = T(0);
         if (WS) {
             kernel_values<T, W>(tab, (T)L.dw, k);
+            // taps q0 .. q0+PW-1 of the w-kernel (0 beyond the support); q0 is a multiple of
+            // PW, one statically indexed copy per pass keeps k[] in registers
 #pragma unroll
-            for (int s = 0; s < W; ++s) {
-                if (GRID) {
-                    row_[2 * s] = k[s] * val.re;
-                    row_[2 * s + 1] = k[s] * val.im;
-                } else {
-                    row_[s] = k[s];
+            for (int g0 = 0; g0 < W; g0 += C::PW) {
+                if (q0 != g0) continue;
+#pragma unroll
+                for (int s = 0; s < C::PW; ++s) {
+                    const T kq = g0 + s < W ? k[g0 + s < W ? g0 + s : 0] : T(0);
+                    if (GRID) {
+                        row_[2 * s] = kq * val.re;
+                        row_[2 * s + 1] = kq * val.im;
+                    } else {
+                        row_[s] = kq;
+                    }
                 }
             }
         } else {
@@ -128,11 +138,11 @@ __device__ __forceinline__ void prepare(const VisGeo &g, const KernelTab<T, W> &
 }
 
 // the w-kernel row of sample v, as C::KW_T values of T
-template <typename T, int W, bool WS, bool GRID>
-__device__ __forceinline__ void load_kw(const Stage<T, W, WS, GRID> &st, int v,
-                                        T (&out)[Cfg<T, W, WS, GRID>::KW_N16 * Cfg<T, W, WS, GRID>::KW_V])
+template <typename T, int W, int PWB, bool GRID>
+__device__ __forceinline__ void load_kw(const Stage<T, W, PWB, GRID> &st, int v,
+                                        T (&out)[Cfg<T, W, PWB, GRID>::KW_N16 * Cfg<T, W, PWB, GRID>::KW_V])
 {
-    using C = Cfg<T, W, WS, GRID>;
+    using C = Cfg<T, W, PWB, GRID>;
     using V = typename Vec16<T>::type;
     const V *src = reinterpret_cast<const V *>(st.kw) + v * C::KW_S16;
 #pragma unroll
@@ -140,11 +150,11 @@ __device__ __forceinline__ void load_kw(const Stage<T, W, WS, GRID> &st, int v,
 }
 
 // ku values of this lane's IPL row classes (lane-constant offset i0) and its kv value
-template <typename T, int W, bool WS, bool GRID>
-__device__ __forceinline__ void load_kuv(const Stage<T, W, WS, GRID> &st, int v, int i0, int j,
-                                         T (&ku)[Cfg<T, W, WS, GRID>::IPL], T &kv)
+template <typename T, int W, int PWB, bool GRID>
+__device__ __forceinline__ void load_kuv(const Stage<T, W, PWB, GRID> &st, int v, int i0, int j,
+                                         T (&ku)[Cfg<T, W, PWB, GRID>::IPL], T &kv)
 {
-    using C = Cfg<T, W, WS, GRID>;
+    using C = Cfg<T, W, PWB, GRID>;
     using P = typename V2<T>::type;
     if (C::KU_VEC) {
         const P t = *reinterpret_cast<const P *>(st.ku + v * C::KUS + i0);
@@ -182,17 +192,18 @@ __device__ __forceinline__ unsigned moved_mask(bool active, int oxy, int oz, int
 // ------------------------------------------------------------------------------------
 // Gridding
 // ------------------------------------------------------------------------------------
-template <typename T, int W, bool WS>
+template <typename T, int W, int PWB>
 __global__ void __launch_bounds__(32 * kWarps)
 grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ sidx,
-                    long long begin, long long end, int plane0, int slot0,
+                    long long begin, long long end, int plane0, int slot0, int q0,
                     const cplx<T> *__restrict__ ms, const T *__restrict__ wgt,
                     cplx<T> *__restrict__ ring)
 {
-    using C = Cfg<T, W, WS, true>;
-    using S = Stage<T, W, WS, true>;
+    using C = Cfg<T, W, PWB, true>;
+    using S = Stage<T, W, PWB, true>;
     using P = typename V2<T>::type;
     constexpr int PW = C::PW, IPL = C::IPL;
+    constexpr bool WS = C::WS;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     S *stage_all = reinterpret_cast<S *>(smem_raw);
 
@@ -219,9 +230,10 @@ grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ 
     int carry_xy = -1, carry_z = -1;
 
     auto flush_k = [&](int k) {
-        const int sbase = cur_p - plane0 + slot0;
+        const int sbase = cur_p - plane0 + slot0 + q0;
 #pragma unroll
         for (int q = 0; q < PW; ++q) {
+            if (WS && W % PW != 0 && q0 + q >= W) continue;  // ragged last pass
             cplx<T> *base = ring + (long long)wrap_inc(sbase + q, g.nslots) * g.plane_stride;
             red_add(base + coff[k], acc[k][q].x, acc[k][q].y);
             acc[k][q] = mk2(T(0), T(0));
@@ -259,7 +271,7 @@ grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ 
         int oxy = 0, oz = 0;
         if (active) {
             bool flip;
-            prepare<T, W, WS, true>(g, tab, idx, lane, st, val, flip, oxy, oz);
+            prepare<T, W, PWB, true>(g, tab, idx, lane, st, val, q0, flip, oxy, oz);
         }
         const unsigned act = __ballot_sync(kFull, active);
         const unsigned mov = moved_mask(active, oxy, oz, lane, act, carry_xy, carry_z);
@@ -306,8 +318,8 @@ grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ 
 #pragma unroll 4
             for (; v < vend; ++v) {
                 T kwr[C::KW_N16 * C::KW_V], kur[IPL], kvr;
-                load_kw<T, W, WS, true>(st, v, kwr);
-                load_kuv<T, W, WS, true>(st, v, i0, j, kur, kvr);
+                load_kw<T, W, PWB, true>(st, v, kwr);
+                load_kuv<T, W, PWB, true>(st, v, i0, j, kur, kvr);
 #pragma unroll
                 for (int k = 0; k < IPL; ++k) {
                     // classes outside the footprint accumulate into registers never flushed
@@ -329,17 +341,18 @@ grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ 
 // ------------------------------------------------------------------------------------
 // Degridding
 // ------------------------------------------------------------------------------------
-template <typename T, int W, bool WS>
+template <typename T, int W, int PWB>
 __global__ void __launch_bounds__(32 * kWarps)
 degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ sidx,
-                      long long begin, long long end, int plane0, int slot0,
+                      long long begin, long long end, int plane0, int slot0, int q0,
                       const T *__restrict__ wgt, cplx<T> *__restrict__ out,
                       const cplx<T> *__restrict__ ring)
 {
-    using C = Cfg<T, W, WS, false>;
-    using S = Stage<T, W, WS, false>;
+    using C = Cfg<T, W, PWB, false>;
+    using S = Stage<T, W, PWB, false>;
     using P = typename V2<T>::type;
     constexpr int PW = C::PW, IPL = C::IPL;
+    constexpr bool WS = C::WS;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     S *stage_all = reinterpret_cast<S *>(smem_raw);
     Partials<T> *part_all = reinterpret_cast<Partials<T> *>(smem_raw + kWarps * sizeof(S));
@@ -375,9 +388,10 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
     int carry_xy = -1, carry_z = -1;
 
     auto load_k = [&](int k) {
-        const int sbase = cur_p - plane0 + slot0;
+        const int sbase = cur_p - plane0 + slot0 + q0;
 #pragma unroll
         for (int q = 0; q < PW; ++q) {
+            if (WS && W % PW != 0 && q0 + q >= W) continue;  // ragged last pass: stays zero
             const cplx<T> *base = ring + (long long)wrap_inc(sbase + q, g.nslots) * g.plane_stride;
             const cplx<T> c = base[coff[k]];
             gv[k][q] = mk2(c.re, c.im);
@@ -403,7 +417,7 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
         bool my_flip = false;
         int oxy = 0, oz = 0;
         if (active)
-            prepare<T, W, WS, false>(g, tab, my_idx, lane, st, cplx<T>{T(1), T(1)}, my_flip, oxy, oz);
+            prepare<T, W, PWB, false>(g, tab, my_idx, lane, st, cplx<T>{T(1), T(1)}, q0, my_flip, oxy, oz);
         const unsigned act = __ballot_sync(kFull, active);
         const unsigned mov = moved_mask(active, oxy, oz, lane, act, carry_xy, carry_z);
         __syncwarp();
@@ -445,8 +459,8 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
 #pragma unroll 4
                 for (; v < vend; ++v) {
                     T kwr[C::KW_N16 * C::KW_V], kur[IPL], kvr;
-                    if (WS) load_kw<T, W, WS, false>(st, v, kwr);
-                    load_kuv<T, W, WS, false>(st, v, i0, j, kur, kvr);
+                    if (WS) load_kw<T, W, PWB, false>(st, v, kwr);
+                    load_kuv<T, W, PWB, false>(st, v, i0, j, kur, kvr);
                     P s = mk2(T(0), T(0));
 #pragma unroll
                     for (int k = 0; k < IPL; ++k) {
@@ -478,7 +492,13 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
         }
         if (lane < n) {
             if (my_flip) res.y = -res.y;
-            out[my_idx] = cplx<T>{res.x * my_w, res.y * my_w};
+            cplx<T> r{res.x * my_w, res.y * my_w};
+            if (q0 > 0) {  // later passes add their planes' share
+                const cplx<T> prev = out[my_idx];
+                r.re += prev.re;
+                r.im += prev.im;
+            }
+            out[my_idx] = r;
         }
         __syncwarp();
     }
@@ -493,43 +513,49 @@ static unsigned nblocks_for(long long n)
     return (unsigned)((n + per_block - 1) / per_block);
 }
 
-template <typename T, int W, bool WS> static int grid_inst(const VisLaunch<T> &L)
+template <typename T, int W, int PWB> static int grid_inst(const VisLaunch<T> &L)
 {
     const long long n = L.end - L.begin;
     if (n <= 0) return 0;
-    const size_t smem = kWarps * sizeof(Stage<T, W, WS, true>);
-    cudaError_t e = cudaFuncSetAttribute(grid_warprun_kernel<T, W, WS>,
+    const size_t smem = kWarps * sizeof(Stage<T, W, PWB, true>);
+    cudaError_t e = cudaFuncSetAttribute(grid_warprun_kernel<T, W, PWB>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
-    grid_warprun_kernel<T, W, WS><<<nblocks_for(n), 32 * kWarps, smem, L.stream>>>(
-        L.geo, make_tab<T, W>(L.coef), L.sidx, L.begin, L.end, L.plane0, L.slot0, L.ms, L.wgt,
-        L.ring);
-    return (int)cudaGetLastError();
+    // one pass per group of PWB w-planes of the samples' support
+    for (int q0 = 0; q0 < (PWB > 0 ? W : 1); q0 += (PWB > 0 ? PWB : 1)) {
+        grid_warprun_kernel<T, W, PWB><<<nblocks_for(n), 32 * kWarps, smem, L.stream>>>(
+            L.geo, make_tab<T, W>(L.coef), L.sidx, L.begin, L.end, L.plane0, L.slot0, q0, L.ms,
+            L.wgt, L.ring);
+        if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;
+    }
+    return 0;
 }
-template <typename T, int W, bool WS> static int degrid_inst(const VisLaunch<T> &L)
+template <typename T, int W, int PWB> static int degrid_inst(const VisLaunch<T> &L)
 {
     const long long n = L.end - L.begin;
     if (n <= 0) return 0;
-    const size_t smem = kWarps * (sizeof(Stage<T, W, WS, false>) + sizeof(Partials<T>));
-    cudaError_t e = cudaFuncSetAttribute(degrid_warprun_kernel<T, W, WS>,
+    const size_t smem = kWarps * (sizeof(Stage<T, W, PWB, false>) + sizeof(Partials<T>));
+    cudaError_t e = cudaFuncSetAttribute(degrid_warprun_kernel<T, W, PWB>,
                                          cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
-    degrid_warprun_kernel<T, W, WS><<<nblocks_for(n), 32 * kWarps, smem, L.stream>>>(
-        L.geo, make_tab<T, W>(L.coef), L.sidx, L.begin, L.end, L.plane0, L.slot0, L.wgt,
-        L.ms_out, L.ring);
-    return (int)cudaGetLastError();
+    for (int q0 = 0; q0 < (PWB > 0 ? W : 1); q0 += (PWB > 0 ? PWB : 1)) {
+        degrid_warprun_kernel<T, W, PWB><<<nblocks_for(n), 32 * kWarps, smem, L.stream>>>(
+            L.geo, make_tab<T, W>(L.coef), L.sidx, L.begin, L.end, L.plane0, L.slot0, q0, L.wgt,
+            L.ms_out, L.ring);
+        if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;
+    }
+    return 0;
 }
 
 template <> bool warprun_supported<float>(int W, bool) { return W >= 4 && W <= 8; }
-template <> bool warprun_supported<double>(int W, bool wstack)
-{
-    return W >= 4 && (wstack ? W <= 8 : W <= 16);
-}
+template <> bool warprun_supported<double>(int W, bool) { return W >= 4 && W <= 16; }
 
+// w-stacking: all W planes in one pass up to W = 8; wider (fp64-only) kernels keep 4 (W <= 12)
+// or 3 planes per pass in registers and run ceil(W/4) or ceil(W/3) passes
 #define B2G_CASE(FN, WW) \
-    case WW: return L.wstack ? FN<T, WW, true>(L) : FN<T, WW, false>(L);
-#define B2G_CASE2D(FN, WW) \
-    case WW: return L.wstack ? -1 : FN<T, WW, false>(L);
+    case WW: return L.wstack ? FN<T, WW, WW>(L) : FN<T, WW, 0>(L);
+#define B2G_CASE_WIDE(FN, WW) \
+    case WW: return L.wstack ? FN<T, WW, (WW <= 12 ? 4 : 3)>(L) : FN<T, WW, 0>(L);
 
 template <> int launch_grid_warprun<float>(const VisLaunch<float> &L)
 {
@@ -555,9 +581,9 @@ template <> int launch_grid_warprun<double>(const VisLaunch<double> &L)
     switch (L.W) {
         B2G_CASE(grid_inst, 4) B2G_CASE(grid_inst, 5) B2G_CASE(grid_inst, 6)
         B2G_CASE(grid_inst, 7) B2G_CASE(grid_inst, 8)
-        B2G_CASE2D(grid_inst, 9) B2G_CASE2D(grid_inst, 10) B2G_CASE2D(grid_inst, 11)
-        B2G_CASE2D(grid_inst, 12) B2G_CASE2D(grid_inst, 13) B2G_CASE2D(grid_inst, 14)
-        B2G_CASE2D(grid_inst, 15) B2G_CASE2D(grid_inst, 16)
+        B2G_CASE_WIDE(grid_inst, 9) B2G_CASE_WIDE(grid_inst, 10) B2G_CASE_WIDE(grid_inst, 11)
+        B2G_CASE_WIDE(grid_inst, 12) B2G_CASE_WIDE(grid_inst, 13) B2G_CASE_WIDE(grid_inst, 14)
+        B2G_CASE_WIDE(grid_inst, 15) B2G_CASE_WIDE(grid_inst, 16)
     default: return -1;
     }
 }
@@ -567,9 +593,9 @@ template <> int launch_degrid_warprun<double>(const VisLaunch<double> &L)
     switch (L.W) {
         B2G_CASE(degrid_inst, 4) B2G_CASE(degrid_inst, 5) B2G_CASE(degrid_inst, 6)
         B2G_CASE(degrid_inst, 7) B2G_CASE(degrid_inst, 8)
-        B2G_CASE2D(degrid_inst, 9) B2G_CASE2D(degrid_inst, 10) B2G_CASE2D(degrid_inst, 11)
-        B2G_CASE2D(degrid_inst, 12) B2G_CASE2D(degrid_inst, 13) B2G_CASE2D(degrid_inst, 14)
-        B2G_CASE2D(degrid_inst, 15) B2G_CASE2D(degrid_inst, 16)
+        B2G_CASE_WIDE(degrid_inst, 9) B2G_CASE_WIDE(degrid_inst, 10) B2G_CASE_WIDE(degrid_inst, 11)
+        B2G_CASE_WIDE(degrid_inst, 12) B2G_CASE_WIDE(degrid_inst, 13) B2G_CASE_WIDE(degrid_inst, 14)
+        B2G_CASE_WIDE(degrid_inst, 15) B2G_CASE_WIDE(degrid_inst, 16)
     default: return -1;
     }
 }
