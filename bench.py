@@ -467,9 +467,32 @@ def main():
     ap.add_argument("--no-cpu", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
-    if args.impl == "reference":
-        return run_reference(args)
-    return run_b200(args)
+    # stdout carries exactly one JSON line: whatever libraries print while the job runs
+    # (e.g. NCCL's version banner) goes to stderr
+    sys.stdout.flush()
+    saved = os.dup(1)
+    os.dup2(2, 1)
+    lines = []
+    real_print = print
+
+    def capture(*a, **k):
+        if k.get("file") in (None, sys.stdout):
+            lines.append(" ".join(str(x) for x in a))
+        else:
+            real_print(*a, **k)
+
+    import builtins
+    builtins.print = capture
+    try:
+        rc = run_reference(args) if args.impl == "reference" else run_b200(args)
+    finally:
+        builtins.print = real_print
+        sys.stdout.flush()
+        os.dup2(saved, 1)
+        os.close(saved)
+    for line in lines:
+        real_print(line, flush=True)
+    return rc
 
 
 if __name__ == "__main__":

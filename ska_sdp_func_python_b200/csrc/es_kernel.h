@@ -168,17 +168,20 @@ struct PolyKernel {
     }
 };
 
-// FFT-friendly even size >= n with prime factors {2,3,5,7} (cuFFT's fast radices).
+// FFT-friendly even size >= n: 2^a * 3^b * 5^c with a >= 3, b <= 2, c <= 2.  Measured on B200
+// (cuFFT 12.9, 2-D c2c in place): such sizes run at 3.5-3.7 TB/s of plane traffic (4 plane
+// passes), sizes with a factor 7 or many odd factors (16800 = 2^5*3*5^2*7) at 1.4 TB/s.
 inline int64_t good_size_even(int64_t n)
 {
-    if (n < 2) n = 2;
-    int64_t half = (n + 1) / 2;
-    for (int64_t m = half;; ++m) {
-        int64_t r = m;
-        for (int p : {2, 3, 5, 7})
-            while (r % p == 0) r /= p;
-        if (r == 1) return 2 * m;
-    }
+    if (n < 8) n = 8;
+    int64_t best = -1;
+    for (int64_t p5 = 1, c = 0; c <= 2; ++c, p5 *= 5)
+        for (int64_t p3 = 1, b = 0; b <= 2; ++b, p3 *= 3) {
+            int64_t m = 8 * p3 * p5;
+            while (m < n) m *= 2;
+            if (best < 0 || m < best) best = m;
+        }
+    return best;
 }
 
 inline int cols_per_lane(int W) { return (W * W + 31) / 32; }
@@ -196,14 +199,27 @@ inline double cost_model(int W, double sigma, bool wstack, double nvis, int64_t 
     const int64_t nv = good_size_even((int64_t)std::ceil(sigma * npix_y));
     const int pw = wstack ? W : 1;
     const double nplanes = wstack ? std::ceil(planes_per_sigma * sigma) + W : 1.0;
-    const double fp = csize == 8 ? 1.0 : 2.5;
-    const double instr = 30.0 + cols_per_lane(W) * (8.0 + 2.5 * pw);
-    double t_vis = nvis * instr * fp / 4.0e11;
+    // visibility side: warp instructions per sample of the warp-run kernels (measured on C2:
+    // 40 for W = 7 gridding, ~1.3x that for degridding), issued at ~62 % of 148 SMs x 4
+    // schedulers x 1.965 GHz; fp64 FMAs issue at half rate and wide kernels re-run the
+    // preparation once per group of planes
+    const int jl = W <= 5 ? W : (W <= 8 ? 8 : 16);
+    const int ipl = (W + 32 / jl - 1) / (32 / jl);
+    const double fp = csize == 8 ? 1.0 : 2.0;
+    const double prep = 16.0 * (csize == 8 ? 1.0 : W / 8.0 + 1.0);
+    const double passes = (wstack && W > 8) ? std::ceil(W / (W <= 12 ? 4.0 : 3.0)) : 1.0;
+    const double instr = passes * prep + 0.5 * pw + ipl * (2.0 + pw) * fp;
+    double t_vis = 1.15 * nvis * instr / 7.2e11;
+    // sparse uv coverage: every sample that opens a new footprint flushes / reloads its cells
     const double density = nvis / (double(nu) * double(nv) * std::max(1.0, nplanes - W + 1));
-    const double flushes = std::min(1.0, 1.0 / std::max(density, 1e-30)) * W * pw;
-    t_vis += nvis * flushes * 1.3 * fp / (148.0 * 1.5e9);
-    const double t_img = nplanes * (double(nu) * double(nv) * 6.0 * csize +
-                                    double(npix_x) * npix_y * 3.0 * (csize / 2)) / 5.0e12;
+    const double moved = std::min(1.0, 1.0 / std::max(density, 1e-30));
+    t_vis += nvis * moved * (W * pw * 1.2 + 60.0) * fp / 7.2e11 / 4.0;
+    // image side per w-plane: cuFFT = 4 passes over the padded plane at ~3.3 TB/s, one more
+    // plane pass for the memset (invert) or the screen write (predict) and the cropped read at
+    // ~6 TB/s
+    const double plane = double(nu) * double(nv) * csize;
+    const double t_img = nplanes * (plane * (4.0 / 3.3e12 + 1.5 / 6.0e12) +
+                                    double(npix_x) * npix_y * csize / 6.0e12);
     return t_vis + t_img;
 }
 

@@ -51,16 +51,16 @@ template <typename T> bool warprun_supported(int W, bool wstack);
 template <typename T> int launch_grid_warprun(const VisLaunch<T> &L);
 template <typename T> int launch_degrid_warprun(const VisLaunch<T> &L);
 
-// Sort keys: key = ((chunk*nplanes + p0)*nu + iu0)*nv + iv0, chunk = row / rows_per_chunk (0 if
-// rows_per_chunk == 0); also a histogram of p0 (plane_counts[nplanes]).
-int launch_keygen(const VisGeo &geo, int W, long long nvis, uint32_t rows_per_chunk,
-                  uint64_t *keys, uint32_t *idx, unsigned long long *plane_counts,
-                  cudaStream_t stream);
+// Histogram of the first w-plane p0 of every sample (plane_counts[nplanes]): slab boundaries.
+int launch_plane_hist(const VisGeo &geo, int W, long long nvis, unsigned long long *plane_counts,
+                      cudaStream_t stream);
 
-// Radix sort of (key, idx) pairs on the lowest key_bits bits; result in keys_out/idx_out.
+// Radix sort of the sample indices 0..n-1 by key = ((chunk*nplanes + p0)*nu + iu0)*nv + iv0
+// (chunk = row / rows_per_chunk, 0 if rows_per_chunk == 0) on its lowest key_bits bits; the
+// key is recomputed from the index in every pass.  Result in idx_out, idx_tmp is scratch.
 // Returns 0 or a cudaError_t.
-int sort_pairs(uint64_t *keys_in, uint64_t *keys_out, uint32_t *idx_in, uint32_t *idx_out,
-               long long n, int key_bits, cudaStream_t stream);
+int sort_samples(const VisGeo &geo, int W, uint32_t rows_per_chunk, uint32_t *idx_tmp,
+                 uint32_t *idx_out, long long n, int key_bits, cudaStream_t stream);
 
 // uvw statistics over rows: out = {min|w|, max|w|, max|u|, max|v|} (metres)
 int launch_uvw_stats(const double *uvw, long long nrow, double *out4_dev, cudaStream_t stream);

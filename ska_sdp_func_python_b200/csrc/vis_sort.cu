@@ -1,6 +1,6 @@
 // vis_sort.cu -- the uv-cell / w-plane sort ("bucket") pass.
 //
-// Every visibility gets the key  ((chunk*nplanes + p0)*nu + iu0)*nv + iv0  where chunk is the
+// Every visibility has the key  ((chunk*nplanes + p0)*nu + iu0)*nv + iv0  where chunk is the
 // row chunk of a host-streaming plan (0 otherwise) and (iu0, iv0, p0) is the
 // lower corner of its kernel footprint (first cell in u and v, first w-plane), and the
 // (key, index) pairs are radix-sorted; a histogram of p0 gives the slab boundaries.  This is the B200 counterpart of the scan/bucket pass at the start
@@ -10,21 +10,40 @@
 // per visibility and exact, because the gridding kernels accumulate runs of identical
 // origins in registers.
 //
+// The sort moves 4-byte sample indices only: every pass recomputes the key of a sample from
+// its index (locate() is ~60 fp64/integer instructions, cheaper than carrying 8-byte keys
+// through HBM twice per pass), so the scratch is one index array (4 B/sample) next to the
+// result instead of 20 B/sample -- what lets the 4e9-sample C4 plan fit one GPU.
+//
 // LSD radix sort, 8 bits per pass, three kernels per pass:
 //   1. per-tile digit histogram (shared-memory counters, one tile = 4096 pairs per block)
 //   2. exclusive scan of the [digit][tile] table (single cooperative-free two-level scan)
 //   3. stable scatter: each warp ranks its 128-pair strip with match.any, strips are
 //      combined through a shared-memory digit table.
+#include <algorithm>
+
 #include "kernels.h"
 
 namespace b2g {
 
 namespace {
 
+// key of sample idx: ((chunk*nplanes + p0)*nu + iu0)*nv + iv0
+__device__ __forceinline__ uint64_t sample_key(const VisGeo &g, int W, uint32_t rows_per_chunk,
+                                               uint32_t idx, int *p0_out = nullptr)
+{
+    uint32_t row, chan;
+    g.split(idx, row, chan);
+    const Located L = locate(g, W, row, chan);
+    if (p0_out) *p0_out = L.p0;
+    // row chunks (host-streaming plans) are the most significant key component
+    uint64_t key = rows_per_chunk ? (uint64_t)(row / rows_per_chunk) * (uint64_t)g.nplanes : 0ull;
+    key = (key + (uint64_t)L.p0) * (uint64_t)g.nu + (uint64_t)L.iu0;
+    return key * (uint64_t)g.nv + (uint64_t)L.iv0;
+}
+
 __global__ void __launch_bounds__(256)
-keygen_kernel(VisGeo g, int W, long long nvis, uint32_t rows_per_chunk,
-              uint64_t *__restrict__ keys, uint32_t *__restrict__ idx,
-              unsigned long long *__restrict__ plane_counts)
+plane_hist_kernel(VisGeo g, int W, long long nvis, unsigned long long *__restrict__ plane_counts)
 {
     extern __shared__ unsigned int sh_cnt[];  // [nplanes] when nplanes <= 4096
     const int np = g.nplanes;
@@ -33,18 +52,12 @@ keygen_kernel(VisGeo g, int W, long long nvis, uint32_t rows_per_chunk,
         for (int i = threadIdx.x; i < np; i += blockDim.x) sh_cnt[i] = 0;
         __syncthreads();
     }
-    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i < nvis) {
-        const uint32_t row = (uint32_t)(i / g.nchan), chan = (uint32_t)(i - (long long)row * g.nchan);
-        const Located L = locate(g, W, row, chan);
-        // row chunks (host-streaming plans) are the most significant key component
-        uint64_t key = rows_per_chunk ? (uint64_t)(row / rows_per_chunk) * (uint64_t)g.nplanes : 0ull;
-        key = (key + (uint64_t)L.p0) * (uint64_t)g.nu + (uint64_t)L.iu0;
-        key = key * (uint64_t)g.nv + (uint64_t)L.iv0;
-        keys[i] = key;
-        idx[i] = (uint32_t)i;
-        if (use_sh) atomicAdd(&sh_cnt[L.p0], 1u);
-        else atomicAdd(&plane_counts[L.p0], 1ull);
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < nvis;
+         i += (long long)gridDim.x * blockDim.x) {
+        int p0;
+        sample_key(g, W, 0u, (uint32_t)i, &p0);
+        if (use_sh) atomicAdd(&sh_cnt[p0], 1u);
+        else atomicAdd(&plane_counts[p0], 1ull);
     }
     if (use_sh) {
         __syncthreads();
@@ -60,7 +73,8 @@ constexpr int kItems = 16;                          // pairs per thread
 constexpr int kTile = kSortThreads * kItems;        // 4096 pairs per block
 
 __global__ void __launch_bounds__(kSortThreads)
-radix_hist_kernel(const uint64_t *__restrict__ keys, long long n, int shift, int ntiles,
+radix_hist_kernel(VisGeo g, int W, uint32_t rows_per_chunk, const uint32_t *__restrict__ idx_in,
+                  long long n, int shift, int ntiles,
                   uint32_t *__restrict__ table /* [kRadix][ntiles] */)
 {
     __shared__ unsigned int cnt[kRadix];
@@ -73,7 +87,8 @@ radix_hist_kernel(const uint64_t *__restrict__ keys, long long n, int shift, int
         const bool live = i < n;
         const unsigned livemask = __ballot_sync(0xffffffffu, live);
         if (live) {
-            const unsigned d = (unsigned)(keys[i] >> shift) & (kRadix - 1);
+            const uint32_t id = idx_in ? idx_in[i] : (uint32_t)i;  // first pass: identity
+            const unsigned d = (unsigned)(sample_key(g, W, rows_per_chunk, id) >> shift) & (kRadix - 1);
             // warp-aggregated increment: consecutive visibilities mostly share the digit
             const unsigned peers = __match_any_sync(livemask, d);
             if ((int)(threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(&cnt[d], __popc(peers));
@@ -168,9 +183,9 @@ scan_apply_kernel(const uint32_t *__restrict__ in, long long n, const uint64_t *
 // pairs in input order.  Within a round: warp-level ranks by match.any, cross-warp
 // offsets through warp_cnt[warp][digit]; running per-digit offsets carry across rounds.
 __global__ void __launch_bounds__(kSortThreads)
-radix_scatter_kernel(const uint64_t *__restrict__ keys_in, const uint32_t *__restrict__ idx_in,
-                     uint64_t *__restrict__ keys_out, uint32_t *__restrict__ idx_out, long long n,
-                     int shift, int ntiles, const uint64_t *__restrict__ offs /* [kRadix][ntiles] */)
+radix_scatter_kernel(VisGeo g, int W, uint32_t rows_per_chunk, const uint32_t *__restrict__ idx_in,
+                     uint32_t *__restrict__ idx_out, long long n, int shift, int ntiles,
+                     const uint64_t *__restrict__ offs /* [kRadix][ntiles] */)
 {
     constexpr int NW = kSortThreads / 32;
     __shared__ unsigned long long dig_base[kRadix];   // global position of next pair of digit d
@@ -183,13 +198,11 @@ radix_scatter_kernel(const uint64_t *__restrict__ keys_in, const uint32_t *__res
         __syncthreads();
         const long long i = base + (long long)it * kSortThreads + threadIdx.x;
         const bool live = i < n;
-        uint64_t key = 0;
         uint32_t id = 0;
         unsigned d = 0, rank_in_warp = 0;
         if (live) {
-            key = keys_in[i];
-            id = idx_in[i];
-            d = (unsigned)(key >> shift) & (kRadix - 1);
+            id = idx_in ? idx_in[i] : (uint32_t)i;
+            d = (unsigned)(sample_key(g, W, rows_per_chunk, id) >> shift) & (kRadix - 1);
         }
         const unsigned livemask = __ballot_sync(0xffffffffu, live);
         if (live) {
@@ -211,31 +224,28 @@ radix_scatter_kernel(const uint64_t *__restrict__ keys_in, const uint32_t *__res
             for (int w = 0; w < NW; ++w) tot += warp_cnt[w][threadIdx.x];
             dig_base[threadIdx.x] += tot;
         }
-        if (live) {
-            keys_out[pos] = key;
-            idx_out[pos] = id;
-        }
+        if (live) idx_out[pos] = id;
         __syncthreads();
     }
 }
 
 }  // namespace
 
-int launch_keygen(const VisGeo &geo, int W, long long nvis, uint32_t rows_per_chunk,
-                  uint64_t *keys, uint32_t *idx, unsigned long long *plane_counts,
-                  cudaStream_t stream)
+int launch_plane_hist(const VisGeo &geo, int W, long long nvis, unsigned long long *plane_counts,
+                      cudaStream_t stream)
 {
     cudaMemsetAsync(plane_counts, 0, sizeof(unsigned long long) * geo.nplanes, stream);
     if (nvis <= 0) return 0;
-    const unsigned blocks = (unsigned)((nvis + 255) / 256);
+    const unsigned blocks = (unsigned)std::min<long long>((nvis + 255) / 256, 148 * 32);
     const size_t sh = geo.nplanes <= 4096 ? sizeof(unsigned int) * geo.nplanes : 0;
-    keygen_kernel<<<blocks, 256, sh, stream>>>(geo, W, nvis, rows_per_chunk, keys, idx, plane_counts);
+    plane_hist_kernel<<<blocks, 256, sh, stream>>>(geo, W, nvis, plane_counts);
     return (int)cudaGetLastError();
 }
 
-// Scratch is allocated per call with the stream-ordered allocator.
-int sort_pairs(uint64_t *keys_in, uint64_t *keys_out, uint32_t *idx_in, uint32_t *idx_out,
-               long long n, int key_bits, cudaStream_t stream)
+// Sorted sample indices into idx_out; idx_tmp is the one scratch array (n entries each).
+// Table scratch is allocated per call with the stream-ordered allocator.
+int sort_samples(const VisGeo &geo, int W, uint32_t rows_per_chunk, uint32_t *idx_tmp,
+                 uint32_t *idx_out, long long n, int key_bits, cudaStream_t stream)
 {
     if (n <= 0) return 0;
     const int ntiles = (int)((n + kTile - 1) / kTile);
@@ -247,26 +257,22 @@ int sort_pairs(uint64_t *keys_in, uint64_t *keys_out, uint32_t *idx_in, uint32_t
     if ((e = cudaMallocAsync(&table, sizeof(uint32_t) * tab_n, stream)) != cudaSuccess) return (int)e;
     if ((e = cudaMallocAsync(&offs, sizeof(uint64_t) * tab_n, stream)) != cudaSuccess) return (int)e;
     if ((e = cudaMallocAsync(&bsum, sizeof(uint64_t) * nb, stream)) != cudaSuccess) return (int)e;
-    // ping-pong: pass 0 reads *_in and writes *_out, pass 1 the other way round, ...
-    uint64_t *ka = keys_in, *kb = keys_out;
-    uint32_t *ia = idx_in, *ib = idx_out;
     int npass = (key_bits + kRadixBits - 1) / kRadixBits;
     if (npass < 1) npass = 1;
+    // ping-pong so that the last pass writes idx_out; the first pass reads the identity
+    const uint32_t *src = nullptr;
+    uint32_t *dst = (npass & 1) ? idx_out : idx_tmp;
     for (int p = 0; p < npass; ++p) {
         const int shift = p * kRadixBits;
-        radix_hist_kernel<<<ntiles, kSortThreads, 0, stream>>>(ka, n, shift, ntiles, table);
+        radix_hist_kernel<<<ntiles, kSortThreads, 0, stream>>>(geo, W, rows_per_chunk, src, n, shift,
+                                                              ntiles, table);
         scan_partial_kernel<<<(unsigned)nb, 256, 0, stream>>>(table, tab_n, bsum);
         scan_finish_kernel<<<1, 1024, 0, stream>>>(bsum, nb);
         scan_apply_kernel<<<(unsigned)nb, 256, 0, stream>>>(table, tab_n, bsum, offs);
-        radix_scatter_kernel<<<ntiles, kSortThreads, 0, stream>>>(ka, ia, kb, ib, n, shift, ntiles,
-                                                                 offs);
-        uint64_t *tk = ka; ka = kb; kb = tk;
-        uint32_t *ti = ia; ia = ib; ib = ti;
-    }
-    // result is in (ka, ia); make sure it ends in the *_out buffers
-    if (ka != keys_out) {
-        cudaMemcpyAsync(keys_out, ka, sizeof(uint64_t) * n, cudaMemcpyDeviceToDevice, stream);
-        cudaMemcpyAsync(idx_out, ia, sizeof(uint32_t) * n, cudaMemcpyDeviceToDevice, stream);
+        radix_scatter_kernel<<<ntiles, kSortThreads, 0, stream>>>(geo, W, rows_per_chunk, src, dst, n,
+                                                                 shift, ntiles, offs);
+        src = dst;
+        dst = (dst == idx_out) ? idx_tmp : idx_out;
     }
     cudaFreeAsync(table, stream);
     cudaFreeAsync(offs, stream);

@@ -118,6 +118,16 @@ def observation(config, seed=SEED, ntimes=None, nchan=None, row_fraction=1.0):
     freq = np.linspace(cfg["f0"], cfg["f1"], nc) if nc > 1 else np.array([cfg["f0"]])
     uvmax = np.abs(uvw[:, :2]).max() * cfg["f1"] / C_M_S
     cellsize = cfg.get("cellsize") or 1.0 / (4.0 * uvmax)
+    if cfg.get("nplanes"):
+        # w rescaled by a constant so that the reference model (sigma = 1.5,
+        # W = 7, dw = 1/(2 sigma max|n-1|)) needs ceil((wmax-wmin)/dw) + W = nplanes w-planes
+        xm = cellsize * cfg["npix"] / 2.0
+        r2 = 2.0 * xm * xm
+        nm1 = r2 / (np.sqrt(1.0 - r2) + 1.0)
+        dw = 0.5 / (1.5 * nm1)
+        wmax = np.abs(uvw[:, 2]).max() * cfg["f1"] / C_M_S
+        uvw = uvw.copy()
+        uvw[:, 2] *= (cfg["nplanes"] - 7 - 0.5) * dw / wmax
     return dict(name=name, uvw=np.ascontiguousarray(uvw), freq=freq, auto=auto, nbaselines=nbl,
                 ntimes=nt, npix=cfg["npix"], cellsize=float(cellsize), epsilon=cfg["epsilon"],
                 precision=cfg["precision"], nplanes=cfg.get("nplanes"))

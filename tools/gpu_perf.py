@@ -60,7 +60,7 @@ def main():
               + " ".join(f"{k}={v:.2f}" for k, v in ti.items() if k != "total"))
         print(f"       predict {tp['total']:.2f} ms ({nrow * nchan / tp['total'] / 1e6:.1f} Gvis/s)  "
               + " ".join(f"{k}={v:.2f}" for k, v in tp.items() if k != "total"))
-    print("dirty stats", float(dirty.abs().max()), "vis stats", float(vis.abs().max()))
+    print("dirty stats", float(dirty.abs().max()), "vis[:1000] stats", float(vis[:1000].abs().max()))
 
 
 if __name__ == "__main__":
