@@ -8,7 +8,8 @@ import ctypes
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb200wgridder.so")
+# B2G_LIB: development override (kernel variants built side by side)
+LIB_PATH = os.environ.get("B2G_LIB") or os.path.join(_HERE, "libb200wgridder.so")
 
 F32, F64 = 0, 1
 HOST, DEVICE = 0, 1

@@ -21,6 +21,7 @@ namespace b2g {
 struct KernelRow {
     int W;
     double sigma, beta, e0, eps, eps_max;
+    double amp;  // psihat(0) / psihat(1/(2 sigma)): rim amplification of the gridding correction
 };
 
 static const KernelRow kKernelDB[] = {
@@ -225,14 +226,14 @@ inline double cost_model(int W, double sigma, bool wstack, double nvis, int64_t 
 
 // Pick the cheapest table row whose error meets eps_dim (per-dimension target).
 // Returns index into kKernelDB or -1.
-inline int select_kernel(double eps_dim, bool wstack, int maxW, double nvis, int64_t npix_x,
-                         int64_t npix_y, double planes_per_sigma, int csize)
+inline int select_kernel(double eps_dim, double amp_max, bool wstack, int maxW, double nvis,
+                         int64_t npix_x, int64_t npix_y, double planes_per_sigma, int csize)
 {
     int best = -1;
     double bestc = 0;
     for (int i = 0; i < kKernelDBSize; ++i) {
         const KernelRow &r = kKernelDB[i];
-        if (r.W > maxW || r.eps > eps_dim) continue;
+        if (r.W > maxW || r.eps > eps_dim || r.amp > amp_max) continue;
         double c = cost_model(r.W, r.sigma, wstack, nvis, npix_x, npix_y, planes_per_sigma, csize);
         if (best < 0 || c < bestc) {
             best = i;

@@ -274,11 +274,15 @@ int choose_kernel(double epsilon, bool wstack, int precision, int64_t npix_x, in
 {
     if (!(epsilon > 0.0)) return fail("epsilon must be positive (got %g)", epsilon);
     // Error budget: the aliasing errors of the 2 (3) separable dimensions add in quadrature;
-    // 1.5x head-room covers the polynomial fit and the difference between the tabulated
+    // 1.75x head-room covers the polynomial fit and the difference between the tabulated
     // mean over |x| <= 1/(2 sigma) and the actual image; `floor` is the rounding noise of
     // the arithmetic type, which no kernel can remove.
     const double floor = precision == B2G_F32 ? 6e-7 : 3e-13;
-    const double eps_dim = (epsilon - floor) / (1.5 * std::sqrt(wstack ? 3.0 : 2.0));
+    const double eps_dim = (epsilon - floor) / (1.75 * std::sqrt(wstack ? 3.0 : 2.0));
+    // Small oversampling with a wide kernel makes psi-hat tiny at the image rim: the correction
+    // 1/psi-hat(x) psi-hat(y) then amplifies a corner pixel (and the rounding noise around it) by
+    // amp^2.  Keep machine-epsilon * amp^2 below a quarter of the requested accuracy.
+    const double amp_max = std::sqrt(0.25 * epsilon / (precision == B2G_F32 ? 6e-8 : 1.1e-16));
     const int maxW = precision == B2G_F32 ? 8 : kMaxW;
     const int csize = precision == B2G_F32 ? 8 : 16;
     if (precision == B2G_F32 && epsilon < 2e-6)
@@ -294,7 +298,7 @@ int choose_kernel(double epsilon, bool wstack, int precision, int64_t npix_x, in
         if (std::sscanf(force, "%d,%lf", &fw, &fsig) == 2)
             for (int i = 0; i < kKernelDBSize; ++i)
                 if (kKernelDB[i].W == fw && std::fabs(kKernelDB[i].sigma - fsig) < 1e-6 &&
-                    kKernelDB[i].eps <= eps_dim && fw <= maxW)
+                    kKernelDB[i].eps <= eps_dim && kKernelDB[i].amp <= amp_max && fw <= maxW)
                     best = i;
     }
     if (best >= 0) {
@@ -305,13 +309,13 @@ int choose_kernel(double epsilon, bool wstack, int precision, int64_t npix_x, in
                         (long long)nv_req);
         for (int i = 0; i < kKernelDBSize; ++i) {
             const KernelRow &r = kKernelDB[i];
-            if (r.W > maxW || r.eps > eps_dim || r.sigma > smax + 1e-9) continue;
+            if (r.W > maxW || r.eps > eps_dim || r.amp > amp_max || r.sigma > smax + 1e-9) continue;
             if (best < 0 || r.W < kKernelDB[best].W ||
                 (r.W == kKernelDB[best].W && r.sigma > kKernelDB[best].sigma))
                 best = i;
         }
     } else {
-        best = select_kernel(eps_dim, wstack, maxW, nvis, npix_x, npix_y, planes_per_sigma, csize);
+        best = select_kernel(eps_dim, amp_max, wstack, maxW, nvis, npix_x, npix_y, planes_per_sigma, csize);
     }
     if (best < 0)
         return fail("no gridding kernel reaches epsilon=%g in %s precision", epsilon,

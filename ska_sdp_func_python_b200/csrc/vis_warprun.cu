@@ -28,6 +28,13 @@
 //    one 64-bit register pair.
 #include "kernels.h"
 
+#ifndef B2G_MINB_GRID
+#define B2G_MINB_GRID 6
+#endif
+#ifndef B2G_MINB_DEGRID
+#define B2G_MINB_DEGRID 6
+#endif
+
 namespace b2g {
 
 namespace {
@@ -35,6 +42,11 @@ namespace {
 constexpr int kWarps = 4;        // warps per block
 constexpr int kChunk = 256;      // samples per warp (multiple of 32)
 constexpr unsigned kFull = 0xffffffffu;
+
+// resident blocks per SM the register allocation is asked to allow (fp32 kernels only; the
+// fp64 kernels need their registers for the accumulators)
+template <typename T> constexpr int min_blocks(bool grid) { return 1; }
+template <> constexpr int min_blocks<float>(bool grid) { return grid ? B2G_MINB_GRID : B2G_MINB_DEGRID; }
 
 template <typename T> struct Vec16;
 template <> struct Vec16<float> { using type = float4; };
@@ -145,8 +157,19 @@ __device__ __forceinline__ void load_kw(const Stage<T, W, PWB, GRID> &st, int v,
     using C = Cfg<T, W, PWB, GRID>;
     using V = typename Vec16<T>::type;
     const V *src = reinterpret_cast<const V *>(st.kw) + v * C::KW_S16;
+    // whole 16-byte vectors, then the remainder in the widest aligned pieces (a broadcast
+    // LDS.128 costs two shared-memory wavefronts, LDS.64 / LDS.32 one)
+    constexpr int NF = C::KW_T / C::KW_V, REM = C::KW_T % C::KW_V;
 #pragma unroll
-    for (int n = 0; n < C::KW_N16; ++n) *reinterpret_cast<V *>(out + n * C::KW_V) = src[n];
+    for (int n = 0; n < NF; ++n) *reinterpret_cast<V *>(out + n * C::KW_V) = src[n];
+    const T *tail = reinterpret_cast<const T *>(src + NF);
+    if (REM >= 2) {
+        using P = typename V2<T>::type;
+        const P t = *reinterpret_cast<const P *>(tail);
+        out[NF * C::KW_V] = t.x;
+        out[NF * C::KW_V + 1] = t.y;
+    }
+    if (REM & 1) out[NF * C::KW_V + (REM & ~1)] = tail[REM & ~1];
 }
 
 // ku values of this lane's IPL row classes (lane-constant offset i0) and its kv value
@@ -193,7 +216,7 @@ __device__ __forceinline__ unsigned moved_mask(bool active, int oxy, int oz, int
 // Gridding
 // ------------------------------------------------------------------------------------
 template <typename T, int W, int PWB>
-__global__ void __launch_bounds__(32 * kWarps)
+__global__ void __launch_bounds__(32 * kWarps, min_blocks<T>(true))
 grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ sidx,
                     long long begin, long long end, int plane0, int slot0, int q0,
                     const cplx<T> *__restrict__ ms, const T *__restrict__ wgt,
@@ -342,7 +365,7 @@ grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ 
 // Degridding
 // ------------------------------------------------------------------------------------
 template <typename T, int W, int PWB>
-__global__ void __launch_bounds__(32 * kWarps)
+__global__ void __launch_bounds__(32 * kWarps, min_blocks<T>(false))
 degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ sidx,
                       long long begin, long long end, int plane0, int slot0, int q0,
                       const T *__restrict__ wgt, cplx<T> *__restrict__ out,

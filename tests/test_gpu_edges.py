@@ -60,7 +60,8 @@ def test_linearity_and_mask(wg):
     ms2 = np.roll(ms, 7, axis=0)
     with wg.Plan(uvw, freq, 64, 64, 1e-3, 1e-3, 1e-10, True) as p:
         a, b, c = p.invert(ms, wgt), p.invert(ms2, wgt), p.invert(2 * ms - 3 * ms2, wgt)
-    assert rel_max(c, 2 * a - 3 * b) < 1e-12
+    # linear up to fp64 rounding (atomic order, gridding correction towards the rim): << epsilon
+    assert rel_max(c, 2 * a - 3 * b) < 1e-11
     mask = (np.arange(ms.size).reshape(ms.shape) % 3 != 0).astype(np.uint8)
     dm = wg.ms2dirty(uvw, freq, ms, wgt, 64, 64, 1e-3, 1e-3, 0, 0, 1e-10, True, mask=mask)
     dw = wg.ms2dirty(uvw, freq, ms, wgt * mask, 64, 64, 1e-3, 1e-3, 0, 0, 1e-10, True)

@@ -57,7 +57,7 @@ def test_selection_meets_budget(built, prec, eps, ws):
     W, sigma, eps_k = int(out[0]), out[1], out[4]
     assert 4 <= W <= (8 if prec == 0 else 16)
     assert 1.15 <= sigma <= 2.6
-    assert eps_k * 1.5 * np.sqrt(3 if ws else 2) <= eps
+    assert eps_k * 1.75 * np.sqrt(3 if ws else 2) <= eps
 
 
 def test_selection_rejects_unreachable_epsilon(built):
