@@ -86,6 +86,18 @@ int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, const double *
                     double epsilon, int do_wstacking, int precision, int algo,
                     int verbosity, void *stream);
 
+/* Plan over a SUBSET of the observation's samples (w-plane sharding across GPUs, SURVEY.md
+ * section 8e): sel[i] = row*nchan + chan of plan sample i (uint32, same memory space as uvw,
+ * entries < nrow*nchan, no duplicates).  The plan's w-planes cover the selected samples only, and
+ * the ms / wgt arrays of b2g_plan_invert / b2g_plan_predict are then COMPACT: nsel entries in
+ * the order of sel.  A device sel array is referenced, not copied, and must outlive the plan.
+ * sel == NULL gives b2g_plan_create. */
+int b2g_plan_create_sel(b2g_plan **plan, int64_t nrow, int64_t nchan, const double *uvw,
+                        const double *freq, int uvw_space, const uint32_t *sel, int64_t nsel,
+                        int64_t npix_x, int64_t npix_y, double pixsize_x, double pixsize_y,
+                        int64_t nu, int64_t nv, double epsilon, int do_wstacking, int precision,
+                        int algo, int verbosity, void *stream);
+
 void b2g_plan_destroy(b2g_plan *plan);
 
 /* ms2dirty on a plan.  ms/wgt: component type vis_dtype in vis_space;

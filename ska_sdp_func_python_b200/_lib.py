@@ -19,7 +19,7 @@ EXPORTS = (
     "b2g_last_error", "b2g_version", "b2g_plan_create", "b2g_plan_destroy",
     "b2g_plan_invert", "b2g_plan_predict", "b2g_plan_info", "b2g_plan_timings",
     "b2g_ms2dirty", "b2g_dirty2ms", "b2g_sumwt", "b2g_kernel_select", "b2g_kernel_eval",
-    "b2g_kernel_corr", "b2g_vis_prepare", "b2g_vis_finish", "b2g_set_host_chunk_samples",
+    "b2g_kernel_corr", "b2g_vis_prepare", "b2g_vis_finish", "b2g_set_host_chunk_samples", "b2g_plan_create_sel",
 )
 FLAG_NONE, FLAG_U8, FLAG_I32, FLAG_I64, FLAG_F64 = 0, 1, 2, 3, 4
 
@@ -49,6 +49,9 @@ def lib():
     L.b2g_plan_create.restype = ci
     L.b2g_plan_create.argtypes = [ctypes.POINTER(vp), i64, i64, vp, vp, ci, i64, i64, dbl, dbl,
                                   i64, i64, dbl, ci, ci, ci, ci, vp]
+    L.b2g_plan_create_sel.restype = ci
+    L.b2g_plan_create_sel.argtypes = [ctypes.POINTER(vp), i64, i64, vp, vp, ci, vp, i64, i64, i64,
+                                      dbl, dbl, i64, i64, dbl, ci, ci, ci, ci, vp]
     L.b2g_plan_destroy.restype = None
     L.b2g_plan_destroy.argtypes = [vp]
     L.b2g_plan_invert.restype = ci

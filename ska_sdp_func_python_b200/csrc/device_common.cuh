@@ -55,6 +55,8 @@ template <typename T, int W> struct KernelTab {
 struct VisGeo {
     const double *uvw;     // [nrow][3]
     const double *fscale;  // [nchan]
+    const uint32_t *sel;   // optional sample selection: plan sample i is observation sample
+                           // sel[i] = row*nchan + chan (w-plane-sharded plans); NULL = all
     uint32_t nchan;
     uint32_t nchan_mul;   // idx / nchan == (t + ((idx - t) >> nchan_sh1)) >> nchan_sh2,
     int nchan_sh1, nchan_sh2;  //   t = umulhi(nchan_mul, idx)   (set by set_nchan)
@@ -78,6 +80,7 @@ struct VisGeo {
     }
     __device__ __forceinline__ void split(uint32_t idx, uint32_t &row, uint32_t &chan) const
     {
+        if (sel) idx = __ldg(sel + idx);
         const uint32_t t = __umulhi(nchan_mul, idx);
         row = (t + ((idx - t) >> nchan_sh1)) >> nchan_sh2;
         chan = idx - row * nchan;

@@ -62,6 +62,9 @@ int launch_plane_hist(const VisGeo &geo, int W, long long nvis, unsigned long lo
 int sort_samples(const VisGeo &geo, int W, uint32_t rows_per_chunk, uint32_t *idx_tmp,
                  uint32_t *idx_out, long long n, int key_bits, cudaStream_t stream);
 
+// min / max |w| in wavelengths over the selected samples (geo.sel, nsel): out2 = {min, max}
+int launch_sel_wstats(const VisGeo &geo, long long nsel, double *out2_dev, cudaStream_t stream);
+
 // uvw statistics over rows: out = {min|w|, max|w|, max|u|, max|v|} (metres)
 int launch_uvw_stats(const double *uvw, long long nrow, double *out4_dev, cudaStream_t stream);
 

@@ -162,6 +162,8 @@ struct b2g_plan {
     double *d_cu = nullptr, *d_cv = nullptr, *d_cheb = nullptr;
     int ncheb = 0;
     uint32_t *d_sidx = nullptr;
+    const uint32_t *d_sel = nullptr;  // sample selection of a w-plane-sharded plan (NULL = all)
+    bool own_sel = false;
     std::vector<long long> slab_begin;
     // host-streaming plans (nslabs == 1): sorted by (row chunk, p0, iu0, iv0); chunk c holds
     // rows [c*rows_per_chunk, (c+1)*rows_per_chunk)
@@ -200,6 +202,7 @@ struct b2g_plan {
     {
         VisGeo g;
         g.uvw = d_uvw;
+        g.sel = d_sel;
         g.fscale = d_fscale;
         g.set_nchan((uint32_t)nchan);
         g.nu = (int)nu;
@@ -243,6 +246,8 @@ struct b2g_plan {
         if (d_cv) cudaFreeAsync(d_cv, stream);
         if (d_cheb) cudaFreeAsync(d_cheb, stream);
         if (d_sidx) cudaFreeAsync(d_sidx, stream);
+        if (own_sel && d_sel) cudaFreeAsync(const_cast<uint32_t *>(d_sel), stream);
+        d_sel = nullptr;
         if (d_ring) cudaFreeAsync(d_ring, stream);
         if (d_acc) cudaFreeAsync(d_acc, stream);
         if (d_scratch) cudaFreeAsync(d_scratch, stream);
@@ -443,10 +448,24 @@ extern "C" int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, con
                                double epsilon, int do_wstacking, int precision, int algo,
                                int verbosity, void *stream)
 {
+    return b2g_plan_create_sel(plan, nrow, nchan, uvw, freq, uvw_space, nullptr, 0, npix_x, npix_y,
+                               pixsize_x, pixsize_y, nu, nv, epsilon, do_wstacking, precision, algo,
+                               verbosity, stream);
+}
+
+extern "C" int b2g_plan_create_sel(b2g_plan **plan, int64_t nrow, int64_t nchan, const double *uvw,
+                                   const double *freq, int uvw_space, const uint32_t *sel,
+                                   int64_t nsel, int64_t npix_x, int64_t npix_y, double pixsize_x,
+                                   double pixsize_y, int64_t nu, int64_t nv, double epsilon,
+                                   int do_wstacking, int precision, int algo, int verbosity,
+                                   void *stream)
+{
     g_err.clear();
     if (!plan) return fail("plan pointer is NULL");
     *plan = nullptr;
     if (nrow < 0 || nchan < 1) return fail("bad shape nrow=%lld nchan=%lld", (long long)nrow, (long long)nchan);
+    if (nsel < 0 || (nsel > 0 && !sel)) return fail("bad sample selection (nsel=%lld)", (long long)nsel);
+    if (sel && nrow * nchan >= (1ll << 32)) return fail("selection needs nrow*nchan < 2^32");
     if (npix_x < 2 || npix_y < 2 || (npix_x & 1) || (npix_y & 1))
         return fail("image dimensions must be even and >= 2 (got %lld x %lld)", (long long)npix_x,
                     (long long)npix_y);
@@ -480,7 +499,7 @@ extern "C" int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, con
     CUDA_OK(cudaEventRecord(p->ev_plan0, p->stream));
     p->nrow = nrow;
     p->nchan = nchan;
-    p->nvis = nrow * nchan;
+    p->nvis = sel ? nsel : nrow * nchan;
     p->npix_x = npix_x;
     p->npix_y = npix_y;
     p->psx = pixsize_x;
@@ -530,6 +549,32 @@ extern "C" int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, con
         return fail("uvw contains NaN or Inf");
     p->wmin = st[0] * fsmin;
     p->wmax = st[1] * fsmax;
+    if (sel) {
+        // w-plane-sharded plan: the w-range (hence the planes) of the selected samples only
+        if (uvw_space == B2G_DEVICE) {
+            p->d_sel = sel;
+        } else {
+            uint32_t *d = nullptr;
+            CUDA_OK(cudaMallocAsync(&d, sizeof(uint32_t) * std::max<int64_t>(nsel, 1), p->stream));
+            p->d_sel = d;
+            p->own_sel = true;
+            if (nsel > 0)
+                CUDA_OK(cudaMemcpyAsync(d, sel, sizeof(uint32_t) * nsel, cudaMemcpyHostToDevice, p->stream));
+        }
+        VisGeo g0;
+        std::memset(&g0, 0, sizeof(g0));
+        g0.uvw = p->d_uvw;
+        g0.fscale = p->d_fscale;
+        g0.sel = p->d_sel;
+        g0.set_nchan((uint32_t)nchan);
+        double ws[2] = {0, 0};
+        KERNEL_OK(launch_sel_wstats(g0, nsel, p->d_scratch + 8, p->stream));
+        CUDA_OK(cudaMemcpyAsync(ws, p->d_scratch + 8, sizeof(ws), cudaMemcpyDeviceToHost, p->stream));
+        CUDA_OK(cudaStreamSynchronize(p->stream));
+        p->wmin = ws[0];
+        p->wmax = ws[1];
+        if (nsel == 0) p->wmin = p->wmax = 0.0;
+    }
     if (nrow == 0) p->wmin = p->wmax = 0.0;
 
     // field of view -> most negative n-1
@@ -592,7 +637,7 @@ extern "C" int b2g_plan_create(b2g_plan **plan, int64_t nrow, int64_t nchan, con
     // host-streaming plans: row chunks as the outermost sort component (all planes resident)
     {
         const long long per = g_host_chunk_samples.load();
-        if (uvw_space == B2G_HOST && p->nslabs == 1 && per > 0 && p->nvis >= 2 * per) {
+        if (uvw_space == B2G_HOST && !sel && p->nslabs == 1 && per > 0 && p->nvis >= 2 * per) {
             int nc = (int)std::min<long long>(kMaxChunks, p->nvis / per);
             p->rows_per_chunk = (nrow + nc - 1) / nc;
             p->nchunks = (int)((nrow + p->rows_per_chunk - 1) / p->rows_per_chunk);

@@ -66,6 +66,37 @@ plane_hist_kernel(VisGeo g, int W, long long nvis, unsigned long long *__restric
     }
 }
 
+// min / max of |w| in wavelengths over the selected samples of a plan: out2 = {min, max}
+__global__ void __launch_bounds__(256)
+sel_wstats_kernel(VisGeo g, long long nsel, double *__restrict__ out2)
+{
+    __shared__ double sh[2][256];
+    double wmin = 1e300, wmax = 0.0;
+    for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < nsel;
+         i += (long long)gridDim.x * 256) {
+        uint32_t row, chan;
+        g.split((uint32_t)i, row, chan);
+        const double w = fabs(__ldg(g.uvw + 3ull * row + 2) * __ldg(g.fscale + chan));
+        wmin = fmin(wmin, w);
+        wmax = fmax(wmax, w);
+    }
+    sh[0][threadIdx.x] = wmin;
+    sh[1][threadIdx.x] = wmax;
+    __syncthreads();
+    for (int s = 128; s > 0; s >>= 1) {
+        if ((int)threadIdx.x < s) {
+            sh[0][threadIdx.x] = fmin(sh[0][threadIdx.x], sh[0][threadIdx.x + s]);
+            sh[1][threadIdx.x] = fmax(sh[1][threadIdx.x], sh[1][threadIdx.x + s]);
+        }
+        __syncthreads();
+    }
+    if (threadIdx.x == 0) {
+        // non-negative doubles: integer compare on the bit pattern is order-preserving
+        atomicMin((unsigned long long *)&out2[0], (unsigned long long)__double_as_longlong(sh[0][0]));
+        atomicMax((unsigned long long *)&out2[1], (unsigned long long)__double_as_longlong(sh[1][0]));
+    }
+}
+
 constexpr int kRadixBits = 8;
 constexpr int kRadix = 1 << kRadixBits;
 constexpr int kSortThreads = 256;
@@ -230,6 +261,16 @@ radix_scatter_kernel(VisGeo g, int W, uint32_t rows_per_chunk, const uint32_t *_
 }
 
 }  // namespace
+
+int launch_sel_wstats(const VisGeo &geo, long long nsel, double *out2_dev, cudaStream_t stream)
+{
+    const double init[2] = {1e300, 0.0};
+    cudaMemcpyAsync(out2_dev, init, sizeof(init), cudaMemcpyHostToDevice, stream);
+    if (nsel <= 0) return 0;
+    const unsigned blocks = (unsigned)std::min<long long>((nsel + 255) / 256, 148 * 16);
+    sel_wstats_kernel<<<blocks, 256, 0, stream>>>(geo, nsel, out2_dev);
+    return (int)cudaGetLastError();
+}
 
 int launch_plane_hist(const VisGeo &geo, int W, long long nvis, unsigned long long *plane_counts,
                       cudaStream_t stream)

@@ -74,3 +74,97 @@ def predict_sharded(local_predict, model, src=0, group=None):
     if dist.is_available() and dist.is_initialized() and dist.get_world_size(group) > 1:
         dist.broadcast(model, src=src, group=group)
     return local_predict(model)
+
+
+# ----------------------------------------------------------------------------------------
+# w-plane sharding (option 2): rank r owns the samples whose |w| (in
+# wavelengths) lies in [t_r, t_{r+1}).  Its plan then spans only the w-planes of that range (plus
+# the W-1 planes of kernel support), so the per-plane FFT / screen work divides by the number
+# of ranks together with the gridding work.  No exchange between ranks: invert ends with the
+# same single all-reduce of the image, predict outputs are disjoint by construction.
+# ----------------------------------------------------------------------------------------
+C_M_S = 299792458.0
+
+
+def _plane_cost_in_samples(npix, precision):
+    """Cost of one more w-plane (cuFFT passes + screen + memset, es_kernel.h cost model) in units
+    of the cost of one sample."""
+    csize = 8 if precision in ("single", 0) else 16
+    nu = 1.5 * npix
+    t_plane = nu * nu * csize * (4.0 / 3.3e12 + 1.5 / 6.0e12) + npix * npix * csize / 6.0e12
+    t_sample = 65e-12 if csize == 8 else 1.5e-9
+    return t_plane / t_sample
+
+
+def wplane_thresholds(uvw, freq, world_size, npix, pixsize, precision="single", sigma=1.5,
+                      nbins=8192, block_rows=1 << 16):
+    """|w| thresholds t_0 = 0 < t_1 < ... < t_world = inf that balance (samples + planes) cost.
+    uvw: [nrow, 3] metres (numpy or torch, any device), freq: [nchan] Hz.  Deterministic: every
+    rank computes the same thresholds from the same inputs, no communication."""
+    import torch
+    uvw_t = torch.as_tensor(uvw)
+    dev = uvw_t.device
+    w = uvw_t[:, 2].abs().to(torch.float64)
+    fs = torch.as_tensor(np.asarray(freq, dtype=np.float64) / C_M_S, device=dev)
+    wmax = float(w.max().item()) * float(fs.max().item()) if w.numel() else 0.0
+    if world_size <= 1 or wmax <= 0.0:
+        return [0.0] + [float("inf")] * max(1, world_size)
+    hist = torch.zeros(nbins, dtype=torch.float64, device=dev)
+    scale = nbins / (wmax * (1.0 + 1e-12))
+    for r0 in range(0, w.numel(), block_rows):
+        b = (w[r0:r0 + block_rows, None] * fs[None, :] * scale).to(torch.int64).clamp_(0, nbins - 1)
+        hist += torch.bincount(b.reshape(-1), minlength=nbins).to(torch.float64)
+    # plane spacing of the reference model: dw = 1 / (2 sigma max|n-1|)
+    xm = pixsize * npix / 2.0
+    r2 = min(2.0 * xm * xm, 0.999)
+    nm1 = r2 / (np.sqrt(1.0 - r2) + 1.0)
+    dw = 0.5 / (sigma * max(nm1, 1e-12))
+    planes_per_bin = (wmax / nbins) / dw
+    cost = torch.cumsum(hist + planes_per_bin * _plane_cost_in_samples(npix, precision), 0)
+    total = float(cost[-1].item())
+    targets = torch.tensor([total * r / world_size for r in range(1, world_size)],
+                           dtype=torch.float64, device=dev)
+    cut = torch.searchsorted(cost, targets).clamp_(0, nbins - 1).cpu().numpy()
+    edges = [0.0] + [float((c + 1) * wmax / nbins) for c in cut] + [float("inf")]
+    for i in range(1, len(edges)):  # monotone even for degenerate histograms
+        edges[i] = max(edges[i], edges[i - 1])
+    return edges
+
+
+def wplane_selection(uvw, freq, world_size, rank, npix, pixsize, precision="single", sigma=1.5,
+                     thresholds=None, block_rows=1 << 16):
+    """Indices (row*nchan + chan, ascending, int64 tensor on uvw's device) of the samples owned
+    by ``rank`` under w-plane sharding.  The selections of all ranks partition the samples."""
+    import torch
+    if thresholds is None:
+        thresholds = wplane_thresholds(uvw, freq, world_size, npix, pixsize, precision, sigma,
+                                       block_rows=block_rows)
+    lo, hi = thresholds[rank], thresholds[rank + 1]
+    uvw_t = torch.as_tensor(uvw)
+    dev = uvw_t.device
+    w = uvw_t[:, 2].abs().to(torch.float64)
+    fs = torch.as_tensor(np.asarray(freq, dtype=np.float64) / C_M_S, device=dev)
+    nchan = fs.numel()
+    parts = []
+    for r0 in range(0, w.numel(), block_rows):
+        wl = w[r0:r0 + block_rows, None] * fs[None, :]
+        m = (wl >= lo) & (wl < hi)
+        parts.append(torch.nonzero(m.reshape(-1)).reshape(-1) + r0 * nchan)
+    if not parts:
+        return torch.zeros(0, dtype=torch.int64, device=dev)
+    return torch.cat(parts)
+
+
+def compact(samples, sel):
+    """The rank's own entries of a full [nrow, nchan] sample array (torch tensor or numpy)."""
+    import torch
+    if isinstance(samples, np.ndarray):
+        return samples.reshape(-1)[np.asarray(sel.cpu() if hasattr(sel, "cpu") else sel)]
+    return samples.reshape(-1)[torch.as_tensor(sel, device=samples.device)]
+
+
+def scatter_back(full, sel, values):
+    """Write the rank's predicted samples into a full [nrow, nchan] array (in place)."""
+    flat = full.reshape(-1)
+    flat[sel if not isinstance(full, np.ndarray) else np.asarray(sel.cpu() if hasattr(sel, "cpu") else sel)] = values
+    return full

@@ -108,7 +108,7 @@ class Plan:
 
     def __init__(self, uvw, freq, npix_x, npix_y, pixsize_x, pixsize_y, epsilon,
                  do_wstacking=True, precision="double", nu=0, nv=0, algo=ALGO_AUTO,
-                 verbosity=0, stream=None):
+                 verbosity=0, stream=None, sel=None):
         L = _lib.lib()
         self._L = L
         self._h = ctypes.c_void_p()
@@ -129,12 +129,28 @@ class Plan:
         self.nchan = int(freq_a.shape[0])
         self.npix_x, self.npix_y = int(npix_x), int(npix_y)
         self.precision = _prec_code(precision)
-        self._keep = (uvw_a, freq_a)  # device uvw is referenced, not copied, by the plan
+        # sel: optional sample selection (w-plane sharding); ms / wgt are then compact [nsel]
+        sel_a, sel_p, self.nsel = None, ctypes.c_void_p(), None
+        if sel is not None:
+            if space_u == DEVICE:
+                torch = _torch()
+                sel_a = torch.as_tensor(sel, device=uvw_a.device).to(torch.int64)
+                sel_a = sel_a.to(torch.uint32) if hasattr(torch, "uint32") else sel_a
+                sel_a = sel_a.contiguous()
+                sel_p = ctypes.c_void_p(sel_a.data_ptr())
+            else:
+                if _is_torch(sel):
+                    sel = sel.detach().cpu().numpy()
+                sel_a = np.ascontiguousarray(np.asarray(sel).astype(np.uint32))
+                sel_p = ctypes.c_void_p(sel_a.ctypes.data)
+            self.nsel = int(sel_a.shape[0])
+        self.vis_shape = (self.nrow, self.nchan) if sel is None else (self.nsel,)
+        self._keep = (uvw_a, freq_a, sel_a)  # device arrays are referenced, not copied
         self.stream = stream
         sp = ctypes.c_void_p(int(stream) if stream else 0)
-        _lib.check(L.b2g_plan_create(
-            ctypes.byref(self._h), self.nrow, self.nchan, uvw_p, freq_p, space_u,
-            self.npix_x, self.npix_y, float(pixsize_x), float(pixsize_y), int(nu), int(nv),
+        _lib.check(L.b2g_plan_create_sel(
+            ctypes.byref(self._h), self.nrow, self.nchan, uvw_p, freq_p, space_u, sel_p,
+            self.nsel or 0, self.npix_x, self.npix_y, float(pixsize_x), float(pixsize_y), int(nu), int(nv),
             float(epsilon), int(bool(do_wstacking)), self.precision, int(algo),
             int(verbosity), sp))
 
@@ -160,11 +176,11 @@ class Plan:
     def invert(self, ms, wgt=None, out=None, out_dtype=None):
         """ms2dirty on this plan.  Returns dirty [npix_x, npix_y]."""
         m = _Arr(ms, "complex")
-        if tuple(m.shape) != (self.nrow, self.nchan):
-            raise ValueError(f"ms has shape {tuple(m.shape)}, expected {(self.nrow, self.nchan)}")
+        if tuple(m.shape) != self.vis_shape:
+            raise ValueError(f"ms has shape {tuple(m.shape)}, expected {self.vis_shape}")
         w = _Arr(wgt, "real", allow_none=True)
         if w.ptr is not None:
-            if tuple(w.shape) != (self.nrow, self.nchan):
+            if tuple(w.shape) != self.vis_shape:
                 raise ValueError("wgt shape does not match ms")
             if w.space != m.space or w.code != m.code:
                 w = _Arr(_coerce_like(wgt, m), "real")
@@ -197,10 +213,10 @@ class Plan:
         if out is None:
             if d.is_torch:
                 torch = _torch()
-                out = torch.empty((self.nrow, self.nchan), device=d.keep.device,
+                out = torch.empty(self.vis_shape, device=d.keep.device,
                                   dtype=torch.complex128 if out_code == F64 else torch.complex64)
             else:
-                out = np.empty((self.nrow, self.nchan), dtype=out_dtype)
+                out = np.empty(self.vis_shape, dtype=out_dtype)
         o = _Arr(out, "complex")
         if o.keep is not out:
             raise ValueError("out must be a contiguous complex64/complex128 array")

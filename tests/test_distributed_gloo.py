@@ -86,3 +86,33 @@ def test_normalise_zero_sumwt():
     d = torch.ones((4, 4), dtype=torch.float64)
     assert float(b2dist.normalise(d.clone(), 2.0)[0, 0]) == 0.5
     assert float(b2dist.normalise(d.clone(), 0.0).abs().max()) == 0.0   # imaging/base.py:127-128
+
+
+def test_wplane_selection_partitions_and_balances():
+    """w-plane sharding: the ranks' selections partition the samples, each rank's |w| range is an
+    interval, and sample counts are balanced when planes are cheap."""
+    import torch
+    from ska_sdp_func_python_b200 import distributed as b2d
+    rng = np.random.default_rng(5)
+    nrow, nchan, world = 3000, 7, 4
+    uvw = rng.normal(size=(nrow, 3)) * np.array([300.0, 300.0, 40.0])
+    freq = np.linspace(100e6, 130e6, nchan)
+    th = b2d.wplane_thresholds(uvw, freq, world, npix=64, pixsize=1e-3, block_rows=700)
+    assert len(th) == world + 1 and th[0] == 0.0 and th[-1] == float("inf")
+    assert all(a <= b for a, b in zip(th, th[1:]))
+    sels = [b2d.wplane_selection(uvw, freq, world, r, 64, 1e-3, thresholds=th, block_rows=700)
+            for r in range(world)]
+    allsel = torch.cat(sels).numpy()
+    assert len(allsel) == nrow * nchan and len(np.unique(allsel)) == nrow * nchan
+    wl = np.abs(uvw[:, 2:3]) * freq[None, :] / 299792458.0
+    for r, s in enumerate(sels):
+        s = s.numpy()
+        assert np.all(np.diff(s) > 0)
+        ws = wl.reshape(-1)[s]
+        assert ws.min() >= th[r] and ws.max() < th[r + 1]
+        assert 0.5 * nrow * nchan / world < len(s) < 2.0 * nrow * nchan / world
+    ms = rng.normal(size=(nrow, nchan))
+    back = np.zeros_like(ms)
+    for s in sels:
+        b2d.scatter_back(back, s, b2d.compact(ms, s))
+    assert np.array_equal(back, ms)

@@ -167,3 +167,47 @@ def test_host_streaming_chunks(wg, built, prec, eps, ws):
     assert max(errs) < tol, errs
     # predict without weights covers every sample, also the zero-weight rows of `wgt`
     assert np.all(np.isfinite(v1)) and rel_l2(v1[wgt != 0], (vref / np.where(wgt == 0, 1, wgt))[wgt != 0]) < eps
+
+
+@pytest.mark.parametrize("prec,eps", [("single", 1e-5), ("double", 1e-9)])
+@pytest.mark.parametrize("space", ["host", "device"])
+def test_wplane_shards_sum_to_full(wg, prec, eps, space):
+    """w-plane sharding (b2g_plan_create_sel): plans over the per-rank sample selections cover
+    fewer w-planes each, their dirty images add up to the full image (the all-reduce), and their
+    predicted samples are the full prediction restricted to the selection."""
+    import torch
+    from ska_sdp_func_python_b200 import distributed as b2d
+    uvw, freq, ms, wgt, model, dref, vref = _oracle("wide", True)
+    nrow, nchan, npx, npy, psx, psy, _ = GEOS["wide"]
+    cdt, rdt = (np.complex128, np.float64) if prec == "double" else (np.complex64, np.float32)
+    world = 3
+    th = b2d.wplane_thresholds(uvw, freq, world, npx, psx, prec)
+    with wg.Plan(uvw, freq, npx, npy, psx, psy, eps, True, precision=prec) as full:
+        nplanes_full = full.info()["nplanes"]
+        v_full = full.predict(model.astype(rdt))
+    dsum = np.zeros((npx, npy))
+    vback = np.zeros((nrow, nchan), dtype=np.complex128)
+    nsel_total = 0
+    for r in range(world):
+        sel = b2d.wplane_selection(uvw, freq, world, r, npx, psx, thresholds=th).numpy()
+        nsel_total += len(sel)
+        ms_r, wgt_r = ms.reshape(-1)[sel].astype(cdt), wgt.reshape(-1)[sel].astype(rdt)
+        if space == "device":
+            dev = torch.device("cuda:0")
+            plan = wg.Plan(torch.as_tensor(uvw, device=dev), freq, npx, npy, psx, psy, eps, True,
+                           precision=prec, sel=torch.as_tensor(sel, device=dev))
+            d = plan.invert(torch.as_tensor(ms_r, device=dev), torch.as_tensor(wgt_r, device=dev)).cpu().numpy()
+            v = plan.predict(torch.as_tensor(model.astype(rdt), device=dev)).cpu().numpy()
+        else:
+            plan = wg.Plan(uvw, freq, npx, npy, psx, psy, eps, True, precision=prec, sel=sel)
+            d, v = plan.invert(ms_r, wgt_r), plan.predict(model.astype(rdt))
+        assert plan.info()["nvis"] == len(sel) and v.shape == (len(sel),)
+        assert plan.info()["nplanes"] < nplanes_full
+        plan.close()
+        dsum += d
+        b2d.scatter_back(vback, torch.as_tensor(sel), v)
+    assert nsel_total == nrow * nchan
+    assert rel_l2(dsum, dref) < eps
+    # predict has no weights here: compare with the full plan's prediction; the shard plans have
+    # their own w-plane lattices, so the two differ by the kernel's approximation error (< eps)
+    assert rel_l2(vback, v_full) < eps
