@@ -185,6 +185,44 @@ int b2g_vis_finish(int64_t nrow, int64_t nchan, int npol_img, int npol_vis, cons
                    const double *fscale, int64_t row0, int64_t nrow_total, void *vis_out,
                    int vis_dtype, void *stream);
 
+/*
+ * Density weighting and tapering of the imaging weights (the step before invert_ng).  ALL array
+ * pointers are DEVICE pointers except sumwt_host / sumsq_host (host outputs).  Cubes are
+ * [nrow][nchan][npol] float64 (flags: B2G_FLAG_* type, may be NULL), uvw [nrow][3] metres,
+ * kscale [nchan] = freq / c, vis_to_im [nchan] int32 = image channel of each visibility channel.
+ * The weight grid [nchan_img][npol][ny][nx] float64 has the image's shape and the linear UU / VV
+ * axes of the reference's GridData: cell = round(u_lambda / cdelt + crpix - 1), crpix 1-based.
+ *
+ * b2g_weight_grid   replaces grid_visibility_weight_to_griddata
+ *                   (/root/reference/src/ska_sdp_func_python/grid_data/gridding.py:258-334): zeroes
+ *                   grid, adds weight*(1-flags) of every sample to its cell and to the cell of the
+ *                   conjugate sample (both must be on the grid); sumwt_host [nchan_img][npol] =
+ *                   2 * in-grid weight sum; sumsq_host (1 value, may be NULL) = sum(grid^2).
+ * b2g_weight_apply  replaces griddata_visibility_reweight (gridding.py:362-499):
+ *                   mode 0 uniform  imaging_weight = w / g;  mode 1 robust  w / (1 + f2 * g);
+ *                   0 where g <= 0 or the sample is off the grid.  w = weight*(1-flags).
+ * b2g_weight_taper  replaces taper_visibility_gaussian (mode 0, param = pi^2 beam^2 / (4 ln 2))
+ *                   and taper_visibility_tukey (mode 1, param = tukey) of
+ *                   imaging/weighting.py:68-140; wave [nchan] = c / freq; imaging_weight is
+ *                   multiplied in place by (1-flags) * taper.
+ */
+int b2g_weight_grid(int64_t nrow, int64_t nchan, int npol, const double *uvw,
+                    const double *kscale, const double *weight, const void *flags,
+                    int flag_dtype, const int32_t *vis_to_im, int nchan_img, int64_t nx,
+                    int64_t ny, double cdelt_u, double cdelt_v, double crpix_u, double crpix_v,
+                    double *grid, double *sumwt_host, double *sumsq_host, void *stream);
+
+int b2g_weight_apply(int64_t nrow, int64_t nchan, int npol, const double *uvw,
+                     const double *kscale, const double *weight, const void *flags,
+                     int flag_dtype, const int32_t *vis_to_im, int nchan_img, int64_t nx,
+                     int64_t ny, double cdelt_u, double cdelt_v, double crpix_u, double crpix_v,
+                     const double *grid, int mode, double f2, double *imaging_weight,
+                     void *stream);
+
+int b2g_weight_taper(int64_t nrow, int64_t nchan, int npol, const double *uvw,
+                     const double *wave, const void *flags, int flag_dtype, int mode,
+                     double param, double *imaging_weight, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -20,6 +20,7 @@ EXPORTS = (
     "b2g_plan_invert", "b2g_plan_predict", "b2g_plan_info", "b2g_plan_timings",
     "b2g_ms2dirty", "b2g_dirty2ms", "b2g_sumwt", "b2g_kernel_select", "b2g_kernel_eval",
     "b2g_kernel_corr", "b2g_vis_prepare", "b2g_vis_finish", "b2g_set_host_chunk_samples", "b2g_plan_create_sel",
+    "b2g_weight_grid", "b2g_weight_apply", "b2g_weight_taper",
 )
 FLAG_NONE, FLAG_U8, FLAG_I32, FLAG_I64, FLAG_F64 = 0, 1, 2, 3, 4
 
@@ -83,6 +84,14 @@ def lib():
                                   i64, ci, vp, vp, ci, vp]
     L.b2g_vis_finish.restype = ci
     L.b2g_vis_finish.argtypes = [i64, i64, ci, ci, vp, ci, pd, pd, vp, vp, i64, i64, vp, ci, vp]
+    L.b2g_weight_grid.restype = ci
+    L.b2g_weight_grid.argtypes = [i64, i64, ci, vp, vp, vp, vp, ci, vp, ci, i64, i64, dbl, dbl,
+                                  dbl, dbl, vp, pd, pd, vp]
+    L.b2g_weight_apply.restype = ci
+    L.b2g_weight_apply.argtypes = [i64, i64, ci, vp, vp, vp, vp, ci, vp, ci, i64, i64, dbl, dbl,
+                                   dbl, dbl, vp, ci, dbl, vp, vp]
+    L.b2g_weight_taper.restype = ci
+    L.b2g_weight_taper.argtypes = [i64, i64, ci, vp, vp, vp, ci, ci, dbl, vp, vp]
     _lib = L
     return L
 

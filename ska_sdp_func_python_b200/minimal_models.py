@@ -153,6 +153,15 @@ class _Var:
     def shape(self):
         return self.data.shape
 
+    def __array__(self, dtype=None, copy=None):
+        return numpy.asarray(self.data, dtype=dtype)
+
+    def __len__(self):
+        return len(self.data)
+
+    def __getitem__(self, key):
+        return self.data[key]
+
 
 class _Dataset:
     def __init__(self, variables, attrs):
@@ -247,9 +256,26 @@ class _VisAccessor:
         return self._v["imaging_weight"].data * (1 - self._v["flags"].data)
 
     @property
+    def flagged_weight(self):
+        return self._v["weight"].data * (1 - self._v["flags"].data)
+
+    @property
+    def u(self):
+        return _Var(self._v["uvw"].data[..., 0])
+
+    @property
+    def v(self):
+        return _Var(self._v["uvw"].data[..., 1])
+
+    @property
     def uvw_lambda(self):
         k = self._v["frequency"].data / C_M_S
-        return _Var(numpy.einsum("tbs,k->tbks", self._v["uvw"].data, k))
+        # values of einsum("tbs,k->tbks") (visibility/base.py:54-55), stored so that the
+        # [..., chan, axis] slices the reference takes (gridding.py:49-51) are contiguous:
+        # numpy >= 2 hands out read-only copies for .flat of non-contiguous slices, which the
+        # reference's nan_to_num call cannot write to
+        lam = numpy.ascontiguousarray(numpy.einsum("tbs,k->kstb", self._v["uvw"].data, k))
+        return _Var(lam.transpose(2, 3, 0, 1))
 
 
 class Visibility(_Dataset):
@@ -289,3 +315,50 @@ class Visibility(_Dataset):
                          self.attrs["polarisation_frame"], v["weight"], v["imaging_weight"],
                          v["flags"])
         return out
+
+
+class _GridAccessor:
+    def __init__(self, gd):
+        self._gd = gd
+
+    @property
+    def griddata_wcs(self):
+        return self._gd.attrs["griddata_wcs"]
+
+    @property
+    def polarisation_frame(self):
+        return self._gd.attrs["polarisation_frame"]
+
+    @property
+    def shape(self):
+        return self._gd["pixels"].data.shape
+
+
+class GridData(_Dataset):
+    """pixels [nchan, npol, nv, nu] complex128 + UU/VV/STOKES/FREQ WCS (the attributes
+    grid_data/gridding.py touches: griddata_acc.{griddata_wcs, polarisation_frame, shape})."""
+
+    def __init__(self, pixels, griddata_wcs, polarisation_frame):
+        super().__init__({"pixels": numpy.asarray(pixels)},
+                         {"griddata_wcs": griddata_wcs, "polarisation_frame": polarisation_frame})
+
+    @property
+    def griddata_acc(self):
+        return _GridAccessor(self)
+
+
+def create_griddata_from_image(im, polarisation_frame=None, ft_types=None):
+    """Stand-in for datamodels' create_griddata_from_image (external ska_sdp_datamodels 0.2.1,
+    restated from its published behaviour): a grid of the image's shape whose UU / VV axes have
+    cdelt = 1 / (n * cdelt_image[rad]) -- negative along u because RA decreases with x --
+    crpix = n // 2 + 1, crval = 0."""
+    ft_types = ft_types or ["UU", "VV"]
+    nchan, npol, ny, nx = im["pixels"].data.shape
+    w = im.image_acc.wcs.wcs
+    d2r = numpy.pi / 180.0
+    cdelt = [1.0 / (nx * w.cdelt[0] * d2r), 1.0 / (ny * w.cdelt[1] * d2r), w.cdelt[2], w.cdelt[3]]
+    gwcs = WCS(crval=[0.0, 0.0, w.crval[2], w.crval[3]],
+               crpix=[nx // 2 + 1, ny // 2 + 1, w.crpix[2], w.crpix[3]],
+               cdelt=cdelt, ctype=[ft_types[0], ft_types[1], w.ctype[2], w.ctype[3]])
+    pf = polarisation_frame or im.image_acc.polarisation_frame
+    return GridData(numpy.zeros((nchan, pf.npol, ny, nx), dtype=complex), gwcs, pf)
