@@ -223,6 +223,23 @@ int b2g_weight_taper(int64_t nrow, int64_t nchan, int npol, const double *uvw,
                      const double *wave, const void *flags, int flag_dtype, int mode,
                      double param, double *imaging_weight, void *stream);
 
+/*
+ * Direct Fourier transform of sky components to visibilities: replaces dft_kernel /
+ * dft_cpu_looped and the cupy kernel string of
+ * /root/reference/src/ska_sdp_func_python/imaging/dft.py:121-183, :185-262, :265-285.
+ *   vis[row][chan][pol] (+)= sum_comp flux[comp][fchan][pol] * exp(-2 pi i (u l + v m + w n'))
+ * ALL pointers are DEVICE pointers.  uvw [nrow][3] metres with kscale [nchan] = freq / c, or --
+ * kscale == NULL -- uvw [nrow*nchan][3] already in wavelengths (the reference's uvw_lambda);
+ * dircos [ncomp][3] = (l, m, sqrt(1-l^2-m^2)-1); flux [ncomp][flux_nchan][npol] complex double
+ * (flux_nchan = nchan, or 1 = same flux in every channel); vis_out [nrow][nchan][npol] complex
+ * double.  trig_precision B2G_F64 (default) or B2G_F32 (fp32 sine / cosine after the exact fp64
+ * range reduction); accumulate != 0 adds to vis_out instead of overwriting it.
+ */
+int b2g_dft_predict(int64_t nrow, int64_t nchan, int npol, int64_t ncomp, const double *uvw,
+                    const double *kscale, const double *dircos, const void *flux,
+                    int64_t flux_nchan, void *vis_out, int trig_precision, int accumulate,
+                    void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -35,6 +35,7 @@ constexpr unsigned kFull = 0xffffffffu;
 struct WGeo {
     int nx, ny;               // grid (= image) size along u (fastest) and v
     double cdelt_u, cdelt_v;  // wavelengths per cell (cdelt_u < 0 for RA-decreasing images)
+    double rcdelt_u, rcdelt_v;  // 1 / cdelt (fast path of cell_pair)
     double crpix_u, crpix_v;  // 1-based reference pixel (nx//2 + 1, ny//2 + 1)
     int nchan_img, npol;
 };
@@ -59,12 +60,27 @@ __device__ __forceinline__ double nan_to_num(double x)
     return x;
 }
 
-// round(x / cdelt + crpix - 1) as an int, -1 if outside [0, n)
-__device__ __forceinline__ int cell_of(double x, double cdelt, double crpix, int n)
+// Cells of x and of -x along one axis: round(+-x / cdelt + crpix - 1) as the reference computes
+// it (correctly rounded division, then the two additions, then round-half-even), -1 if outside
+// [0, n).  (-x) / cdelt == -(x / cdelt) exactly, so one quotient serves both.  The quotient is
+// first approximated by a multiplication with 1/cdelt; only when the result lies within 1e-7 of
+// a rounding boundary (where the approximation could change the cell) is the exact division
+// evaluated -- the cell indices are therefore always those of the exact expression.
+__device__ __forceinline__ void cell_pair(double x, double cdelt, double rcdelt, double crpix, int n,
+                                          int &p, int &pc)
 {
-    const double p = rint(__dadd_rn(__ddiv_rn(x, cdelt), crpix) - 1.0);
-    if (!(p >= 0.0 && p < (double)n)) return -1;
-    return (int)p;
+    const double c1 = crpix - 1.0;
+    double q = __dmul_rn(x, rcdelt);
+    double t = q + c1, tc = c1 - q;
+    double r = rint(t), rc = rint(tc);
+    const double tol = 1e-7 * fmax(1.0, fabs(q));
+    if (!(fabs(fabs(t - r) - 0.5) > tol && fabs(fabs(tc - rc) - 0.5) > tol)) {
+        q = __ddiv_rn(x, cdelt);
+        r = rint(__dadd_rn(q, crpix) - 1.0);
+        rc = rint(__dadd_rn(-q, crpix) - 1.0);
+    }
+    p = (r >= 0.0 && r < (double)n) ? (int)r : -1;
+    pc = (rc >= 0.0 && rc < (double)n) ? (int)rc : -1;
 }
 
 // cell index pv*nx + pu of the sample and of its conjugate; false if either is off the grid
@@ -74,14 +90,26 @@ __device__ __forceinline__ bool map_sample(const WGeo &g, const double *uvw, con
     const double k = kscale[chan];
     const double u = nan_to_num(__dmul_rn(uvw[3 * row + 0], k));
     const double v = nan_to_num(__dmul_rn(uvw[3 * row + 1], k));
-    const int pu = cell_of(u, g.cdelt_u, g.crpix_u, g.nx);
-    const int pv = cell_of(v, g.cdelt_v, g.crpix_v, g.ny);
-    const int puc = cell_of(-u, g.cdelt_u, g.crpix_u, g.nx);
-    const int pvc = cell_of(-v, g.cdelt_v, g.crpix_v, g.ny);
+    int pu, pv, puc, pvc;
+    cell_pair(u, g.cdelt_u, g.rcdelt_u, g.crpix_u, g.nx, pu, puc);
+    cell_pair(v, g.cdelt_v, g.rcdelt_v, g.crpix_v, g.ny, pv, pvc);
     if ((pu | pv | puc | pvc) < 0) return false;
     cell = pv * g.nx + pu;
     cellc = pvc * g.nx + puc;
     return true;
+}
+
+// flattened sample index -> (row, chan); 32-bit division whenever the index fits
+__device__ __forceinline__ void split_index(long long i, int nchan, long long &row, int &chan)
+{
+    if (i < 0x100000000ll) {
+        const unsigned r = (unsigned)i / (unsigned)nchan;
+        row = r;
+        chan = (int)((unsigned)i - r * (unsigned)nchan);
+    } else {
+        row = i / nchan;
+        chan = (int)(i - row * nchan);
+    }
 }
 
 // Histogram of the flagged weights.  Thread = (row, chan), lanes run along chan, so neighbouring
@@ -99,8 +127,9 @@ weight_grid_kernel(WGeo g, long long nrow, int nchan, const double *__restrict__
     int cell = -1, cellc = -1, imchan = 0;
     bool ok = false;
     if (i < n) {
-        const long long row = i / nchan;
-        const int chan = (int)(i - row * nchan);
+        long long row;
+        int chan;
+        split_index(i, nchan, row, chan);
         imchan = vis_to_im[chan];
         ok = imchan >= 0 && imchan < g.nchan_img && map_sample(g, uvw, kscale, row, chan, cell, cellc);
     }
@@ -150,8 +179,9 @@ weight_apply_kernel(WGeo g, long long nrow, int nchan, const double *__restrict_
     const long long n = nrow * nchan;
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const long long row = i / nchan;
-    const int chan = (int)(i - row * nchan);
+    long long row;
+    int chan;
+    split_index(i, nchan, row, chan);
     const int imchan = vis_to_im[chan];
     int cell = -1, cellc = -1;
     const bool ok = imchan >= 0 && imchan < g.nchan_img && map_sample(g, uvw, kscale, row, chan, cell, cellc);
@@ -180,8 +210,9 @@ weight_taper_kernel(long long nrow, int nchan, int npol, const double *__restric
     const long long n = nrow * nchan;
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= n) return;
-    const long long row = i / nchan;
-    const int chan = (int)(i - row * nchan);
+    long long row;
+    int chan;
+    split_index(i, nchan, row, chan);
     const double u = uvw[3 * row], v = uvw[3 * row + 1];
     const double wv = wave[chan];
     const double d2 = __dadd_rn(__dmul_rn(u, u), __dmul_rn(v, v));
@@ -271,6 +302,8 @@ WGeo make_geo(int64_t nx, int64_t ny, double cdelt_u, double cdelt_v, double crp
     g.ny = (int)ny;
     g.cdelt_u = cdelt_u;
     g.cdelt_v = cdelt_v;
+    g.rcdelt_u = 1.0 / cdelt_u;
+    g.rcdelt_v = 1.0 / cdelt_v;
     g.crpix_u = crpix_u;
     g.crpix_v = crpix_v;
     g.nchan_img = nchan_img;

@@ -362,3 +362,19 @@ def create_griddata_from_image(im, polarisation_frame=None, ft_types=None):
                cdelt=cdelt, ctype=[ft_types[0], ft_types[1], w.ctype[2], w.ctype[3]])
     pf = polarisation_frame or im.image_acc.polarisation_frame
     return GridData(numpy.zeros((nchan, pf.npol, ny, nx), dtype=complex), gwcs, pf)
+
+
+class SkyComponent:
+    """direction (SkyCoord), frequency [nchan], flux [nchan, npol], polarisation_frame: the
+    attributes imaging/dft.py:59-118 reads."""
+
+    def __init__(self, direction, frequency, flux, polarisation_frame, name="", shape="Point"):
+        self.direction = direction
+        self.frequency = numpy.atleast_1d(numpy.asarray(frequency, dtype=float))
+        self.flux = numpy.asarray(flux, dtype=float)
+        self.polarisation_frame = polarisation_frame
+        self.name, self.shape = name, shape
+
+    def copy(self):
+        return SkyComponent(self.direction, self.frequency.copy(), self.flux.copy(),
+                            self.polarisation_frame, self.name, self.shape)

@@ -136,7 +136,7 @@ def test_oracle_larger(wt, unit_weights):
         assert np.array_equal(out, ref), (weighting, rob)
     tg = wt.taper(G, weight, flags, "gaussian", 4 * cell).cpu().numpy()
     np.testing.assert_allclose(tg, ow.taper_gaussian(uvw, freq, flags, weight, 4 * cell),
-                               rtol=4e-16, atol=0)
+                               rtol=1e-15, atol=0)  # exp: <= 1 ulp each side
 
 
 def test_edges(wt):
