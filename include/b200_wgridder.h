@@ -109,6 +109,18 @@ int b2g_plan_invert(b2g_plan *plan, const void *ms, const void *wgt, int vis_dty
 int b2g_plan_predict(b2g_plan *plan, const void *dirty, int dirty_dtype, int dirty_space,
                      const void *wgt, void *ms_out, int vis_dtype, int vis_space);
 
+/* Major-cycle residual on a plan: dirty_out = ms2dirty(ms - dirty2ms(model), wgt) in one call.
+ * The degridder subtracts the model from the data as it writes each sample and the residual
+ * samples feed the gridder without leaving HBM (the reference predicts, subtracts
+ * [visibility/operations.py:86 subtract_visibility] and inverts in three passes over host
+ * arrays: sky_model/skymodel_imaging.py:70-151, :154-235).  The model is degridded WITHOUT
+ * weights (predict_ng passes wgt=None, ng.py:103), wgt weights the gridding.  model / dirty_out:
+ * dirty_dtype in dirty_space; ms / wgt / ms_resid: vis_dtype in vis_space; ms_resid (the residual
+ * visibilities) may be NULL, or equal to ms for an in-place update. */
+int b2g_plan_residual(b2g_plan *plan, const void *model, int dirty_dtype, int dirty_space,
+                      const void *ms, const void *wgt, int vis_dtype, int vis_space,
+                      void *ms_resid, void *dirty_out);
+
 /* Plan introspection: fills up to n entries of
  *   iinfo = {W, nu, nv, nplanes, nslabs, planes_per_slab, algo_used, poly_degree,
  *            nvis_sorted, key_bits, launches_last_call}

@@ -21,6 +21,7 @@ template <typename T> struct VisLaunch {
     const cplx<T> *ms;      // gridding input  [nrow][nchan]
     const T *wgt;           // optional weights [nrow][nchan]
     cplx<T> *ms_out;        // degridding output [nrow][nchan]
+    const cplx<T> *sub_from = nullptr;  // degridding: ms_out = sub_from - model (residual), may alias ms_out
     cplx<T> *ring;          // [nslots][nu][nv]
     cudaStream_t stream;
 };

@@ -992,7 +992,8 @@ int invert_impl(b2g_plan *p, const void *ms, const void *wgt, int vis_dtype, int
 
 template <typename T>
 int predict_impl(b2g_plan *p, const void *dirty, int dirty_dtype, int dirty_space,
-                 const void *wgt, void *ms_out, int vis_dtype, int vis_space)
+                 const void *wgt, void *ms_out, int vis_dtype, int vis_space,
+                 const void *sub_from = nullptr, int sub_dtype = 0, int sub_space = 0)
 {
     StageTimer &tm = p->timer;
     cudaStream_t s = p->stream;
@@ -1013,8 +1014,10 @@ int predict_impl(b2g_plan *p, const void *dirty, int dirty_dtype, int dirty_spac
         CUDA_OK(cudaMemcpyAsync(d_dirty_tmp, dirty, real_size(dirty_dtype) * npx, cudaMemcpyHostToDevice, s));
         d_dirty = d_dirty_tmp;
     }
-    Staged<T> d_wgt;
+    Staged<T> d_wgt, d_sub;
     B2G_OK(stage_in<T>(wgt, vis_dtype, vis_space, n, s, &d_wgt));
+    // residual mode (b2g_plan_residual): ms_out = sub_from - model
+    B2G_OK(stage_in<T>(sub_from, sub_dtype, sub_space, 2 * n, s, &d_sub));
     tm.end();
 
     tm.begin(S_CORRECT);
@@ -1051,6 +1054,7 @@ int predict_impl(b2g_plan *p, const void *dirty, int dirty_dtype, int dirty_spac
         VisLaunch<T> L = make_launch<T>(p, sl);
         L.wgt = d_wgt.ptr;
         L.ms_out = d_out;
+        L.sub_from = reinterpret_cast<const cplx<T> *>(d_sub.ptr);
         tm.begin(S_VIS);
         for (int c = 0; c < p->nchunks; ++c) {
             if (p->nchunks > 1) {
@@ -1126,6 +1130,65 @@ extern "C" int b2g_plan_predict(b2g_plan *plan, const void *dirty, int dirty_dty
     return plan->precision == B2G_F32
                ? predict_impl<float>(plan, dirty, dirty_dtype, dirty_space, wgt, ms_out, vis_dtype, vis_space)
                : predict_impl<double>(plan, dirty, dirty_dtype, dirty_space, wgt, ms_out, vis_dtype, vis_space);
+}
+
+namespace {
+
+// residual image = invert(ms - predict(model)): the degridder subtracts the model from the data
+// as it writes each sample, and the residual samples go straight into the gridder without
+// leaving HBM
+template <typename T>
+int residual_impl(b2g_plan *p, const void *model, int dirty_dtype, int dirty_space, const void *ms,
+                  const void *wgt, int vis_dtype, int vis_space, void *ms_resid, void *dirty_out)
+{
+    const long long n = p->nvis;
+    const int want = sizeof(T) == 8 ? B2G_F64 : B2G_F32;
+    cudaStream_t s = p->stream;
+    // residual samples in the plan's own type, on the device; the caller's array if it is one
+    T *d_res = nullptr;
+    bool own = false;
+    if (ms_resid && vis_space == B2G_DEVICE && vis_dtype == want) {
+        d_res = static_cast<T *>(ms_resid);
+    } else if (n > 0) {
+        CUDA_OK(cudaMallocAsync(&d_res, sizeof(T) * 2 * n, s));
+        own = true;
+    }
+    int rc = predict_impl<T>(p, model, dirty_dtype, dirty_space, nullptr, d_res, want, B2G_DEVICE, ms,
+                             vis_dtype, vis_space);
+    double t_pred[8];
+    for (int i = 0; i < 8; ++i) t_pred[i] = p->timings[i];
+    const int l_pred = p->launches_last;
+    if (rc == 0) rc = invert_impl<T>(p, d_res, wgt, want, B2G_DEVICE, dirty_out, dirty_dtype, dirty_space);
+    if (rc == 0 && ms_resid && own) rc = stage_out<T>(d_res, ms_resid, vis_dtype, vis_space, 2 * n, s);
+    if (own) {
+        cudaStreamSynchronize(s);
+        cudaFreeAsync(d_res, s);
+    }
+    if (rc) return rc;
+    for (int i = 0; i < 8; ++i) p->timings[i] += t_pred[i];
+    p->launches_last += l_pred;
+    p->t_last_ms = p->timings[S_TOTAL];
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int b2g_plan_residual(b2g_plan *plan, const void *model, int dirty_dtype, int dirty_space,
+                                 const void *ms, const void *wgt, int vis_dtype, int vis_space,
+                                 void *ms_resid, void *dirty_out)
+{
+    g_err.clear();
+    if (!plan) return fail("plan is NULL");
+    if (!model || !dirty_out) return fail("model / dirty_out is NULL");
+    if (plan->nvis > 0 && !ms) return fail("ms is NULL");
+    B2G_OK(check_codes(vis_dtype, vis_space, "visibility"));
+    B2G_OK(check_codes(dirty_dtype, dirty_space, "image"));
+    CUDA_OK(cudaSetDevice(plan->device));
+    return plan->precision == B2G_F32
+               ? residual_impl<float>(plan, model, dirty_dtype, dirty_space, ms, wgt, vis_dtype,
+                                      vis_space, ms_resid, dirty_out)
+               : residual_impl<double>(plan, model, dirty_dtype, dirty_space, ms, wgt, vis_dtype,
+                                       vis_space, ms_resid, dirty_out);
 }
 
 extern "C" int b2g_plan_info(const b2g_plan *p, int64_t *iinfo, int ni, double *dinfo, int nd)

@@ -58,7 +58,7 @@ template <typename T, int W, bool WS>
 __global__ void __launch_bounds__(128)
 degrid_simple_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ sidx,
                      long long begin, long long end, int plane0, int slot0,
-                     const T *__restrict__ wgt, cplx<T> *__restrict__ out,
+                     const T *__restrict__ wgt, cplx<T> *out, const cplx<T> *sub_from,
                      const cplx<T> *__restrict__ ring)
 {
     constexpr int PW = WS ? W : 1;
@@ -71,7 +71,7 @@ degrid_simple_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__
     if (wgt) {
         wv = wgt[idx];
         if (wv == T(0)) {
-            out[idx] = cplx<T>{T(0), T(0)};
+            out[idx] = sub_from ? sub_from[idx] : cplx<T>{T(0), T(0)};
             return;
         }
     }
@@ -105,7 +105,13 @@ degrid_simple_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__
         sim = fma(pim, fq, sim);
     }
     if (L.flip) sim = -sim;
-    out[idx] = cplx<T>{sre * wv, sim * wv};
+    cplx<T> r{sre * wv, sim * wv};
+    if (sub_from) {  // residual mode: data - model
+        const cplx<T> d = sub_from[idx];
+        r.re = d.re - r.re;
+        r.im = d.im - r.im;
+    }
+    out[idx] = r;
 }
 
 
@@ -125,7 +131,7 @@ template <typename T, int W, bool WS> static int degrid_simple_inst(const VisLau
     unsigned blocks = (unsigned)((n + 127) / 128);
     degrid_simple_kernel<T, W, WS><<<blocks, 128, 0, L.stream>>>(
         L.geo, make_tab<T, W>(L.coef), L.sidx, L.begin, L.end, L.plane0, L.slot0, L.wgt, L.ms_out,
-        L.ring);
+        L.sub_from, L.ring);
     return (int)cudaGetLastError();
 }
 

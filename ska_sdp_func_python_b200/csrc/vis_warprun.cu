@@ -368,7 +368,7 @@ template <typename T, int W, int PWB>
 __global__ void __launch_bounds__(32 * kWarps, min_blocks<T>(false))
 degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ sidx,
                       long long begin, long long end, int plane0, int slot0, int q0,
-                      const T *__restrict__ wgt, cplx<T> *__restrict__ out,
+                      const T *__restrict__ wgt, cplx<T> *out, const cplx<T> *sub_from,
                       const cplx<T> *__restrict__ ring)
 {
     using C = Cfg<T, W, PWB, false>;
@@ -516,7 +516,11 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
         if (lane < n) {
             if (my_flip) res.y = -res.y;
             cplx<T> r{res.x * my_w, res.y * my_w};
-            if (q0 > 0) {  // later passes add their planes' share
+            if (sub_from) {  // residual mode: data - model (later passes subtract their share)
+                const cplx<T> prev = q0 > 0 ? out[my_idx] : sub_from[my_idx];
+                r.re = prev.re - r.re;
+                r.im = prev.im - r.im;
+            } else if (q0 > 0) {  // later passes add their planes' share
                 const cplx<T> prev = out[my_idx];
                 r.re += prev.re;
                 r.im += prev.im;
@@ -564,7 +568,7 @@ template <typename T, int W, int PWB> static int degrid_inst(const VisLaunch<T> 
     for (int q0 = 0; q0 < (PWB > 0 ? W : 1); q0 += (PWB > 0 ? PWB : 1)) {
         degrid_warprun_kernel<T, W, PWB><<<nblocks_for(n), 32 * kWarps, smem, L.stream>>>(
             L.geo, make_tab<T, W>(L.coef), L.sidx, L.begin, L.end, L.plane0, L.slot0, q0, L.wgt,
-            L.ms_out, L.ring);
+            L.ms_out, L.sub_from, L.ring);
         if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;
     }
     return 0;

@@ -63,18 +63,21 @@ __device__ __forceinline__ double nan_to_num(double x)
 // Cells of x and of -x along one axis: round(+-x / cdelt + crpix - 1) as the reference computes
 // it (correctly rounded division, then the two additions, then round-half-even), -1 if outside
 // [0, n).  (-x) / cdelt == -(x / cdelt) exactly, so one quotient serves both.  The quotient is
-// first approximated by a multiplication with 1/cdelt; only when the result lies within 1e-7 of
-// a rounding boundary (where the approximation could change the cell) is the exact division
-// evaluated -- the cell indices are therefore always those of the exact expression.
+// first approximated by a multiplication with 1/cdelt (relative error < 4e-16, i.e. < 4e-7 cells
+// for |q| < 1e9); only when the result lies within 1e-6 of a rounding boundary (where the
+// approximation could change the cell) is the exact division evaluated -- the cell indices are
+// therefore always those of the exact expression.  rint() is the add-and-subtract-2^52*1.5
+// idiom (round-half-even, exact for |t| < 2^51).
 __device__ __forceinline__ void cell_pair(double x, double cdelt, double rcdelt, double crpix, int n,
                                           int &p, int &pc)
 {
+    const double kMagic = 6755399441055744.0;
     const double c1 = crpix - 1.0;
     double q = __dmul_rn(x, rcdelt);
-    double t = q + c1, tc = c1 - q;
-    double r = rint(t), rc = rint(tc);
-    const double tol = 1e-7 * fmax(1.0, fabs(q));
-    if (!(fabs(fabs(t - r) - 0.5) > tol && fabs(fabs(tc - rc) - 0.5) > tol)) {
+    const double t = __dadd_rn(q, c1), tc = __dadd_rn(c1, -q);
+    double r = __dadd_rn(__dadd_rn(t, kMagic), -kMagic), rc = __dadd_rn(__dadd_rn(tc, kMagic), -kMagic);
+    const double lim = 0.5 - 1e-6;
+    if (!(fabs(t - r) < lim && fabs(tc - rc) < lim && fabs(q) < 1e9)) {
         q = __ddiv_rn(x, cdelt);
         r = rint(__dadd_rn(q, crpix) - 1.0);
         rc = rint(__dadd_rn(-q, crpix) - 1.0);
@@ -99,16 +102,36 @@ __device__ __forceinline__ bool map_sample(const WGeo &g, const double *uvw, con
     return true;
 }
 
-// flattened sample index -> (row, chan); 32-bit division whenever the index fits
-__device__ __forceinline__ void split_index(long long i, int nchan, long long &row, int &chan)
+// flattened sample index -> (row, chan): exact division by the run-time constant nchan with a
+// multiply-high (Granlund & Montgomery) whenever the index fits 32 bits
+struct ChanDiv {
+    unsigned d, mul;
+    int sh1, sh2;
+};
+
+inline ChanDiv make_chandiv(unsigned d)
+{
+    ChanDiv c;
+    c.d = d;
+    int l = 0;
+    while ((1ull << l) < d) ++l;
+    c.mul = (unsigned)(((1ull << 32) * ((1ull << l) - d)) / d + 1);
+    c.sh1 = l < 1 ? l : 1;
+    c.sh2 = l > 1 ? l - 1 : 0;
+    return c;
+}
+
+__device__ __forceinline__ void split_index(long long i, const ChanDiv &c, long long &row, int &chan)
 {
     if (i < 0x100000000ll) {
-        const unsigned r = (unsigned)i / (unsigned)nchan;
+        const unsigned x = (unsigned)i;
+        const unsigned t = __umulhi(c.mul, x);
+        const unsigned r = (t + ((x - t) >> c.sh1)) >> c.sh2;
         row = r;
-        chan = (int)((unsigned)i - r * (unsigned)nchan);
+        chan = (int)(x - r * c.d);
     } else {
-        row = i / nchan;
-        chan = (int)(i - row * nchan);
+        row = i / c.d;
+        chan = (int)(i - row * c.d);
     }
 }
 
@@ -116,7 +139,7 @@ __device__ __forceinline__ void split_index(long long i, int nchan, long long &r
 // lanes mostly hit the same cell: a full-warp segmented scan over runs of equal cells leaves one
 // fp64 atomic per run instead of one per sample.
 __global__ void __launch_bounds__(256)
-weight_grid_kernel(WGeo g, long long nrow, int nchan, const double *__restrict__ uvw,
+weight_grid_kernel(WGeo g, long long nrow, int nchan, ChanDiv cd, const double *__restrict__ uvw,
                    const double *__restrict__ kscale, const double *__restrict__ weight,
                    const void *__restrict__ flags, int flag_type,
                    const int *__restrict__ vis_to_im, double *__restrict__ grid)
@@ -129,7 +152,7 @@ weight_grid_kernel(WGeo g, long long nrow, int nchan, const double *__restrict__
     if (i < n) {
         long long row;
         int chan;
-        split_index(i, nchan, row, chan);
+        split_index(i, cd, row, chan);
         imchan = vis_to_im[chan];
         ok = imchan >= 0 && imchan < g.nchan_img && map_sample(g, uvw, kscale, row, chan, cell, cellc);
     }
@@ -170,7 +193,7 @@ weight_grid_kernel(WGeo g, long long nrow, int nchan, const double *__restrict__
 //   mode 0 uniform: w / g          mode 1 robust: w / (1 + f2 * g)        (g > 0, in grid)
 //   0 where g <= 0 or the sample (or its conjugate) is off the grid   gridding.py:449-493
 __global__ void __launch_bounds__(256)
-weight_apply_kernel(WGeo g, long long nrow, int nchan, const double *__restrict__ uvw,
+weight_apply_kernel(WGeo g, long long nrow, int nchan, ChanDiv cd, const double *__restrict__ uvw,
                     const double *__restrict__ kscale, const double *__restrict__ weight,
                     const void *__restrict__ flags, int flag_type,
                     const int *__restrict__ vis_to_im, const double *__restrict__ grid, int mode,
@@ -181,7 +204,7 @@ weight_apply_kernel(WGeo g, long long nrow, int nchan, const double *__restrict_
     if (i >= n) return;
     long long row;
     int chan;
-    split_index(i, nchan, row, chan);
+    split_index(i, cd, row, chan);
     const int imchan = vis_to_im[chan];
     int cell = -1, cellc = -1;
     const bool ok = imchan >= 0 && imchan < g.nchan_img && map_sample(g, uvw, kscale, row, chan, cell, cellc);
@@ -203,7 +226,7 @@ weight_apply_kernel(WGeo g, long long nrow, int nchan, const double *__restrict_
 // mode 0 Gaussian: imw = imw*(1-flags) * exp(-scale * (u^2 + v^2) / wave^2)   weighting.py:88-99
 // mode 1 Tukey:    imw = imw*(1-flags) * tukey((d / wave) / (dmax / wave), r)  weighting.py:121-138
 __global__ void __launch_bounds__(256)
-weight_taper_kernel(long long nrow, int nchan, int npol, const double *__restrict__ uvw,
+weight_taper_kernel(long long nrow, int nchan, ChanDiv cd, int npol, const double *__restrict__ uvw,
                     const double *__restrict__ wave, const void *__restrict__ flags, int flag_type,
                     int mode, double param, double dmax, double *__restrict__ imaging_weight)
 {
@@ -212,7 +235,7 @@ weight_taper_kernel(long long nrow, int nchan, int npol, const double *__restric
     if (i >= n) return;
     long long row;
     int chan;
-    split_index(i, nchan, row, chan);
+    split_index(i, cd, row, chan);
     const double u = uvw[3 * row], v = uvw[3 * row + 1];
     const double wv = wave[chan];
     const double d2 = __dadd_rn(__dmul_rn(u, u), __dmul_rn(v, v));
@@ -352,7 +375,7 @@ extern "C" int b2g_weight_grid(int64_t nrow, int64_t nchan, int npol, const doub
     const long long n = nrow * nchan;
     if (n > 0) {
         const unsigned blocks = (unsigned)((n + 255) / 256);
-        weight_grid_kernel<<<blocks, 256, 0, s>>>(g, nrow, (int)nchan, uvw, kscale, weight, flags,
+        weight_grid_kernel<<<blocks, 256, 0, s>>>(g, nrow, (int)nchan, make_chandiv((unsigned)nchan), uvw, kscale, weight, flags,
                                                   flags ? flag_dtype : B2G_FLAG_NONE, vis_to_im, grid);
         if (int rc = check_launch()) return rc;
     }
@@ -386,8 +409,8 @@ extern "C" int b2g_weight_apply(int64_t nrow, int64_t nchan, int npol, const dou
     const WGeo g = make_geo(nx, ny, cdelt_u, cdelt_v, crpix_u, crpix_v, nchan_img, npol);
     const unsigned blocks = (unsigned)((n + 255) / 256);
     weight_apply_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(
-        g, nrow, (int)nchan, uvw, kscale, weight, flags, flags ? flag_dtype : B2G_FLAG_NONE,
-        vis_to_im, grid, mode, f2, imaging_weight);
+        g, nrow, (int)nchan, make_chandiv((unsigned)nchan), uvw, kscale, weight, flags,
+        flags ? flag_dtype : B2G_FLAG_NONE, vis_to_im, grid, mode, f2, imaging_weight);
     return check_launch();
 }
 
@@ -408,7 +431,7 @@ extern "C" int b2g_weight_taper(int64_t nrow, int64_t nchan, int npol, const dou
     if (mode == 1)
         if (int rc = reduce_to_host(2, uvw, nrow, 0, 1, &dmax, s)) return rc;
     const unsigned blocks = (unsigned)((n + 255) / 256);
-    weight_taper_kernel<<<blocks, 256, 0, s>>>(nrow, (int)nchan, npol, uvw, wave, flags,
+    weight_taper_kernel<<<blocks, 256, 0, s>>>(nrow, (int)nchan, make_chandiv((unsigned)nchan), npol, uvw, wave, flags,
                                                flags ? flag_dtype : B2G_FLAG_NONE, mode, param, dmax,
                                                imaging_weight);
     return check_launch();

@@ -32,7 +32,7 @@ from .polarisation import pol_matrix
 
 log = logging.getLogger("func-python-logger")
 
-__all__ = ["invert_ng", "predict_ng", "invert_visibility", "predict_visibility"]
+__all__ = ["invert_ng", "predict_ng", "residual_ng", "invert_visibility", "predict_visibility"]
 
 C_M_S = 299792458.0
 _CHUNK_BYTES = 1 << 29  # raw Visibility bytes staged per prepare / finish launch
@@ -229,6 +229,21 @@ def invert_ng(bvis, model, dopsf=False, normalise=True, **kwargs):
     """Invert using the B200 gridder.  Drop-in for ska_sdp_func_python.imaging.ng.invert_ng
     (ng.py:146-294): returns (Image like ``model`` holding the dirty image or PSF,
     sumwt[nchan, npol])."""
+    return _invert(bvis, model, dopsf, normalise, False, kwargs)
+
+
+def residual_ng(bvis, model, normalise=True, **kwargs):
+    """Residual image of one major cycle: what
+    ``invert_ng(subtract_visibility(bvis, predict_ng(bvis, model)), model)`` computes with the
+    reference (ng.py:38-294, visibility/operations.py:86; the loop of
+    sky_model/skymodel_imaging.py:70-235), in ONE pass per polarisation plane: the same plan
+    (uv/w sort) serves the degridding of ``model`` and the gridding of the residual, the model is
+    subtracted as it is degridded and the residual samples never leave the device
+    (b2g_plan_residual).  Returns (residual Image, sumwt[nchan, npol])."""
+    return _invert(bvis, model, False, normalise, True, kwargs)
+
+
+def _invert(bvis, model, dopsf, normalise, subtract_model, kwargs):
     assert _is_image(model), model
     assert model.image_acc.is_canonical()
     opt = _options(kwargs)
@@ -268,6 +283,10 @@ def invert_ng(bvis, model, dopsf=False, normalise=True, **kwargs):
     D = _Device(uvw, freq)
     torch = D.torch
     ms, wg = _prepare(D, vis, flags, weight, M, shift, dopsf, prec, npol)
+    mpix = None
+    if subtract_model:
+        assert npol == vnpol  # predict_ng's own requirement (ng.py:78)
+        mpix = D.up(numpy.asarray(model["pixels"].data, dtype=numpy.float64))
 
     # ---- sum of weights: the reference's own numpy expression (bit-exact) ----------------
     sumwt = numpy.zeros([nchan, npol])
@@ -291,6 +310,14 @@ def invert_ng(bvis, model, dopsf=False, normalise=True, **kwargs):
     rdt = torch.float32 if prec == _lib.F32 else torch.float64
     pix = torch.zeros((nchan, npol, ny, nx), device=D.dev, dtype=torch.float64)
     nonzero = (ms.abs().amax(dim=1) > 0).cpu().numpy()  # [npol, vnchan]: ng.py:238, :267
+    if subtract_model:
+        nonzero[...] = True  # a zero visibility still has a residual
+
+    def run(plan, ichan, pol, m, w):
+        if mpix is None:
+            plan.invert(m, w, out=dirty)
+        else:
+            plan.residual(mpix[ichan, pol].t().contiguous().to(rdt), m, w, out=dirty)
     common = dict(epsilon=opt["epsilon"], do_wstacking=opt["do_wstacking"], precision=prec,
                   verbosity=opt["verbosity"], stream=D.stream)
     dirty = torch.empty((nx, ny), device=D.dev, dtype=rdt)
@@ -298,7 +325,7 @@ def invert_ng(bvis, model, dopsf=False, normalise=True, **kwargs):
         with wgridder.Plan(D.uvw, freq, nx, ny, pixsize, pixsize, **common) as plan:
             for pol in range(npol):
                 if nonzero[pol].any():
-                    plan.invert(ms[pol], wg[pol], out=dirty)
+                    run(plan, 0, pol, ms[pol], wg[pol])
                     pix[0, pol] += dirty.t()
     else:
         # one gridding per (image channel, pol) over all visibility channels mapped to it
@@ -313,8 +340,8 @@ def invert_ng(bvis, model, dopsf=False, normalise=True, **kwargs):
             with wgridder.Plan(D.uvw, freq[sel], nx, ny, pixsize, pixsize, **common) as plan:
                 for pol in range(npol):
                     if nonzero[pol, sel].any():
-                        plan.invert(ms[pol].index_select(1, tsel).contiguous(),
-                                    wg[pol].index_select(1, tsel).contiguous(), out=dirty)
+                        run(plan, ichan, pol, ms[pol].index_select(1, tsel).contiguous(),
+                            wg[pol].index_select(1, tsel).contiguous())
                         pix[ichan, pol] += dirty.t()
     if normalise:
         # normalise_sumwt, 2-D sumwt branch (imaging/base.py:117-128)

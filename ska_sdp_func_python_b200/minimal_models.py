@@ -162,6 +162,9 @@ class _Var:
     def __getitem__(self, key):
         return self.data[key]
 
+    def __setitem__(self, key, value):
+        self.data[key] = value
+
 
 class _Dataset:
     def __init__(self, variables, attrs):
@@ -378,3 +381,37 @@ class SkyComponent:
     def copy(self):
         return SkyComponent(self.direction, self.frequency.copy(), self.flux.copy(),
                             self.polarisation_frame, self.name, self.shape)
+
+
+class SkyModel:
+    """image, components, mask, gaintable: the attributes sky_model/skymodel_imaging.py reads."""
+
+    def __init__(self, image=None, components=None, gaintable=None, mask=None, fixed=False):
+        self.image = image
+        self.components = [] if components is None else list(components)
+        self.gaintable = gaintable
+        self.mask = mask
+        self.fixed = fixed
+
+
+def time_slices(vis):
+    """[(index, Visibility of one time sample)]: what ``vis.groupby("time", squeeze=False)``
+    yields for the xarray data model."""
+    out = []
+    for t in range(vis["vis"].data.shape[0]):
+        sl = slice(t, t + 1)
+        out.append((t, Visibility(vis["vis"].data[sl].copy(), vis["uvw"].data[sl].copy(),
+                                  vis["frequency"].data.copy(), vis.attrs["phasecentre"],
+                                  vis.attrs["polarisation_frame"], vis["weight"].data[sl].copy(),
+                                  vis["imaging_weight"].data[sl].copy(), vis["flags"].data[sl].copy())))
+    return out
+
+
+def concatenate_visibility(vis_list, dim="time"):
+    """Stand-in for datamodels' concatenate_visibility along time."""
+    assert dim == "time"
+    first = vis_list[0]
+    cat = lambda k: numpy.concatenate([v[k].data for v in vis_list], axis=0)  # noqa: E731
+    return Visibility(cat("vis"), cat("uvw"), first["frequency"].data.copy(),
+                      first.attrs["phasecentre"], first.attrs["polarisation_frame"], cat("weight"),
+                      cat("imaging_weight"), cat("flags"))

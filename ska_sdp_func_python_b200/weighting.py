@@ -56,7 +56,8 @@ class WeightGrid:
     def cube(self, a):
         """[nrow, nchan, npol] float64 on the device."""
         t = self._up(a, self.torch.float64)
-        return t.reshape(self.nrow, self.nchan, -1)
+        npol = t.shape[-1] if t.dim() >= 3 else 1
+        return t.reshape(self.nrow, self.nchan, npol)
 
     def flags(self, flags):
         """(device tensor or None, B2G_FLAG_* code)"""

@@ -227,6 +227,36 @@ class Plan:
                                             o.code, o.space))
         return out
 
+    def residual(self, model, ms, wgt=None, out=None, ms_resid=None):
+        """Residual image ms2dirty(ms - dirty2ms(model), wgt) in one call (b2g_plan_residual):
+        the model is subtracted as it is degridded and the residual samples are gridded without
+        leaving the device.  ``ms_resid`` (optional, same type / place as ``ms``; may be ``ms``
+        itself) receives the residual visibilities.  Returns the residual image."""
+        d = _Arr(model, "real")
+        if tuple(d.shape) != (self.npix_x, self.npix_y):
+            raise ValueError(f"model has shape {tuple(d.shape)}, expected "
+                             f"{(self.npix_x, self.npix_y)}")
+        m = _Arr(ms, "complex")
+        if tuple(m.shape) != self.vis_shape:
+            raise ValueError(f"ms has shape {tuple(m.shape)}, expected {self.vis_shape}")
+        w = _Arr(wgt, "real", allow_none=True)
+        if w.ptr is not None and (w.space != m.space or w.code != m.code):
+            w = _Arr(_coerce_like(wgt, m), "real")
+        r = _Arr(ms_resid, "complex", allow_none=True)
+        if r.ptr is not None and (r.keep is not ms_resid or r.space != m.space or r.code != m.code):
+            raise ValueError("ms_resid must be a contiguous array of the type and place of ms")
+        if out is None:
+            if d.is_torch:
+                out = _torch().empty_like(d.keep)
+            else:
+                out = np.empty_like(d.keep)
+        o = _Arr(out, "real")
+        if o.keep is not out or o.space != d.space or o.code != d.code:
+            raise ValueError("out must be a contiguous array of the type and place of model")
+        _lib.check(self._L.b2g_plan_residual(self._h, d.ptr, d.code, d.space, m.ptr, w.ptr, m.code,
+                                             m.space, r.ptr, o.ptr))
+        return out
+
     # -- introspection --------------------------------------------------------------
     def info(self):
         ii = (ctypes.c_int64 * 11)()
