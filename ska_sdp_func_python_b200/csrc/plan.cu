@@ -1158,7 +1158,11 @@ int residual_impl(b2g_plan *p, const void *model, int dirty_dtype, int dirty_spa
     double t_pred[8];
     for (int i = 0; i < 8; ++i) t_pred[i] = p->timings[i];
     const int l_pred = p->launches_last;
-    if (rc == 0) rc = invert_impl<T>(p, d_res, wgt, want, B2G_DEVICE, dirty_out, dirty_dtype, dirty_space);
+    // the weights in the plan's type on the device (the residual samples already are)
+    Staged<T> d_wgt;
+    if (rc == 0) rc = stage_in<T>(wgt, vis_dtype, vis_space, n, s, &d_wgt);
+    if (rc == 0)
+        rc = invert_impl<T>(p, d_res, d_wgt.ptr, want, B2G_DEVICE, dirty_out, dirty_dtype, dirty_space);
     if (rc == 0 && ms_resid && own) rc = stage_out<T>(d_res, ms_resid, vis_dtype, vis_space, 2 * n, s);
     if (own) {
         cudaStreamSynchronize(s);

@@ -362,7 +362,8 @@ extern "C" int b2g_weight_grid(int64_t nrow, int64_t nchan, int npol, const doub
 {
     if (npol < 1 || npol > 4 || nchan_img < 1 || nx < 1 || ny < 1 || nx * ny > 0x3fffffff)
         return b2g::wrapper_fail("b2g_weight_grid: bad shape");
-    if (!uvw || !kscale || !weight || !vis_to_im || !grid) return b2g::wrapper_fail("b2g_weight_grid: NULL pointer");
+    if (!grid || !kscale || !vis_to_im || (nrow * nchan > 0 && (!uvw || !weight)))
+        return b2g::wrapper_fail("b2g_weight_grid: NULL pointer");
     if (cdelt_u == 0.0 || cdelt_v == 0.0) return b2g::wrapper_fail("b2g_weight_grid: zero cell size");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
@@ -398,7 +399,7 @@ extern "C" int b2g_weight_apply(int64_t nrow, int64_t nchan, int npol, const dou
     if (npol < 1 || npol > 4 || nchan_img < 1 || nx < 1 || ny < 1 || nx * ny > 0x3fffffff)
         return b2g::wrapper_fail("b2g_weight_apply: bad shape");
     if (mode != 0 && mode != 1) return b2g::wrapper_fail("b2g_weight_apply: mode must be 0 (uniform) or 1 (robust)");
-    if (!uvw || !kscale || !weight || !vis_to_im || !grid || !imaging_weight)
+    if (nrow * nchan > 0 && (!uvw || !kscale || !weight || !vis_to_im || !grid || !imaging_weight))
         return b2g::wrapper_fail("b2g_weight_apply: NULL pointer");
     if (cdelt_u == 0.0 || cdelt_v == 0.0) return b2g::wrapper_fail("b2g_weight_apply: zero cell size");
     int ndev = 0;
@@ -420,7 +421,8 @@ extern "C" int b2g_weight_taper(int64_t nrow, int64_t nchan, int npol, const dou
 {
     if (npol < 1 || npol > 4) return b2g::wrapper_fail("b2g_weight_taper: bad npol");
     if (mode != 0 && mode != 1) return b2g::wrapper_fail("b2g_weight_taper: mode must be 0 (gaussian) or 1 (tukey)");
-    if (!uvw || !wave || !imaging_weight) return b2g::wrapper_fail("b2g_weight_taper: NULL pointer");
+    if (nrow * nchan > 0 && (!uvw || !wave || !imaging_weight))
+        return b2g::wrapper_fail("b2g_weight_taper: NULL pointer");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
         return b2g::wrapper_fail("b2g_weight_taper: no CUDA device available (this library has no CPU path)");
