@@ -96,39 +96,84 @@ def _plane_cost_in_samples(npix, precision):
     return t_plane / t_sample
 
 
-def wplane_thresholds(uvw, freq, world_size, npix, pixsize, precision="single", sigma=1.5,
-                      nbins=8192, block_rows=1 << 16):
-    """|w| thresholds t_0 = 0 < t_1 < ... < t_world = inf that balance (samples + planes) cost.
-    uvw: [nrow, 3] metres (numpy or torch, any device), freq: [nchan] Hz.  Deterministic: every
-    rank computes the same thresholds from the same inputs, no communication."""
+def _w_histogram(uvw, freq, nbins, block_rows):
+    """Histogram of |w| in wavelengths over all (row, chan) samples: (hist [nbins] f64, wmax)."""
     import torch
     uvw_t = torch.as_tensor(uvw)
     dev = uvw_t.device
     w = uvw_t[:, 2].abs().to(torch.float64)
     fs = torch.as_tensor(np.asarray(freq, dtype=np.float64) / C_M_S, device=dev)
     wmax = float(w.max().item()) * float(fs.max().item()) if w.numel() else 0.0
-    if world_size <= 1 or wmax <= 0.0:
-        return [0.0] + [float("inf")] * max(1, world_size)
     hist = torch.zeros(nbins, dtype=torch.float64, device=dev)
+    if wmax <= 0.0:
+        return hist, 0.0
     scale = nbins / (wmax * (1.0 + 1e-12))
     for r0 in range(0, w.numel(), block_rows):
         b = (w[r0:r0 + block_rows, None] * fs[None, :] * scale).to(torch.int64).clamp_(0, nbins - 1)
         hist += torch.bincount(b.reshape(-1), minlength=nbins).to(torch.float64)
-    # plane spacing of the reference model: dw = 1 / (2 sigma max|n-1|)
+    return hist, wmax
+
+
+def _plane_spacing(npix, pixsize, sigma):
+    """dw = 1 / (2 sigma max|n-1|) of the reference model."""
     xm = pixsize * npix / 2.0
     r2 = min(2.0 * xm * xm, 0.999)
     nm1 = r2 / (np.sqrt(1.0 - r2) + 1.0)
-    dw = 0.5 / (sigma * max(nm1, 1e-12))
-    planes_per_bin = (wmax / nbins) / dw
-    cost = torch.cumsum(hist + planes_per_bin * _plane_cost_in_samples(npix, precision), 0)
+    return 0.5 / (sigma * max(nm1, 1e-12))
+
+
+def _cut(cost, wmax, world_size):
+    import torch
+    nbins = cost.numel()
     total = float(cost[-1].item())
     targets = torch.tensor([total * r / world_size for r in range(1, world_size)],
-                           dtype=torch.float64, device=dev)
+                           dtype=torch.float64, device=cost.device)
     cut = torch.searchsorted(cost, targets).clamp_(0, nbins - 1).cpu().numpy()
     edges = [0.0] + [float((c + 1) * wmax / nbins) for c in cut] + [float("inf")]
     for i in range(1, len(edges)):  # monotone even for degenerate histograms
         edges[i] = max(edges[i], edges[i - 1])
     return edges
+
+
+def wplane_thresholds(uvw, freq, world_size, npix, pixsize, precision="single", sigma=1.5,
+                      nbins=8192, block_rows=1 << 16):
+    """|w| thresholds t_0 = 0 < t_1 < ... < t_world = inf that balance (samples + planes) cost.
+    uvw: [nrow, 3] metres (numpy or torch, any device), freq: [nchan] Hz.  Deterministic: every
+    rank computes the same thresholds from the same inputs, no communication."""
+    import torch
+    hist, wmax = _w_histogram(uvw, freq, nbins, block_rows)
+    if world_size <= 1 or wmax <= 0.0:
+        return [0.0] + [float("inf")] * max(1, world_size)
+    planes_per_bin = (wmax / nbins) / _plane_spacing(npix, pixsize, sigma)
+    cost = torch.cumsum(hist + planes_per_bin * _plane_cost_in_samples(npix, precision), 0)
+    return _cut(cost, wmax, world_size)
+
+
+def wplane_rebalance(uvw, freq, world_size, npix, pixsize, thresholds, samples_per_rank,
+                     vis_ms_per_rank, plane_ms, sigma=1.5, nbins=8192, block_rows=1 << 16):
+    """New thresholds from MEASURED costs of a first step under ``thresholds``: the samples of
+    rank r's old |w| interval cost vis_ms_per_rank[r] / samples_per_rank[r] each (sparse long
+    baselines are several times dearer per sample than the dense core, which an a-priori model
+    does not know), every w-plane costs ``plane_ms`` (FFT + screen + clear, both directions).  All
+    ranks must pass the same (all-gathered) numbers; no communication here."""
+    import torch
+    hist, wmax = _w_histogram(uvw, freq, nbins, block_rows)
+    if world_size <= 1 or wmax <= 0.0:
+        return [0.0] + [float("inf")] * max(1, world_size)
+    centres = (torch.arange(nbins, dtype=torch.float64, device=hist.device) + 0.5) * (wmax / nbins)
+    edges = torch.tensor([t if np.isfinite(t) else 4.0 * wmax for t in thresholds[1:-1]],
+                         dtype=torch.float64, device=hist.device)
+    owner = torch.searchsorted(edges, centres, right=True)          # old rank of every bin
+    per = torch.tensor([v / max(n, 1) for v, n in zip(vis_ms_per_rank, samples_per_rank)],
+                       dtype=torch.float64, device=hist.device)
+    # ranks that held too few samples to time reliably inherit their neighbour's cost
+    few = 1e-3 * float(sum(samples_per_rank))
+    for r in range(1, world_size):
+        if samples_per_rank[r] < few:
+            per[r] = per[r - 1]
+    planes_per_bin = (wmax / nbins) / _plane_spacing(npix, pixsize, sigma)
+    cost = torch.cumsum(hist * per[owner] + planes_per_bin * float(plane_ms), 0)
+    return _cut(cost, wmax, world_size)
 
 
 def wplane_selection(uvw, freq, world_size, rank, npix, pixsize, precision="single", sigma=1.5,

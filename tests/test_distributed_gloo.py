@@ -116,3 +116,28 @@ def test_wplane_selection_partitions_and_balances():
     for s in sels:
         b2d.scatter_back(back, s, b2d.compact(ms, s))
     assert np.array_equal(back, ms)
+
+
+def test_wplane_rebalance_follows_measured_costs():
+    """Measured re-balancing: equal measured costs reproduce a sample-balanced cut; when the outer
+    ranks report dearer samples their intervals shrink (thresholds move outwards less far)."""
+    from ska_sdp_func_python_b200 import distributed as b2d
+    rng = np.random.default_rng(6)
+    nrow, nchan, world = 4000, 5, 4
+    uvw = rng.normal(size=(nrow, 3)) * np.array([300.0, 300.0, 40.0])
+    freq = np.linspace(100e6, 130e6, nchan)
+    th0 = b2d.wplane_thresholds(uvw, freq, world, npix=64, pixsize=1e-3)
+    sels = [b2d.wplane_selection(uvw, freq, world, r, 64, 1e-3, thresholds=th0) for r in range(world)]
+    n = [int(s.numel()) for s in sels]
+    flat = b2d.wplane_rebalance(uvw, freq, world, 64, 1e-3, th0, n, [1e-3 * k for k in n], 0.0)
+    cnt = [int(b2d.wplane_selection(uvw, freq, world, r, 64, 1e-3, thresholds=flat).numel())
+           for r in range(world)]
+    assert max(cnt) - min(cnt) < 0.05 * nrow * nchan          # uniform cost -> equal counts
+    dear = b2d.wplane_rebalance(uvw, freq, world, 64, 1e-3, th0, n,
+                                [1e-3 * k * (1 + 2 * r) for r, k in enumerate(n)], 0.0)
+    assert dear[0] == 0.0 and dear[-1] == float("inf")
+    assert all(a <= b for a, b in zip(dear, dear[1:]))
+    cnt2 = [int(b2d.wplane_selection(uvw, freq, world, r, 64, 1e-3, thresholds=dear).numel())
+            for r in range(world)]
+    assert sum(cnt2) == nrow * nchan
+    assert cnt2[0] > cnt[0] and cnt2[-1] < cnt[-1]            # cheap core rank takes more samples
