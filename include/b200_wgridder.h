@@ -252,6 +252,26 @@ int b2g_dft_predict(int64_t nrow, int64_t nchan, int npol, int64_t ncomp, const 
                     int64_t flux_nchan, void *vis_out, int trig_precision, int accumulate,
                     void *stream);
 
+/*
+ * Hogbom CLEAN minor cycle on device-resident images: replaces hogbom()
+ * (/root/reference/src/ska_sdp_func_python/image/cleaners.py:23-133).  ALL image pointers are
+ * DEVICE pointers to C-contiguous float64 arrays: dirty / comps / res / window [nx][ny], psf
+ * [px][py]; window may be NULL; res may equal dirty (in place).  pmax = psf.max() (the caller
+ * checks that it is 1 as the reference asserts).  Every step is the reference's fp64 operation in
+ * the reference's order, so comps and res are bit-exact; iters_host receives the number of
+ * iterations performed.
+ *
+ * b2g_image_peak: mode 0: value and flat index of max |img * window| (first occurrence, as
+ * numpy.argmax); mode 1: max img.  Host outputs.
+ */
+int b2g_hogbom(const double *dirty, const double *psf, const double *window, int64_t nx,
+               int64_t ny, int64_t px, int64_t py, double gain, double pmax, double thresh,
+               double fracthresh, int64_t niter, double *comps, double *res, int64_t *iters_host,
+               void *stream);
+
+int b2g_image_peak(const double *img, const double *window, int64_t nx, int64_t ny, int mode,
+                   double *val_host, int64_t *idx_host, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,290 @@
+// clean_kernels.cu -- Hogbom CLEAN minor cycle on a device-resident residual (SURVEY.md section
+// 8f row N4: the consumer of invert_ng's dirty image and PSF).
+//
+// Replaces the interpreted loop of hogbom()
+// (/root/reference/src/ska_sdp_func_python/image/cleaners.py:23-133, overlapIndices :235-267):
+//   repeat niter times
+//     (mx, my) = argmax |res * window|            (first occurrence in C order, like numpy.argmax)
+//     mval     = res[mx, my] * gain / pmax
+//     comps[mx, my] += mval
+//     res[overlap] -= psf[overlap] * mval         (PSF centred on the peak, clipped to the image)
+//     stop if |res[mx, my]| < 0.9 * absolutethresh
+//
+// Every arithmetic step is the reference's own fp64 operation in the reference's order (separate
+// multiply and subtract, no fused multiply-add), so components and residual are BIT-EXACT.
+//
+// Design: the residual, PSF and window of a 2048^2 image (3 x 33 MB) live in the 126 MB L2, so one
+// iteration is one pass over L2-resident data: the kernel that subtracts the shifted PSF also
+// reduces |res * window| of the UPDATED residual to one (value, index) candidate per block, and a
+// one-block kernel picks the next peak, updates the component and evaluates the stop test.  The
+// host enqueues iterations back to back and looks at the stop flag every 64 iterations; kernels
+// of iterations enqueued after the stop exit immediately.
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "../../include/b200_wgridder.h"
+
+namespace b2g {
+int wrapper_fail(const char *msg);  // plan.cu
+}
+
+namespace {
+
+constexpr unsigned kFull = 0xffffffffu;
+constexpr int kBlocks = 592;   // 148 SMs x 4
+constexpr int kThreads = 256;
+
+struct Cand {
+    double val;
+    long long idx;
+};
+
+__device__ __forceinline__ double neg_inf() { return __longlong_as_double(0xfff0000000000000ll); }
+
+// numpy.argmax order: larger value wins, equal values keep the smaller flat index
+__device__ __forceinline__ bool better(double v, long long i, double bv, long long bi)
+{
+    return v > bv || (v == bv && i < bi);
+}
+
+__device__ __forceinline__ Cand warp_best(Cand c)
+{
+#pragma unroll
+    for (int d = 16; d > 0; d >>= 1) {
+        const double ov = __shfl_xor_sync(kFull, c.val, d);
+        const long long oi = __shfl_xor_sync(kFull, c.idx, d);
+        if (better(ov, oi, c.val, c.idx)) {
+            c.val = ov;
+            c.idx = oi;
+        }
+    }
+    return c;
+}
+
+__device__ Cand block_best(Cand c)
+{
+    __shared__ double sv[32];
+    __shared__ long long si[32];
+    c = warp_best(c);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (lane == 0) {
+        sv[warp] = c.val;
+        si[warp] = c.idx;
+    }
+    __syncthreads();
+    const int nw = (blockDim.x + 31) >> 5;
+    Cand r{lane < nw ? sv[lane] : neg_inf(), lane < nw ? si[lane] : (long long)0x7fffffffffffffffll};
+    r = warp_best(r);
+    __syncthreads();
+    return r;
+}
+
+struct CleanState {
+    int mx, my;        // current peak
+    double mval;       // component just added at the peak
+    int stop;          // set once the stop test fires (or niter is reached)
+    int iters;         // iterations completed
+    double peak0;      // max |dirty| (no window), for absolutethresh
+};
+
+// mode 0: candidate = |a[i] * w[i]| (w may be NULL), mode 1: candidate = a[i]
+__global__ void __launch_bounds__(kThreads)
+peak_partial_kernel(const double *__restrict__ a, const double *__restrict__ w, long long n, int mode,
+                    Cand *__restrict__ part)
+{
+    Cand best{neg_inf(), 0x7fffffffffffffffll};  // -inf
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n;
+         i += (long long)gridDim.x * blockDim.x) {
+        const double v = mode == 1 ? a[i] : fabs(w ? __dmul_rn(a[i], w[i]) : a[i]);
+        if (better(v, i, best.val, best.idx)) {
+            best.val = v;
+            best.idx = i;
+        }
+    }
+    best = block_best(best);
+    if (threadIdx.x == 0) part[blockIdx.x] = best;
+}
+
+__global__ void __launch_bounds__(kThreads)
+peak_final_kernel(const Cand *__restrict__ part, int npart, Cand *__restrict__ out)
+{
+    Cand best{neg_inf(), 0x7fffffffffffffffll};
+    for (int i = threadIdx.x; i < npart; i += blockDim.x)
+        if (better(part[i].val, part[i].idx, best.val, best.idx)) best = part[i];
+    best = block_best(best);
+    if (threadIdx.x == 0) *out = best;
+}
+
+// res -= psf(shifted to the peak) * mval on the overlap; candidates of the updated residual
+__global__ void __launch_bounds__(kThreads)
+clean_subtract_kernel(double *__restrict__ res, const double *__restrict__ psf,
+                      const double *__restrict__ window, int nx, int ny, int px, int py,
+                      const CleanState *__restrict__ st, Cand *__restrict__ part)
+{
+    if (st->stop) return;
+    const int mx = st->mx, my = st->my;
+    const double mval = st->mval;
+    const int pwx = px / 2, pwy = py / 2;
+    const int xlo = max(0, mx - pwx), xhi = min(nx, mx + pwx);
+    const int ylo = max(0, my - pwy), yhi = min(ny, my + pwy);
+    Cand best{neg_inf(), 0x7fffffffffffffffll};
+    // rows over blocks, columns over threads: no index division in the loop
+    for (int x = blockIdx.x; x < nx; x += gridDim.x) {
+        const bool xin = x >= xlo && x < xhi;
+        const double *prow = psf + (long long)(x - mx + pwx) * py + (pwy - my);
+        for (int y = threadIdx.x; y < ny; y += blockDim.x) {
+            const long long i = (long long)x * ny + y;
+            double r = res[i];
+            if (xin && y >= ylo && y < yhi) {
+                r = __dadd_rn(r, -__dmul_rn(prow[y], mval));
+                res[i] = r;
+            }
+            const double v = fabs(window ? __dmul_rn(r, window[i]) : r);
+            if (better(v, i, best.val, best.idx)) {
+                best.val = v;
+                best.idx = i;
+            }
+        }
+    }
+    best = block_best(best);
+    if (threadIdx.x == 0) part[blockIdx.x] = best;
+}
+
+// One block: stop test of the iteration just subtracted (first == 0), then the next peak.
+__global__ void __launch_bounds__(kThreads)
+clean_select_kernel(const double *__restrict__ res, double *__restrict__ comps, int ny,
+                    const Cand *__restrict__ part, int npart, double gain, double pmax,
+                    double stop_level, int niter, int first, CleanState *__restrict__ st)
+{
+    if (st->stop) return;
+    __shared__ int s_stop;
+    if (threadIdx.x == 0) {
+        s_stop = 0;
+        if (!first) {
+            st->iters += 1;
+            const double r = res[(long long)st->mx * ny + st->my];
+            if (fabs(r) < stop_level || st->iters >= niter) {
+                st->stop = 1;
+                s_stop = 1;
+            }
+        }
+    }
+    __syncthreads();
+    if (s_stop) return;
+    Cand best{neg_inf(), 0x7fffffffffffffffll};
+    for (int i = threadIdx.x; i < npart; i += blockDim.x)
+        if (better(part[i].val, part[i].idx, best.val, best.idx)) best = part[i];
+    best = block_best(best);
+    if (threadIdx.x == 0) {
+        const int mx = (int)(best.idx / ny), my = (int)(best.idx - (long long)mx * ny);
+        const double mval = __ddiv_rn(__dmul_rn(res[best.idx], gain), pmax);
+        st->mx = mx;
+        st->my = my;
+        st->mval = mval;
+        comps[best.idx] = __dadd_rn(comps[best.idx], mval);
+    }
+}
+
+int cuda_fail(cudaError_t e) { return b2g::wrapper_fail(cudaGetErrorString(e)); }
+
+}  // namespace
+
+static int run_peak(const double *img, const double *window, long long n, int mode, Cand *d_part,
+                    Cand *d_out, cudaStream_t s)
+{
+    peak_partial_kernel<<<kBlocks, kThreads, 0, s>>>(img, window, n, mode, d_part);
+    peak_final_kernel<<<1, kThreads, 0, s>>>(d_part, kBlocks, d_out);
+    cudaError_t e = cudaGetLastError();
+    return e == cudaSuccess ? 0 : cuda_fail(e);
+}
+
+extern "C" int b2g_image_peak(const double *img, const double *window, int64_t nx, int64_t ny,
+                              int mode, double *val_host, int64_t *idx_host, void *stream)
+{
+    if (!img || nx < 1 || ny < 1) return b2g::wrapper_fail("b2g_image_peak: bad arguments");
+    if (mode != 0 && mode != 1) return b2g::wrapper_fail("b2g_image_peak: mode must be 0 (argmax |a*w|) or 1 (max a)");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return b2g::wrapper_fail("b2g_image_peak: no CUDA device available (this library has no CPU path)");
+    cudaStream_t s = (cudaStream_t)stream;
+    Cand *d = nullptr;
+    cudaError_t e = cudaMallocAsync(&d, sizeof(Cand) * (kBlocks + 1), s);
+    if (e != cudaSuccess) return cuda_fail(e);
+    int rc = run_peak(img, window, nx * ny, mode, d, d + kBlocks, s);
+    Cand h{0.0, 0};
+    if (rc == 0) {
+        e = cudaMemcpyAsync(&h, d + kBlocks, sizeof(Cand), cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) rc = cuda_fail(e);
+    }
+    cudaFreeAsync(d, s);
+    if (rc) return rc;
+    if (val_host) *val_host = h.val;
+    if (idx_host) *idx_host = h.idx;
+    return 0;
+}
+
+extern "C" int b2g_hogbom(const double *dirty, const double *psf, const double *window, int64_t nx,
+                          int64_t ny, int64_t px, int64_t py, double gain, double pmax,
+                          double thresh, double fracthresh, int64_t niter, double *comps,
+                          double *res, int64_t *iters_host, void *stream)
+{
+    if (!dirty || !psf || !comps || !res) return b2g::wrapper_fail("b2g_hogbom: NULL pointer");
+    if (nx < 1 || ny < 1 || px < 1 || py < 1 || nx * ny > 0x7fffffffll)
+        return b2g::wrapper_fail("b2g_hogbom: bad image shape");
+    if (!(gain > 0.0 && gain < 2.0)) return b2g::wrapper_fail("b2g_hogbom: need 0 < gain < 2");
+    if (niter < 1) return b2g::wrapper_fail("b2g_hogbom: need niter > 0");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return b2g::wrapper_fail("b2g_hogbom: no CUDA device available (this library has no CPU path)");
+    cudaStream_t s = (cudaStream_t)stream;
+    const long long n = nx * ny;
+    Cand *d_part = nullptr;
+    cudaError_t e = cudaMallocAsync(&d_part, sizeof(Cand) * (kBlocks + 1) + sizeof(CleanState), s);
+    if (e != cudaSuccess) return cuda_fail(e);
+    Cand *d_peak = d_part + kBlocks;
+    CleanState *d_st = reinterpret_cast<CleanState *>(d_part + kBlocks + 1);
+    int rc = 0;
+    auto done = [&](int code) {
+        cudaStreamSynchronize(s);
+        cudaFreeAsync(d_part, s);
+        return code;
+    };
+#define CK(call)                                   \
+    do {                                           \
+        cudaError_t e_ = (call);                   \
+        if (e_ != cudaSuccess) return done(cuda_fail(e_)); \
+    } while (0)
+    // absolutethresh = max(thresh, fracthresh * max|dirty|)          cleaners.py:57
+    if ((rc = run_peak(dirty, nullptr, n, 0, d_part, d_peak, s))) return done(rc);
+    Cand h{0.0, 0};
+    CK(cudaMemcpyAsync(&h, d_peak, sizeof(Cand), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    const double absolutethresh = thresh > fracthresh * h.val ? thresh : fracthresh * h.val;
+    const double stop_level = 0.9 * absolutethresh;
+    CK(cudaMemsetAsync(d_st, 0, sizeof(CleanState), s));
+    CK(cudaMemsetAsync(comps, 0, sizeof(double) * n, s));
+    if (res != dirty) CK(cudaMemcpyAsync(res, dirty, sizeof(double) * n, cudaMemcpyDeviceToDevice, s));
+    // first peak
+    peak_partial_kernel<<<kBlocks, kThreads, 0, s>>>(res, window, n, 0, d_part);
+    clean_select_kernel<<<1, kThreads, 0, s>>>(res, comps, (int)ny, d_part, kBlocks, gain, pmax,
+                                               stop_level, (int)niter, 1, d_st);
+    CleanState hs;
+    hs.stop = 0;
+    hs.iters = 0;
+    for (long long i = 0; i < niter; ++i) {
+        clean_subtract_kernel<<<kBlocks, kThreads, 0, s>>>(res, psf, window, (int)nx, (int)ny, (int)px,
+                                                           (int)py, d_st, d_part);
+        clean_select_kernel<<<1, kThreads, 0, s>>>(res, comps, (int)ny, d_part, kBlocks, gain, pmax,
+                                                   stop_level, (int)niter, 0, d_st);
+        if ((i & 63) == 63 || i + 1 == niter) {
+            CK(cudaGetLastError());
+            CK(cudaMemcpyAsync(&hs, d_st, sizeof(CleanState), cudaMemcpyDeviceToHost, s));
+            CK(cudaStreamSynchronize(s));
+            if (hs.stop) break;
+        }
+    }
+#undef CK
+    if (iters_host) *iters_host = hs.iters;
+    return done(0);
+}
