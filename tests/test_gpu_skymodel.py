@@ -96,8 +96,10 @@ def test_skymodel_primary_beam_loop_golden(mods):
         assert rel_max(f["pixels"].data, g[f"sens_pb_flat{int(flat)}"]) < 1e-12
 
 
-@pytest.mark.parametrize("prec,eps,algo,tol", [("double", 1e-9, -1, 1e-12), ("double", 1e-12, -1, 1e-12),
-                                               ("single", 1e-5, -1, 2e-6), ("double", 1e-9, 0, 1e-12)])
+# tol: the two paths grid the same samples and differ only by the order of the atomics, whose
+# rounding noise the gridding correction may amplify up to epsilon / 4 at the image rim
+@pytest.mark.parametrize("prec,eps,algo,tol", [("double", 1e-9, -1, 2.5e-10), ("double", 1e-12, -1, 1e-12),
+                                               ("single", 1e-5, -1, 2.5e-6), ("double", 1e-9, 0, 2.5e-10)])
 def test_plan_residual_identity(mods, prec, eps, algo, tol):
     """residual(model, ms, wgt) == invert(ms - predict(model), wgt) on the same plan, device
     and host arrays, with and without the residual visibilities returned / updated in place."""
