@@ -12,7 +12,7 @@ degridding runs in the CUDA library behind include/b200_wgridder.h.  There is no
 
 New optional kwargs (absent in the reference): ``precision`` ("double" default as the reference
 forces fp64, ng.py:198/:203; "single" is the fp32 opt-in for epsilon >= 2e-6), ``nthreads``
-(alias of ``threads``; both ignored on the GPU), ``sumwt_on_device`` (default False: sumwt is
+(alias of ``threads``; both ignored on the GPU), ``sumwt_on_device`` (default None = automatic, see ``_invert``; False: sumwt is
 computed with the reference's own numpy expression so that it is bit-exact).
 
 The ``Visibility`` / ``Image`` arguments are used through the attributes the reference touches
@@ -109,7 +109,7 @@ def _options(kwargs):
         do_wstacking=kwargs.get("do_wstacking", True),
         verbosity=kwargs.get("verbosity", 0),
         precision=kwargs.get("precision", "double"),
-        sumwt_on_device=kwargs.get("sumwt_on_device", False),
+        sumwt_on_device=kwargs.get("sumwt_on_device", None),
     )
 
 
@@ -168,6 +168,10 @@ class _Device:
     def up(self, a):
         return self.torch.from_numpy(numpy.ascontiguousarray(a)).to(self.dev)
 
+    def stager(self):
+        from ._xfer import Stager
+        return Stager(self.torch, self.dev)
+
 
 def _rows_per_chunk(nchan, npol, bytes_per_elem):
     return max(1, int(_CHUNK_BYTES // max(1, nchan * npol * bytes_per_elem)))
@@ -197,11 +201,24 @@ def _prepare(D, vis, flags, weight, M, shift, dopsf, prec_code, npol_out):
         lmn = numpy.array([-shift[0], shift[1], -shift[2]], dtype=numpy.float64)
     L = _lib.lib()
     step = _rows_per_chunk(nchan, npol_in, vis.dtype.itemsize + weight.dtype.itemsize + 8)
+    # staging through pinned buffers (_xfer.Stager); a single-precision plan takes its inputs as
+    # complex64 / float32 (converted during the staging copy: half the PCIe bytes), integer flags
+    # travel as uint8 when their values allow it
+    stage = D.stager()
+    vdt = wdt = None
+    if prec_code == _lib.F32:
+        vdt, wdt = torch.complex64, torch.float32
+        vcode = wcode = _lib.F32
+    fdt = None
+    if flags is not None and flags.dtype.kind in "iub" and flags.dtype.itemsize > 1:
+        lo, hi = torch.from_numpy(flags.reshape(-1)).aminmax()
+        if int(lo) >= 0 and int(hi) <= 255:
+            fdt, fcode = torch.uint8, _lib.FLAG_U8
     for r0 in range(0, nrow, step):
         r1 = min(nrow, r0 + step)
-        dv = D.up(vis[r0:r1])
-        dw = D.up(weight[r0:r1])
-        df = D.up(flags[r0:r1]) if flags is not None else None
+        dv = stage.put(vis[r0:r1], vdt)
+        dw = stage.put(weight[r0:r1], wdt)
+        df = stage.put(flags[r0:r1], fdt) if flags is not None else None
         _lib.check(L.b2g_vis_prepare(
             r1 - r0, nchan, npol_in, npol_out, _ptr(dv), vcode, _ptr(df), fcode, _ptr(dw), wcode,
             _dptr(polmat), _dptr(lmn), _ptr(D.uvw), _ptr(D.fscale), r0, nrow, int(bool(dopsf)),
@@ -290,7 +307,15 @@ def _invert(bvis, model, dopsf, normalise, subtract_model, kwargs):
 
     # ---- sum of weights: the reference's own numpy expression (bit-exact) ----------------
     sumwt = numpy.zeros([nchan, npol])
-    if opt["sumwt_on_device"]:
+    on_device = opt["sumwt_on_device"]
+    if on_device is None:
+        # integer-valued weights (natural weighting: 0 / 1) sum exactly in any order as long as the
+        # total stays below 2^53 (2^24 for a single-precision plan): the device sum then IS the
+        # reference's numpy sum, bit for bit, without a host pass over the weight cube
+        big = 2.0 ** 24 if prec == _lib.F32 else 2.0 ** 53   # each weight exact in the plan's type
+        on_device = bool(((wg == wg.round()).all() & (wg.abs().amax() < big)
+                          & (wg.abs().sum(dtype=torch.float64) < 2.0 ** 53)).item()) if wg.numel() else True
+    if on_device:
         wsum = wg.sum(dim=1, dtype=torch.float64).cpu().numpy()  # [npol, vnchan]
         for pol in range(npol):
             if mfs:
@@ -409,8 +434,9 @@ def predict_ng(bvis, model, **kwargs):
         lmn = numpy.array([-shift[0], shift[1], -shift[2]], dtype=numpy.float64)
     Mh = numpy.ascontiguousarray(M, dtype=numpy.complex128)
     vis = numpy.empty((nrow, vnchan, vnpol), dtype=numpy.complex128)
-    step = _rows_per_chunk(vnchan, vnpol, 16)
+    step = max(1, _rows_per_chunk(vnchan, vnpol, 16) // 2)
     L = _lib.lib()
+    stage = D.stager()
     for r0 in range(0, nrow, step):
         r1 = min(nrow, r0 + step)
         chunk = torch.empty((r1 - r0, vnchan, vnpol), device=D.dev, dtype=torch.complex128)
@@ -418,7 +444,8 @@ def predict_ng(bvis, model, **kwargs):
             r1 - r0, vnchan, m_npol, vnpol, _ptr(vist), prec, _dptr(Mh.view(numpy.float64)),
             _dptr(lmn), _ptr(D.uvw), _ptr(D.fscale), r0, nrow, _ptr(chunk), _lib.F64,
             ctypes.c_void_p(D.stream)))
-        vis[r0:r1] = chunk.cpu().numpy()
+        stage.get(chunk, vis[r0:r1])   # D2H into pinned memory while the next chunk is finished
+    stage.finish()
     newbvis["vis"].data = vis.reshape([nrows, nbaselines, vnchan, vnpol])
     if update_pc:
         newbvis.attrs["phasecentre"] = model.image_acc.phasecentre

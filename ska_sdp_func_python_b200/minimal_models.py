@@ -180,10 +180,7 @@ class _Dataset:
     def _copy_vars(self, zero_keys=()):
         out = {}
         for k, v in self._vars.items():
-            d = numpy.array(v.data, copy=True)
-            if k in zero_keys:
-                d[...] = 0
-            out[k] = d
+            out[k] = numpy.zeros_like(v.data) if k in zero_keys else numpy.array(v.data, copy=True)
         return out
 
 

@@ -48,10 +48,30 @@ class WeightGrid:
         if isinstance(a, torch.Tensor):
             t = a.to(self.dev)
         else:
+            a = numpy.asarray(a)
+            if a.nbytes >= (1 << 24):
+                return self._up_staged(a, dtype)
             t = torch.from_numpy(numpy.ascontiguousarray(a)).to(self.dev)
         if dtype is not None and t.dtype != dtype:
             t = t.to(dtype)
         return t.contiguous()
+
+    def _up_staged(self, a, dtype, chunk_bytes=1 << 28):
+        """Large host arrays go up in chunks through pinned buffers (_xfer.Stager), converted to
+        ``dtype`` during the staging copy."""
+        from ._xfer import Stager
+        torch = self.torch
+        a = numpy.ascontiguousarray(a)
+        flat = a.reshape(-1)
+        dt = dtype or torch.from_numpy(flat[:1]).dtype
+        out = torch.empty(a.shape, device=self.dev, dtype=dt)
+        oflat = out.reshape(-1)
+        st = Stager(torch, self.dev, slots=3)
+        step = max(1, chunk_bytes // a.dtype.itemsize)
+        for i0 in range(0, flat.shape[0], step):
+            oflat[i0:i0 + step].copy_(st.put(flat[i0:i0 + step], dt), non_blocking=True)
+        st.finish()
+        return out
 
     def cube(self, a):
         """[nrow, nchan, npol] float64 on the device."""
@@ -71,6 +91,10 @@ class WeightGrid:
                 flags = flags.to(self.torch.float64)
             return flags.to(self.dev).contiguous(), codes[flags.dtype]
         f, code = _flags_for_device(numpy.asarray(flags))
+        if f.dtype.kind in "iu" and f.dtype.itemsize > 1 and f.size:
+            lo, hi = self.torch.from_numpy(f.reshape(-1)).aminmax()
+            if int(lo) >= 0 and int(hi) <= 255:     # 0 / 1 flags travel as bytes
+                return self._up(f, self.torch.uint8), _lib.FLAG_U8
         return self._up(f), code
 
 
@@ -146,9 +170,21 @@ def _grid_from_image(vis, model):
                       nx // 2 + 1, ny // 2 + 1)
 
 
-def _store(vis, imw_dev):
-    shape = vis["imaging_weight"].data.shape
-    vis["imaging_weight"].data[...] = imw_dev.cpu().numpy().reshape(shape)
+def _store(vis, imw_dev, chunk_bytes=1 << 28):
+    """imaging_weight of ``vis`` <- device tensor, in place, through pinned buffers."""
+    dst = vis["imaging_weight"].data
+    if not (isinstance(dst, numpy.ndarray) and dst.flags.c_contiguous and dst.dtype == numpy.float64
+            and dst.flags.writeable):
+        dst[...] = imw_dev.cpu().numpy().reshape(dst.shape)
+        return vis
+    from ._xfer import Stager
+    torch = _torch()
+    st = Stager(torch, imw_dev.device, slots=3)
+    flat, src = dst.reshape(-1), imw_dev.reshape(-1)
+    step = max(1, chunk_bytes // 8)
+    for i0 in range(0, flat.shape[0], step):
+        st.get(src[i0:i0 + step], flat[i0:i0 + step])
+    st.finish()
     return vis
 
 
