@@ -410,6 +410,22 @@ def run_b200(args):
         "note": "the visibility-side kernels are FP32-issue bound, not HBM bound (DESIGN.md); "
                 "the HBM fraction is reported because the metric asks for it",
     }
+    # context for the note: the kernel's algorithmic FP32 rate against the FP32 FMA peak
+    # (W^2 footprint cells x Wp w-planes x (re, im) FMAs per sample; kernel-value evaluation,
+    # index work and the 15 of 64 idle lane slots at W = 7 earn no credit)
+    Wk = info["W"]
+    fma_per_sample = Wk * Wk * (Wk if info["nplanes"] > 1 else 1) * 2
+    try:
+        sm_count = torch.cuda.get_device_properties(dev).multi_processor_count
+    except Exception:  # noqa: BLE001
+        sm_count = 148
+    fp32_peak = sm_count * 128 * 2 * 1.965e9 / 1e12
+    fp32_ach = nsamp * fma_per_sample * 2 / (kms * 1e-3) / 1e12
+    roofline["compute_context"] = {
+        "fp32_tflops_algorithmic": fp32_ach, "fp32_peak_tflops_nominal": fp32_peak,
+        "frac": fp32_ach / fp32_peak, "fma_per_sample": fma_per_sample,
+        "ncu": "profiles/r01_d_warprun_c2_full.csv: FMA pipe 59-62 % busy, issue slots 65 %, "
+               "shared-memory wavefronts 60-66 %, DRAM 2.6-4.2 %"}
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(traffic_file):
         try:
