@@ -272,6 +272,19 @@ int b2g_hogbom(const double *dirty, const double *psf, const double *window, int
 int b2g_image_peak(const double *img, const double *window, int64_t nx, int64_t ny, int mode,
                    double *val_host, int64_t *idx_host, void *stream);
 
+/*
+ * Adjoint of b2g_dft_predict: replaces the sums of idft_visibility_skycomponent
+ * (/root/reference/src/ska_sdp_func_python/imaging/dft.py:334-384).  DEVICE pointers.
+ *   flux_out[comp][chan][pol] = sum_rows weight*(1-flags) * vis*(1-flags) * exp(+2 pi i (u l + v m + w n'))
+ *   wsum_out[chan][pol]       = sum_rows weight*(1-flags)
+ * vis [nrow][nchan][npol] complex double, weight / flags same shape (weight may be NULL = ones,
+ * flags may be NULL), npol 1, 2 or 4.  The caller divides flux by wsum where wsum > 0.
+ */
+int b2g_dft_invert(int64_t nrow, int64_t nchan, int npol, int64_t ncomp, const double *uvw,
+                   const double *kscale, const double *dircos, const void *vis,
+                   const double *weight, const void *flags, int flag_dtype, void *flux_out,
+                   double *wsum_out, void *stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -179,3 +179,23 @@ def dft_components(direction_cosines, uvw_lambda, vfluxes):
         for pol in range(npol):
             vis[..., pol] += vfluxes[icomp, :, pol] * phasor
     return vis
+
+
+def idft_components(direction_cosines, uvw_lambda, vis, weight, flags):
+    """Adjoint of dft_components: the sums of idft_visibility_skycomponent
+    (/root/reference/src/ska_sdp_func_python/imaging/dft.py:334-384).  uvw_lambda [nrow, nchan, 3],
+    vis / weight / flags [nrow, nchan, npol] -> (flux [ncomp, nchan, npol] already divided by the
+    weight sum where it is positive, wsum [nchan, npol]).  Pinned by tests/golden/idft_case.npz."""
+    import numpy as np
+    fw = weight * (1 - flags)
+    fv = vis * (1 - flags)
+    wsum = np.sum(fw, axis=0)
+    out = []
+    for dc in direction_cosines:
+        phase = np.sum(uvw_lambda * dc, axis=-1)
+        phasor = np.exp(2j * np.pi * (phase - np.rint(phase)))[..., None]
+        f = np.sum(fw * fv * phasor, axis=0)
+        f[wsum > 0.0] = f[wsum > 0.0] / wsum[wsum > 0.0]
+        f[wsum <= 0.0] = 0.0
+        out.append(f)
+    return np.array(out), wsum

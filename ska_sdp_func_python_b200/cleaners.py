@@ -17,7 +17,7 @@ from .imaging import _ptr, _torch
 
 log = logging.getLogger("func-python-logger")
 
-__all__ = ["hogbom", "image_peak"]
+__all__ = ["hogbom", "hogbom_kernel_list", "common_arguments", "image_peak"]
 
 
 def _dev64(a, dev):
@@ -72,3 +72,57 @@ def hogbom(dirty, psf, window, gain, thresh, niter, fracthresh, prefix=""):
     if on_device:
         return comps, res
     return comps.cpu().numpy(), res.cpu().numpy()
+
+
+def common_arguments(**kwargs):
+    """fracthresh, gain, niter, thresh, scales from kwargs, with the reference's defaults and
+    range checks (image/deconvolution.py:514-540)."""
+    gain = kwargs.get("gain", 0.1)
+    if gain <= 0.0 or gain >= 2.0:
+        raise ValueError("Loop gain must be between 0 and 2")
+    thresh = kwargs.get("threshold", 0.0)
+    if thresh < 0.0:
+        raise ValueError("Threshold must be positive or zero")
+    niter = kwargs.get("niter", 100)
+    if niter < 0:
+        raise ValueError("niter must be greater than zero")
+    fracthresh = kwargs.get("fractional_threshold", 0.01)
+    if fracthresh < 0.0 or fracthresh > 1.0:
+        raise ValueError("Fractional threshold should be in range 0.0, 1.0")
+    scales = kwargs.get("scales", [0, 3, 10, 30])
+    return fracthresh, gain, niter, thresh, scales
+
+
+def _new_image_like(im, data):
+    """Image of ``im``'s class / WCS / polarisation frame holding ``data`` (Image.constructor of the
+    datamodels when available, image/deconvolution.py:629-638)."""
+    if hasattr(type(im), "constructor"):
+        return type(im).constructor(data=data, polarisation_frame=im.image_acc.polarisation_frame,
+                                    wcs=im.image_acc.wcs)
+    return type(im)(data, im.image_acc.wcs, im.image_acc.polarisation_frame)
+
+
+def hogbom_kernel_list(dirty_list, prefix, psf_list, window_list, **kwargs):
+    """Hogbom CLEAN of lists of single-frequency images, each polarisation separately
+    (image/deconvolution.py:543-643): returns (component image list, residual image list).
+    Polarisations whose PSF plane is all zero are skipped (left zero), as in the reference."""
+    fracthresh, gain, niter, thresh, _ = common_arguments(**kwargs)
+    comp_images, residual_images = [], []
+    for channel, dirty in enumerate(dirty_list):
+        psf = psf_list[channel]
+        dpix = dirty["pixels"].data
+        comp_array = numpy.zeros(dpix.shape)
+        residual_array = numpy.zeros(dpix.shape)
+        for pol in range(dpix.shape[1]):
+            if psf["pixels"].data[0, pol, :, :].max():
+                window = None
+                if window_list is not None and window_list[channel] is not None:
+                    window = window_list[channel]["pixels"].data[0, pol, :, :]
+                comp_array[0, pol, :, :], residual_array[0, pol, :, :] = hogbom(
+                    dpix[0, pol, :, :], psf["pixels"].data[0, pol, :, :], window, gain, thresh,
+                    niter, fracthresh, prefix)
+            else:
+                log.info("hogbom_kernel_list %s: Skipping pol %d, channel %d", prefix, pol, channel)
+        comp_images.append(_new_image_like(dirty, comp_array))
+        residual_images.append(_new_image_like(dirty, residual_array))
+    return comp_images, residual_images

@@ -11,11 +11,11 @@ import ctypes
 import numpy
 
 from . import _lib
-from .imaging import C_M_S, _ptr, _radec, _torch, skycoord_to_lmn
+from .imaging import C_M_S, _flags_for_device, _ptr, _radec, _torch, skycoord_to_lmn
 from .polarisation import pol_matrix
 
 __all__ = ["dft_skycomponent_visibility", "extract_direction_and_flux", "dft_kernel",
-           "dft_predict_device"]
+           "dft_predict_device", "idft_visibility_skycomponent", "dft_invert_device"]
 
 
 def dft_predict_device(uvw, kscale, direction_cosines, vfluxes, nchan, out=None, precision="double",
@@ -115,3 +115,62 @@ def dft_skycomponent_visibility(vis, sc, dft_compute_kernel=None):
                              torch.from_numpy(numpy.ascontiguousarray(vfluxes)).to(dev), nchan)
     vis["vis"].data = out.cpu().numpy().reshape(shape[0], shape[1], nchan, vfluxes.shape[2])
     return vis
+
+
+def dft_invert_device(uvw, kscale, direction_cosines, vis, weight=None, flags=None, flag_code=_lib.FLAG_NONE):
+    """Array-level adjoint on CUDA tensors: (flux [ncomp, nchan, npol] complex128, wsum
+    [nchan, npol] float64) with flux = sum_rows weight (1-flags) vis (1-flags) conj(phasor)."""
+    torch = _torch()
+    nrow, nchan, npol = vis.shape
+    ncomp = direction_cosines.shape[0]
+    flux = torch.empty((ncomp, nchan, npol), device=vis.device, dtype=torch.complex128)
+    wsum = torch.empty((nchan, npol), device=vis.device, dtype=torch.float64)
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    _lib.check(_lib.lib().b2g_dft_invert(nrow, nchan, npol, ncomp, _ptr(uvw), _ptr(kscale),
+                                         _ptr(direction_cosines), _ptr(vis), _ptr(weight), _ptr(flags),
+                                         flag_code, _ptr(flux), _ptr(wsum), stream))
+    return flux, wsum
+
+
+def idft_visibility_skycomponent(vis, sc):
+    """Inverse DFT a SkyComponent (or list) from Visibility (dft.py:334-384): returns (list of
+    components with the weighted-mean flux at their direction, list of weight arrays)."""
+    if sc is None:
+        return sc
+    if not isinstance(sc, collections.abc.Iterable):
+        sc = [sc]
+    sc = list(sc)
+    torch = _torch()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    shape = vis["vis"].data.shape
+    nchan, npol = shape[2], shape[3]
+    ra0, dec0 = _radec(vis.phasecentre)
+    dcs = []
+    for comp in sc:
+        ra, dec = _radec(comp.direction)
+        l, m, _ = skycoord_to_lmn(ra, dec, ra0, dec0)
+        dcs.append([l, m, numpy.sqrt(1 - l ** 2 - m ** 2) - 1.0])   # visibility/base.py:36-37
+    up = lambda a, dt=None: torch.from_numpy(numpy.ascontiguousarray(a)).to(dev) if dt is None else \
+        torch.from_numpy(numpy.ascontiguousarray(a)).to(dev).to(dt)  # noqa: E731
+    fl, fcode = _flags_for_device(numpy.asarray(vis["flags"].data).reshape(-1, nchan, npol))
+    flux, wsum = dft_invert_device(
+        up(numpy.asarray(vis.uvw.data, dtype=numpy.float64).reshape(-1, 3)),
+        up(numpy.asarray(vis.frequency.data, dtype=numpy.float64) / C_M_S),
+        up(numpy.array(dcs, dtype=numpy.float64).reshape(-1, 3)),
+        up(numpy.asarray(vis["vis"].data).reshape(-1, nchan, npol), torch.complex128),
+        up(numpy.asarray(vis["weight"].data).reshape(-1, nchan, npol), torch.float64),
+        up(fl), fcode)
+    flux, weight = flux.cpu().numpy(), wsum.cpu().numpy()
+    vpf = vis.visibility_acc.polarisation_frame
+    newsc, weights_list = [], []
+    for k, comp in enumerate(sc):
+        newcomp = comp.copy()
+        f = flux[k].copy()
+        f[weight > 0.0] = f[weight > 0.0] / weight[weight > 0.0]
+        f[weight <= 0.0] = 0.0
+        if comp.polarisation_frame != vpf:
+            f = f @ pol_matrix(vpf, comp.polarisation_frame).T
+        newcomp.flux = f
+        newsc.append(newcomp)
+        weights_list.append(weight.copy())
+    return newsc, weights_list

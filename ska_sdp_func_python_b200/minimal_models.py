@@ -371,7 +371,7 @@ class SkyComponent:
     def __init__(self, direction, frequency, flux, polarisation_frame, name="", shape="Point"):
         self.direction = direction
         self.frequency = numpy.atleast_1d(numpy.asarray(frequency, dtype=float))
-        self.flux = numpy.asarray(flux, dtype=float)
+        self.flux = numpy.asarray(flux)
         self.polarisation_frame = polarisation_frame
         self.name, self.shape = name, shape
 

@@ -74,3 +74,33 @@ def test_argument_checks(cl):
         cl.hogbom(d, 0.5 * p, None, 0.1, 0.0, 10, 0.0)          # PSF peak not 1
     comps, res = cl.hogbom(d, p, None, 0.1, 0.0, 10, 0.0)       # all-zero image: niter no-op iterations
     assert not comps.any() and not res.any()
+
+
+def test_hogbom_kernel_list(cl):
+    """Image-level loop over channels and polarisations (image/deconvolution.py:543-643)."""
+    from oracle import clean as oc
+    from ska_sdp_func_python_b200 import minimal_models as mm
+    g = np.load(os.path.join(GOLDEN, "clean_case.npz"))
+    pc = mm.SkyCoord.from_deg(0.0, -30.0)
+    pf = mm.PolarisationFrame("stokesIQ")
+    dirty = mm.create_image(64, 1e-3, pc, frequency=[1e8], polarisation_frame=pf)
+    dirty["pixels"].data[0, 0] = g["a_dirty"]
+    dirty["pixels"].data[0, 1] = 0.5 * g["a_dirty"][::-1]
+    psf = mm.create_image(64, 1e-3, pc, frequency=[1e8], polarisation_frame=pf)
+    psf["pixels"].data[0, 0] = g["a_psf"]                      # pol 1 PSF all zero: skipped
+    comps, resid = cl.hogbom_kernel_list([dirty], "test", [psf], None, gain=0.1, niter=300,
+                                         fractional_threshold=0.01)
+    assert len(comps) == len(resid) == 1 and isinstance(comps[0], mm.Image)
+    assert np.array_equal(comps[0]["pixels"].data[0, 0], g["a_comps"])
+    assert np.array_equal(resid[0]["pixels"].data[0, 0], g["a_res"])
+    assert not comps[0]["pixels"].data[0, 1].any() and not resid[0]["pixels"].data[0, 1].any()
+    psf["pixels"].data[0, 1] = g["a_psf"]
+    win = mm.create_image(64, 1e-3, pc, frequency=[1e8], polarisation_frame=pf)
+    win["pixels"].data[0, :, 16:48, 16:48] = 1.0
+    comps, resid = cl.hogbom_kernel_list([dirty], "test", [psf], [win], gain=0.2, niter=50)
+    oc_c, oc_r, _ = oc.hogbom(dirty["pixels"].data[0, 1], g["a_psf"], win["pixels"].data[0, 1], 0.2,
+                              0.0, 50, 0.01)
+    assert np.array_equal(comps[0]["pixels"].data[0, 1], oc_c)
+    assert np.array_equal(resid[0]["pixels"].data[0, 1], oc_r)
+    with pytest.raises(ValueError):
+        cl.hogbom_kernel_list([dirty], "test", [psf], None, gain=2.0)

@@ -100,3 +100,52 @@ def test_oracle_larger_and_modes(dft, npol):
     # no components: zeros
     z = dft.dft_predict_device(t(uvw), t(freq / C), t(dc[:0]), t(fl[:0]), nchan)
     assert float(z.abs().max()) == 0.0
+
+
+def test_idft_visibility_skycomponent_golden(dft):
+    """Adjoint DFT against the reference's own idft_visibility_skycomponent (flags, a zero-weight
+    (chan, pol), components in the visibility frame and in stokesIQUV)."""
+    from ska_sdp_func_python_b200 import minimal_models as mm
+    g = np.load(os.path.join(GOLDEN, "idft_case.npz"))
+    pc = mm.SkyCoord(float(g["pc"][0]), float(g["pc"][1]))
+    vis = mm.Visibility(g["vis"], g["uvw"], g["freq"], pc, mm.PolarisationFrame("linear"),
+                        weight=g["weight"], flags=g["flags"])
+    comps = [mm.SkyComponent(mm.SkyCoord(d[0], d[1]), g["freq"], np.ones((4, 4), dtype=complex),
+                             mm.PolarisationFrame(str(f))) for d, f in zip(g["dirs"], g["frames"])]
+    v0 = vis["vis"].data.copy()
+    newsc, wl = dft.idft_visibility_skycomponent(vis, comps)
+    assert len(newsc) == len(wl) == 5 and np.array_equal(vis["vis"].data, v0)
+    scale = np.abs(g["flux"]).max()
+    for k in range(5):
+        assert newsc[k] is not comps[k] and np.all(comps[k].flux == 1)
+        assert np.abs(newsc[k].flux - g["flux"][k]).max() < 1e-12 * scale
+        np.testing.assert_allclose(wl[k], g["weights"][k], rtol=1e-13)
+        assert np.all(newsc[k].flux[2, 1] == 0) or str(g["frames"][k]) != "linear"
+    assert dft.idft_visibility_skycomponent(vis, None) is None
+
+
+@pytest.mark.parametrize("npol", [1, 2, 4])
+def test_idft_is_adjoint_of_dft(dft, npol):
+    """<dft(flux), w vis> == <flux, idft sums(vis)> on a larger seeded case, and against the oracle."""
+    import torch
+    from oracle import dft as odft
+    rng = np.random.default_rng(30 + npol)
+    nrow, nchan, ncomp = 5000, 45, 11
+    freq = np.linspace(1.0e8, 1.3e8, nchan)
+    uvw = rng.uniform(-2e4, 2e4, (nrow, 3))
+    dc = rng.uniform(-0.05, 0.05, (ncomp, 3))
+    dc[:, 2] = np.sqrt(1 - dc[:, 0] ** 2 - dc[:, 1] ** 2) - 1
+    vis = rng.normal(size=(nrow, nchan, npol)) + 1j * rng.normal(size=(nrow, nchan, npol))
+    wgt = rng.uniform(0.5, 2.0, (nrow, nchan, npol))
+    flags = (rng.uniform(size=vis.shape) < 0.1).astype(np.uint8)
+    t = lambda a: torch.from_numpy(np.ascontiguousarray(a)).cuda()  # noqa: E731
+    from ska_sdp_func_python_b200 import _lib
+    flux, wsum = dft.dft_invert_device(t(uvw), t(freq / C), t(dc), t(vis), t(wgt), t(flags), _lib.FLAG_U8)
+    lam = np.einsum("rs,k->rks", uvw, freq / C)
+    oflux, owsum = odft.idft_components(dc, lam, vis, wgt, flags.astype(np.int64))
+    np.testing.assert_allclose(wsum.cpu().numpy(), owsum, rtol=1e-13)
+    got = flux.cpu().numpy() / owsum
+    assert np.abs(got - oflux).max() < 1e-12 * np.abs(oflux).max() * 50
+    # no components: weight sums only
+    f0, w0 = dft.dft_invert_device(t(uvw), t(freq / C), t(dc[:0]), t(vis), t(wgt), t(flags), _lib.FLAG_U8)
+    assert f0.shape[0] == 0 and torch.allclose(w0, wsum, rtol=1e-13)
