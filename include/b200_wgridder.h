@@ -273,6 +273,26 @@ int b2g_image_peak(const double *img, const double *window, int64_t nx, int64_t 
                    double *val_host, int64_t *idx_host, void *stream);
 
 /*
+ * Multi-scale CLEAN minor cycle: replaces the loop of msclean()
+ * (/root/reference/src/ska_sdp_func_python/image/cleaners.py:398-451) with its peak search
+ * find_max_abs_stack() (:565-610).  DEVICE pointers, C-contiguous float64:
+ *   res_stack      [nscales][nx][ny]          scale-convolved residuals, updated in place
+ *   psf_scalescale [nscales][nscales][px][py] doubly convolved PSFs
+ *   psf_scale      [nscales][px][py]          the scale shapes on the PSF's raster
+ *   window_stack   [nscales][nx][ny] or NULL, sensitivity [nx][ny] or NULL
+ *   comps          [nx][ny]                   component image (zeroed here)
+ * coupling_diag is a HOST array [nscales] (= max of psf_scalescale[s][s]); absolutethresh =
+ * max(thresh, fracthresh * max|res_stack[0]|) (:380).  The arithmetic and its order are the
+ * reference's, so for the same stacks the result is bit-exact; iters_host receives the number of
+ * components subtracted.  nscales <= 16.
+ */
+int b2g_msclean(double *res_stack, const double *psf_scalescale, const double *psf_scale,
+                const double *window_stack, const double *sensitivity, const double *coupling_diag,
+                int64_t nscales, int64_t nx, int64_t ny, int64_t px, int64_t py, double gain,
+                double absolutethresh, int64_t niter, double *comps, int64_t *iters_host,
+                void *stream);
+
+/*
  * Adjoint of b2g_dft_predict: replaces the sums of idft_visibility_skycomponent
  * (/root/reference/src/ska_sdp_func_python/imaging/dft.py:334-384).  DEVICE pointers.
  *   flux_out[comp][chan][pol] = sum_rows weight*(1-flags) * vis*(1-flags) * exp(+2 pi i (u l + v m + w n'))

@@ -34,3 +34,142 @@ def hogbom(dirty, psf, window, gain, thresh, niter, fracthresh):
         if numpy.abs(res[mx, my]) < 0.9 * absolutethresh:
             break
     return comps, res, it
+
+
+# ---- multi-scale CLEAN (cleaners.py:279-470 and helpers :473-610, :613-683) -------------------
+# Pinned against tests/golden/msclean_case.npz (outputs of the reference's own msclean(),
+# tests/golden/make_golden_msclean.py) in tests/test_oracle_clean.py.
+
+_PSWF_P = numpy.array([[8.203343e-2, -3.644705e-1, 6.278660e-1, -5.335581e-1, 2.312756e-1],
+                       [4.028559e-3, -3.697768e-2, 1.021332e-1, -1.201436e-1, 6.412774e-2]])
+_PSWF_Q = numpy.array([[1.0, 8.212018e-1, 2.078043e-1], [1.0, 9.599102e-1, 2.918724e-1]])
+
+
+def pswf(nu):
+    """Schwab's rational approximation of the m=6, alpha=1 prolate spheroidal wave function
+    (spheroidal_function, cleaners.py:613-683) for one scalar nu; 0 outside [0, 1]."""
+    if not 0.0 <= nu <= 1.0:
+        return 0.0
+    part, nuend = (0, 0.75) if nu < 0.75 else (1, 1.0)
+    d = nu ** 2 - nuend ** 2
+    top = _PSWF_P[part, 0]
+    for k in range(1, 5):
+        top += _PSWF_P[part, k] * d ** k
+    bot = _PSWF_Q[part, 0]
+    for k in range(1, 3):
+        bot += _PSWF_Q[part, k] * d ** k
+    return max(top / bot, 0.0) if bot != 0.0 else 0.0
+
+
+def scale_stack(shape, scales, norm=True):
+    """create_scalestack (cleaners.py:473-508): tapered-paraboloid blobs of the given widths, each
+    normalised to unit sum; width 0 is a delta.  Centre = ceil(n / 2)."""
+    ns, nx, ny = shape
+    assert ns == len(scales)
+    out = numpy.zeros(shape)
+    xc, yc = int(numpy.ceil(nx / 2.0)), int(numpy.ceil(ny / 2.0))
+    for s, width in enumerate(scales):
+        if width > 0.0:
+            half = int(numpy.ceil(width / 2.0))
+            inv = 1.0 / (float(width) / 2.0) ** 2
+            for y in range(yc - half - 1, yc + half + 1):
+                for x in range(xc - half - 1, xc + half + 1):
+                    fx, fy = float(x - xc), float(y - yc)
+                    r = numpy.sqrt(inv * (fx * fx + fy * fy))
+                    out[s, x, y] = pswf(r) * (1.0 - r ** 2)
+            out[out < 0.0] = 0.0
+            if norm:
+                out[s] /= numpy.sum(out[s])
+        else:
+            out[s, xc, yc] = 1.0
+    return out
+
+
+def _centred_spectrum(a):
+    # the reference wraps every transform in fftshift on both sides; the frequency-side shifts are
+    # permutations applied to every factor of an element-wise product and cancel exactly
+    return numpy.fft.fft2(numpy.fft.fftshift(a))
+
+
+def convolve_stack(stack, img):
+    """convolve_scalestack (cleaners.py:511-531): img correlated with every scale."""
+    fi = _centred_spectrum(img)
+    return numpy.stack([numpy.real(numpy.fft.ifftshift(numpy.fft.ifft2(fi * numpy.conjugate(_centred_spectrum(s)))))
+                        for s in stack])
+
+
+def convolve_convolve_stack(stack, img):
+    """convolve_convolve_scalestack (cleaners.py:534-562): out[s, p] = img * scale_p (x) scale_s."""
+    fi = _centred_spectrum(img)
+    fs = [_centred_spectrum(s) for s in stack]
+    ns = len(fs)
+    out = numpy.zeros((ns, ns) + img.shape)
+    for s in range(ns):
+        for p in range(ns):
+            out[s, p] = numpy.real(numpy.fft.ifftshift(numpy.fft.ifft2(fi * fs[p] * numpy.conjugate(fs[s]))))
+    return out
+
+
+def stack_peak(stack, sensitivity, windowstack, coupling):
+    """find_max_abs_stack (cleaners.py:565-610), including its double use of the sensitivity in
+    the argmax and the strict '>' across scales."""
+    best, bx, by, bs = 0.0, 0, 0, 0
+    for s in range(stack.shape[0]):
+        r = stack[s] * windowstack[s] / coupling[s, s] if windowstack is not None else stack[s] / coupling[s, s]
+        if sensitivity is not None:
+            r = r * sensitivity
+            k = numpy.abs(r * sensitivity).argmax()
+        else:
+            k = numpy.abs(r).argmax()
+        x, y = numpy.unravel_index(k, r.shape)
+        if numpy.abs(r[x, y]) > best:
+            best, bx, by, bs = numpy.abs(r[x, y]), x, y, s
+    return bx, by, bs
+
+
+def msclean_setup(dirty, psf, window, scales):
+    """Everything msclean() builds before its loop (cleaners.py:320-383)."""
+    pmax = psf.max()
+    assert pmax > 0.0
+    lpsf, ldirty = psf / pmax, dirty / pmax
+    ns = len(scales)
+    sstack = scale_stack((ns,) + ldirty.shape, scales)
+    pstack = scale_stack((ns,) + lpsf.shape, scales)
+    res = convolve_stack(sstack, numpy.array(ldirty))
+    pss = convolve_convolve_stack(pstack, numpy.array(lpsf))
+    coupling = pss.max(axis=(2, 3))
+    wstack = None
+    if window is not None:
+        wstack = numpy.zeros_like(sstack)
+        wstack[convolve_stack(sstack, window) > 0.9] = 1.0
+        assert numpy.sum(wstack) > 0
+    return pmax, pstack, res, pss, coupling, wstack
+
+
+def msclean_loop(res, pss, pstack, coupling, wstack, sensitivity, pshape, gain, absolutethresh, niter):
+    """The minor cycle proper (cleaners.py:398-451) on prepared stacks; res is updated in place.
+    Returns (comps, subtractions done)."""
+    shape = res.shape[1:]
+    comps = numpy.zeros(shape)
+    done = 0
+    for _ in range(niter):
+        mx, my, ms = stack_peak(res, sensitivity, wstack, coupling)
+        mval = res[ms, mx, my] / coupling[ms, ms]
+        if numpy.abs(res[ms, mx, my]) < 0.9 * absolutethresh or not numpy.abs(mval) > 0:
+            break
+        a1, a2 = overlap(shape, pshape, mx, my)
+        for s in range(res.shape[0]):
+            res[s, a1[0]:a1[1], a1[2]:a1[3]] -= pss[s, ms, a2[0]:a2[1], a2[2]:a2[3]] * gain * mval
+        comps[a1[0]:a1[1], a1[2]:a1[3]] += pstack[ms, a2[0]:a2[1], a2[2]:a2[3]] * gain * mval
+        done += 1
+    return comps, done
+
+
+def msclean(dirty, psf, window, sensitivity, gain, thresh, niter, scales, fracthresh):
+    """Returns (comps, residual, subtractions done)."""
+    assert 0.0 < gain < 2.0 and niter > 0 and len(scales) > 0
+    pmax, pstack, res, pss, coupling, wstack = msclean_setup(dirty, psf, window, scales)
+    absolutethresh = max(thresh, fracthresh * numpy.max(numpy.abs(res[0])))
+    comps, done = msclean_loop(res, pss, pstack, coupling, wstack, sensitivity, psf.shape, gain,
+                               absolutethresh, niter)
+    return comps, pmax * res[0], done

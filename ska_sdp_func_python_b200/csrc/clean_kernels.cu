@@ -185,6 +185,175 @@ clean_select_kernel(const double *__restrict__ res, double *__restrict__ comps, 
     }
 }
 
+// ---- multi-scale CLEAN (msclean(), cleaners.py:279-470; find_max_abs_stack :565-610) -----------
+//
+// State on the device: the stack of scale-convolved residuals res[ns][nx][ny], the doubly
+// convolved PSFs pss[ns][ns][px][py], the scale shapes pscale[ns][px][py], an optional window
+// stack and sensitivity image, and the coupling diagonal c[s] = max pss[s][s].  One iteration =
+// one launch that subtracts gain * mval * pss[s][mscale] (shifted to the peak) from every scale,
+// adds the scale shape to the component image and reduces the search metric of the UPDATED stack
+// to one candidate per (block, scale), plus a one-block launch that applies the reference's
+// across-scale rule and stop tests.  Arithmetic and its order are the reference's.
+
+constexpr int kMsBlocks = 296;  // per scale: 148 SMs x 2
+constexpr int kMaxScales = 16;
+
+struct MsState {
+    int mx, my, mscale;
+    double mval;
+    int stop;
+    int iters;  // subtractions done
+};
+
+struct MsCoupling {
+    double c[kMaxScales];
+};
+
+// value the search compares across scales (sensitivity applied once) ...
+__device__ __forceinline__ double ms_scaled(double r, const double *wrow, const double *sens,
+                                            long long i, double c)
+{
+    double v = wrow ? __dmul_rn(r, wrow[i]) : r;
+    v = __ddiv_rn(v, c);
+    if (sens) v = __dmul_rn(v, sens[i]);
+    return v;
+}
+// ... and the metric whose argmax picks the pixel within one scale (sensitivity applied twice
+// when there is one, cleaners.py:591-596)
+__device__ __forceinline__ double ms_metric(double v, const double *sens, long long i)
+{
+    return fabs(sens ? __dmul_rn(v, sens[i]) : v);
+}
+
+// Running per-thread argmax of the metric over pixels visited in ascending index order.  Without
+// a sensitivity image and with c > 0 the metric |r w / c| is a non-decreasing function of
+// |r w|, so a pixel whose |r w| is strictly below the one behind the current best cannot beat it
+// (an equal quotient would lose the tie to the earlier index): the division is only done for new
+// running maxima.
+struct MsBest {
+    Cand best;
+    double pre;  // |r w| behind best (fast path only)
+};
+
+__device__ __forceinline__ void ms_visit(MsBest &b, double r, const double *wrow, const double *sens,
+                                         long long i, double c, bool fast)
+{
+    if (fast) {
+        const double a = fabs(wrow ? __dmul_rn(r, wrow[i]) : r);
+        if (a < b.pre) return;
+        const double m = fabs(__ddiv_rn(wrow ? __dmul_rn(r, wrow[i]) : r, c));
+        if (better(m, i, b.best.val, b.best.idx)) {
+            b.best.val = m;
+            b.best.idx = i;
+            b.pre = a;
+        }
+    } else {
+        const double m = ms_metric(ms_scaled(r, wrow, sens, i, c), sens, i);
+        if (better(m, i, b.best.val, b.best.idx)) {
+            b.best.val = m;
+            b.best.idx = i;
+        }
+    }
+}
+
+// grid (kMsBlocks, ns + 1): y < ns updates scale y and reduces its metric; y == ns adds the
+// component.  first != 0: no subtraction, candidates of the initial stack only.
+__global__ void __launch_bounds__(kThreads)
+ms_subtract_kernel(double *__restrict__ res, const double *__restrict__ pss,
+                   const double *__restrict__ pscale, const double *__restrict__ wstack,
+                   const double *__restrict__ sens, double *__restrict__ comps, MsCoupling cp, int ns,
+                   int nx, int ny, int px, int py, double gain, int first,
+                   const MsState *__restrict__ st, Cand *__restrict__ part)
+{
+    if (st->stop) return;
+    const int s = blockIdx.y;
+    const int mx = st->mx, my = st->my, ms = st->mscale;
+    const double mval = st->mval;
+    const int pwx = px / 2, pwy = py / 2;
+    const int xlo = first ? 0 : max(0, mx - pwx), xhi = first ? 0 : min(nx, mx + pwx);
+    const int ylo = max(0, my - pwy), yhi = min(ny, my + pwy);
+    const long long n = (long long)nx * ny, pn = (long long)px * py;
+    if (s == ns) {
+        if (first) return;
+        const double *shape = pscale + (long long)ms * pn;
+        for (int x = xlo + blockIdx.x; x < xhi; x += gridDim.x) {
+            const double *prow = shape + (long long)(x - mx + pwx) * py + (pwy - my);
+            for (int y = ylo + threadIdx.x; y < yhi; y += blockDim.x) {
+                const long long i = (long long)x * ny + y;
+                comps[i] = __dadd_rn(comps[i], __dmul_rn(__dmul_rn(prow[y], gain), mval));
+            }
+        }
+        return;
+    }
+    double *r_s = res + (long long)s * n;
+    const double *w_s = wstack ? wstack + (long long)s * n : nullptr;
+    const double *p_s = pss + ((long long)s * ns + ms) * pn;
+    const double c = cp.c[s];
+    const bool fast = sens == nullptr && c > 0.0;
+    MsBest b{{neg_inf(), 0x7fffffffffffffffll}, -1.0};
+    for (int x = blockIdx.x; x < nx; x += gridDim.x) {
+        const bool xin = x >= xlo && x < xhi;
+        const double *prow = p_s + (long long)(x - mx + pwx) * py + (pwy - my);
+        for (int y = threadIdx.x; y < ny; y += blockDim.x) {
+            const long long i = (long long)x * ny + y;
+            double r = r_s[i];
+            if (xin && y >= ylo && y < yhi) {
+                r = __dadd_rn(r, -__dmul_rn(__dmul_rn(prow[y], gain), mval));
+                r_s[i] = r;
+            }
+            ms_visit(b, r, w_s, sens, i, c, fast);
+        }
+    }
+    const Cand best = block_best(b.best);
+    if (threadIdx.x == 0) part[(long long)s * gridDim.x + blockIdx.x] = best;
+}
+
+// One block: the peak over all scales (strict '>' in scale order, starting from 0 at pixel
+// (0, 0) of scale 0), the component value and the stop tests of the iteration about to start.
+__global__ void __launch_bounds__(kThreads)
+ms_select_kernel(const double *__restrict__ res, const double *__restrict__ wstack,
+                 const double *__restrict__ sens, MsCoupling cp, int ns, int nx, int ny,
+                 const Cand *__restrict__ part, int npart, double stop_level, int niter,
+                 MsState *__restrict__ st)
+{
+    if (st->stop) return;
+    const long long n = (long long)nx * ny;
+    double pabsmax = 0.0;
+    long long pidx = 0;
+    int pscale = 0;
+    for (int s = 0; s < ns; ++s) {
+        Cand best{neg_inf(), 0x7fffffffffffffffll};
+        for (int i = threadIdx.x; i < npart; i += blockDim.x) {
+            const Cand c = part[(long long)s * npart + i];
+            if (better(c.val, c.idx, best.val, best.idx)) best = c;
+        }
+        best = block_best(best);
+        // every thread of warp 0 holds the block's best; thread 0 decides
+        if (threadIdx.x == 0) {
+            const double v = ms_scaled(res[(long long)s * n + best.idx], wstack ? wstack + (long long)s * n : nullptr,
+                                       sens, best.idx, cp.c[s]);
+            if (fabs(v) > pabsmax) {
+                pabsmax = fabs(v);
+                pidx = best.idx;
+                pscale = s;
+            }
+        }
+    }
+    if (threadIdx.x == 0) {
+        const double r = res[(long long)pscale * n + pidx];
+        const double mval = __ddiv_rn(r, cp.c[pscale]);
+        if (st->iters >= niter || fabs(r) < stop_level || !(fabs(mval) > 0.0)) {
+            st->stop = 1;
+        } else {
+            st->mx = (int)(pidx / ny);
+            st->my = (int)(pidx - (long long)st->mx * ny);
+            st->mscale = pscale;
+            st->mval = mval;
+            st->iters += 1;
+        }
+    }
+}
+
 int cuda_fail(cudaError_t e) { return b2g::wrapper_fail(cudaGetErrorString(e)); }
 
 }  // namespace
@@ -280,6 +449,72 @@ extern "C" int b2g_hogbom(const double *dirty, const double *psf, const double *
         if ((i & 63) == 63 || i + 1 == niter) {
             CK(cudaGetLastError());
             CK(cudaMemcpyAsync(&hs, d_st, sizeof(CleanState), cudaMemcpyDeviceToHost, s));
+            CK(cudaStreamSynchronize(s));
+            if (hs.stop) break;
+        }
+    }
+#undef CK
+    if (iters_host) *iters_host = hs.iters;
+    return done(0);
+}
+
+extern "C" int b2g_msclean(double *res_stack, const double *psf_scalescale, const double *psf_scale,
+                           const double *window_stack, const double *sensitivity,
+                           const double *coupling_diag, int64_t nscales, int64_t nx, int64_t ny,
+                           int64_t px, int64_t py, double gain, double absolutethresh, int64_t niter,
+                           double *comps, int64_t *iters_host, void *stream)
+{
+    if (!res_stack || !psf_scalescale || !psf_scale || !coupling_diag || !comps)
+        return b2g::wrapper_fail("b2g_msclean: NULL pointer");
+    if (nscales < 1 || nscales > kMaxScales) return b2g::wrapper_fail("b2g_msclean: need 1..16 scales");
+    if (nx < 1 || ny < 1 || px < 1 || py < 1 || nx * ny > 0x7fffffffll)
+        return b2g::wrapper_fail("b2g_msclean: bad image shape");
+    if (!(gain > 0.0 && gain < 2.0)) return b2g::wrapper_fail("b2g_msclean: need 0 < gain < 2");
+    if (niter < 1) return b2g::wrapper_fail("b2g_msclean: need niter > 0");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return b2g::wrapper_fail("b2g_msclean: no CUDA device available (this library has no CPU path)");
+    cudaStream_t s = (cudaStream_t)stream;
+    const int ns = (int)nscales;
+    MsCoupling cp;
+    for (int i = 0; i < kMaxScales; ++i) cp.c[i] = i < ns ? coupling_diag[i] : 1.0;
+    Cand *d_part = nullptr;
+    cudaError_t e = cudaMallocAsync(&d_part, sizeof(Cand) * kMsBlocks * ns + sizeof(MsState), s);
+    if (e != cudaSuccess) return cuda_fail(e);
+    MsState *d_st = reinterpret_cast<MsState *>(d_part + (size_t)kMsBlocks * ns);
+    auto done = [&](int code) {
+        cudaStreamSynchronize(s);
+        cudaFreeAsync(d_part, s);
+        return code;
+    };
+#define CK(call)                                   \
+    do {                                           \
+        cudaError_t e_ = (call);                   \
+        if (e_ != cudaSuccess) return done(cuda_fail(e_)); \
+    } while (0)
+    const double stop_level = 0.9 * absolutethresh;
+    CK(cudaMemsetAsync(d_st, 0, sizeof(MsState), s));
+    CK(cudaMemsetAsync(comps, 0, sizeof(double) * nx * ny, s));
+    const dim3 grid(kMsBlocks, ns + 1);
+    ms_subtract_kernel<<<grid, kThreads, 0, s>>>(res_stack, psf_scalescale, psf_scale, window_stack,
+                                                 sensitivity, comps, cp, ns, (int)nx, (int)ny, (int)px,
+                                                 (int)py, gain, 1, d_st, d_part);
+    MsState hs;
+    hs.stop = 0;
+    hs.iters = 0;
+    // iteration i: select (stop tests, peak) then subtract; one select more than subtractions so
+    // that the niter limit is seen by the state
+    for (long long i = 0; i <= niter; ++i) {
+        ms_select_kernel<<<1, kThreads, 0, s>>>(res_stack, window_stack, sensitivity, cp, ns, (int)nx,
+                                                (int)ny, d_part, kMsBlocks, stop_level, (int)niter, d_st);
+        if (i < niter)
+            ms_subtract_kernel<<<grid, kThreads, 0, s>>>(res_stack, psf_scalescale, psf_scale,
+                                                         window_stack, sensitivity, comps, cp, ns,
+                                                         (int)nx, (int)ny, (int)px, (int)py, gain, 0,
+                                                         d_st, d_part);
+        if ((i & 63) == 63 || i == niter) {
+            CK(cudaGetLastError());
+            CK(cudaMemcpyAsync(&hs, d_st, sizeof(MsState), cudaMemcpyDeviceToHost, s));
             CK(cudaStreamSynchronize(s));
             if (hs.stop) break;
         }

@@ -1,5 +1,6 @@
-"""The Hogbom oracle (oracle/clean.py) against outputs of the reference's own hogbom()
-(tests/golden/make_golden_clean.py).  CPU only, bit-exact."""
+"""The Hogbom and multi-scale CLEAN oracles (oracle/clean.py) against outputs of the reference's own
+hogbom() / msclean() (tests/golden/make_golden_clean.py, make_golden_msclean.py).  CPU only,
+bit-exact."""
 import os
 
 import numpy as np
@@ -19,3 +20,32 @@ def test_hogbom_bit_exact(name):
     assert np.array_equal(comps, g[f"{name}_comps"])
     assert np.array_equal(res, g[f"{name}_res"])
     assert 1 <= it <= int(niter)
+
+
+MSGOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "msclean_case.npz")
+
+
+def ms_case(g, name):
+    gain, thresh, niter, frac = g[f"{name}_par"]
+    window = g[f"{name}_window"] if f"{name}_window" in g.files else None
+    sens = g[f"{name}_sens"] if f"{name}_sens" in g.files else None
+    return (g[f"{name}_dirty"], g[f"{name}_psf"], window, sens, gain, thresh, int(niter),
+            list(g[f"{name}_scales"]), frac)
+
+
+@pytest.mark.parametrize("name", ["a", "b", "c", "d", "e"])
+def test_msclean_bit_exact(name):
+    g = np.load(MSGOLD)
+    args = ms_case(g, name)
+    comps, res, done = oc.msclean(*args)
+    assert np.array_equal(comps, g[f"{name}_comps"])
+    assert np.array_equal(res, g[f"{name}_res"])
+    assert (done < args[6]) == (name == "e")            # only case e stops at the threshold
+
+
+def test_scale_stack_properties():
+    st = oc.scale_stack((3, 33, 40), [0, 4, 9])
+    assert st[0, 17, 20] == 1.0 and st[0].sum() == 1.0   # delta at ceil(n / 2)
+    assert np.allclose(st.sum(axis=(1, 2)), 1.0, rtol=1e-15) and (st >= 0).all()
+    assert np.unravel_index(st[2].argmax(), st[2].shape) == (17, 20)
+    assert oc.pswf(1.5) == 0.0 and oc.pswf(-0.1) == 0.0 and oc.pswf(0.0) > oc.pswf(0.9) > 0.0
