@@ -173,3 +173,31 @@ def msclean(dirty, psf, window, sensitivity, gain, thresh, niter, scales, fracth
     comps, done = msclean_loop(res, pss, pstack, coupling, wstack, sensitivity, psf.shape, gain,
                                absolutethresh, niter)
     return comps, pmax * res[0], done
+
+
+# ---- restoring beam (image/deconvolution.py:1016-1036) -------------------------------------------
+# PARITY UNPINNED: the reference builds the beam with astropy.convolution.Gaussian2DKernel and
+# convolves with astropy's convolve_fft(boundary="wrap"); astropy is not installed in the build
+# container, so this restates their documented behaviour (kernel of odd size ceil(8 max sigma),
+# sampled at pixel centres, peak-normalised; circular convolution centred on the kernel's middle).
+
+def beam_kernel(sx, sy, theta):
+    size = int(numpy.ceil(8.0 * max(sx, sy)))
+    if size % 2 == 0:
+        size += 1
+    h = size // 2
+    k = numpy.zeros((size, size))
+    ct, st = numpy.cos(theta), numpy.sin(theta)
+    for iy in range(size):
+        for ix in range(size):
+            xr = (ix - h) * ct + (iy - h) * st          # along the x_stddev axis
+            yr = -(ix - h) * st + (iy - h) * ct
+            k[iy, ix] = numpy.exp(-0.5 * ((xr / sx) ** 2 + (yr / sy) ** 2))
+    return k / k.max()
+
+
+def restore_plane(model, residual, sx, sy, theta):
+    """Direct (non-FFT) circular convolution of one plane with the beam, plus the residual."""
+    from scipy import ndimage
+    out = ndimage.convolve(model, beam_kernel(sx, sy, theta), mode="wrap")
+    return out + residual if residual is not None else out

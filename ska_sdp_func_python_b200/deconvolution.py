@@ -1,0 +1,311 @@
+"""Image-level deconvolution entry points on a B200.
+
+Mirrors the parts of /root/reference/src/ska_sdp_func_python/image/deconvolution.py that sit on the
+device kernels of ``cleaners.py``: ``deconvolve_cube`` / ``deconvolve_list`` (:50-160, :1045-1110)
+for the ``hogbom`` and ``msclean`` algorithms with the window / PSF-support plumbing
+(``find_window_list`` :283-350, ``bound_psf_list`` :353-395, ``check_psf_peak`` :266-280),
+``fit_psf`` (:1113-1159) and ``restore_cube`` / ``restore_list`` (:948-1043, :1162-1190), whose
+convolution with the clean beam runs on the device (cuFFT, circular, as the reference's
+``convolve_fft(boundary="wrap")``).
+
+Not mirrored: ``msmfsclean`` / ``hogbom-complex`` / radler (ValueError names them).
+
+Parity notes.  The CLEAN kernels are pinned against the reference's own outputs
+(tests/golden/clean_case.npz, msclean_case.npz).  ``fit_psf`` and the restoring beam depend on
+astropy.modeling / astropy.convolution in the reference, which are not installed in the build
+container, so these two are restated from astropy's documented behaviour (Gaussian2D
+parametrisation, Levenberg-Marquardt through scipy's MINPACK ``leastsq`` exactly as
+``LevMarLSQFitter`` does, ``Gaussian2DKernel`` of 8 sigma + 1 pixels normalised to unit peak) and
+checked against analytic cases only: PARITY UNPINNED for those two.
+"""
+import copy as _copy
+import logging
+
+import numpy
+
+from . import cleaners
+from .imaging import _torch
+
+log = logging.getLogger("func-python-logger")
+
+__all__ = ["deconvolve_cube", "deconvolve_list", "find_window_list", "check_psf_peak",
+           "bound_psf_list", "fit_psf", "restore_cube", "restore_list",
+           "convert_clean_beam_to_degrees", "convert_clean_beam_to_pixels",
+           "image_scatter_channels", "image_gather_channels"]
+
+
+# ---- small image helpers ------------------------------------------------------------------------
+
+def _like(im, data, wcs=None):
+    out = cleaners._new_image_like(im, data)
+    if wcs is not None and hasattr(out, "attrs") and "wcs" in out.attrs:
+        out.attrs["wcs"] = wcs
+    return out
+
+
+def image_scatter_channels(im, subimages=None):
+    """One single-channel image per frequency channel (image/gather_scatter.py
+    image_scatter_channels with its default of one sub-image per channel)."""
+    nchan = im["pixels"].data.shape[0]
+    if subimages is not None and subimages != nchan:
+        raise ValueError("image_scatter_channels: only one sub-image per channel is supported")
+    out = []
+    for chan in range(nchan):
+        wcs = _copy.deepcopy(im.image_acc.wcs)
+        wcs.wcs.crval[3] = wcs.wcs.crval[3] + chan * wcs.wcs.cdelt[3]
+        out.append(_like(im, numpy.array(im["pixels"].data[chan:chan + 1]), wcs))
+    return out
+
+
+def image_gather_channels(image_list):
+    """Inverse of image_scatter_channels."""
+    data = numpy.concatenate([im["pixels"].data for im in image_list], axis=0)
+    out = _like(image_list[0], data, _copy.deepcopy(image_list[0].image_acc.wcs))
+    if "clean_beam" in getattr(image_list[0], "attrs", {}):
+        out.attrs["clean_beam"] = image_list[0].attrs["clean_beam"]
+    return out
+
+
+def convert_clean_beam_to_degrees(im, beam_pixels):
+    """(stddev, stddev, theta) in pixels / radians -> {"bmaj", "bmin", "bpa"} in degrees
+    (image/operations.py:32-55)."""
+    cellsize = numpy.deg2rad(im.image_acc.wcs.wcs.cdelt[1])
+    to_mm = numpy.sqrt(8.0 * numpy.log(2.0))
+    first, second = beam_pixels[0] * cellsize * to_mm, beam_pixels[1] * cellsize * to_mm
+    if beam_pixels[1] > beam_pixels[0]:
+        return {"bmaj": numpy.rad2deg(second), "bmin": numpy.rad2deg(first),
+                "bpa": numpy.rad2deg(beam_pixels[2])}
+    return {"bmaj": numpy.rad2deg(first), "bmin": numpy.rad2deg(second),
+            "bpa": numpy.rad2deg(beam_pixels[2]) + 90.0}
+
+
+def convert_clean_beam_to_pixels(model, clean_beam):
+    """{"bmaj", "bmin", "bpa"} in degrees -> (minor stddev, major stddev, theta) in pixels /
+    radians (image/operations.py:58-75)."""
+    to_mm = numpy.sqrt(8.0 * numpy.log(2.0))
+    cellsize = numpy.deg2rad(model.image_acc.wcs.wcs.cdelt[1])
+    return (numpy.deg2rad(clean_beam["bmin"]) / (cellsize * to_mm),
+            numpy.deg2rad(clean_beam["bmaj"]) / (cellsize * to_mm),
+            numpy.deg2rad(clean_beam["bpa"]))
+
+
+# ---- windows and PSF support ----------------------------------------------------------------------
+
+def check_psf_peak(psf_list):
+    """Every PSF must have unit peak to 6 significant figures (deconvolution.py:266-280)."""
+    for ipsf, psf in enumerate(psf_list):
+        pmax = psf["pixels"].data.max()
+        numpy.testing.assert_approx_equal(
+            pmax, 1.0, significant=6,
+            err_msg=f"check_psf_peak: PSF {ipsf} does not have unit peak {pmax}")
+
+
+def find_window_list(dirty_list, prefix, window_shape=None, **kwargs):
+    """Clean windows per channel: "quarter", "no_edge" (``window_edge`` pixels, default 16) or
+    None; an Image passed as ``mask`` replaces the window (deconvolution.py:283-350, including the
+    exclusive lower edge ``q + 1`` of the reference's slices)."""
+    if window_shape is None:
+        log.info("deconvolve_cube %s: Cleaning entire image", prefix)
+        return None
+    windows = []
+    for dirty in dirty_list:
+        shape = dirty["pixels"].data.shape
+        window_array = numpy.zeros_like(dirty["pixels"].data)
+        if window_shape == "quarter":
+            qx, qy = shape[3] // 4, shape[2] // 4
+            window_array[..., (qy + 1):3 * qy, (qx + 1):3 * qx] = 1.0
+        elif window_shape == "no_edge":
+            edge = kwargs.get("window_edge", 16)
+            window_array[..., (edge + 1):(shape[2] - edge), (edge + 1):(shape[3] - edge)] = 1.0
+        else:
+            raise ValueError(f"Window shape {window_shape} is not recognized")
+        mask = kwargs.get("mask", None)
+        if mask is not None and hasattr(mask, "image_acc"):
+            log.warning("deconvolve_cube %s: Overriding window_shape with mask image", prefix)
+            window_array = mask["pixels"].data
+        windows.append(_like(dirty, window_array))
+    return windows
+
+
+def bound_psf_list(dirty_list, prefix, psf_list, psf_support=None):
+    """Cut every PSF to +/- psf_support pixels around its centre (default: half the dirty image),
+    when it is at least that large (deconvolution.py:353-395)."""
+    psfs = []
+    for channel, dirty in enumerate(dirty_list):
+        psf = psf_list[channel]
+        dshape, pshape = dirty["pixels"].data.shape, psf["pixels"].data.shape
+        if psf_support is None:
+            psf_support = max(dshape[2] // 2, dshape[3] // 2)
+        if psf_support <= pshape[2] // 2 and psf_support <= pshape[3] // 2:
+            # the reference indexes x with the centre of axis 2 and y with that of axis 3
+            cx, cy = pshape[2] // 2, pshape[3] // 2
+            cut = numpy.array(psf["pixels"].data[:, :, cy - psf_support:cy + psf_support,
+                                                 cx - psf_support:cx + psf_support])
+            psf = _like(psf, cut)
+        else:
+            log.info("Using entire psf for deconvolution")
+        psfs.append(psf)
+    return psfs
+
+
+# ---- deconvolve ------------------------------------------------------------------------------------
+
+def deconvolve_list(dirty_list, psf_list, sensitivity_list=None, prefix="", **kwargs):
+    """CLEAN of lists of single-channel images (deconvolution.py:50-160): ``algorithm`` =
+    "msclean" (default) or "hogbom"; kwargs window_shape, mask, window_edge, psf_support, gain,
+    threshold, fractional_threshold, niter, scales."""
+    window_shape = kwargs.get("window_shape", None)
+    window_list = find_window_list(dirty_list, prefix, window_shape=window_shape)
+    check_psf_peak(psf_list)
+    psf_list = bound_psf_list(dirty_list, prefix, psf_list, psf_support=kwargs.get("psf_support", None))
+    check_psf_peak(psf_list)
+    algorithm = kwargs.get("algorithm", "msclean")
+    if algorithm == "msclean":
+        return cleaners.msclean_kernel_list(dirty_list, prefix, psf_list, window_list,
+                                            sensitivity_list, **kwargs)
+    if algorithm == "hogbom":
+        return cleaners.hogbom_kernel_list(dirty_list, prefix, psf_list, window_list, **kwargs)
+    if algorithm in ("msmfsclean", "mfsmsclean", "mmclean", "hogbom-complex"):
+        raise ValueError(f"deconvolve_cube {prefix}: algorithm {algorithm} is not built in the B200 "
+                         "package (DESIGN.md, out of scope)")
+    raise ValueError(f"deconvolve_cube {prefix}: Unknown algorithm {algorithm}")
+
+
+def deconvolve_cube(dirty, psf, sensitivity=None, prefix="", **kwargs):
+    """CLEAN of an image cube, channel by channel (deconvolution.py:1045-1110): returns
+    (component image, residual image).  As in the reference, the sensitivity image is handed on
+    under a keyword the list function does not read, i.e. it is not used."""
+    dirty_list = image_scatter_channels(dirty)
+    psf_list = image_scatter_channels(psf)
+    kwargs.pop("sensitivity", None)
+    comp_list, residual_list = deconvolve_list(dirty_list, psf_list, prefix=prefix, **kwargs)
+    return image_gather_channels(comp_list), image_gather_channels(residual_list)
+
+
+# ---- clean beam ---------------------------------------------------------------------------------------
+
+def _gaussian2d(par, x, y):
+    """astropy.modeling.models.Gaussian2D: amplitude, x_mean, y_mean, x_stddev, y_stddev, theta."""
+    amp, x0, y0, sx, sy, theta = par
+    ct, st = numpy.cos(theta), numpy.sin(theta)
+    s2t = numpy.sin(2.0 * theta)
+    a = 0.5 * (ct * ct / sx ** 2 + st * st / sy ** 2)
+    b = 0.5 * (s2t / sx ** 2 - s2t / sy ** 2)
+    c = 0.5 * (st * st / sx ** 2 + ct * ct / sy ** 2)
+    dx, dy = x - x0, y - y0
+    return amp * numpy.exp(-(a * dx * dx + b * dx * dy + c * dy * dy))
+
+
+def fit_psf(psf):
+    """Gaussian fit to the central 15 x 15 pixels of the PSF (deconvolution.py:1113-1159): returns
+    {"bmaj", "bmin", "bpa"} in degrees.  The fit is the reference's: Gaussian2D started at
+    (max, patch centre, stddev 1, theta 0), Levenberg-Marquardt by MINPACK ``leastsq`` with
+    LevMarLSQFitter's settings (100 evaluations, xtol 1e-7); a 225-pixel problem, done on the host."""
+    from scipy import optimize
+    pix = psf["pixels"].data
+    if hasattr(pix, "is_cuda"):
+        pix = pix.cpu().numpy()
+    npixel = pix.shape[3]
+    sl = slice(npixel // 2 - 7, npixel // 2 + 8)
+    y, x = numpy.mgrid[sl, sl]
+    z = numpy.asarray(pix[0, 0, sl, sl], dtype=float)
+    tiny = numpy.finfo(float).tiny
+
+    def bounded(par):
+        par = numpy.array(par, dtype=float)
+        par[3], par[4] = max(par[3], tiny), max(par[4], tiny)      # astropy's stddev bounds
+        return par
+
+    def misfit(par):
+        return numpy.ravel(_gaussian2d(bounded(par), x, y) - z)
+
+    def jacobian(par):
+        # analytic derivatives, one row per parameter (col_deriv=1), as Gaussian2D.fit_deriv
+        amp, x0, y0, sx, sy, theta = bounded(par)
+        g = _gaussian2d((amp, x0, y0, sx, sy, theta), x, y)
+        ct2, st2 = numpy.cos(theta) ** 2, numpy.sin(theta) ** 2
+        s2t, c2t = numpy.sin(2.0 * theta), numpy.cos(2.0 * theta)
+        a = 0.5 * (ct2 / sx ** 2 + st2 / sy ** 2)
+        b = 0.5 * (s2t / sx ** 2 - s2t / sy ** 2)
+        c = 0.5 * (st2 / sx ** 2 + ct2 / sy ** 2)
+        dx, dy = x - x0, y - y0
+        quad = lambda da, db, dc_: -g * (da * dx * dx + db * dx * dy + dc_ * dy * dy)
+        rows = [g / amp if amp != 0.0 else numpy.exp(-(a * dx * dx + b * dx * dy + c * dy * dy)),
+                g * (2.0 * a * dx + b * dy),
+                g * (b * dx + 2.0 * c * dy),
+                quad(-ct2 / sx ** 3, -s2t / sx ** 3, -st2 / sx ** 3),
+                quad(-st2 / sy ** 3, s2t / sy ** 3, -ct2 / sy ** 3),
+                quad(0.5 * s2t * (1.0 / sy ** 2 - 1.0 / sx ** 2), c2t * (1.0 / sx ** 2 - 1.0 / sy ** 2),
+                     0.5 * s2t * (1.0 / sx ** 2 - 1.0 / sy ** 2))]
+        return numpy.array([numpy.ravel(r) for r in rows])
+
+    beam_pixels = (1.0, 1.0, 0.0)
+    try:
+        start = [numpy.max(z), numpy.mean(x), numpy.mean(y), 1.0, 1.0, 0.0]
+        sol, _, _, _, _ = optimize.leastsq(misfit, start, Dfun=jacobian, col_deriv=1, maxfev=100,
+                                           xtol=1e-7, full_output=True)
+        if sol[3] <= 0.0 or sol[4] <= 0.0 or not numpy.all(numpy.isfinite(sol)):
+            log.warning("fit_psf: error in fitting to psf, using 1 pixel stddev")
+        else:
+            beam_pixels = (float(sol[3]), float(sol[4]), float(sol[5]))
+    except (ValueError, optimize.OptimizeWarning):
+        log.warning("fit_psf: warning in fit to psf, using 1 pixel stddev")
+    return convert_clean_beam_to_degrees(psf, beam_pixels)
+
+
+def _beam_kernel(beam_pixels):
+    """astropy.convolution.Gaussian2DKernel(x_stddev, y_stddev, theta) normalised to unit peak:
+    odd size ceil(8 max(stddev)) (+1 if even), sampled at pixel centres; axis 1 is x."""
+    sx, sy, theta = (float(v) for v in beam_pixels)
+    size = int(numpy.ceil(8.0 * max(sx, sy)))
+    size += 1 - size % 2
+    half = size // 2
+    yy, xx = numpy.mgrid[-half:half + 1, -half:half + 1]
+    k = _gaussian2d((1.0, 0.0, 0.0, sx, sy, theta), xx.astype(float), yy.astype(float))
+    return k / k.max()
+
+
+def restore_list(model_list, psf_list=None, residual_list=None, clean_beam=None):
+    """Model convolved with the clean beam, plus the residual (deconvolution.py:948-1043).  The
+    circular convolution runs on the device: one real-to-complex cuFFT of the beam per image
+    shape, one forward / inverse pair per (channel, polarisation) plane."""
+    torch = _torch()
+    dev = torch.device("cuda", torch.cuda.current_device())
+    restored_list = []
+    for channel, model in enumerate(model_list):
+        psf = psf_list[channel] if psf_list is not None else None
+        residual = residual_list[channel] if residual_list is not None else None
+        if clean_beam is None:
+            if psf is None:
+                raise ValueError("restore_list: Either the psf or the clean_beam must be specified")
+            clean_beam = fit_psf(psf)
+            log.info("restore_list: Using fitted clean beam (deg, deg, deg) = %s", clean_beam)
+        beam_pixels = convert_clean_beam_to_pixels(model, clean_beam)
+        kern = _beam_kernel(beam_pixels)
+        pix = model["pixels"].data
+        ny, nx = pix.shape[2], pix.shape[3]
+        kh = kern.shape[0] // 2
+        if kern.shape[0] > ny or kern.shape[1] > nx:
+            raise ValueError("restore_list: the clean beam kernel is larger than the image")
+        # beam centred on pixel (0, 0) of a periodic raster
+        kimg = torch.zeros((ny, nx), dtype=torch.float64, device=dev)
+        kimg[:kern.shape[0], :kern.shape[1]] = torch.from_numpy(kern).to(dev)
+        kimg = torch.roll(kimg, shifts=(-kh, -kh), dims=(0, 1))
+        fk = torch.fft.rfft2(kimg)
+        d = torch.from_numpy(numpy.ascontiguousarray(pix, dtype=numpy.float64)).to(dev)
+        out = torch.fft.irfft2(torch.fft.rfft2(d) * fk, s=(ny, nx))
+        if residual is not None:
+            out += torch.from_numpy(numpy.ascontiguousarray(residual["pixels"].data, dtype=numpy.float64)).to(dev)
+        restored = _like(model, out.cpu().numpy().astype("float"))
+        restored.attrs["clean_beam"] = clean_beam
+        restored_list.append(restored)
+    return restored_list
+
+
+def restore_cube(model, psf=None, residual=None, clean_beam=None):
+    """Restore an image cube channel by channel (deconvolution.py:1162-1190)."""
+    model_list = image_scatter_channels(model)
+    residual_list = image_scatter_channels(residual) if residual is not None else None
+    psf_list = image_scatter_channels(psf) if psf is not None else None
+    return image_gather_channels(restore_list(model_list=model_list, psf_list=psf_list,
+                                              residual_list=residual_list, clean_beam=clean_beam))
