@@ -293,6 +293,27 @@ int b2g_msclean(double *res_stack, const double *psf_scalescale, const double *p
                 void *stream);
 
 /*
+ * Multi-scale multi-frequency CLEAN minor cycle: replaces the loop of msmfsclean()
+ * (/root/reference/src/ska_sdp_func_python/image/cleaners.py:826-880) with find_global_optimum()
+ * (:901-975, the "RASCIL" / "Algorithm1" peak finder), update_moment_model() (:1004-1031) and
+ * update_scale_moment_residual() (:977-1001).  DEVICE pointers, C-contiguous float64:
+ *   smres        [nscales][nmoment][nx][ny]                scale-convolved moment residuals, in place
+ *   psf_moments  [nscales][nscales][2 nmoment - 1][px][py] [a][b][k] = PSF moment k convolved with
+ *                                                          scale b and correlated with scale a
+ *                                                          (= the reference's ssmmpsf[a][b][t][q], k = t + q)
+ *   psf_scale    [nscales][px][py]                         the scale shapes on the PSF's raster
+ *   window_stack [nscales][nx][ny] or NULL, sensitivity [nx][ny] or NULL
+ *   model        [nmoment][nx][ny]                         moment model (zeroed here)
+ * inv_hessian is a HOST array [nscales][nmoment][nmoment] (:1081-1104).  nscales <= 16,
+ * nmoment <= 4.  iters_host receives the number of components subtracted.
+ */
+int b2g_msmfsclean(double *smres, const double *psf_moments, const double *psf_scale,
+                   const double *window_stack, const double *sensitivity, const double *inv_hessian,
+                   int64_t nscales, int64_t nmoment, int64_t nx, int64_t ny, int64_t px, int64_t py,
+                   double gain, double absolutethresh, int64_t niter, double *model,
+                   int64_t *iters_host, void *stream);
+
+/*
  * Adjoint of b2g_dft_predict: replaces the sums of idft_visibility_skycomponent
  * (/root/reference/src/ska_sdp_func_python/imaging/dft.py:334-384).  DEVICE pointers.
  *   flux_out[comp][chan][pol] = sum_rows weight*(1-flags) * vis*(1-flags) * exp(+2 pi i (u l + v m + w n'))

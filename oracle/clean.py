@@ -201,3 +201,82 @@ def restore_plane(model, residual, sx, sy, theta):
     from scipy import ndimage
     out = ndimage.convolve(model, beam_kernel(sx, sy, theta), mode="wrap")
     return out + residual if residual is not None else out
+
+
+# ---- multi-scale multi-frequency CLEAN (cleaners.py:686-898 and helpers :901-1160) ---------------
+# Pinned against tests/golden/msmfsclean_case.npz (outputs of the reference's own msmfsclean(),
+# tests/golden/make_golden_msmfsclean.py) in tests/test_oracle_clean.py.
+
+def msmfs_setup(dirty, psf, window, scales):
+    """Everything msmfsclean() builds before its loop (cleaners.py:752-795): scale shapes, the
+    scale-convolved moment residuals [ns, nm, nx, ny], the coupled PSFs [ns, ns, nm, nm, px, py],
+    the per-scale moment Hessians (PSF centre values) and their inverses, the window stack."""
+    pmax = psf.max()
+    assert pmax > 0.0
+    lpsf, ldirty = psf / pmax, dirty / pmax
+    nm, ns = dirty.shape[0], len(scales)
+    if nm > 1:
+        assert psf.shape[0] == 2 * nm
+    sstack = scale_stack((ns,) + ldirty.shape[1:], scales)
+    pstack = scale_stack((ns,) + lpsf.shape[1:], scales)
+    smres = numpy.zeros((ns, nm) + ldirty.shape[1:])
+    for t in range(nm):
+        smres[:, t] = convolve_stack(sstack, ldirty[t])
+    nmp = max(lpsf.shape[0] // 2, 1)
+    ssmm = numpy.zeros((ns, ns, nmp, nmp) + lpsf.shape[1:])
+    for t in range(nmp):
+        for q in range(nmp):
+            ssmm[:, :, t, q] = convolve_convolve_stack(pstack, lpsf[t + q])
+    hess = numpy.array([ssmm[s, s, :, :, lpsf.shape[1] // 2, lpsf.shape[2] // 2] for s in range(ns)])
+    ihess = numpy.array([numpy.linalg.inv(h) for h in hess])
+    wstack = None
+    if window is not None:
+        wstack = numpy.zeros_like(sstack)
+        wstack[convolve_stack(sstack, window) > 0.9] = 1.0
+    return pmax, pstack, smres, ssmm, hess, ihess, wstack
+
+
+def msmfs_peak(smres, ihess, wstack, sensitivity):
+    """find_global_optimum, RASCIL / Algorithm1 branch (cleaners.py:901-975, :1124-1157): the scale
+    is chosen on the windowed, sensitivity-weighted principal solution of moment 0, the pixel is the
+    peak of the UN-windowed one."""
+    sol = numpy.einsum("smn,smxy->snxy", ihess, smres)
+    best, bs, bx, by = 0.0, 0, 0, 0
+    for s in range(sol.shape[0]):
+        r = sol[s, 0] * wstack[s] if wstack is not None else sol[s, 0]
+        if sensitivity is not None:
+            r = sensitivity * r
+        top = numpy.max(numpy.abs(r))
+        if top > best:
+            best, bs = top, s
+            bx, by = numpy.unravel_index(numpy.abs(sol[s, 0]).argmax(), sol[s, 0].shape)
+    return bs, bx, by, sol[bs, :, bx, by]
+
+
+def msmfs_loop(smres, ssmm, pstack, ihess, wstack, sensitivity, gain, absolutethresh, niter):
+    """The minor cycle (cleaners.py:826-880); smres is updated in place.  Returns (model, done)."""
+    ns, nm = smres.shape[:2]
+    shape, pshape = smres.shape[2:], ssmm.shape[4:]
+    model = numpy.zeros((nm,) + shape)
+    done = 0
+    for _ in range(niter):
+        ms, mx, my, mval = msmfs_peak(smres, ihess, wstack, sensitivity)
+        if numpy.fabs(mval[0]) < absolutethresh:
+            break
+        a1, a2 = overlap(shape, pshape, mx, my)
+        for t in range(nm):
+            model[t, a1[0]:a1[1], a1[2]:a1[3]] += pstack[ms, a2[0]:a2[1], a2[2]:a2[3]] * gain * mval[t]
+        smres[:, :, a1[0]:a1[1], a1[2]:a1[3]] -= gain * numpy.einsum(
+            "stqxy,q->stxy", ssmm[ms, :, :, :, a2[0]:a2[1], a2[2]:a2[3]], mval)
+        done += 1
+    return model, done
+
+
+def msmfsclean(dirty, psf, window, sensitivity, gain, thresh, niter, scales, fracthresh):
+    """dirty [nmoment, nx, ny], psf [2 nmoment, px, py].  Returns (moment model, moment residual,
+    components subtracted)."""
+    assert 0.0 < gain < 2.0 and niter > 0 and len(scales) > 0
+    pmax, pstack, smres, ssmm, _, ihess, wstack = msmfs_setup(dirty, psf, window, scales)
+    absolutethresh = max(thresh, fracthresh * numpy.max(numpy.abs(smres[0, 0])))
+    model, done = msmfs_loop(smres, ssmm, pstack, ihess, wstack, sensitivity, gain, absolutethresh, niter)
+    return model, pmax * smres[0], done

@@ -17,7 +17,7 @@ from .imaging import _ptr, _torch
 
 log = logging.getLogger("func-python-logger")
 
-__all__ = ["hogbom", "hogbom_kernel_list", "msclean", "msclean_kernel_list", "create_scalestack",
+__all__ = ["hogbom", "hogbom_kernel_list", "msclean", "msclean_kernel_list", "msmfsclean", "create_scalestack",
            "spheroidal_function", "common_arguments", "image_peak"]
 
 
@@ -293,3 +293,89 @@ def msclean_kernel_list(dirty_list, prefix, psf_list, window_list, sensitivity_l
         comp_images.append(_new_image_like(dirty, comp_array))
         residual_images.append(_new_image_like(dirty, residual_array))
     return comp_images, residual_images
+
+
+# ---- multi-scale multi-frequency CLEAN (cleaners.py:686-898) ------------------------------------
+
+def msmfsclean(dirty, psf, window, sensitivity, gain, thresh, niter, scales, fracthresh,
+               findpeak="RASCIL", prefix=""):
+    """Image-plane multi-scale multi-frequency CLEAN (Rau & Cornwell 2011), cleaners.py:686-898:
+    ``dirty`` [nmoment, nx, ny], ``psf`` [2 nmoment, px, py]; returns (moment model, moment
+    residual), both [nmoment, nx, ny].  Setup (scale-convolved moment residuals, coupled PSFs,
+    moment Hessians) with cuFFT on the device, the nmoment x nmoment Hessian inverses on the host
+    (numpy.linalg.inv, as the reference), the minor cycle in csrc/clean_kernels.cu
+    (``b2g_msmfsclean``).  ``findpeak``: "RASCIL" and "Algorithm1" (identical in the reference,
+    cleaners.py:925-972); "CASA" is not built."""
+    assert 0.0 < gain < 2.0
+    assert niter > 0
+    assert len(scales) > 0
+    if findpeak == "CASA":
+        raise ValueError("msmfsclean: findpeak='CASA' is not built in the B200 package")
+    torch = _torch()
+    on_device = isinstance(dirty, torch.Tensor) and dirty.is_cuda
+    dev = dirty.device if on_device else torch.device("cuda", torch.cuda.current_device())
+    d = _dev64(dirty, dev)
+    p = _dev64(psf, dev)
+    if d.dim() != 3 or p.dim() != 3:
+        raise ValueError("msmfsclean: dirty and psf must be [nmoment, nx, ny]")
+    nmoment, ns = int(d.shape[0]), len(scales)
+    if nmoment > 1:
+        assert p.shape[0] == 2 * nmoment
+    if nmoment > 4:
+        raise ValueError("msmfsclean: at most 4 frequency moments")
+    pmax = float(p.max())
+    assert pmax > 0.0
+    lpsf, ldirty = p / pmax, d / pmax
+    shape, pshape = tuple(d.shape[1:]), tuple(p.shape[1:])
+    scalestack = create_scalestack([ns, shape[0], shape[1]], scales, norm=True, device=dev)
+    pscalestack = create_scalestack([ns, pshape[0], pshape[1]], scales, norm=True, device=dev)
+    fscales = _spectrum(torch, scalestack)
+    # smresidual [ns, nmoment, nx, ny]                                          cleaners.py:1034-1052
+    smres = torch.empty((ns, nmoment) + shape, dtype=torch.float64, device=dev)
+    for t in range(nmoment):
+        smres[:, t] = _convolve_scalestack(torch, fscales, ldirty[t])
+    # coupled PSFs by t + q: [a, b, k] = psf[k] * scale_b (x) scale_a          cleaners.py:1055-1078
+    nmp = max(int(p.shape[0]) // 2, 1)
+    if nmp != nmoment:
+        raise ValueError("msmfsclean: psf must hold 2 x nmoment planes")
+    nk = 2 * nmp - 1
+    fp = _spectrum(torch, pscalestack)
+    psfm = torch.empty((ns, ns, nk) + pshape, dtype=torch.float64, device=dev)
+    for k in range(nk):
+        fk = _spectrum(torch, lpsf[k])
+        for a in range(ns):
+            psfm[a, :, k] = _back(torch, (fk[None] * fp) * torch.conj(fp[a])[None], pshape)
+    centre = psfm[:, :, :, pshape[0] // 2, pshape[1] // 2].cpu().numpy()       # [a, b, k]
+    hessian = numpy.zeros((ns, nmoment, nmoment))
+    for s in range(ns):
+        for t in range(nmoment):
+            for q in range(nmoment):
+                hessian[s, t, q] = centre[s, s, t + q]
+    ihessian = numpy.ascontiguousarray(numpy.array([numpy.linalg.inv(h) for h in hessian]))
+    for s in range(ns):
+        log.info("mmclean %s: Moment-moment coupling matrix[scale %d] =\n %s", prefix, s, hessian[s])
+    windowstack = None
+    if window is not None:
+        w = _dev64(window, dev)
+        windowstack = (_convolve_scalestack(torch, fscales, w) > 0.9).to(torch.float64).contiguous()
+    del fscales, fp
+    sens = None if sensitivity is None else _dev64(sensitivity, dev)
+    if sens is not None and tuple(sens.shape) != shape:
+        raise ValueError("msmfsclean: sensitivity must be a 2-D image shaped like one moment plane")
+    maxabs, _ = image_peak(smres[0, 0])
+    absolutethresh = max(thresh, fracthresh * maxabs)
+    log.info("mmclean %s: Max abs in dirty Image = %.6f; this minor cycle will stop at %d iterations "
+             "or peak < %.6f (Jy/beam)", prefix, maxabs, niter, absolutethresh)
+    model = torch.empty((nmoment,) + shape, dtype=torch.float64, device=dev)
+    iters = ctypes.c_int64(0)
+    stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+    _lib.check(_lib.lib().b2g_msmfsclean(
+        _ptr(smres), _ptr(psfm), _ptr(pscalestack), _ptr(windowstack), _ptr(sens),
+        ihessian.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), ns, nmoment, shape[0], shape[1],
+        pshape[0], pshape[1], float(gain), float(absolutethresh), int(niter), _ptr(model),
+        ctypes.byref(iters), stream))
+    log.info("mmclean %s: End of minor cycle after %d components", prefix, iters.value)
+    res = pmax * smres[0]
+    if on_device:
+        return model, res
+    return model.cpu().numpy(), res.cpu().numpy()

@@ -354,7 +354,221 @@ ms_select_kernel(const double *__restrict__ res, const double *__restrict__ wsta
     }
 }
 
+// ---- multi-scale multi-frequency CLEAN (msmfsclean(), cleaners.py:686-898) ---------------------
+//
+// State: scale-convolved moment residuals smres[ns][nm][nx][ny]; coupled PSFs indexed by the SUM of
+// the two moment indices, psfm[ns (peak scale)][ns][2 nm - 1][px][py] (the reference stores all
+// nm x nm pairs, :1055-1078, which only depend on t + q); scale shapes pscale[ns][px][py]; inverse
+// moment Hessians ih[ns][nm][nm].  One iteration = one launch that, for every scale, subtracts
+// gain * sum_q psfm[mscale][s][t + q] * mval[q] from moment t on the clipped overlap, forms the
+// moment-0 principal solution sum_m ih[s][m][0] * smres[s][m] of the UPDATED residuals and reduces
+// (a) max |solution * window * sensitivity| and (b) argmax |solution| per block -- the reference
+// picks the scale on (a) and the pixel on (b), :1124-1157 -- plus one launch that applies the
+// across-scale rule, evaluates all moments of the principal solution at the peak and the stop test.
+
+constexpr int kMaxMoments = 4;
+
+struct MfState {
+    int mx, my, mscale;
+    int stop;
+    int iters;
+    double mval[kMaxMoments];
+};
+
+struct MfHess {
+    double ih[kMaxScales][kMaxMoments][kMaxMoments];
+};
+
+template <int NM>
+__global__ void __launch_bounds__(kThreads)
+mf_subtract_kernel(double *__restrict__ smres, const double *__restrict__ psfm,
+                   const double *__restrict__ pscale, const double *__restrict__ wstack,
+                   const double *__restrict__ sens, double *__restrict__ model, MfHess hs, int ns,
+                   int nx, int ny, int px, int py, double gain, int first,
+                   const MfState *__restrict__ st, Cand *__restrict__ part_scale,
+                   Cand *__restrict__ part_pixel)
+{
+    if (st->stop) return;
+    constexpr int NK = 2 * NM - 1;
+    const int s = blockIdx.y;
+    const int mx = st->mx, my = st->my, ms = st->mscale;
+    double mval[NM];
+#pragma unroll
+    for (int t = 0; t < NM; ++t) mval[t] = st->mval[t];
+    const int pwx = px / 2, pwy = py / 2;
+    const int xlo = first ? 0 : max(0, mx - pwx), xhi = first ? 0 : min(nx, mx + pwx);
+    const int ylo = max(0, my - pwy), yhi = min(ny, my + pwy);
+    const long long n = (long long)nx * ny, pn = (long long)px * py;
+    if (s == ns) {
+        if (first) return;
+        const double *shape = pscale + (long long)ms * pn;
+        for (int x = xlo + blockIdx.x; x < xhi; x += gridDim.x) {
+            const double *prow = shape + (long long)(x - mx + pwx) * py + (pwy - my);
+            for (int y = ylo + threadIdx.x; y < yhi; y += blockDim.x) {
+                const long long i = (long long)x * ny + y;
+                const double pg = __dmul_rn(prow[y], gain);
+#pragma unroll
+                for (int t = 0; t < NM; ++t)
+                    model[t * n + i] = __dadd_rn(model[t * n + i], __dmul_rn(pg, mval[t]));
+            }
+        }
+        return;
+    }
+    double *r_s = smres + (long long)s * NM * n;
+    const double *w_s = wstack ? wstack + (long long)s * n : nullptr;
+    const double *p_s = psfm + ((long long)ms * ns + s) * NK * pn;
+    double ih0[NM];
+#pragma unroll
+    for (int m = 0; m < NM; ++m) ih0[m] = hs.ih[s][m][0];
+    Cand best_scale{neg_inf(), 0x7fffffffffffffffll}, best_pixel{neg_inf(), 0x7fffffffffffffffll};
+    for (int x = blockIdx.x; x < nx; x += gridDim.x) {
+        const bool xin = x >= xlo && x < xhi;
+        const long long poff = (long long)(x - mx + pwx) * py + (pwy - my);
+        for (int y = threadIdx.x; y < ny; y += blockDim.x) {
+            const long long i = (long long)x * ny + y;
+            double r[NM];
+#pragma unroll
+            for (int t = 0; t < NM; ++t) r[t] = r_s[t * n + i];
+            if (xin && y >= ylo && y < yhi) {
+                double pk[NK];
+#pragma unroll
+                for (int k = 0; k < NK; ++k) pk[k] = p_s[k * pn + poff + y];
+#pragma unroll
+                for (int t = 0; t < NM; ++t) {
+                    double acc = __dmul_rn(pk[t], mval[0]);
+#pragma unroll
+                    for (int q = 1; q < NM; ++q) acc = __dadd_rn(acc, __dmul_rn(pk[t + q], mval[q]));
+                    r[t] = __dadd_rn(r[t], -__dmul_rn(gain, acc));
+                    r_s[t * n + i] = r[t];
+                }
+            }
+            double sol = __dmul_rn(ih0[0], r[0]);
+#pragma unroll
+            for (int m = 1; m < NM; ++m) sol = __dadd_rn(sol, __dmul_rn(ih0[m], r[m]));
+            double v = w_s ? __dmul_rn(sol, w_s[i]) : sol;
+            if (sens) v = __dmul_rn(sens[i], v);
+            v = fabs(v);
+            if (v > best_scale.val) best_scale.val = v;
+            const double a = fabs(sol);
+            if (better(a, i, best_pixel.val, best_pixel.idx)) {
+                best_pixel.val = a;
+                best_pixel.idx = i;
+            }
+        }
+    }
+    best_scale.idx = 0;
+    best_scale = block_best(best_scale);
+    best_pixel = block_best(best_pixel);
+    if (threadIdx.x == 0) {
+        part_scale[(long long)s * gridDim.x + blockIdx.x] = best_scale;
+        part_pixel[(long long)s * gridDim.x + blockIdx.x] = best_pixel;
+    }
+}
+
+template <int NM>
+__global__ void __launch_bounds__(kThreads)
+mf_select_kernel(const double *__restrict__ smres, MfHess hs, int ns, int nx, int ny,
+                 const Cand *__restrict__ part_scale, const Cand *__restrict__ part_pixel, int npart,
+                 double absolutethresh, int niter, MfState *__restrict__ st)
+{
+    if (st->stop) return;
+    const long long n = (long long)nx * ny;
+    double optimum = 0.0;
+    long long pidx = 0;
+    int pscale = 0;
+    for (int s = 0; s < ns; ++s) {
+        Cand top{neg_inf(), 0}, pix{neg_inf(), 0x7fffffffffffffffll};
+        for (int i = threadIdx.x; i < npart; i += blockDim.x) {
+            const Cand a = part_scale[(long long)s * npart + i];
+            if (a.val > top.val) top.val = a.val;
+            const Cand b = part_pixel[(long long)s * npart + i];
+            if (better(b.val, b.idx, pix.val, pix.idx)) pix = b;
+        }
+        top = block_best(top);
+        pix = block_best(pix);
+        if (top.val > optimum) {
+            optimum = top.val;
+            pscale = s;
+            pidx = pix.idx;
+        }
+    }
+    if (threadIdx.x == 0) {
+        double mval[NM];
+#pragma unroll
+        for (int nn = 0; nn < NM; ++nn) {
+            double acc = __dmul_rn(hs.ih[pscale][0][nn], smres[((long long)pscale * NM) * n + pidx]);
+#pragma unroll
+            for (int m = 1; m < NM; ++m)
+                acc = __dadd_rn(acc, __dmul_rn(hs.ih[pscale][m][nn], smres[((long long)pscale * NM + m) * n + pidx]));
+            mval[nn] = acc;
+        }
+        if (st->iters >= niter || fabs(mval[0]) < absolutethresh) {
+            st->stop = 1;
+        } else {
+            st->mx = (int)(pidx / ny);
+            st->my = (int)(pidx - (long long)st->mx * ny);
+            st->mscale = pscale;
+#pragma unroll
+            for (int nn = 0; nn < NM; ++nn) st->mval[nn] = mval[nn];
+            st->iters += 1;
+        }
+    }
+}
+
+template <int NM>
+int mf_run(double *smres, const double *psfm, const double *pscale, const double *wstack,
+           const double *sens, const MfHess &hs, int ns, int nx, int ny, int px, int py, double gain,
+           double absolutethresh, long long niter, double *model, int64_t *iters_host, cudaStream_t s);
+
 int cuda_fail(cudaError_t e) { return b2g::wrapper_fail(cudaGetErrorString(e)); }
+
+template <int NM>
+int mf_run(double *smres, const double *psfm, const double *pscale, const double *wstack,
+           const double *sens, const MfHess &hs, int ns, int nx, int ny, int px, int py, double gain,
+           double absolutethresh, long long niter, double *model, int64_t *iters_host, cudaStream_t s)
+{
+    Cand *d_part = nullptr;
+    const size_t npart = (size_t)kMsBlocks * ns;
+    cudaError_t e = cudaMallocAsync(&d_part, sizeof(Cand) * 2 * npart + sizeof(MfState), s);
+    if (e != cudaSuccess) return cuda_fail(e);
+    Cand *d_scale = d_part, *d_pixel = d_part + npart;
+    MfState *d_st = reinterpret_cast<MfState *>(d_part + 2 * npart);
+    auto done = [&](int code) {
+        cudaStreamSynchronize(s);
+        cudaFreeAsync(d_part, s);
+        return code;
+    };
+#define CK(call)                                   \
+    do {                                           \
+        cudaError_t e_ = (call);                   \
+        if (e_ != cudaSuccess) return done(cuda_fail(e_)); \
+    } while (0)
+    CK(cudaMemsetAsync(d_st, 0, sizeof(MfState), s));
+    CK(cudaMemsetAsync(model, 0, sizeof(double) * NM * nx * ny, s));
+    const dim3 grid(kMsBlocks, ns + 1);
+    mf_subtract_kernel<NM><<<grid, kThreads, 0, s>>>(smres, psfm, pscale, wstack, sens, model, hs, ns, nx,
+                                                     ny, px, py, gain, 1, d_st, d_scale, d_pixel);
+    MfState h;
+    h.stop = 0;
+    h.iters = 0;
+    for (long long i = 0; i <= niter; ++i) {
+        mf_select_kernel<NM><<<1, kThreads, 0, s>>>(smres, hs, ns, nx, ny, d_scale, d_pixel, kMsBlocks,
+                                                    absolutethresh, (int)niter, d_st);
+        if (i < niter)
+            mf_subtract_kernel<NM><<<grid, kThreads, 0, s>>>(smres, psfm, pscale, wstack, sens, model, hs,
+                                                             ns, nx, ny, px, py, gain, 0, d_st, d_scale,
+                                                             d_pixel);
+        if ((i & 63) == 63 || i == niter) {
+            CK(cudaGetLastError());
+            CK(cudaMemcpyAsync(&h, d_st, sizeof(MfState), cudaMemcpyDeviceToHost, s));
+            CK(cudaStreamSynchronize(s));
+            if (h.stop) break;
+        }
+    }
+#undef CK
+    if (iters_host) *iters_host = h.iters;
+    return done(0);
+}
 
 }  // namespace
 
@@ -522,4 +736,41 @@ extern "C" int b2g_msclean(double *res_stack, const double *psf_scalescale, cons
 #undef CK
     if (iters_host) *iters_host = hs.iters;
     return done(0);
+}
+
+extern "C" int b2g_msmfsclean(double *smres, const double *psf_moments, const double *psf_scale,
+                              const double *window_stack, const double *sensitivity,
+                              const double *inv_hessian, int64_t nscales, int64_t nmoment, int64_t nx,
+                              int64_t ny, int64_t px, int64_t py, double gain, double absolutethresh,
+                              int64_t niter, double *model, int64_t *iters_host, void *stream)
+{
+    if (!smres || !psf_moments || !psf_scale || !inv_hessian || !model)
+        return b2g::wrapper_fail("b2g_msmfsclean: NULL pointer");
+    if (nscales < 1 || nscales > kMaxScales) return b2g::wrapper_fail("b2g_msmfsclean: need 1..16 scales");
+    if (nmoment < 1 || nmoment > kMaxMoments) return b2g::wrapper_fail("b2g_msmfsclean: need 1..4 moments");
+    if (nx < 1 || ny < 1 || px < 1 || py < 1 || nx * ny > 0x7fffffffll)
+        return b2g::wrapper_fail("b2g_msmfsclean: bad image shape");
+    if (!(gain > 0.0 && gain < 2.0)) return b2g::wrapper_fail("b2g_msmfsclean: need 0 < gain < 2");
+    if (niter < 1) return b2g::wrapper_fail("b2g_msmfsclean: need niter > 0");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return b2g::wrapper_fail("b2g_msmfsclean: no CUDA device available (this library has no CPU path)");
+    MfHess hs;
+    for (int s = 0; s < kMaxScales; ++s)
+        for (int m = 0; m < kMaxMoments; ++m)
+            for (int q = 0; q < kMaxMoments; ++q)
+                hs.ih[s][m][q] = (s < nscales && m < nmoment && q < nmoment)
+                                     ? inv_hessian[(s * nmoment + m) * nmoment + q] : 0.0;
+    cudaStream_t st = (cudaStream_t)stream;
+#define RUN(NM)                                                                                     \
+    return mf_run<NM>(smres, psf_moments, psf_scale, window_stack, sensitivity, hs, (int)nscales,   \
+                      (int)nx, (int)ny, (int)px, (int)py, gain, absolutethresh, niter, model,       \
+                      iters_host, st)
+    switch (nmoment) {
+    case 1: RUN(1);
+    case 2: RUN(2);
+    case 3: RUN(3);
+    default: RUN(4);
+    }
+#undef RUN
 }

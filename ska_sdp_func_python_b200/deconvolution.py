@@ -8,7 +8,9 @@ for the ``hogbom`` and ``msclean`` algorithms with the window / PSF-support plum
 convolution with the clean beam runs on the device (cuFFT, circular, as the reference's
 ``convolve_fft(boundary="wrap")``).
 
-Not mirrored: ``msmfsclean`` / ``hogbom-complex`` / radler (ValueError names them).
+Not wired at this level: ``msmfsclean`` (its kernel is in ``cleaners.msmfsclean``; the list wrapper
+needs the Taylor-term moment images of image/taylor_terms.py), ``hogbom-complex``, radler
+(ValueError names them).
 
 Parity notes.  The CLEAN kernels are pinned against the reference's own outputs
 (tests/golden/clean_case.npz, msclean_case.npz).  ``fit_psf`` and the restoring beam depend on
@@ -166,8 +168,8 @@ def deconvolve_list(dirty_list, psf_list, sensitivity_list=None, prefix="", **kw
     if algorithm == "hogbom":
         return cleaners.hogbom_kernel_list(dirty_list, prefix, psf_list, window_list, **kwargs)
     if algorithm in ("msmfsclean", "mfsmsclean", "mmclean", "hogbom-complex"):
-        raise ValueError(f"deconvolve_cube {prefix}: algorithm {algorithm} is not built in the B200 "
-                         "package (DESIGN.md, out of scope)")
+        raise ValueError(f"deconvolve_cube {prefix}: algorithm {algorithm} is not wired at the image-list "
+                         "level in the B200 package (cleaners.msmfsclean is the kernel; DESIGN.md)")
     raise ValueError(f"deconvolve_cube {prefix}: Unknown algorithm {algorithm}")
 
 

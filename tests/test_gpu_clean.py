@@ -217,3 +217,72 @@ def test_msclean_kernel_list(cl):
                                           fractional_threshold=0.05, scales=[0, 3, 8, 14])
     assert np.abs(comps[0]["pixels"].data[0, 1] - g["c_comps"]).max() < 1e-11
     assert np.abs(resid[0]["pixels"].data[0, 1] - g["c_res"]).max() < 1e-11
+
+
+# ---- multi-scale multi-frequency CLEAN ---------------------------------------------------------
+
+def _mf_case(g, name):
+    gain, thresh, niter, frac = g[f"{name}_par"]
+    window = g[f"{name}_window"] if f"{name}_window" in g.files else None
+    sens = g[f"{name}_sens"] if f"{name}_sens" in g.files else None
+    return (g[f"{name}_dirty"], g[f"{name}_psf"], window, sens, gain, thresh, int(niter),
+            list(g[f"{name}_scales"]), frac)
+
+
+@pytest.mark.parametrize("name", ["a", "b", "c", "d"])
+def test_msmfsclean_golden(cl, name):
+    """Against the reference's own msmfsclean().  The stacks come from cuFFT and pass through the
+    inverse moment Hessians (condition number up to ~1e4 here), so the tolerance is 1e-9 on O(1)
+    data rather than the 1e-11 of msclean."""
+    g = np.load(os.path.join(GOLDEN, "msmfsclean_case.npz"))
+    args = _mf_case(g, name)
+    model, res = cl.msmfsclean(*args)
+    assert model.shape == args[0].shape and res.shape == args[0].shape
+    assert np.abs(model - g[f"{name}_model"]).max() < 1e-9
+    assert np.abs(res - g[f"{name}_res"]).max() < 1e-9
+
+
+@pytest.mark.parametrize("name", ["a", "b", "c", "d"])
+def test_msmfsclean_loop_on_oracle_stacks(cl, name):
+    """The minor cycle alone, through the C ABI, on the ORACLE's stacks: same arithmetic as the
+    reference up to the summation order inside numpy.einsum -> 1e-13, same iteration count."""
+    import ctypes
+    import torch
+    from oracle import clean as oc
+    from ska_sdp_func_python_b200 import _lib
+    g = np.load(os.path.join(GOLDEN, "msmfsclean_case.npz"))
+    dirty, psf, window, sens, gain, thresh, niter, scales, frac = _mf_case(g, name)
+    pmax, pstack, smres, ssmm, hess, ihess, wstack = oc.msmfs_setup(dirty, psf, window, scales)
+    ns, nm = smres.shape[:2]
+    psfm = np.zeros((ns, ns, 2 * nm - 1) + psf.shape[1:])
+    for t in range(nm):
+        for q in range(nm):
+            psfm[:, :, t + q] = ssmm[:, :, t, q]
+    absthresh = max(thresh, frac * np.abs(smres[0, 0]).max())
+    dev = torch.device("cuda", 0)
+    up = lambda a: None if a is None else torch.from_numpy(np.ascontiguousarray(a, dtype=np.float64)).to(dev)
+    ptr = lambda t: ctypes.c_void_p(0 if t is None else t.data_ptr())
+    d_res, d_psfm, d_ps, d_w, d_s = up(smres), up(psfm), up(pstack), up(wstack), up(sens)
+    d_model = torch.empty((nm,) + dirty.shape[1:], dtype=torch.float64, device=dev)
+    ih = np.ascontiguousarray(ihess)
+    iters = ctypes.c_int64(0)
+    _lib.check(_lib.lib().b2g_msmfsclean(ptr(d_res), ptr(d_psfm), ptr(d_ps), ptr(d_w), ptr(d_s),
+                                         ih.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), ns, nm,
+                                         dirty.shape[1], dirty.shape[2], psf.shape[1], psf.shape[2], gain,
+                                         absthresh, niter, ptr(d_model), ctypes.byref(iters),
+                                         ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)))
+    o_model, done = oc.msmfs_loop(smres, ssmm, pstack, ihess, wstack, sens, gain, absthresh, niter)
+    assert iters.value == done
+    assert np.abs(d_model.cpu().numpy() - o_model).max() < 1e-13
+    assert np.abs(d_res.cpu().numpy() - smres).max() < 1e-13
+
+
+def test_msmfsclean_arguments(cl):
+    g = np.load(os.path.join(GOLDEN, "msmfsclean_case.npz"))
+    args = list(_mf_case(g, "b"))
+    with pytest.raises(ValueError):
+        cl.msmfsclean(*args, findpeak="CASA")
+    with pytest.raises(AssertionError):
+        cl.msmfsclean(args[0], args[1][:3], *args[2:])           # psf must hold 2 x nmoment planes
+    with pytest.raises(ValueError):
+        cl.msmfsclean(args[0][0], args[1][0], *args[2:])         # 2-D input

@@ -49,3 +49,19 @@ def test_scale_stack_properties():
     assert np.allclose(st.sum(axis=(1, 2)), 1.0, rtol=1e-15) and (st >= 0).all()
     assert np.unravel_index(st[2].argmax(), st[2].shape) == (17, 20)
     assert oc.pswf(1.5) == 0.0 and oc.pswf(-0.1) == 0.0 and oc.pswf(0.0) > oc.pswf(0.9) > 0.0
+
+
+MFGOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "msmfsclean_case.npz")
+
+
+@pytest.mark.parametrize("name", ["a", "b", "c", "d"])
+def test_msmfsclean_bit_exact(name):
+    g = np.load(MFGOLD)
+    gain, thresh, niter, frac = g[f"{name}_par"]
+    window = g[f"{name}_window"] if f"{name}_window" in g.files else None
+    sens = g[f"{name}_sens"] if f"{name}_sens" in g.files else None
+    model, res, done = oc.msmfsclean(g[f"{name}_dirty"], g[f"{name}_psf"], window, sens, gain, thresh,
+                                     int(niter), list(g[f"{name}_scales"]), frac)
+    assert np.array_equal(model, g[f"{name}_model"])
+    assert np.array_equal(res, g[f"{name}_res"])
+    assert (done < int(niter)) == (name == "d")         # only case d stops at the threshold

@@ -22,6 +22,7 @@ def main():
     ap.add_argument("--niter", type=int, default=2000)
     ap.add_argument("--cpu-niter", type=int, default=50)
     ap.add_argument("--json", default=None)
+    ap.add_argument("--msmfs", action="store_true", help="time msmfsclean (3 moments, scales 0,3,10,30)")
     ap.add_argument("--msclean", action="store_true", help="time multi-scale CLEAN (scales 0,3,10,30) instead")
     a = ap.parse_args()
     import torch
@@ -37,6 +38,8 @@ def main():
     d, p = torch.from_numpy(dirty).cuda(), torch.from_numpy(psf).cuda()
     if a.msclean:
         return msclean_perf(a, cleaners, oc, torch, dirty, psf, d, p)
+    if a.msmfs:
+        return msmfs_perf(a, cleaners, oc, torch, dirty, psf)
     cleaners.hogbom(d, p, None, 0.1, 0.0, 64, 0.0)
     torch.cuda.synchronize()
     t0 = time.perf_counter()
@@ -86,6 +89,43 @@ def msclean_perf(a, cleaners, oc, torch, dirty, psf, d, p):
            "gpu_alg_GBs": byt / per_iter / 1e9, "cpu_setup_ms": 1e3 * t_cpu_setup,
            "cpu_us_per_iter": 1e6 * t_cpu_loop / max(done, 1),
            "cpu_kind": "port (numpy, the reference's loop)", "max_abs_err_vs_oracle": err}
+    print(json.dumps(out))
+    if a.json:
+        with open(a.json, "w") as fh:
+            fh.write(json.dumps(out) + "\n")
+
+
+def msmfs_perf(a, cleaners, oc, torch, dirty, psf):
+    """MSMFS CLEAN, 3 moments x scales [0, 3, 10, 30]; CPU leg = the numpy oracle (the reference's
+    setup and loop) on a bounded number of iterations."""
+    n = a.npix
+    scales = [0, 3, 10, 30]
+    wc = np.linspace(-0.2, 0.2, 5)
+    dm = np.array([dirty * np.mean(wc ** t * (1.0 + 0.5 * wc)) for t in range(3)])
+    dm[1:] += 0.002 * np.random.default_rng(9).normal(size=(2, n, n))
+    pm = np.array([psf * np.mean(wc ** k) for k in range(6)])
+    d, p = torch.from_numpy(dm).cuda(), torch.from_numpy(pm).cuda()
+    run = lambda k: cleaners.msmfsclean(d, p, None, None, 0.7, 0.0, k, scales, 0.0)
+    run(8)
+    torch.cuda.synchronize()
+    t0 = time.perf_counter(); run(8); torch.cuda.synchronize(); t_short = time.perf_counter() - t0
+    t0 = time.perf_counter(); run(a.niter); torch.cuda.synchronize(); t_long = time.perf_counter() - t0
+    per_iter = (t_long - t_short) / (a.niter - 8)
+    out = {"algorithm": "msmfsclean", "scales": scales, "nmoment": 3, "npix": n, "niter": a.niter,
+           "gpu_setup_ms": 1e3 * (t_short - 8 * per_iter), "gpu_us_per_iter": 1e6 * per_iter,
+           # every (scale, moment) residual plane read + written, 5 coupled PSF moment planes per scale read
+           "gpu_alg_GBs": n * n * 8 * (2 * 12 + 20) / per_iter / 1e9}
+    if a.cpu_niter > 0:
+        t0 = time.perf_counter()
+        pmax, pstack, smres, ssmm, _, ihess, _ = oc.msmfs_setup(dm, pm, None, scales)
+        out["cpu_setup_ms"] = 1e3 * (time.perf_counter() - t0)
+        t0 = time.perf_counter()
+        o_model, done = oc.msmfs_loop(smres, ssmm, pstack, ihess, None, None, 0.7, 0.0, a.cpu_niter)
+        out["cpu_us_per_iter"] = 1e6 * (time.perf_counter() - t0) / max(done, 1)
+        out["cpu_kind"] = "port (numpy, the reference's loop)"
+        chk_m, chk_r = run(a.cpu_niter)
+        out["max_abs_err_vs_oracle"] = float(max(np.abs(chk_m.cpu().numpy() - o_model).max(),
+                                                 np.abs(chk_r.cpu().numpy() - pmax * smres[0]).max()))
     print(json.dumps(out))
     if a.json:
         with open(a.json, "w") as fh:
