@@ -132,6 +132,7 @@ clean_subtract_kernel(double *__restrict__ res, const double *__restrict__ psf,
     for (int x = blockIdx.x; x < nx; x += gridDim.x) {
         const bool xin = x >= xlo && x < xhi;
         const double *prow = psf + (long long)(x - mx + pwx) * py + (pwy - my);
+#pragma unroll 4
         for (int y = threadIdx.x; y < ny; y += blockDim.x) {
             const long long i = (long long)x * ny + y;
             double r = res[i];
@@ -424,6 +425,7 @@ mf_subtract_kernel(double *__restrict__ smres, const double *__restrict__ psfm,
     for (int x = blockIdx.x; x < nx; x += gridDim.x) {
         const bool xin = x >= xlo && x < xhi;
         const long long poff = (long long)(x - mx + pwx) * py + (pwy - my);
+#pragma unroll 4
         for (int y = threadIdx.x; y < ny; y += blockDim.x) {
             const long long i = (long long)x * ny + y;
             double r[NM];
