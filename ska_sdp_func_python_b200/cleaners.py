@@ -17,7 +17,7 @@ from .imaging import _ptr, _torch
 
 log = logging.getLogger("func-python-logger")
 
-__all__ = ["hogbom", "hogbom_kernel_list", "msclean", "msclean_kernel_list", "msmfsclean", "create_scalestack",
+__all__ = ["hogbom", "hogbom_kernel_list", "msclean", "msclean_kernel_list", "msmfsclean", "mmclean_kernel_list", "create_scalestack",
            "spheroidal_function", "common_arguments", "image_peak"]
 
 
@@ -360,8 +360,12 @@ def msmfsclean(dirty, psf, window, sensitivity, gain, thresh, niter, scales, fra
         windowstack = (_convolve_scalestack(torch, fscales, w) > 0.9).to(torch.float64).contiguous()
     del fscales, fp
     sens = None if sensitivity is None else _dev64(sensitivity, dev)
+    if sens is not None and sens.dim() == 3:
+        # a moment cube of sensitivities (what mmclean_kernel_list passes) broadcasts against the
+        # 2-D solution in the reference; max over moments of |s_t r| = |r| max_t |s_t| exactly
+        sens = sens.abs().amax(dim=0).contiguous()
     if sens is not None and tuple(sens.shape) != shape:
-        raise ValueError("msmfsclean: sensitivity must be a 2-D image shaped like one moment plane")
+        raise ValueError("msmfsclean: sensitivity must be shaped like one moment plane (or a cube of them)")
     maxabs, _ = image_peak(smres[0, 0])
     absolutethresh = max(thresh, fracthresh * maxabs)
     log.info("mmclean %s: Max abs in dirty Image = %.6f; this minor cycle will stop at %d iterations "
@@ -379,3 +383,54 @@ def msmfsclean(dirty, psf, window, sensitivity, gain, thresh, niter, scales, fra
     if on_device:
         return model, res
     return model.cpu().numpy(), res.cpu().numpy()
+
+
+def mmclean_kernel_list(dirty_list, prefix, psf_list, window_list, sensitivity_list=None, **kwargs):
+    """MSMFS CLEAN of lists of single-frequency images (image/deconvolution.py:646-824): frequency
+    moments of the dirty images and PSFs (2 nmoment of the latter), ``msmfsclean`` per
+    polarisation with the Stokes-I PSF moments, and channel images rebuilt from the moment
+    model / residual.  kwargs: nmoment (3), findpeak, gain (0.7), threshold, niter,
+    fractional_threshold, scales."""
+    from .taylor_terms import (calculate_image_list_frequency_moments,
+                               calculate_image_list_from_frequency_taylor_terms)
+    findpeak = kwargs.get("findpeak", "RASCIL")
+    nmoment = kwargs.get("nmoment", 3)
+    if not nmoment >= 1:
+        raise ValueError("Number of frequency moments must be greater than or equal to one")
+    fracthresh, gain, niter, thresh, scales = common_arguments(**kwargs)
+    gain = kwargs.get("gain", 0.7)
+    if not 0.0 < gain < 2.0:
+        raise ValueError("Loop gain must be between 0 and 2")
+    nchan = len(dirty_list)
+    if not nchan > 2 * (nmoment - 1):
+        raise ValueError(f"Requires `nchan > 2 * (nmoment - 1)` ({nchan} > {2 * (nmoment - 1)})")
+    dirty_taylor = calculate_image_list_frequency_moments(dirty_list, nmoment=nmoment)
+    sensitivity_taylor = None
+    if sensitivity_list is not None:
+        sensitivity_taylor = calculate_image_list_frequency_moments(sensitivity_list, nmoment=nmoment)
+        sensitivity_taylor["pixels"].data /= nchan
+    window_taylor = None
+    if window_list is not None:
+        window_taylor = calculate_image_list_frequency_moments(window_list, nmoment=nmoment)
+        window_taylor["pixels"].data /= nchan
+    psf_taylor = calculate_image_list_frequency_moments(psf_list, nmoment=2 * nmoment if nmoment > 1 else 1)
+    psf_peak = numpy.max(psf_taylor["pixels"].data)
+    dirty_taylor["pixels"].data /= psf_peak
+    psf_taylor["pixels"].data /= psf_peak
+    dpix = dirty_taylor["pixels"].data
+    comp_array = numpy.zeros(dpix.shape)
+    residual_array = numpy.zeros(dpix.shape)
+    for pol in range(dpix.shape[1]):
+        sens = sensitivity_taylor["pixels"].data[:, pol, :, :] if sensitivity_taylor is not None else None
+        if psf_taylor["pixels"].data[0, 0, :, :].max():
+            window = window_taylor["pixels"].data[0, pol, :, :] if window_taylor is not None else None
+            ppix = psf_taylor["pixels"].data[:, 0, :, :]
+            comp_array[:, pol, :, :], residual_array[:, pol, :, :] = msmfsclean(
+                dpix[:, pol, :, :], ppix, window, sens, gain, thresh, niter, scales, fracthresh,
+                findpeak, prefix)
+        else:
+            log.info("deconvolve_cube %s: Skipping pol %d", prefix, pol)
+    comp_taylor = _new_image_like(dirty_taylor, comp_array)
+    residual_taylor = _new_image_like(dirty_taylor, residual_array)
+    return (calculate_image_list_from_frequency_taylor_terms(dirty_list, comp_taylor),
+            calculate_image_list_from_frequency_taylor_terms(dirty_list, residual_taylor))

@@ -100,3 +100,31 @@ def test_scatter_gather_channels():
     back = dc.image_gather_channels(parts)
     assert np.array_equal(back["pixels"].data, im["pixels"].data)
     assert back.image_acc.wcs.wcs.crval[3] == pytest.approx(1e8)
+
+
+def test_frequency_moments_and_back():
+    """image/taylor_terms.py:160-288: moment k = sum_c w_c^k image_c with w_c = (nu_c - nu_ref) / nu_ref,
+    nu_ref = the middle channel; rebuilding evaluates the polynomial in w_c."""
+    from ska_sdp_func_python_b200 import taylor_terms as tt
+    rng = np.random.default_rng(2)
+    nchan = 5
+    im = image(16, nchan=nchan, npol=2)
+    im["pixels"].data[:] = rng.normal(size=(nchan, 2, 16, 16))
+    parts = dc.image_scatter_channels(im)
+    freq = 1e8 + 1e6 * np.arange(nchan)
+    w = (freq - freq[2]) / freq[2]
+    mom = tt.calculate_image_list_frequency_moments(parts, nmoment=3)
+    assert mom["pixels"].data.shape == (3, 2, 16, 16) and mom.image_acc.wcs.wcs.ctype[3] == "MOMENT"
+    for k in range(3):
+        want = sum(w[c] ** k * im["pixels"].data[c] for c in range(nchan))
+        assert np.allclose(mom["pixels"].data[k], want, rtol=0, atol=1e-14)
+    back = tt.calculate_image_list_from_frequency_taylor_terms(parts, mom)
+    assert len(back) == nchan
+    for c in range(nchan):
+        want = sum(w[c] ** k * mom["pixels"].data[k] for k in range(3))
+        assert np.allclose(back[c]["pixels"].data[0], want, rtol=0, atol=1e-14)
+    with pytest.raises(ValueError):
+        tt.calculate_image_list_frequency_moments(parts, nmoment=6)
+    with pytest.raises(ValueError):
+        tt.calculate_image_list_frequency_moments(parts, nmoment=0)
+    assert tt.calculate_image_list_frequency_moments([None], nmoment=1) is None

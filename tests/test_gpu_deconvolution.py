@@ -54,7 +54,9 @@ def test_deconvolve_cube_windows_and_support(dc):
     assert np.array_equal(comp["pixels"].data[0, 0], o_c) and np.array_equal(resid["pixels"].data[0, 0], o_r)
     assert not comp["pixels"].data[0, 0][window == 0].any()
     with pytest.raises(ValueError):
-        dc.deconvolve_cube(dirty, psf, algorithm="mmclean")
+        dc.deconvolve_cube(dirty, psf, algorithm="mmclean")          # one channel < 2 (nmoment - 1) + 1
+    with pytest.raises(ValueError):
+        dc.deconvolve_cube(dirty, psf, algorithm="hogbom-complex")
     with pytest.raises(ValueError):
         dc.deconvolve_cube(dirty, psf, algorithm="nonsense")
     psf["pixels"].data *= 0.5
@@ -98,3 +100,54 @@ def test_restore_cube(dc, beam_pix):
     assert np.abs(out2["pixels"].data[1, 1] - want).max() < 1e-6
     with pytest.raises(ValueError):
         dc.restore_list([model], None, None, None)
+
+
+@pytest.mark.parametrize("nmoment,use_window", [(2, False), (3, True), (1, False)])
+def test_deconvolve_cube_mmclean(dc, nmoment, use_window):
+    """The MSMFS wrapper (image/deconvolution.py:646-824): moments of the channel images, the device
+    kernel, channel images rebuilt from the moment model -- against the same steps written out with
+    the numpy oracle."""
+    from oracle import clean as oc
+    rng = np.random.default_rng(31)
+    nchan, n = 7, 48
+    g = np.load(os.path.join(GOLDEN, "clean_case.npz"))
+    psf0 = g["b_psf"]                                             # 33 x 41 -> embed in 48 x 48
+    base = np.zeros((n, n))
+    base[8:41, 4:45] = psf0
+    base = np.roll(base, (24 - (8 + 16), 24 - (4 + 20)), axis=(0, 1))
+    assert base[24, 24] == 1.0
+    dirty, psf = image(n, nchan=nchan), image(n, nchan=nchan)
+    freq = 1e8 + 1e6 * np.arange(nchan)
+    wc = (freq - freq[nchan // 2]) / freq[nchan // 2]
+    src = rng.integers(8, 40, (5, 2))
+    for c in range(nchan):
+        psf["pixels"].data[c, 0] = base
+        sky = np.zeros((n, n))
+        for k, (x, y) in enumerate(src):
+            sky[x, y] = (1.0 + k) * (1.0 + 20.0 * (k - 2) * wc[c])
+        shifted = np.roll(base, (-24, -24), axis=(0, 1))
+        dirty["pixels"].data[c, 0] = np.real(np.fft.ifft2(np.fft.fft2(sky) * np.fft.fft2(shifted))) \
+            + 0.005 * rng.normal(size=(n, n))
+    kw = dict(algorithm="mmclean", nmoment=nmoment, gain=0.5, niter=30, scales=[0, 3],
+              fractional_threshold=0.01, threshold=0.0)
+    if use_window:
+        kw["window_shape"] = "no_edge"
+    comp, resid = dc.deconvolve_cube(dirty, psf, **kw)
+    assert comp["pixels"].data.shape == (nchan, 1, n, n)
+    # the same, step by step, with the oracle
+    dm = np.array([sum(wc[c] ** t * dirty["pixels"].data[c, 0] for c in range(nchan)) for t in range(nmoment)])
+    npm = 2 * nmoment if nmoment > 1 else 1
+    pm = np.array([sum(wc[c] ** t * psf["pixels"].data[c, 0] for c in range(nchan)) for t in range(npm)])
+    peak = pm.max()
+    window = None
+    if use_window:
+        window = np.zeros((n, n))
+        window[17:32, 17:32] = 1.0
+        window = window * nchan / nchan
+    o_model, o_res, done = oc.msmfsclean(dm / peak, pm / peak, window, None, 0.5, 0.0, 30, [0, 3], 0.01)
+    assert done > 5
+    for c in range(nchan):
+        want_c = sum(wc[c] ** t * o_model[t] for t in range(nmoment))
+        want_r = sum(wc[c] ** t * o_res[t] for t in range(nmoment))
+        assert np.abs(comp["pixels"].data[c, 0] - want_c).max() < 1e-9
+        assert np.abs(resid["pixels"].data[c, 0] - want_r).max() < 1e-9
