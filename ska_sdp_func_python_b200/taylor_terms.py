@@ -18,48 +18,44 @@ def _image_frequency(im):
     return w.crval[3] + (1.0 - w.crpix[3]) * w.cdelt[3]
 
 
+def _moment_weights(freq, reference_frequency, nmoment):
+    """w[k, c] = ((nu_c - nu_ref) / nu_ref)^k; nu_ref defaults to the middle channel."""
+    freq = numpy.asarray(freq, dtype=float)
+    ref = freq[len(freq) // 2] if reference_frequency is None else reference_frequency
+    return numpy.power(((freq - ref) / ref)[None, :], numpy.arange(nmoment)[:, None])
+
+
 def calculate_image_list_frequency_moments(im_list, reference_frequency=None, nmoment=1):
-    """moment k = sum over channels of ((nu - nu_ref) / nu_ref)^k x channel image; nu_ref defaults
-    to the middle channel; the spectral axis becomes a MOMENT axis."""
+    """moment k = sum over channels of ((nu - nu_ref) / nu_ref)^k x channel image; the spectral axis
+    becomes a MOMENT axis.  Channels are accumulated one after the other, in list order."""
     if nmoment <= 0:
         raise ValueError(f"Number of moments {nmoment} must be > 0")
     if im_list[0] is None:
         return None
-    nchan = len(im_list)
-    _, npol, ny, nx = im_list[0]["pixels"].data.shape
-    freq = [_image_frequency(im) for im in im_list]
-    if nmoment > nchan:
-        raise ValueError(f"Number of moments {nmoment} cannot exceed the number of channels {nchan}")
-    if reference_frequency is None:
-        reference_frequency = freq[nchan // 2]
-    moment_data = numpy.zeros([nmoment, npol, ny, nx])
-    for moment in range(nmoment):
-        for chan, im in enumerate(im_list):
-            weight = numpy.power((freq[chan] - reference_frequency) / reference_frequency, moment)
-            moment_data[moment, ...] += im["pixels"].data[0, ...] * weight
-    out = _new_image_like(im_list[0], moment_data)
+    if nmoment > len(im_list):
+        raise ValueError(f"Number of moments {nmoment} cannot exceed the number of channels {len(im_list)}")
+    w = _moment_weights([_image_frequency(im) for im in im_list], reference_frequency, nmoment)
+    cube = numpy.zeros((nmoment,) + im_list[0]["pixels"].data.shape[1:])
+    for chan, im in enumerate(im_list):
+        plane = im["pixels"].data[0]
+        for k in range(nmoment):
+            cube[k] += plane * w[k, chan]
+    out = _new_image_like(im_list[0], cube)
     wcs = _copy.deepcopy(im_list[0].image_acc.wcs)
-    wcs.wcs.ctype[3] = "MOMENT"
-    wcs.wcs.crval[3] = 0.0
-    wcs.wcs.crpix[3] = 1.0
-    wcs.wcs.cdelt[3] = 1.0
+    wcs.wcs.ctype[3], wcs.wcs.crval[3], wcs.wcs.crpix[3], wcs.wcs.cdelt[3] = "MOMENT", 0.0, 1.0, 1.0
     if hasattr(out, "attrs") and "wcs" in out.attrs:
         out.attrs["wcs"] = wcs
     return out
 
 
 def calculate_image_list_from_frequency_taylor_terms(im_list, moment_image, reference_frequency=None):
-    """Channel images back from the moment cube: sum over k of moment k x ((nu - nu_ref) / nu_ref)^k."""
-    nchan = len(im_list)
-    nmoment = moment_image["pixels"].data.shape[0]
-    frequency = numpy.array([_image_frequency(d) for d in im_list])
-    if reference_frequency is None:
-        reference_frequency = frequency[nchan // 2]
-    newims = []
-    for chan in range(nchan):
-        newim_data = numpy.zeros_like(im_list[chan]["pixels"].data[...])
-        for moment in range(nmoment):
-            weight = numpy.power((frequency[chan] - reference_frequency) / reference_frequency, moment)
-            newim_data[0, ...] += moment_image["pixels"].data[moment, ...] * weight
-        newims.append(_new_image_like(im_list[chan], newim_data))
-    return newims
+    """Channel images back from the moment cube: image_c = sum over k of moment k x w[k, c]."""
+    cube = moment_image["pixels"].data
+    w = _moment_weights([_image_frequency(d) for d in im_list], reference_frequency, cube.shape[0])
+    rebuilt = []
+    for chan, template in enumerate(im_list):
+        data = numpy.zeros_like(template["pixels"].data)
+        for k in range(cube.shape[0]):
+            data[0] += cube[k] * w[k, chan]
+        rebuilt.append(_new_image_like(template, data))
+    return rebuilt
