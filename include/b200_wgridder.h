@@ -273,6 +273,20 @@ int b2g_image_peak(const double *img, const double *window, int64_t nx, int64_t 
                    double *val_host, int64_t *idx_host, void *stream);
 
 /*
+ * Complex Hogbom CLEAN of a polarised image Q + iU: replaces hogbom_complex()
+ * (/root/reference/src/ska_sdp_func_python/image/cleaners.py:136-232).  DEVICE pointers,
+ * C-contiguous float64 [nx][ny] (psf [px][py], shared by Q and U as the reference asserts); window
+ * may be NULL; res_* may equal dirty_* (in place).  pmax = psf.max().  numpy's complex arithmetic
+ * is followed operation by operation (|z| = hypot, division of a complex by a real = product with
+ * 1 / pmax), so components and residuals match the reference bit for bit.
+ */
+int b2g_hogbom_complex(const double *dirty_q, const double *dirty_u, const double *psf,
+                       const double *window, int64_t nx, int64_t ny, int64_t px, int64_t py,
+                       double gain, double pmax, double thresh, double fracthresh, int64_t niter,
+                       double *comps_q, double *comps_u, double *res_q, double *res_u,
+                       int64_t *iters_host, void *stream);
+
+/*
  * Multi-scale CLEAN minor cycle: replaces the loop of msclean()
  * (/root/reference/src/ska_sdp_func_python/image/cleaners.py:398-451) with its peak search
  * find_max_abs_stack() (:565-610).  DEVICE pointers, C-contiguous float64:

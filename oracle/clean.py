@@ -280,3 +280,32 @@ def msmfsclean(dirty, psf, window, sensitivity, gain, thresh, niter, scales, fra
     absolutethresh = max(thresh, fracthresh * numpy.max(numpy.abs(smres[0, 0])))
     model, done = msmfs_loop(smres, ssmm, pstack, ihess, wstack, sensitivity, gain, absolutethresh, niter)
     return model, pmax * smres[0], done
+
+
+# ---- complex Hogbom CLEAN of Q + iU (cleaners.py:136-232) -----------------------------------------
+# Pinned bit-exact against tests/golden/clean_complex_case.npz (outputs of the reference's own
+# hogbom_complex(), tests/golden/make_golden_clean_complex.py).
+
+def hogbom_complex(dirty_q, dirty_u, psf_q, psf_u, window, gain, thresh, niter, fracthresh):
+    """Returns (comps_q, comps_u, res_q, res_u, iterations).  numpy complex128 arithmetic, as the
+    reference: note the stop test without the 0.9 of the real-valued hogbom()."""
+    assert 0.0 < gain < 2.0 and niter > 0
+    assert numpy.all(psf_q == psf_u)
+    z = dirty_q + 1j * dirty_u
+    absolutethresh = max(thresh, fracthresh * numpy.absolute(z).max())
+    comps = numpy.zeros(z.shape, dtype="complex128")
+    res = numpy.array(z)
+    pmax = psf_q.max()
+    assert pmax > 0.0
+    it = 0
+    for i in range(niter):
+        it = i + 1
+        a = numpy.absolute(res * window) if window is not None else numpy.absolute(res)
+        mx, my = numpy.unravel_index(a.argmax(), z.shape)
+        mval = res[mx, my] * gain / pmax
+        comps[mx, my] += mval
+        a1, a2 = overlap(z.shape, psf_q.shape, mx, my)
+        res[a1[0]:a1[1], a1[2]:a1[3]] -= psf_q[a2[0]:a2[1], a2[2]:a2[3]] * mval
+        if numpy.abs(res[mx, my]) < absolutethresh:
+            break
+    return comps.real, comps.imag, res.real, res.imag, it

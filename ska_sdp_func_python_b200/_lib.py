@@ -21,7 +21,7 @@ EXPORTS = (
     "b2g_ms2dirty", "b2g_dirty2ms", "b2g_sumwt", "b2g_kernel_select", "b2g_kernel_eval",
     "b2g_kernel_corr", "b2g_vis_prepare", "b2g_vis_finish", "b2g_set_host_chunk_samples", "b2g_plan_create_sel",
     "b2g_weight_grid", "b2g_weight_apply", "b2g_weight_taper", "b2g_dft_predict",
-    "b2g_plan_residual", "b2g_hogbom", "b2g_image_peak", "b2g_dft_invert", "b2g_msclean", "b2g_msmfsclean",
+    "b2g_plan_residual", "b2g_hogbom", "b2g_image_peak", "b2g_dft_invert", "b2g_msclean", "b2g_msmfsclean", "b2g_hogbom_complex",
 )
 FLAG_NONE, FLAG_U8, FLAG_I32, FLAG_I64, FLAG_F64 = 0, 1, 2, 3, 4
 
@@ -110,6 +110,9 @@ def lib():
     L.b2g_msmfsclean.restype = ci
     L.b2g_msmfsclean.argtypes = [vp, vp, vp, vp, vp, pd, i64, i64, i64, i64, i64, i64, dbl, dbl, i64, vp,
                                  ctypes.POINTER(i64), vp]
+    L.b2g_hogbom_complex.restype = ci
+    L.b2g_hogbom_complex.argtypes = [vp, vp, vp, vp, i64, i64, i64, i64, dbl, dbl, dbl, dbl, i64, vp, vp, vp, vp,
+                                     ctypes.POINTER(i64), vp]
     _lib = L
     return L
 

@@ -186,6 +186,107 @@ clean_select_kernel(const double *__restrict__ res, double *__restrict__ comps, 
     }
 }
 
+// ---- complex Hogbom CLEAN of Q + iU (hogbom_complex(), cleaners.py:136-232) --------------------
+//
+// Same loop as hogbom() on the complex image res = Q + iU, kept as two real planes.  numpy's
+// arithmetic is mirrored operation by operation: |z| is hypot(re, im); complex x real products are
+// component-wise; mval = res * gain / pmax divides a complex by a real through Smith's method,
+// i.e. multiplies both parts by 1.0 / pmax; the stop test is |res[peak]| < absolutethresh (no 0.9).
+
+struct CplxCleanState {
+    int mx, my;
+    double mre, mim;
+    int stop;
+    int iters;
+};
+
+__device__ __forceinline__ double cabs_win(double re, double im, const double *window, long long i)
+{
+    if (window) {
+        const double w = window[i];
+        re = __dmul_rn(re, w);
+        im = __dmul_rn(im, w);
+    }
+    return hypot(re, im);
+}
+
+// first != 0: candidates of the initial residual only
+__global__ void __launch_bounds__(kThreads)
+cclean_subtract_kernel(double *__restrict__ res_re, double *__restrict__ res_im,
+                       const double *__restrict__ psf, const double *__restrict__ window, int nx,
+                       int ny, int px, int py, int first, const CplxCleanState *__restrict__ st,
+                       Cand *__restrict__ part)
+{
+    if (st->stop) return;
+    const int mx = st->mx, my = st->my;
+    const double mre = st->mre, mim = st->mim;
+    const int pwx = px / 2, pwy = py / 2;
+    const int xlo = first ? 0 : max(0, mx - pwx), xhi = first ? 0 : min(nx, mx + pwx);
+    const int ylo = max(0, my - pwy), yhi = min(ny, my + pwy);
+    Cand best{neg_inf(), 0x7fffffffffffffffll};
+    for (int x = blockIdx.x; x < nx; x += gridDim.x) {
+        const bool xin = x >= xlo && x < xhi;
+        const double *prow = psf + (long long)(x - mx + pwx) * py + (pwy - my);
+        for (int y = threadIdx.x; y < ny; y += blockDim.x) {
+            const long long i = (long long)x * ny + y;
+            double re = res_re[i], im = res_im[i];
+            if (xin && y >= ylo && y < yhi) {
+                const double p = prow[y];
+                re = __dadd_rn(re, -__dmul_rn(p, mre));
+                im = __dadd_rn(im, -__dmul_rn(p, mim));
+                res_re[i] = re;
+                res_im[i] = im;
+            }
+            const double v = cabs_win(re, im, window, i);
+            if (better(v, i, best.val, best.idx)) {
+                best.val = v;
+                best.idx = i;
+            }
+        }
+    }
+    best = block_best(best);
+    if (threadIdx.x == 0) part[blockIdx.x] = best;
+}
+
+__global__ void __launch_bounds__(kThreads)
+cclean_select_kernel(const double *__restrict__ res_re, const double *__restrict__ res_im,
+                     double *__restrict__ comps_re, double *__restrict__ comps_im, int ny,
+                     const Cand *__restrict__ part, int npart, double gain, double pmax,
+                     double absolutethresh, int niter, int first, CplxCleanState *__restrict__ st)
+{
+    if (st->stop) return;
+    __shared__ int s_stop;
+    if (threadIdx.x == 0) {
+        s_stop = 0;
+        if (!first) {
+            st->iters += 1;
+            const long long i = (long long)st->mx * ny + st->my;
+            if (hypot(res_re[i], res_im[i]) < absolutethresh || st->iters >= niter) {
+                st->stop = 1;
+                s_stop = 1;
+            }
+        }
+    }
+    __syncthreads();
+    if (s_stop) return;
+    Cand best{neg_inf(), 0x7fffffffffffffffll};
+    for (int i = threadIdx.x; i < npart; i += blockDim.x)
+        if (better(part[i].val, part[i].idx, best.val, best.idx)) best = part[i];
+    best = block_best(best);
+    if (threadIdx.x == 0) {
+        const int mx = (int)(best.idx / ny), my = (int)(best.idx - (long long)mx * ny);
+        const double scl = __ddiv_rn(1.0, pmax);
+        const double mre = __dmul_rn(__dmul_rn(res_re[best.idx], gain), scl);
+        const double mim = __dmul_rn(__dmul_rn(res_im[best.idx], gain), scl);
+        st->mx = mx;
+        st->my = my;
+        st->mre = mre;
+        st->mim = mim;
+        comps_re[best.idx] = __dadd_rn(comps_re[best.idx], mre);
+        comps_im[best.idx] = __dadd_rn(comps_im[best.idx], mim);
+    }
+}
+
 // ---- multi-scale CLEAN (msclean(), cleaners.py:279-470; find_max_abs_stack :565-610) -----------
 //
 // State on the device: the stack of scale-convolved residuals res[ns][nx][ny], the doubly
@@ -775,4 +876,75 @@ extern "C" int b2g_msmfsclean(double *smres, const double *psf_moments, const do
     default: RUN(4);
     }
 #undef RUN
+}
+
+extern "C" int b2g_hogbom_complex(const double *dirty_q, const double *dirty_u, const double *psf,
+                                  const double *window, int64_t nx, int64_t ny, int64_t px, int64_t py,
+                                  double gain, double pmax, double thresh, double fracthresh,
+                                  int64_t niter, double *comps_q, double *comps_u, double *res_q,
+                                  double *res_u, int64_t *iters_host, void *stream)
+{
+    if (!dirty_q || !dirty_u || !psf || !comps_q || !comps_u || !res_q || !res_u)
+        return b2g::wrapper_fail("b2g_hogbom_complex: NULL pointer");
+    if (nx < 1 || ny < 1 || px < 1 || py < 1 || nx * ny > 0x7fffffffll)
+        return b2g::wrapper_fail("b2g_hogbom_complex: bad image shape");
+    if (!(gain > 0.0 && gain < 2.0)) return b2g::wrapper_fail("b2g_hogbom_complex: need 0 < gain < 2");
+    if (niter < 1) return b2g::wrapper_fail("b2g_hogbom_complex: need niter > 0");
+    if (!(pmax > 0.0)) return b2g::wrapper_fail("b2g_hogbom_complex: need psf.max() > 0");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
+        return b2g::wrapper_fail("b2g_hogbom_complex: no CUDA device available (this library has no CPU path)");
+    cudaStream_t s = (cudaStream_t)stream;
+    const long long n = nx * ny;
+    Cand *d_part = nullptr;
+    cudaError_t e = cudaMallocAsync(&d_part, sizeof(Cand) * (kBlocks + 1) + sizeof(CplxCleanState), s);
+    if (e != cudaSuccess) return cuda_fail(e);
+    Cand *d_peak = d_part + kBlocks;
+    CplxCleanState *d_st = reinterpret_cast<CplxCleanState *>(d_part + kBlocks + 1);
+    auto done = [&](int code) {
+        cudaStreamSynchronize(s);
+        cudaFreeAsync(d_part, s);
+        return code;
+    };
+#define CK(call)                                   \
+    do {                                           \
+        cudaError_t e_ = (call);                   \
+        if (e_ != cudaSuccess) return done(cuda_fail(e_)); \
+    } while (0)
+    CK(cudaMemsetAsync(d_st, 0, sizeof(CplxCleanState), s));
+    CK(cudaMemsetAsync(comps_q, 0, sizeof(double) * n, s));
+    CK(cudaMemsetAsync(comps_u, 0, sizeof(double) * n, s));
+    if (res_q != dirty_q) CK(cudaMemcpyAsync(res_q, dirty_q, sizeof(double) * n, cudaMemcpyDeviceToDevice, s));
+    if (res_u != dirty_u) CK(cudaMemcpyAsync(res_u, dirty_u, sizeof(double) * n, cudaMemcpyDeviceToDevice, s));
+    // absolutethresh = max(thresh, fracthresh * max |Q + iU|) (no window)          cleaners.py:176-178
+    cclean_subtract_kernel<<<kBlocks, kThreads, 0, s>>>(res_q, res_u, psf, nullptr, (int)nx, (int)ny,
+                                                        (int)px, (int)py, 1, d_st, d_part);
+    peak_final_kernel<<<1, kThreads, 0, s>>>(d_part, kBlocks, d_peak);
+    Cand h{0.0, 0};
+    CK(cudaMemcpyAsync(&h, d_peak, sizeof(Cand), cudaMemcpyDeviceToHost, s));
+    CK(cudaStreamSynchronize(s));
+    const double absolutethresh = thresh > fracthresh * h.val ? thresh : fracthresh * h.val;
+    // first peak
+    cclean_subtract_kernel<<<kBlocks, kThreads, 0, s>>>(res_q, res_u, psf, window, (int)nx, (int)ny,
+                                                        (int)px, (int)py, 1, d_st, d_part);
+    cclean_select_kernel<<<1, kThreads, 0, s>>>(res_q, res_u, comps_q, comps_u, (int)ny, d_part, kBlocks,
+                                                gain, pmax, absolutethresh, (int)niter, 1, d_st);
+    CplxCleanState hs;
+    hs.stop = 0;
+    hs.iters = 0;
+    for (long long i = 0; i < niter; ++i) {
+        cclean_subtract_kernel<<<kBlocks, kThreads, 0, s>>>(res_q, res_u, psf, window, (int)nx, (int)ny,
+                                                            (int)px, (int)py, 0, d_st, d_part);
+        cclean_select_kernel<<<1, kThreads, 0, s>>>(res_q, res_u, comps_q, comps_u, (int)ny, d_part,
+                                                    kBlocks, gain, pmax, absolutethresh, (int)niter, 0, d_st);
+        if ((i & 63) == 63 || i + 1 == niter) {
+            CK(cudaGetLastError());
+            CK(cudaMemcpyAsync(&hs, d_st, sizeof(CplxCleanState), cudaMemcpyDeviceToHost, s));
+            CK(cudaStreamSynchronize(s));
+            if (hs.stop) break;
+        }
+    }
+#undef CK
+    if (iters_host) *iters_host = hs.iters;
+    return done(0);
 }

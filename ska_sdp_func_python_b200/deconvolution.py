@@ -2,13 +2,13 @@
 
 Mirrors the parts of /root/reference/src/ska_sdp_func_python/image/deconvolution.py that sit on the
 device kernels of ``cleaners.py``: ``deconvolve_cube`` / ``deconvolve_list`` (:50-160, :1045-1110)
-for the ``hogbom``, ``msclean`` and ``msmfsclean`` / ``mmclean`` algorithms with the window / PSF-support plumbing
+for the ``hogbom``, ``hogbom-complex``, ``msclean`` and ``msmfsclean`` / ``mmclean`` algorithms with the window / PSF-support plumbing
 (``find_window_list`` :283-350, ``bound_psf_list`` :353-395, ``check_psf_peak`` :266-280),
 ``fit_psf`` (:1113-1159) and ``restore_cube`` / ``restore_list`` (:948-1043, :1162-1190), whose
 convolution with the clean beam runs on the device (cuFFT, circular, as the reference's
 ``convolve_fft(boundary="wrap")``).
 
-Not built: ``hogbom-complex`` and radler (ValueError names the former).
+Not built: the radler back end (``radler_deconvolve_list``).
 
 Parity notes.  The CLEAN kernels are pinned against the reference's own outputs
 (tests/golden/clean_case.npz, msclean_case.npz).  ``fit_psf`` and the restoring beam depend on
@@ -152,7 +152,7 @@ def bound_psf_list(dirty_list, prefix, psf_list, psf_support=None):
 
 def deconvolve_list(dirty_list, psf_list, sensitivity_list=None, prefix="", **kwargs):
     """CLEAN of lists of single-channel images (deconvolution.py:50-160): ``algorithm`` =
-    "msclean" (default), "hogbom" or "msmfsclean" / "mfsmsclean" / "mmclean"; kwargs window_shape, mask, window_edge, psf_support, gain,
+    "msclean" (default), "hogbom", "hogbom-complex" or "msmfsclean" / "mfsmsclean" / "mmclean"; kwargs window_shape, mask, window_edge, psf_support, gain,
     threshold, fractional_threshold, niter, scales."""
     window_shape = kwargs.get("window_shape", None)
     window_list = find_window_list(dirty_list, prefix, window_shape=window_shape)
@@ -169,8 +169,7 @@ def deconvolve_list(dirty_list, psf_list, sensitivity_list=None, prefix="", **kw
         return cleaners.mmclean_kernel_list(dirty_list, prefix, psf_list, window_list,
                                             sensitivity_list, **kwargs)
     if algorithm == "hogbom-complex":
-        raise ValueError(f"deconvolve_cube {prefix}: algorithm {algorithm} is not built in the B200 "
-                         "package (DESIGN.md, out of scope)")
+        return cleaners.complex_hogbom_kernel_list(dirty_list, psf_list, window_list, **kwargs)
     raise ValueError(f"deconvolve_cube {prefix}: Unknown algorithm {algorithm}")
 
 

@@ -286,3 +286,54 @@ def test_msmfsclean_arguments(cl):
         cl.msmfsclean(args[0], args[1][:3], *args[2:])           # psf must hold 2 x nmoment planes
     with pytest.raises(ValueError):
         cl.msmfsclean(args[0][0], args[1][0], *args[2:])         # 2-D input
+
+
+# ---- complex Hogbom (Q + iU) -------------------------------------------------------------------
+
+@pytest.mark.parametrize("name", ["a", "b", "c", "d"])
+def test_hogbom_complex_golden_bit_exact(cl, name):
+    """Against the reference's own hogbom_complex(): windows (bool / float), PSF smaller / larger than
+    the image, a PSF peak != 1 (numpy divides a complex by a real through 1 / pmax), threshold stop."""
+    g = np.load(os.path.join(GOLDEN, "clean_complex_case.npz"))
+    gain, thresh, niter, frac = g[f"{name}_par"]
+    window = g[f"{name}_window"] if f"{name}_window" in g.files else None
+    outs = cl.hogbom_complex(g[f"{name}_dq"], g[f"{name}_du"], g[f"{name}_psf"], g[f"{name}_psf"].copy(),
+                             window, gain, thresh, int(niter), frac)
+    for got, key in zip(outs, ("cq", "cu", "rq", "ru")):
+        assert isinstance(got, np.ndarray) and np.array_equal(got, g[f"{name}_{key}"]), key
+
+
+def test_hogbom_complex_larger_and_list(cl):
+    import torch
+    from oracle import clean as oc
+    from ska_sdp_func_python_b200 import deconvolution as dc, minimal_models as mm
+    rng = np.random.default_rng(12)
+    n = 256
+    yy, xx = np.meshgrid(np.arange(n) - n // 2, np.arange(n) - n // 2)
+    r = np.hypot(xx, yy)
+    psf = np.exp(-(r / 2.0) ** 2) + 0.05 * np.cos(r / 3.1) * np.exp(-r / 30.0) * (r > 0)
+    dq, du = 0.01 * rng.normal(size=(n, n)), 0.01 * rng.normal(size=(n, n))
+    pos = rng.integers(20, n - 20, (30, 2))
+    dq[pos[:, 0], pos[:, 1]] += rng.normal(size=30) * 2
+    du[pos[:, 0], pos[:, 1]] += rng.normal(size=30) * 2
+    want = oc.hogbom_complex(dq, du, psf, psf, None, 0.2, 0.0, 400, 0.001)
+    t = lambda a: torch.from_numpy(a).cuda()  # noqa: E731
+    got = cl.hogbom_complex(t(dq), t(du), t(psf), t(psf), None, 0.2, 0.0, 400, 0.001)
+    for a, b in zip(got, want[:4]):
+        assert a.is_cuda and np.array_equal(a.cpu().numpy(), b)
+    with pytest.raises(AssertionError):
+        cl.hogbom_complex(dq, du, psf, 2 * psf, None, 0.2, 0.0, 10, 0.0)
+    # image-list level: I and V by hogbom, Q + iU by hogbom_complex (image/deconvolution.py:398-511)
+    pf = mm.PolarisationFrame("stokesIQUV")
+    pc = mm.SkyCoord.from_deg(0.0, -30.0)
+    dirty = mm.create_image(n, 1e-3, pc, frequency=[1e8], polarisation_frame=pf)
+    psf_im = mm.create_image(n, 1e-3, pc, frequency=[1e8], polarisation_frame=pf)
+    dirty["pixels"].data[0] = np.stack([dq + du, dq, du, dq - du])
+    psf_im["pixels"].data[0, :3] = psf                        # V PSF all zero: skipped
+    comp, resid = dc.deconvolve_cube(dirty, psf_im, algorithm="hogbom-complex", gain=0.2, niter=400,
+                                     fractional_threshold=0.001, psf_support=n // 2)
+    assert np.array_equal(comp["pixels"].data[0, 1], want[0]) and np.array_equal(comp["pixels"].data[0, 2], want[1])
+    assert np.array_equal(resid["pixels"].data[0, 1], want[2]) and np.array_equal(resid["pixels"].data[0, 2], want[3])
+    ci, ri, _ = oc.hogbom(dq + du, psf, None, 0.2, 0.0, 400, 0.001)
+    assert np.array_equal(comp["pixels"].data[0, 0], ci) and np.array_equal(resid["pixels"].data[0, 0], ri)
+    assert not comp["pixels"].data[0, 3].any()

@@ -56,7 +56,7 @@ def test_deconvolve_cube_windows_and_support(dc):
     with pytest.raises(ValueError):
         dc.deconvolve_cube(dirty, psf, algorithm="mmclean")          # one channel < 2 (nmoment - 1) + 1
     with pytest.raises(ValueError):
-        dc.deconvolve_cube(dirty, psf, algorithm="hogbom-complex")
+        dc.deconvolve_cube(dirty, psf, algorithm="hogbom-complex")   # needs stokesIQUV
     with pytest.raises(ValueError):
         dc.deconvolve_cube(dirty, psf, algorithm="nonsense")
     psf["pixels"].data *= 0.5

@@ -65,3 +65,18 @@ def test_msmfsclean_bit_exact(name):
     assert np.array_equal(model, g[f"{name}_model"])
     assert np.array_equal(res, g[f"{name}_res"])
     assert (done < int(niter)) == (name == "d")         # only case d stops at the threshold
+
+
+CGOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "clean_complex_case.npz")
+
+
+@pytest.mark.parametrize("name", ["a", "b", "c", "d"])
+def test_hogbom_complex_bit_exact(name):
+    g = np.load(CGOLD)
+    gain, thresh, niter, frac = g[f"{name}_par"]
+    window = g[f"{name}_window"] if f"{name}_window" in g.files else None
+    cq, cu, rq, ru, it = oc.hogbom_complex(g[f"{name}_dq"], g[f"{name}_du"], g[f"{name}_psf"], g[f"{name}_psf"],
+                                           window, gain, thresh, int(niter), frac)
+    for got, key in ((cq, "cq"), (cu, "cu"), (rq, "rq"), (ru, "ru")):
+        assert np.array_equal(got, g[f"{name}_{key}"])
+    assert (it < int(niter)) == (name == "b")
