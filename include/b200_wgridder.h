@@ -318,14 +318,16 @@ int b2g_msclean(double *res_stack, const double *psf_scalescale, const double *p
  *   psf_scale    [nscales][px][py]                         the scale shapes on the PSF's raster
  *   window_stack [nscales][nx][ny] or NULL, sensitivity [nx][ny] or NULL
  *   model        [nmoment][nx][ny]                         moment model (zeroed here)
- * inv_hessian is a HOST array [nscales][nmoment][nmoment] (:1081-1104).  nscales <= 16,
- * nmoment <= 4.  iters_host receives the number of components subtracted.
+ * inv_hessian and hessian are HOST arrays [nscales][nmoment][nmoment] (:1081-1104; hessian may be
+ * NULL unless findpeak == 1).  findpeak: 0 = "RASCIL" / "Algorithm1" (peak of the moment-0 principal
+ * solution), 1 = "CASA" (peak of the chi^2 decrease, :936-960).  nscales <= 8, nmoment <= 4.
+ * iters_host receives the number of components subtracted.
  */
 int b2g_msmfsclean(double *smres, const double *psf_moments, const double *psf_scale,
                    const double *window_stack, const double *sensitivity, const double *inv_hessian,
-                   int64_t nscales, int64_t nmoment, int64_t nx, int64_t ny, int64_t px, int64_t py,
-                   double gain, double absolutethresh, int64_t niter, double *model,
-                   int64_t *iters_host, void *stream);
+                   const double *hessian, int findpeak, int64_t nscales, int64_t nmoment, int64_t nx,
+                   int64_t ny, int64_t px, int64_t py, double gain, double absolutethresh,
+                   int64_t niter, double *model, int64_t *iters_host, void *stream);
 
 /*
  * Adjoint of b2g_dft_predict: replaces the sums of idft_visibility_skycomponent

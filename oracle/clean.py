@@ -236,31 +236,42 @@ def msmfs_setup(dirty, psf, window, scales):
     return pmax, pstack, smres, ssmm, hess, ihess, wstack
 
 
-def msmfs_peak(smres, ihess, wstack, sensitivity):
+def msmfs_peak(smres, ihess, wstack, sensitivity, hess=None, findpeak="RASCIL"):
     """find_global_optimum, RASCIL / Algorithm1 branch (cleaners.py:901-975, :1124-1157): the scale
     is chosen on the windowed, sensitivity-weighted principal solution of moment 0, the pixel is the
     peak of the UN-windowed one."""
     sol = numpy.einsum("smn,smxy->snxy", ihess, smres)
+    search = sol
+    if findpeak == "CASA":
+        # CASA 4.7 (cleaners.py:936-960): search the decrease of chi^2 instead
+        ns, nm = sol.shape[:2]
+        search = numpy.zeros((ns, 1) + sol.shape[2:])
+        for s in range(ns):
+            for m1 in range(nm):
+                search[s, 0] += 2.0 * sol[s, m1] * smres[s, m1]
+                for m2 in range(nm):
+                    search[s, 0] -= hess[s, m1, m2] * sol[s, m1] * sol[s, m2]
     best, bs, bx, by = 0.0, 0, 0, 0
     for s in range(sol.shape[0]):
-        r = sol[s, 0] * wstack[s] if wstack is not None else sol[s, 0]
+        r = search[s, 0] * wstack[s] if wstack is not None else search[s, 0]
         if sensitivity is not None:
             r = sensitivity * r
         top = numpy.max(numpy.abs(r))
         if top > best:
             best, bs = top, s
-            bx, by = numpy.unravel_index(numpy.abs(sol[s, 0]).argmax(), sol[s, 0].shape)
+            bx, by = numpy.unravel_index(numpy.abs(search[s, 0]).argmax(), search[s, 0].shape)
     return bs, bx, by, sol[bs, :, bx, by]
 
 
-def msmfs_loop(smres, ssmm, pstack, ihess, wstack, sensitivity, gain, absolutethresh, niter):
+def msmfs_loop(smres, ssmm, pstack, ihess, wstack, sensitivity, gain, absolutethresh, niter,
+               hess=None, findpeak="RASCIL"):
     """The minor cycle (cleaners.py:826-880); smres is updated in place.  Returns (model, done)."""
     ns, nm = smres.shape[:2]
     shape, pshape = smres.shape[2:], ssmm.shape[4:]
     model = numpy.zeros((nm,) + shape)
     done = 0
     for _ in range(niter):
-        ms, mx, my, mval = msmfs_peak(smres, ihess, wstack, sensitivity)
+        ms, mx, my, mval = msmfs_peak(smres, ihess, wstack, sensitivity, hess, findpeak)
         if numpy.fabs(mval[0]) < absolutethresh:
             break
         a1, a2 = overlap(shape, pshape, mx, my)
@@ -272,13 +283,14 @@ def msmfs_loop(smres, ssmm, pstack, ihess, wstack, sensitivity, gain, absoluteth
     return model, done
 
 
-def msmfsclean(dirty, psf, window, sensitivity, gain, thresh, niter, scales, fracthresh):
+def msmfsclean(dirty, psf, window, sensitivity, gain, thresh, niter, scales, fracthresh, findpeak="RASCIL"):
     """dirty [nmoment, nx, ny], psf [2 nmoment, px, py].  Returns (moment model, moment residual,
     components subtracted)."""
     assert 0.0 < gain < 2.0 and niter > 0 and len(scales) > 0
-    pmax, pstack, smres, ssmm, _, ihess, wstack = msmfs_setup(dirty, psf, window, scales)
+    pmax, pstack, smres, ssmm, hess, ihess, wstack = msmfs_setup(dirty, psf, window, scales)
     absolutethresh = max(thresh, fracthresh * numpy.max(numpy.abs(smres[0, 0])))
-    model, done = msmfs_loop(smres, ssmm, pstack, ihess, wstack, sensitivity, gain, absolutethresh, niter)
+    model, done = msmfs_loop(smres, ssmm, pstack, ihess, wstack, sensitivity, gain, absolutethresh, niter,
+                             hess, findpeak)
     return model, pmax * smres[0], done
 
 

@@ -108,7 +108,7 @@ def lib():
     L.b2g_msclean.argtypes = [vp, vp, vp, vp, vp, pd, i64, i64, i64, i64, i64, dbl, dbl, i64, vp,
                               ctypes.POINTER(i64), vp]
     L.b2g_msmfsclean.restype = ci
-    L.b2g_msmfsclean.argtypes = [vp, vp, vp, vp, vp, pd, i64, i64, i64, i64, i64, i64, dbl, dbl, i64, vp,
+    L.b2g_msmfsclean.argtypes = [vp, vp, vp, vp, vp, pd, pd, ci, i64, i64, i64, i64, i64, i64, dbl, dbl, i64, vp,
                                  ctypes.POINTER(i64), vp]
     L.b2g_hogbom_complex.restype = ci
     L.b2g_hogbom_complex.argtypes = [vp, vp, vp, vp, i64, i64, i64, i64, dbl, dbl, dbl, dbl, i64, vp, vp, vp, vp,

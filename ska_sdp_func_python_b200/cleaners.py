@@ -304,13 +304,11 @@ def msmfsclean(dirty, psf, window, sensitivity, gain, thresh, niter, scales, fra
     residual), both [nmoment, nx, ny].  Setup (scale-convolved moment residuals, coupled PSFs,
     moment Hessians) with cuFFT on the device, the nmoment x nmoment Hessian inverses on the host
     (numpy.linalg.inv, as the reference), the minor cycle in csrc/clean_kernels.cu
-    (``b2g_msmfsclean``).  ``findpeak``: "RASCIL" and "Algorithm1" (identical in the reference,
-    cleaners.py:925-972); "CASA" is not built."""
+    (``b2g_msmfsclean``).  ``findpeak``: "CASA" searches the chi^2 decrease (cleaners.py:936-960);
+    "RASCIL", "Algorithm1" and anything else the moment-0 principal solution (:925-972)."""
     assert 0.0 < gain < 2.0
     assert niter > 0
     assert len(scales) > 0
-    if findpeak == "CASA":
-        raise ValueError("msmfsclean: findpeak='CASA' is not built in the B200 package")
     torch = _torch()
     on_device = isinstance(dirty, torch.Tensor) and dirty.is_cuda
     dev = dirty.device if on_device else torch.device("cuda", torch.cuda.current_device())
@@ -321,8 +319,8 @@ def msmfsclean(dirty, psf, window, sensitivity, gain, thresh, niter, scales, fra
     nmoment, ns = int(d.shape[0]), len(scales)
     if nmoment > 1:
         assert p.shape[0] == 2 * nmoment
-    if nmoment > 4:
-        raise ValueError("msmfsclean: at most 4 frequency moments")
+    if nmoment > 4 or ns > 8:
+        raise ValueError("msmfsclean: at most 4 frequency moments and 8 scales")
     pmax = float(p.max())
     assert pmax > 0.0
     lpsf, ldirty = p / pmax, d / pmax
@@ -375,7 +373,9 @@ def msmfsclean(dirty, psf, window, sensitivity, gain, thresh, niter, scales, fra
     stream = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
     _lib.check(_lib.lib().b2g_msmfsclean(
         _ptr(smres), _ptr(psfm), _ptr(pscalestack), _ptr(windowstack), _ptr(sens),
-        ihessian.ctypes.data_as(ctypes.POINTER(ctypes.c_double)), ns, nmoment, shape[0], shape[1],
+        ihessian.ctypes.data_as(ctypes.POINTER(ctypes.c_double)),
+        numpy.ascontiguousarray(hessian).ctypes.data_as(ctypes.POINTER(ctypes.c_double)),
+        1 if findpeak == "CASA" else 0, ns, nmoment, shape[0], shape[1],
         pshape[0], pshape[1], float(gain), float(absolutethresh), int(niter), _ptr(model),
         ctypes.byref(iters), stream))
     log.info("mmclean %s: End of minor cycle after %d components", prefix, iters.value)

@@ -477,11 +477,14 @@ struct MfState {
     double mval[kMaxMoments];
 };
 
+constexpr int kMaxMfScales = 8;
+
 struct MfHess {
-    double ih[kMaxScales][kMaxMoments][kMaxMoments];
+    double ih[kMaxMfScales][kMaxMoments][kMaxMoments];  // inverse moment Hessians
+    double h[kMaxMfScales][kMaxMoments][kMaxMoments];   // the Hessians themselves (findpeak "CASA")
 };
 
-template <int NM>
+template <int NM, bool CASA>
 __global__ void __launch_bounds__(kThreads)
 mf_subtract_kernel(double *__restrict__ smres, const double *__restrict__ psfm,
                    const double *__restrict__ pscale, const double *__restrict__ wstack,
@@ -548,6 +551,29 @@ mf_subtract_kernel(double *__restrict__ smres, const double *__restrict__ psfm,
             double sol = __dmul_rn(ih0[0], r[0]);
 #pragma unroll
             for (int m = 1; m < NM; ++m) sol = __dadd_rn(sol, __dmul_rn(ih0[m], r[m]));
+            if (CASA) {
+                // CASA 4.7 peak finder (cleaners.py:936-960): the search image is the decrease of
+                // chi^2, sum_m 2 sol[m] res[m] - sum_{m,q} H[m][q] sol[m] sol[q], accumulated in the
+                // reference's order
+                double sl[NM];
+                sl[0] = sol;
+#pragma unroll
+                for (int nn = 1; nn < NM; ++nn) {
+                    double acc = __dmul_rn(hs.ih[s][0][nn], r[0]);
+#pragma unroll
+                    for (int m = 1; m < NM; ++m) acc = __dadd_rn(acc, __dmul_rn(hs.ih[s][m][nn], r[m]));
+                    sl[nn] = acc;
+                }
+                double dch = 0.0;
+#pragma unroll
+                for (int m1 = 0; m1 < NM; ++m1) {
+                    dch = __dadd_rn(dch, __dmul_rn(__dmul_rn(2.0, sl[m1]), r[m1]));
+#pragma unroll
+                    for (int m2 = 0; m2 < NM; ++m2)
+                        dch = __dadd_rn(dch, -__dmul_rn(__dmul_rn(hs.h[s][m1][m2], sl[m1]), sl[m2]));
+                }
+                sol = dch;
+            }
             double v = w_s ? __dmul_rn(sol, w_s[i]) : sol;
             if (sens) v = __dmul_rn(sens[i], v);
             v = fabs(v);
@@ -621,14 +647,16 @@ mf_select_kernel(const double *__restrict__ smres, MfHess hs, int ns, int nx, in
 template <int NM>
 int mf_run(double *smres, const double *psfm, const double *pscale, const double *wstack,
            const double *sens, const MfHess &hs, int ns, int nx, int ny, int px, int py, double gain,
-           double absolutethresh, long long niter, double *model, int64_t *iters_host, cudaStream_t s);
+           double absolutethresh, long long niter, int casa, double *model, int64_t *iters_host,
+           cudaStream_t s);
 
 int cuda_fail(cudaError_t e) { return b2g::wrapper_fail(cudaGetErrorString(e)); }
 
 template <int NM>
 int mf_run(double *smres, const double *psfm, const double *pscale, const double *wstack,
            const double *sens, const MfHess &hs, int ns, int nx, int ny, int px, int py, double gain,
-           double absolutethresh, long long niter, double *model, int64_t *iters_host, cudaStream_t s)
+           double absolutethresh, long long niter, int casa, double *model, int64_t *iters_host,
+           cudaStream_t s)
 {
     Cand *d_part = nullptr;
     const size_t npart = (size_t)kMsBlocks * ns;
@@ -649,18 +677,24 @@ int mf_run(double *smres, const double *psfm, const double *pscale, const double
     CK(cudaMemsetAsync(d_st, 0, sizeof(MfState), s));
     CK(cudaMemsetAsync(model, 0, sizeof(double) * NM * nx * ny, s));
     const dim3 grid(kMsBlocks, ns + 1);
-    mf_subtract_kernel<NM><<<grid, kThreads, 0, s>>>(smres, psfm, pscale, wstack, sens, model, hs, ns, nx,
-                                                     ny, px, py, gain, 1, d_st, d_scale, d_pixel);
+    auto subtract = [&](int first) {
+        if (casa)
+            mf_subtract_kernel<NM, true><<<grid, kThreads, 0, s>>>(smres, psfm, pscale, wstack, sens, model, hs,
+                                                                   ns, nx, ny, px, py, gain, first, d_st,
+                                                                   d_scale, d_pixel);
+        else
+            mf_subtract_kernel<NM, false><<<grid, kThreads, 0, s>>>(smres, psfm, pscale, wstack, sens, model,
+                                                                    hs, ns, nx, ny, px, py, gain, first, d_st,
+                                                                    d_scale, d_pixel);
+    };
+    subtract(1);
     MfState h;
     h.stop = 0;
     h.iters = 0;
     for (long long i = 0; i <= niter; ++i) {
         mf_select_kernel<NM><<<1, kThreads, 0, s>>>(smres, hs, ns, nx, ny, d_scale, d_pixel, kMsBlocks,
                                                     absolutethresh, (int)niter, d_st);
-        if (i < niter)
-            mf_subtract_kernel<NM><<<grid, kThreads, 0, s>>>(smres, psfm, pscale, wstack, sens, model, hs,
-                                                             ns, nx, ny, px, py, gain, 0, d_st, d_scale,
-                                                             d_pixel);
+        if (i < niter) subtract(0);
         if ((i & 63) == 63 || i == niter) {
             CK(cudaGetLastError());
             CK(cudaMemcpyAsync(&h, d_st, sizeof(MfState), cudaMemcpyDeviceToHost, s));
@@ -843,13 +877,16 @@ extern "C" int b2g_msclean(double *res_stack, const double *psf_scalescale, cons
 
 extern "C" int b2g_msmfsclean(double *smres, const double *psf_moments, const double *psf_scale,
                               const double *window_stack, const double *sensitivity,
-                              const double *inv_hessian, int64_t nscales, int64_t nmoment, int64_t nx,
-                              int64_t ny, int64_t px, int64_t py, double gain, double absolutethresh,
-                              int64_t niter, double *model, int64_t *iters_host, void *stream)
+                              const double *inv_hessian, const double *hessian, int findpeak,
+                              int64_t nscales, int64_t nmoment, int64_t nx, int64_t ny, int64_t px,
+                              int64_t py, double gain, double absolutethresh, int64_t niter,
+                              double *model, int64_t *iters_host, void *stream)
 {
     if (!smres || !psf_moments || !psf_scale || !inv_hessian || !model)
         return b2g::wrapper_fail("b2g_msmfsclean: NULL pointer");
-    if (nscales < 1 || nscales > kMaxScales) return b2g::wrapper_fail("b2g_msmfsclean: need 1..16 scales");
+    if (findpeak != 0 && findpeak != 1) return b2g::wrapper_fail("b2g_msmfsclean: findpeak must be 0 (RASCIL / Algorithm1) or 1 (CASA)");
+    if (findpeak == 1 && !hessian) return b2g::wrapper_fail("b2g_msmfsclean: findpeak CASA needs the Hessians");
+    if (nscales < 1 || nscales > kMaxMfScales) return b2g::wrapper_fail("b2g_msmfsclean: need 1..8 scales");
     if (nmoment < 1 || nmoment > kMaxMoments) return b2g::wrapper_fail("b2g_msmfsclean: need 1..4 moments");
     if (nx < 1 || ny < 1 || px < 1 || py < 1 || nx * ny > 0x7fffffffll)
         return b2g::wrapper_fail("b2g_msmfsclean: bad image shape");
@@ -859,16 +896,18 @@ extern "C" int b2g_msmfsclean(double *smres, const double *psf_moments, const do
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
         return b2g::wrapper_fail("b2g_msmfsclean: no CUDA device available (this library has no CPU path)");
     MfHess hs;
-    for (int s = 0; s < kMaxScales; ++s)
+    for (int s = 0; s < kMaxMfScales; ++s)
         for (int m = 0; m < kMaxMoments; ++m)
-            for (int q = 0; q < kMaxMoments; ++q)
-                hs.ih[s][m][q] = (s < nscales && m < nmoment && q < nmoment)
-                                     ? inv_hessian[(s * nmoment + m) * nmoment + q] : 0.0;
+            for (int q = 0; q < kMaxMoments; ++q) {
+                const bool in = s < nscales && m < nmoment && q < nmoment;
+                hs.ih[s][m][q] = in ? inv_hessian[(s * nmoment + m) * nmoment + q] : 0.0;
+                hs.h[s][m][q] = in && hessian ? hessian[(s * nmoment + m) * nmoment + q] : 0.0;
+            }
     cudaStream_t st = (cudaStream_t)stream;
 #define RUN(NM)                                                                                     \
     return mf_run<NM>(smres, psf_moments, psf_scale, window_stack, sensitivity, hs, (int)nscales,   \
-                      (int)nx, (int)ny, (int)px, (int)py, gain, absolutethresh, niter, model,       \
-                      iters_host, st)
+                      (int)nx, (int)ny, (int)px, (int)py, gain, absolutethresh, niter, findpeak,    \
+                      model, iters_host, st)
     switch (nmoment) {
     case 1: RUN(1);
     case 2: RUN(2);

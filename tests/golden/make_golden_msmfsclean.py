@@ -45,10 +45,13 @@ def main():
     out = {}
     cases = [
         # name, nx, ny, px, py, nmoment, window, sensitivity, gain, thresh, niter, fracthresh, scales
+        # (cases e, f: findpeak="CASA")
         ("a", 64, 64, 64, 64, 3, None, False, 0.7, 0.0, 50, 0.01, [0, 3, 10]),
         ("b", 48, 72, 32, 40, 2, "quarter", False, 0.3, 0.0, 80, 0.02, [0, 4]),
         ("c", 64, 64, 64, 64, 2, "float", True, 0.5, 0.0, 40, 0.05, [0, 3, 8]),
         ("d", 40, 40, 40, 40, 1, None, False, 0.7, 1.2, 400, 0.0, [0, 3]),       # one moment; threshold stop
+        ("e", 64, 64, 64, 64, 3, None, False, 0.7, 0.0, 40, 0.01, [0, 3, 10]),
+        ("f", 48, 72, 32, 40, 2, "quarter", True, 0.3, 0.0, 60, 0.02, [0, 4]),
     ]
     for name, nx, ny, px, py, nm, wk, use_sens, gain, thresh, niter, frac, scales in cases:
         dirty, psf = moment_images(90 + ord(name), nx, ny, px, py, nm, 8)
@@ -65,7 +68,9 @@ def main():
         if use_sens:
             xx, yy = np.meshgrid(np.linspace(-1, 1, nx), np.linspace(-1, 1, ny), indexing="ij")
             sens = np.exp(-(xx ** 2 + yy ** 2))
-        model, res = ref.msmfsclean(dirty.copy(), psf.copy(), window, sens, gain, thresh, niter, scales, frac)
+        findpeak = "CASA" if name in "ef" else "RASCIL"
+        model, res = ref.msmfsclean(dirty.copy(), psf.copy(), window, sens, gain, thresh, niter, scales, frac,
+                                    findpeak=findpeak)
         out.update({f"{name}_dirty": dirty, f"{name}_psf": psf, f"{name}_model": model,
                     f"{name}_res": res, f"{name}_par": np.array([gain, thresh, niter, frac]),
                     f"{name}_scales": np.array(scales, dtype=float)})

@@ -54,14 +54,15 @@ def test_scale_stack_properties():
 MFGOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "msmfsclean_case.npz")
 
 
-@pytest.mark.parametrize("name", ["a", "b", "c", "d"])
+@pytest.mark.parametrize("name", ["a", "b", "c", "d", "e", "f"])
 def test_msmfsclean_bit_exact(name):
     g = np.load(MFGOLD)
     gain, thresh, niter, frac = g[f"{name}_par"]
     window = g[f"{name}_window"] if f"{name}_window" in g.files else None
     sens = g[f"{name}_sens"] if f"{name}_sens" in g.files else None
     model, res, done = oc.msmfsclean(g[f"{name}_dirty"], g[f"{name}_psf"], window, sens, gain, thresh,
-                                     int(niter), list(g[f"{name}_scales"]), frac)
+                                     int(niter), list(g[f"{name}_scales"]), frac,
+                                     findpeak="CASA" if name in "ef" else "RASCIL")
     assert np.array_equal(model, g[f"{name}_model"])
     assert np.array_equal(res, g[f"{name}_res"])
     assert (done < int(niter)) == (name == "d")         # only case d stops at the threshold
