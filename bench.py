@@ -259,6 +259,9 @@ def run_b200(args):
                          "use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
+    # several ranks per node: keep each rank's pinned buffers and host copies on its GPU's socket
+    from ska_sdp_func_python_b200 import _xfer
+    affinity = _xfer.bind_host_to_gpu(torch, local_rank) if world > 1 else "unchanged (one rank)"
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     cfg = simulate.CONFIGS[args.config]
@@ -379,6 +382,7 @@ def run_b200(args):
         d2h = npix * npix * (csize // 2) + nsamp * csize
         e2e = {"value": nsamp * world / dt, "unit": UNIT, "ms_per_step": 1e3 * dt,
                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+               "host_affinity": affinity,
                "path": "Plan(host uvw) + Plan.invert(host ms, wgt) + Plan.predict(host image) "
                        "through the C ABI with pinned host buffers; plan creation (uvw upload, "
                        "uv/w sort) inside the timed region every step; sample arrays streamed "

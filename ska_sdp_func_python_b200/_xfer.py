@@ -72,3 +72,36 @@ class Stager:
             if self.events[k] is not None:
                 self.events[k].synchronize()
             self._flush(k)
+
+
+def bind_host_to_gpu(torch, index):
+    """Pin the calling process to the CPUs next to GPU ``index`` (its PCIe root's NUMA node, from
+    sysfs), so that pinned staging buffers are allocated in -- and host copies run from -- the
+    memory the GPU's DMA engines reach without crossing the socket interconnect.  With several
+    ranks per node this keeps each rank's host <-> device traffic on its own socket.  Returns a
+    short description; does nothing when the platform does not say (containers, one node)."""
+    import os
+    try:
+        props = torch.cuda.get_device_properties(index)
+        bus = "%04x:%02x:%02x.0" % (props.pci_domain_id, props.pci_bus_id, props.pci_device_id)
+        base = "/sys/bus/pci/devices/" + bus
+        with open(base + "/numa_node") as fh:
+            node = int(fh.read().strip())
+        if node < 0:
+            return "unchanged (no NUMA node reported for %s)" % bus
+        with open(base + "/local_cpulist") as fh:
+            text = fh.read().strip()
+        cpus = set()
+        for part in text.split(","):
+            if "-" in part:
+                lo, hi = part.split("-")
+                cpus.update(range(int(lo), int(hi) + 1))
+            elif part:
+                cpus.add(int(part))
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return "unchanged (no allowed CPU on NUMA node %d)" % node
+        os.sched_setaffinity(0, cpus)
+        return "NUMA node %d of GPU %s, %d CPUs" % (node, bus, len(cpus))
+    except (OSError, AttributeError, ValueError) as exc:
+        return "unchanged (%s)" % type(exc).__name__
