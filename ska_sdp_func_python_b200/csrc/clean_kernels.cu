@@ -31,7 +31,7 @@ int wrapper_fail(const char *msg);  // plan.cu
 namespace {
 
 constexpr unsigned kFull = 0xffffffffu;
-constexpr int kBlocks = 592;   // 148 SMs x 4
+constexpr int kBlocks = 1184;  // 148 SMs x 8
 constexpr int kThreads = 256;
 
 struct Cand {
@@ -77,6 +77,78 @@ __device__ Cand block_best(Cand c)
     r = warp_best(r);
     __syncthreads();
     return r;
+}
+
+// The minor cycles are launch bound on small images (two short kernels per iteration), so the
+// iterations are replayed from a CUDA graph of kBatch iterations; the state block tells the host
+// after every batch whether the stop test fired (iterations enqueued after it are no-ops, and the
+// kernels themselves enforce niter).  The legacy default stream cannot be captured: the whole call
+// then runs on a private stream ordered after the caller's work (LoopStream).
+constexpr int kBatch = 64;
+
+struct LoopStream {
+    cudaStream_t s;
+    bool own = false;
+    explicit LoopStream(cudaStream_t user) : s(user)
+    {
+        if (user != nullptr && user != cudaStreamLegacy) return;
+        cudaStream_t ls = nullptr;
+        cudaEvent_t ev = nullptr;
+        if (cudaStreamCreateWithFlags(&ls, cudaStreamNonBlocking) != cudaSuccess) return;
+        if (cudaEventCreateWithFlags(&ev, cudaEventDisableTiming) != cudaSuccess) {
+            cudaStreamDestroy(ls);
+            return;
+        }
+        cudaEventRecord(ev, user);
+        cudaStreamWaitEvent(ls, ev, 0);
+        cudaEventDestroy(ev);
+        s = ls;
+        own = true;
+    }
+    ~LoopStream()
+    {
+        if (own) {
+            cudaStreamSynchronize(s);
+            cudaStreamDestroy(s);
+        }
+    }
+    LoopStream(const LoopStream &) = delete;
+    LoopStream &operator=(const LoopStream &) = delete;
+};
+
+// one(): enqueue one iteration on s.  Returns 0 or the wrapper's error code; *h holds the final state.
+template <typename State, typename F>
+int iterate_until_stop(cudaStream_t s, long long niter, F one, const State *d_st, State *h)
+{
+    cudaGraphExec_t exec = nullptr;
+    if (niter >= 2 * kBatch && cudaStreamBeginCapture(s, cudaStreamCaptureModeThreadLocal) == cudaSuccess) {
+        for (int k = 0; k < kBatch; ++k) one();
+        cudaGraph_t g = nullptr;
+        if (cudaStreamEndCapture(s, &g) == cudaSuccess && g != nullptr &&
+            cudaGraphInstantiate(&exec, g, 0) != cudaSuccess)
+            exec = nullptr;
+        if (g) cudaGraphDestroy(g);
+    }
+    (void)cudaGetLastError();  // not capturable: plain launches below
+    int rc = 0;
+    h->stop = 0;
+    for (long long batch = 0; batch <= niter / kBatch + 1 && !h->stop; ++batch) {
+        cudaError_t e;
+        if (exec) {
+            e = cudaGraphLaunch(exec, s);
+        } else {
+            for (int k = 0; k < kBatch; ++k) one();
+            e = cudaGetLastError();
+        }
+        if (e == cudaSuccess) e = cudaMemcpyAsync(h, d_st, sizeof(State), cudaMemcpyDeviceToHost, s);
+        if (e == cudaSuccess) e = cudaStreamSynchronize(s);
+        if (e != cudaSuccess) {
+            rc = b2g::wrapper_fail(cudaGetErrorString(e));
+            break;
+        }
+    }
+    if (exec) cudaGraphExecDestroy(exec);
+    return rc;
 }
 
 struct CleanState {
@@ -297,7 +369,7 @@ cclean_select_kernel(const double *__restrict__ res_re, const double *__restrict
 // to one candidate per (block, scale), plus a one-block launch that applies the reference's
 // across-scale rule and stop tests.  Arithmetic and its order are the reference's.
 
-constexpr int kMsBlocks = 296;  // per scale: 148 SMs x 2
+constexpr int kMsBlocks = 592;  // upper bound of blocks per scale plane (see plane_blocks)
 constexpr int kMaxScales = 16;
 
 struct MsState {
@@ -652,6 +724,20 @@ int mf_run(double *smres, const double *psfm, const double *pscale, const double
 
 int cuda_fail(cudaError_t e) { return b2g::wrapper_fail(cudaGetErrorString(e)); }
 
+// Blocks per scale plane so that the whole (planes + 1)-deep grid is exactly one resident wave:
+// more blocks than fit leave a partial second wave (measured: 1480 blocks at 6 resident per SM ran
+// 1.67 waves).
+template <typename K> int plane_blocks(K kernel, int planes)
+{
+    int occ = 0, dev = 0, nsm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, kThreads, 0) != cudaSuccess || occ < 1) occ = 4;
+    cudaGetDevice(&dev);
+    if (cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess || nsm < 1) nsm = 148;
+    const int bx = occ * nsm / planes;
+    return bx < 1 ? 1 : (bx > kMsBlocks ? kMsBlocks : bx);
+}
+
+
 template <int NM>
 int mf_run(double *smres, const double *psfm, const double *pscale, const double *wstack,
            const double *sens, const MfHess &hs, int ns, int nx, int ny, int px, int py, double gain,
@@ -659,7 +745,9 @@ int mf_run(double *smres, const double *psfm, const double *pscale, const double
            cudaStream_t s)
 {
     Cand *d_part = nullptr;
-    const size_t npart = (size_t)kMsBlocks * ns;
+    const int bx = casa ? plane_blocks(mf_subtract_kernel<NM, true>, ns + 1)
+                        : plane_blocks(mf_subtract_kernel<NM, false>, ns + 1);
+    const size_t npart = (size_t)bx * ns;
     cudaError_t e = cudaMallocAsync(&d_part, sizeof(Cand) * 2 * npart + sizeof(MfState), s);
     if (e != cudaSuccess) return cuda_fail(e);
     Cand *d_scale = d_part, *d_pixel = d_part + npart;
@@ -676,7 +764,7 @@ int mf_run(double *smres, const double *psfm, const double *pscale, const double
     } while (0)
     CK(cudaMemsetAsync(d_st, 0, sizeof(MfState), s));
     CK(cudaMemsetAsync(model, 0, sizeof(double) * NM * nx * ny, s));
-    const dim3 grid(kMsBlocks, ns + 1);
+    const dim3 grid(bx, ns + 1);
     auto subtract = [&](int first) {
         if (casa)
             mf_subtract_kernel<NM, true><<<grid, kThreads, 0, s>>>(smres, psfm, pscale, wstack, sens, model, hs,
@@ -689,19 +777,13 @@ int mf_run(double *smres, const double *psfm, const double *pscale, const double
     };
     subtract(1);
     MfState h;
-    h.stop = 0;
     h.iters = 0;
-    for (long long i = 0; i <= niter; ++i) {
-        mf_select_kernel<NM><<<1, kThreads, 0, s>>>(smres, hs, ns, nx, ny, d_scale, d_pixel, kMsBlocks,
+    const int rc = iterate_until_stop(s, niter, [&] {
+        mf_select_kernel<NM><<<1, kThreads, 0, s>>>(smres, hs, ns, nx, ny, d_scale, d_pixel, bx,
                                                     absolutethresh, (int)niter, d_st);
-        if (i < niter) subtract(0);
-        if ((i & 63) == 63 || i == niter) {
-            CK(cudaGetLastError());
-            CK(cudaMemcpyAsync(&h, d_st, sizeof(MfState), cudaMemcpyDeviceToHost, s));
-            CK(cudaStreamSynchronize(s));
-            if (h.stop) break;
-        }
-    }
+        subtract(0);
+    }, d_st, &h);
+    if (rc) return done(rc);
 #undef CK
     if (iters_host) *iters_host = h.iters;
     return done(0);
@@ -757,7 +839,8 @@ extern "C" int b2g_hogbom(const double *dirty, const double *psf, const double *
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
         return b2g::wrapper_fail("b2g_hogbom: no CUDA device available (this library has no CPU path)");
-    cudaStream_t s = (cudaStream_t)stream;
+    LoopStream loop_stream((cudaStream_t)stream);
+    cudaStream_t s = loop_stream.s;
     const long long n = nx * ny;
     Cand *d_part = nullptr;
     cudaError_t e = cudaMallocAsync(&d_part, sizeof(Cand) * (kBlocks + 1) + sizeof(CleanState), s);
@@ -790,20 +873,14 @@ extern "C" int b2g_hogbom(const double *dirty, const double *psf, const double *
     clean_select_kernel<<<1, kThreads, 0, s>>>(res, comps, (int)ny, d_part, kBlocks, gain, pmax,
                                                stop_level, (int)niter, 1, d_st);
     CleanState hs;
-    hs.stop = 0;
     hs.iters = 0;
-    for (long long i = 0; i < niter; ++i) {
+    rc = iterate_until_stop(s, niter, [&] {
         clean_subtract_kernel<<<kBlocks, kThreads, 0, s>>>(res, psf, window, (int)nx, (int)ny, (int)px,
                                                            (int)py, d_st, d_part);
         clean_select_kernel<<<1, kThreads, 0, s>>>(res, comps, (int)ny, d_part, kBlocks, gain, pmax,
                                                    stop_level, (int)niter, 0, d_st);
-        if ((i & 63) == 63 || i + 1 == niter) {
-            CK(cudaGetLastError());
-            CK(cudaMemcpyAsync(&hs, d_st, sizeof(CleanState), cudaMemcpyDeviceToHost, s));
-            CK(cudaStreamSynchronize(s));
-            if (hs.stop) break;
-        }
-    }
+    }, d_st, &hs);
+    if (rc) return done(rc);
 #undef CK
     if (iters_host) *iters_host = hs.iters;
     return done(0);
@@ -825,14 +902,16 @@ extern "C" int b2g_msclean(double *res_stack, const double *psf_scalescale, cons
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
         return b2g::wrapper_fail("b2g_msclean: no CUDA device available (this library has no CPU path)");
-    cudaStream_t s = (cudaStream_t)stream;
+    LoopStream loop_stream((cudaStream_t)stream);
+    cudaStream_t s = loop_stream.s;
     const int ns = (int)nscales;
     MsCoupling cp;
     for (int i = 0; i < kMaxScales; ++i) cp.c[i] = i < ns ? coupling_diag[i] : 1.0;
     Cand *d_part = nullptr;
-    cudaError_t e = cudaMallocAsync(&d_part, sizeof(Cand) * kMsBlocks * ns + sizeof(MsState), s);
+    const int bx = plane_blocks(ms_subtract_kernel, ns + 1);
+    cudaError_t e = cudaMallocAsync(&d_part, sizeof(Cand) * bx * ns + sizeof(MsState), s);
     if (e != cudaSuccess) return cuda_fail(e);
-    MsState *d_st = reinterpret_cast<MsState *>(d_part + (size_t)kMsBlocks * ns);
+    MsState *d_st = reinterpret_cast<MsState *>(d_part + (size_t)bx * ns);
     auto done = [&](int code) {
         cudaStreamSynchronize(s);
         cudaFreeAsync(d_part, s);
@@ -846,30 +925,22 @@ extern "C" int b2g_msclean(double *res_stack, const double *psf_scalescale, cons
     const double stop_level = 0.9 * absolutethresh;
     CK(cudaMemsetAsync(d_st, 0, sizeof(MsState), s));
     CK(cudaMemsetAsync(comps, 0, sizeof(double) * nx * ny, s));
-    const dim3 grid(kMsBlocks, ns + 1);
+    const dim3 grid(bx, ns + 1);
     ms_subtract_kernel<<<grid, kThreads, 0, s>>>(res_stack, psf_scalescale, psf_scale, window_stack,
                                                  sensitivity, comps, cp, ns, (int)nx, (int)ny, (int)px,
                                                  (int)py, gain, 1, d_st, d_part);
     MsState hs;
-    hs.stop = 0;
     hs.iters = 0;
-    // iteration i: select (stop tests, peak) then subtract; one select more than subtractions so
-    // that the niter limit is seen by the state
-    for (long long i = 0; i <= niter; ++i) {
+    // iteration: select (stop tests, peak) then subtract; the select after the last subtraction
+    // sees iters == niter and stops
+    const int rc = iterate_until_stop(s, niter, [&] {
         ms_select_kernel<<<1, kThreads, 0, s>>>(res_stack, window_stack, sensitivity, cp, ns, (int)nx,
-                                                (int)ny, d_part, kMsBlocks, stop_level, (int)niter, d_st);
-        if (i < niter)
-            ms_subtract_kernel<<<grid, kThreads, 0, s>>>(res_stack, psf_scalescale, psf_scale,
-                                                         window_stack, sensitivity, comps, cp, ns,
-                                                         (int)nx, (int)ny, (int)px, (int)py, gain, 0,
-                                                         d_st, d_part);
-        if ((i & 63) == 63 || i == niter) {
-            CK(cudaGetLastError());
-            CK(cudaMemcpyAsync(&hs, d_st, sizeof(MsState), cudaMemcpyDeviceToHost, s));
-            CK(cudaStreamSynchronize(s));
-            if (hs.stop) break;
-        }
-    }
+                                                (int)ny, d_part, bx, stop_level, (int)niter, d_st);
+        ms_subtract_kernel<<<grid, kThreads, 0, s>>>(res_stack, psf_scalescale, psf_scale, window_stack,
+                                                     sensitivity, comps, cp, ns, (int)nx, (int)ny, (int)px,
+                                                     (int)py, gain, 0, d_st, d_part);
+    }, d_st, &hs);
+    if (rc) return done(rc);
 #undef CK
     if (iters_host) *iters_host = hs.iters;
     return done(0);
@@ -903,7 +974,8 @@ extern "C" int b2g_msmfsclean(double *smres, const double *psf_moments, const do
                 hs.ih[s][m][q] = in ? inv_hessian[(s * nmoment + m) * nmoment + q] : 0.0;
                 hs.h[s][m][q] = in && hessian ? hessian[(s * nmoment + m) * nmoment + q] : 0.0;
             }
-    cudaStream_t st = (cudaStream_t)stream;
+    LoopStream loop_stream((cudaStream_t)stream);
+    cudaStream_t st = loop_stream.s;
 #define RUN(NM)                                                                                     \
     return mf_run<NM>(smres, psf_moments, psf_scale, window_stack, sensitivity, hs, (int)nscales,   \
                       (int)nx, (int)ny, (int)px, (int)py, gain, absolutethresh, niter, findpeak,    \
@@ -933,7 +1005,8 @@ extern "C" int b2g_hogbom_complex(const double *dirty_q, const double *dirty_u, 
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0)
         return b2g::wrapper_fail("b2g_hogbom_complex: no CUDA device available (this library has no CPU path)");
-    cudaStream_t s = (cudaStream_t)stream;
+    LoopStream loop_stream((cudaStream_t)stream);
+    cudaStream_t s = loop_stream.s;
     const long long n = nx * ny;
     Cand *d_part = nullptr;
     cudaError_t e = cudaMallocAsync(&d_part, sizeof(Cand) * (kBlocks + 1) + sizeof(CplxCleanState), s);
@@ -969,20 +1042,14 @@ extern "C" int b2g_hogbom_complex(const double *dirty_q, const double *dirty_u, 
     cclean_select_kernel<<<1, kThreads, 0, s>>>(res_q, res_u, comps_q, comps_u, (int)ny, d_part, kBlocks,
                                                 gain, pmax, absolutethresh, (int)niter, 1, d_st);
     CplxCleanState hs;
-    hs.stop = 0;
     hs.iters = 0;
-    for (long long i = 0; i < niter; ++i) {
+    const int rc = iterate_until_stop(s, niter, [&] {
         cclean_subtract_kernel<<<kBlocks, kThreads, 0, s>>>(res_q, res_u, psf, window, (int)nx, (int)ny,
                                                             (int)px, (int)py, 0, d_st, d_part);
         cclean_select_kernel<<<1, kThreads, 0, s>>>(res_q, res_u, comps_q, comps_u, (int)ny, d_part,
                                                     kBlocks, gain, pmax, absolutethresh, (int)niter, 0, d_st);
-        if ((i & 63) == 63 || i + 1 == niter) {
-            CK(cudaGetLastError());
-            CK(cudaMemcpyAsync(&hs, d_st, sizeof(CplxCleanState), cudaMemcpyDeviceToHost, s));
-            CK(cudaStreamSynchronize(s));
-            if (hs.stop) break;
-        }
-    }
+    }, d_st, &hs);
+    if (rc) return done(rc);
 #undef CK
     if (iters_host) *iters_host = hs.iters;
     return done(0);
