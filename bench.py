@@ -380,9 +380,36 @@ def run_b200(args):
         dt = float(tt.item())
         h2d = nrow * 24 + nchan * 8 + nsamp * (csize + csize // 2) + npix * npix * (csize // 2)
         d2h = npix * npix * (csize // 2) + nsamp * csize
+        # context for the number above: what this box's PCIe link moves from / to pinned memory
+        # (the e2e step cannot be shorter than h2d / up + d2h / down: invert's uploads and
+        # predict's downloads do not overlap each other)
+        pcie = {}
+        try:
+            nb = min(ms_h.numel() * ms_h.element_size(), 1 << 30)
+            hbuf = ms_h.view(torch.uint8).reshape(-1)[:nb]
+            dbuf = torch.empty(nb, dtype=torch.uint8, device=dev)
+            ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+            dbuf.copy_(hbuf, non_blocking=True)
+            torch.cuda.synchronize()
+            ev[0].record()
+            dbuf.copy_(hbuf, non_blocking=True)
+            ev[1].record()
+            vis_h.view(torch.uint8).reshape(-1)[:nb].copy_(dbuf, non_blocking=True)
+            ev[2].record()
+            torch.cuda.synchronize()
+            up, down = nb / (ev[0].elapsed_time(ev[1]) * 1e-3), nb / (ev[1].elapsed_time(ev[2]) * 1e-3)
+            pcie = {"h2d_GBs": up / 1e9, "d2h_GBs": down / 1e9,
+                    "floor_ms_per_step": 1e3 * (h2d / up + d2h / down)}
+            import pynvml
+            pynvml.nvmlInit()
+            hnd = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
+            pcie["link"] = "gen%d x%d" % (pynvml.nvmlDeviceGetCurrPcieLinkGeneration(hnd),
+                                          pynvml.nvmlDeviceGetCurrPcieLinkWidth(hnd))
+        except Exception as exc:  # context only: never fail the bench over it
+            pcie["note"] = type(exc).__name__
         e2e = {"value": nsamp * world / dt, "unit": UNIT, "ms_per_step": 1e3 * dt,
                "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-               "host_affinity": affinity,
+               "host_affinity": affinity, "pcie": pcie,
                "path": "Plan(host uvw) + Plan.invert(host ms, wgt) + Plan.predict(host image) "
                        "through the C ABI with pinned host buffers; plan creation (uvw upload, "
                        "uv/w sort) inside the timed region every step; sample arrays streamed "
