@@ -18,7 +18,8 @@ from .imaging import _ptr, _torch
 log = logging.getLogger("func-python-logger")
 
 __all__ = ["hogbom", "hogbom_complex", "hogbom_kernel_list", "complex_hogbom_kernel_list", "msclean", "msclean_kernel_list", "msmfsclean", "mmclean_kernel_list", "create_scalestack",
-           "spheroidal_function", "common_arguments", "image_peak"]
+           "spheroidal_function", "common_arguments", "image_peak", "overlapIndices", "argmax",
+           "convolve_scalestack", "convolve_convolve_scalestack"]
 
 
 def _dev64(a, dev):
@@ -498,3 +499,49 @@ def complex_hogbom_kernel_list(dirty_list, psf_list, window_list, **kwargs):
         comp_images.append(_new_image_like(dirty, comp_array))
         residual_images.append(_new_image_like(dirty, residual_array))
     return comp_images, residual_images
+
+
+# ---- small public helpers of the reference module ---------------------------------------------
+
+def overlapIndices(res, psf, peakx, peaky):
+    """Index ranges where the PSF centred on (peakx, peaky) overlaps the image (cleaners.py:235-267):
+    ((x0, x1, y0, y1) in the image, (x0, x1, y0, y1) in the PSF).  The kernels evaluate the same
+    clipping on the device; this is the host form for callers that slice arrays themselves."""
+    nx, ny = res.shape[0], res.shape[1]
+    hx, hy = psf.shape[0] // 2, psf.shape[1] // 2
+    x0, y0 = max(0, peakx - hx), max(0, peaky - hy)
+    x1, y1 = min(nx, peakx + hx), min(peaky + hy, ny)
+    return ((x0, x1, y0, y1),
+            (max(0, hx + (x0 - peakx)), min(psf.shape[0], hx + (x1 - peakx)),
+             max(0, hy + (y0 - peaky)), min(hy + (y1 - peaky), psf.shape[1])))
+
+
+def argmax(a):
+    """Unravelled index of the maximum (cleaners.py:270-276), on the device for CUDA tensors."""
+    torch = _torch()
+    if isinstance(a, torch.Tensor):
+        return tuple(int(v) for v in numpy.unravel_index(int(a.reshape(-1).argmax()), tuple(a.shape)))
+    return numpy.unravel_index(a.argmax(), a.shape)
+
+
+def convolve_scalestack(scalestack, img):
+    """img correlated with every plane of scalestack (cleaners.py:511-531), with cuFFT; numpy in,
+    numpy out (CUDA tensors in, CUDA tensor out)."""
+    torch = _torch()
+    on_device = isinstance(img, torch.Tensor) and img.is_cuda
+    dev = img.device if on_device else torch.device("cuda", torch.cuda.current_device())
+    st, im = _dev64(scalestack, dev), _dev64(img, dev)
+    out = _convolve_scalestack(torch, _spectrum(torch, st), im)
+    return out if on_device else out.cpu().numpy()
+
+
+def convolve_convolve_scalestack(scalestack, img):
+    """[s, p] = img convolved with scale p and correlated with scale s (cleaners.py:534-562)."""
+    torch = _torch()
+    on_device = isinstance(img, torch.Tensor) and img.is_cuda
+    dev = img.device if on_device else torch.device("cuda", torch.cuda.current_device())
+    st, im = _dev64(scalestack, dev), _dev64(img, dev)
+    fs, fi = _spectrum(torch, st), _spectrum(torch, im)
+    out = torch.stack([_back(torch, (fi[None] * fs) * torch.conj(fs[s])[None], tuple(im.shape))
+                       for s in range(st.shape[0])])
+    return out if on_device else out.cpu().numpy()

@@ -338,3 +338,18 @@ def test_hogbom_complex_larger_and_list(cl):
     ci, ri, _ = oc.hogbom(dq + du, psf, None, 0.2, 0.0, 400, 0.001)
     assert np.array_equal(comp["pixels"].data[0, 0], ci) and np.array_equal(resid["pixels"].data[0, 0], ri)
     assert not comp["pixels"].data[0, 3].any()
+
+
+def test_public_helpers_match_oracle(cl):
+    import torch
+    from oracle import clean as oc
+    rng = np.random.default_rng(4)
+    img = rng.normal(size=(33, 40))
+    stack = oc.scale_stack((3, 33, 40), [0, 4, 9])
+    assert np.abs(cl.convolve_scalestack(stack, img) - oc.convolve_stack(stack, img)).max() < 1e-13
+    assert np.abs(cl.convolve_convolve_scalestack(stack, img) - oc.convolve_convolve_stack(stack, img)).max() < 1e-13
+    assert cl.convolve_scalestack(torch.from_numpy(stack).cuda(), torch.from_numpy(img).cuda()).is_cuda
+    for shape, pshape, px, py in (((64, 64), (64, 64), 3, 60), ((48, 80), (33, 41), 47, 0), ((40, 40), (80, 80), 20, 20)):
+        assert cl.overlapIndices(np.zeros(shape), np.zeros(pshape), px, py) == oc.overlap(shape, pshape, px, py)
+    a = rng.normal(size=(17, 23))
+    assert tuple(cl.argmax(a)) == tuple(np.unravel_index(a.argmax(), a.shape)) == cl.argmax(torch.from_numpy(a).cuda())
