@@ -1,0 +1,111 @@
+"""Stand-alone forms of the two small steps of the path that ``invert_ng`` / ``predict_ng`` otherwise
+fuse into their device kernels, for callers that use them
+on their own:
+
+* ``shift_vis_to_image`` / ``phaserotate_visibility`` (imaging/base.py:48-92, visibility/base.py:27-125,
+  tangent-plane case): vis *= conj(phasor) (or phasor for ``inverse``), phasor =
+  exp(-2 pi i uvw_lambda . [l, m, sqrt(1 - l^2 - m^2) - 1]), on the device through ``b2g_vis_finish``
+  (exact range reduction of the phase, ``sincospi``);
+* ``normalise_sumwt`` (imaging/base.py:95-156).
+"""
+import ctypes
+import logging
+
+import numpy
+
+from . import _lib
+from .imaging import (_Device, _dptr, _is_image, _ptr, _radec, _rows_per_chunk, image_centre_radec,
+                      separation, skycoord_to_lmn)
+from .skymodel_imaging import _normalise_sumwt_image
+
+log = logging.getLogger("func-python-logger")
+
+__all__ = ["shift_vis_to_image", "phaserotate_visibility", "normalise_sumwt"]
+
+
+def _rotate(vis, lmn, inverse):
+    """vis["vis"] *= exp(-+ 2 pi i (u l + v m + w (n - 1)) f / c) on the device, chunk by chunk."""
+    data = vis["vis"].data
+    nrows, nbl, nchan, npol = data.shape
+    nrow = nrows * nbl
+    D = _Device(numpy.asarray(vis["uvw"].data, dtype=numpy.float64).reshape(nrow, 3),
+                numpy.asarray(vis.frequency.data))
+    torch = D.torch
+    # b2g_vis_finish multiplies by exp(-2 pi i uvw . lmn): that is the phasor itself (inverse);
+    # the forward rotation multiplies by its conjugate, i.e. the phasor of -lmn
+    sgn = 1.0 if inverse else -1.0
+    lmn = numpy.array([sgn * lmn[0], sgn * lmn[1], sgn * lmn[2]], dtype=numpy.float64)
+    ident = numpy.ascontiguousarray(numpy.eye(npol, dtype=numpy.complex128))
+    flat = numpy.ascontiguousarray(data.reshape(nrow, nchan, npol), dtype=numpy.complex128)
+    out = numpy.empty_like(flat)
+    step = max(1, _rows_per_chunk(nchan, npol, 16) // 2)
+    L = _lib.lib()
+    stage = D.stager()
+    for r0 in range(0, nrow, step):
+        r1 = min(nrow, r0 + step)
+        rows = r1 - r0
+        # the kernel reads polarisation planes [npol][rows][nchan] and writes [rows][nchan][npol]
+        planes = stage.put(flat[r0:r1]).permute(2, 0, 1).contiguous()
+        chunk = torch.empty((rows, nchan, npol), device=D.dev, dtype=torch.complex128)
+        _lib.check(L.b2g_vis_finish(
+            rows, nchan, npol, npol, _ptr(planes), _lib.F64, _dptr(ident.view(numpy.float64)),
+            _dptr(lmn), _ptr(D.uvw[r0:r1]), _ptr(D.fscale), 0, rows, _ptr(chunk), _lib.F64,
+            ctypes.c_void_p(D.stream)))
+        stage.get(chunk, out[r0:r1])
+    stage.finish()
+    return out.reshape(data.shape)
+
+
+def _phaserotate(vis, ra_n, dec_n, inverse):
+    ra_v, dec_v = _radec(vis.phasecentre)
+    l, m, nm1 = skycoord_to_lmn(ra_n, dec_n, ra_v, dec_v)
+    if abs(nm1) < 1e-15:                                   # "no significant change", visibility/base.py:78
+        return vis
+    newvis = vis.copy(deep=True)
+    s = (l, m, float(numpy.sqrt(1.0 - l * l - m * m) - 1.0))
+    newvis["vis"].data = _rotate(newvis, s, inverse)
+    return newvis
+
+
+def phaserotate_visibility(vis, newphasecentre, tangent=True, inverse=False):
+    """Phase rotate to a new phase centre on the same tangent plane (visibility/base.py:60-125).
+    Returns ``vis`` itself when the change is insignificant, else a rotated deep copy.  The
+    ``tangent=False`` branch (uvw re-projection) is outside the imaging path and not built."""
+    if not tangent:
+        raise NotImplementedError("phaserotate_visibility: tangent=False (uvw re-projection) is not built")
+    ra_n, dec_n = _radec(newphasecentre)
+    return _phaserotate(vis, ra_n, dec_n, inverse)
+
+
+def shift_vis_to_image(vis, im, tangent=True, inverse=False):
+    """Shift the visibility phases to the image's FFT centre pixel (imaging/base.py:48-92); sets
+    ``attrs["phasecentre"]`` as the reference does."""
+    ra_i, dec_i = image_centre_radec(im)
+    ra_v, dec_v = _radec(vis.phasecentre)
+    if separation(ra_v, dec_v, ra_i, dec_i) > 1e-15:
+        if not tangent:
+            raise NotImplementedError("shift_vis_to_image: tangent=False (uvw re-projection) is not built")
+        vis = _phaserotate(vis, ra_i, dec_i, inverse)
+        vis.attrs["phasecentre"] = im.image_acc.phasecentre
+    return vis
+
+
+def normalise_sumwt(im, sumwt, min_weight=0.1, flat_sky=False):
+    """Divide out the sum of weights (imaging/base.py:95-156): per (channel, polarisation) for a
+    2-D ``sumwt`` (planes with sumwt <= 0 are zeroed), pixel by pixel / by its maximum for an Image."""
+    nchan, npol, _, _ = im["pixels"].data.shape
+    assert sumwt is not None
+    if isinstance(sumwt, numpy.ndarray):
+        assert nchan == sumwt.shape[0]
+        assert npol == sumwt.shape[1]
+        pix = im["pixels"].data
+        for chan in range(nchan):
+            for pol in range(npol):
+                if sumwt[chan, pol] > 0.0:
+                    pix[chan, pol, :, :] = pix[chan, pol, :, :] / sumwt[chan, pol]
+                else:
+                    pix[chan, pol, :, :] = 0.0
+        return im
+    if _is_image(sumwt) and im["pixels"].data.shape == sumwt["pixels"].data.shape:
+        return _normalise_sumwt_image(im, sumwt, min_weight=min_weight, flat_sky=flat_sky)
+    raise ValueError("sumwt is not a 2D or 4D array - cannot perform normalisation")
