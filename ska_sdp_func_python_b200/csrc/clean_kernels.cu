@@ -17,8 +17,8 @@
 // iteration is one pass over L2-resident data: the kernel that subtracts the shifted PSF also
 // reduces |res * window| of the UPDATED residual to one (value, index) candidate per block, and a
 // one-block kernel picks the next peak, updates the component and evaluates the stop test.  The
-// host enqueues iterations back to back and looks at the stop flag every 64 iterations; kernels
-// of iterations enqueued after the stop exit immediately.
+// host replays batches of 64 iterations from a CUDA graph (iterate_until_stop) and looks at the
+// stop flag after each batch; kernels of iterations enqueued after the stop exit immediately.
 #include <cuda_runtime.h>
 #include <stdint.h>
 
@@ -430,7 +430,7 @@ __device__ __forceinline__ void ms_visit(MsBest &b, double r, const double *wrow
     }
 }
 
-// grid (kMsBlocks, ns + 1): y < ns updates scale y and reduces its metric; y == ns adds the
+// grid (plane_blocks, ns + 1): y < ns updates scale y and reduces its metric; y == ns adds the
 // component.  first != 0: no subtraction, candidates of the initial stack only.
 __global__ void __launch_bounds__(kThreads)
 ms_subtract_kernel(double *__restrict__ res, const double *__restrict__ pss,
