@@ -152,6 +152,7 @@ int iterate_until_stop(cudaStream_t s, long long niter, F one, const State *d_st
 }
 
 struct CleanState {
+    unsigned int ticket;  // blocks of the running iteration that have delivered their candidate
     int mx, my;        // current peak
     double mval;       // component just added at the peak
     int stop;          // set once the stop test fires (or niter is reached)
@@ -187,11 +188,69 @@ peak_final_kernel(const Cand *__restrict__ part, int npart, Cand *__restrict__ o
     if (threadIdx.x == 0) *out = best;
 }
 
-// res -= psf(shifted to the peak) * mval on the overlap; candidates of the updated residual
+// Coherent (L2) loads of values written by other blocks of the same launch.
+__device__ __forceinline__ Cand load_cand(const Cand *p)
+{
+    return Cand{__ldcg(&p->val), __ldcg(&p->idx)};
+}
+
+// Executed by ONE whole block: stop test of the iteration just subtracted (first == 0), then the
+// next peak, the component value and the component image update.
+__device__ void clean_select_block(const double *res, double *__restrict__ comps, int ny, const Cand *part,
+                                   int npart, double gain, double pmax, double stop_level, int niter,
+                                   int first, CleanState *st)
+{
+    __shared__ int s_stop;
+    if (threadIdx.x == 0) {
+        s_stop = 0;
+        if (!first) {
+            st->iters += 1;
+            const double r = __ldcg(&res[(long long)st->mx * ny + st->my]);
+            if (fabs(r) < stop_level || st->iters >= niter) {
+                st->stop = 1;
+                s_stop = 1;
+            }
+        }
+    }
+    __syncthreads();
+    if (s_stop) return;
+    Cand best{neg_inf(), 0x7fffffffffffffffll};
+    for (int i = threadIdx.x; i < npart; i += blockDim.x) {
+        const Cand c = load_cand(part + i);
+        if (better(c.val, c.idx, best.val, best.idx)) best = c;
+    }
+    best = block_best(best);
+    if (threadIdx.x == 0) {
+        const int mx = (int)(best.idx / ny), my = (int)(best.idx - (long long)mx * ny);
+        const double mval = __ddiv_rn(__dmul_rn(__ldcg(&res[best.idx]), gain), pmax);
+        st->mx = mx;
+        st->my = my;
+        st->mval = mval;
+        comps[best.idx] = __dadd_rn(comps[best.idx], mval);
+    }
+}
+
+// The first peak (no subtraction yet).
 __global__ void __launch_bounds__(kThreads)
-clean_subtract_kernel(double *__restrict__ res, const double *__restrict__ psf,
-                      const double *__restrict__ window, int nx, int ny, int px, int py,
-                      const CleanState *__restrict__ st, Cand *__restrict__ part)
+clean_select_kernel(const double *res, double *__restrict__ comps, int ny, const Cand *part, int npart,
+                    double gain, double pmax, double stop_level, int niter, int first, CleanState *st)
+{
+    if (st->stop) return;
+    clean_select_block(res, comps, ny, part, npart, gain, pmax, stop_level, niter, first, st);
+}
+
+// One iteration in one launch: res -= psf(shifted to the peak) * mval on the overlap, candidates of
+// the updated residual per block, and -- in the block that finishes last (ticket counter behind a
+// __threadfence) -- the stop test, the next peak and the component update.  Every block reads the
+// state at its start; the last block rewrites it only after all others have taken their ticket.
+// The pointers stay __restrict__ for the streaming loop (without it the unrolled loads are not
+// batched: measured 2 x slower); the last block reads other blocks' results with explicit L2 loads
+// (__ldcg) behind the fences.
+__global__ void __launch_bounds__(kThreads)
+clean_iter_kernel(double *__restrict__ res, const double *__restrict__ psf,
+                  const double *__restrict__ window, double *__restrict__ comps, int nx, int ny, int px,
+                  int py, double gain, double pmax, double stop_level, int niter,
+                  CleanState *__restrict__ st, Cand *__restrict__ part)
 {
     if (st->stop) return;
     const int mx = st->mx, my = st->my;
@@ -220,42 +279,17 @@ clean_subtract_kernel(double *__restrict__ res, const double *__restrict__ psf,
         }
     }
     best = block_best(best);
-    if (threadIdx.x == 0) part[blockIdx.x] = best;
-}
-
-// One block: stop test of the iteration just subtracted (first == 0), then the next peak.
-__global__ void __launch_bounds__(kThreads)
-clean_select_kernel(const double *__restrict__ res, double *__restrict__ comps, int ny,
-                    const Cand *__restrict__ part, int npart, double gain, double pmax,
-                    double stop_level, int niter, int first, CleanState *__restrict__ st)
-{
-    if (st->stop) return;
-    __shared__ int s_stop;
+    __shared__ int s_last;
     if (threadIdx.x == 0) {
-        s_stop = 0;
-        if (!first) {
-            st->iters += 1;
-            const double r = res[(long long)st->mx * ny + st->my];
-            if (fabs(r) < stop_level || st->iters >= niter) {
-                st->stop = 1;
-                s_stop = 1;
-            }
-        }
+        part[blockIdx.x] = best;
+        __threadfence();
+        s_last = atomicAdd(&st->ticket, 1u) == gridDim.x - 1;
     }
     __syncthreads();
-    if (s_stop) return;
-    Cand best{neg_inf(), 0x7fffffffffffffffll};
-    for (int i = threadIdx.x; i < npart; i += blockDim.x)
-        if (better(part[i].val, part[i].idx, best.val, best.idx)) best = part[i];
-    best = block_best(best);
-    if (threadIdx.x == 0) {
-        const int mx = (int)(best.idx / ny), my = (int)(best.idx - (long long)mx * ny);
-        const double mval = __ddiv_rn(__dmul_rn(res[best.idx], gain), pmax);
-        st->mx = mx;
-        st->my = my;
-        st->mval = mval;
-        comps[best.idx] = __dadd_rn(comps[best.idx], mval);
-    }
+    if (!s_last) return;
+    __threadfence();
+    if (threadIdx.x == 0) st->ticket = 0;
+    clean_select_block(res, comps, ny, part, (int)gridDim.x, gain, pmax, stop_level, niter, 0, st);
 }
 
 // ---- complex Hogbom CLEAN of Q + iU (hogbom_complex(), cleaners.py:136-232) --------------------
@@ -875,10 +909,9 @@ extern "C" int b2g_hogbom(const double *dirty, const double *psf, const double *
     CleanState hs;
     hs.iters = 0;
     rc = iterate_until_stop(s, niter, [&] {
-        clean_subtract_kernel<<<kBlocks, kThreads, 0, s>>>(res, psf, window, (int)nx, (int)ny, (int)px,
-                                                           (int)py, d_st, d_part);
-        clean_select_kernel<<<1, kThreads, 0, s>>>(res, comps, (int)ny, d_part, kBlocks, gain, pmax,
-                                                   stop_level, (int)niter, 0, d_st);
+        clean_iter_kernel<<<kBlocks, kThreads, 0, s>>>(res, psf, window, comps, (int)nx, (int)ny, (int)px,
+                                                       (int)py, gain, pmax, stop_level, (int)niter, d_st,
+                                                       d_part);
     }, d_st, &hs);
     if (rc) return done(rc);
 #undef CK
