@@ -132,12 +132,15 @@ int iterate_until_stop(cudaStream_t s, long long niter, F one, const State *d_st
     (void)cudaGetLastError();  // not capturable: plain launches below
     int rc = 0;
     h->stop = 0;
-    for (long long batch = 0; batch <= niter / kBatch + 1 && !h->stop; ++batch) {
+    // short runs: no more launches per batch than iterations asked for (+ 1: the multi-scale loops
+    // need the select after the last subtraction to see the limit)
+    const int per_batch = exec ? kBatch : (int)(niter + 1 < kBatch ? niter + 1 : kBatch);
+    for (long long batch = 0; batch <= niter / per_batch + 1 && !h->stop; ++batch) {
         cudaError_t e;
         if (exec) {
             e = cudaGraphLaunch(exec, s);
         } else {
-            for (int k = 0; k < kBatch; ++k) one();
+            for (int k = 0; k < per_batch; ++k) one();
             e = cudaGetLastError();
         }
         if (e == cudaSuccess) e = cudaMemcpyAsync(h, d_st, sizeof(State), cudaMemcpyDeviceToHost, s);
