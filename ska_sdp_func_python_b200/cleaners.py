@@ -1,11 +1,19 @@
-"""Drop-in Hogbom CLEAN on a B200 (the minor cycle that consumes the
-dirty image and PSF made by ``invert_ng``).
+"""Drop-in CLEAN minor cycles on a B200 (the consumers of the dirty
+image and PSF made by ``invert_ng``), mirroring
+/root/reference/src/ska_sdp_func_python/image/cleaners.py function by function -- same arguments,
+same assertions, same return values:
 
-``hogbom`` mirrors /root/reference/src/ska_sdp_func_python/image/cleaners.py:23-133 -- same
-arguments, same assertions, same return value (component image, residual image) -- with the
-iteration loop on the device (csrc/clean_kernels.cu): one pass over the L2-resident residual per
-iteration subtracts the shifted PSF and finds the next peak.  All arithmetic is the reference's own
-fp64 operations in the reference's order, so the results are bit-exact.  No CPU fallback.
+  hogbom (:23-133), hogbom_complex (:136-232), msclean (:279-470), msmfsclean (:686-898) and the
+  module's helpers (overlapIndices, argmax, create_scalestack, convolve_scalestack,
+  convolve_convolve_scalestack, spheroidal_function),
+
+plus the image-list wrappers that call them (image/deconvolution.py: hogbom_kernel_list,
+complex_hogbom_kernel_list, msclean_kernel_list, mmclean_kernel_list, common_arguments).
+
+The iteration loops run on the device (csrc/clean_kernels.cu) in the reference's own fp64
+operations and order: Hogbom and complex Hogbom are bit-exact; the multi-scale variants are
+bit-exact given the same scale-convolved stacks, which are formed here with cuFFT instead of
+numpy's FFT (agreement ~1e-12 end to end).  No CPU fallback.
 """
 import ctypes
 import logging
