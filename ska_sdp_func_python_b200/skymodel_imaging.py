@@ -63,24 +63,16 @@ def _normalise_sumwt_image(im, sumwt, min_weight=0.1, flat_sky=False):
 
 def _dft_sky_component(vis_slice, skymodel, pb=None, **kwargs):
     """Run DFT of sky components (skymodel_imaging.py:22-45).  With a mask or a primary beam the
-    component fluxes are first scaled by the reference's ``apply_beam_to_skycomponent``
-    (sky_component package, astropy-based; taken from the reference when importable or passed as
-    ``apply_beam_to_skycomponent=``)."""
+    component fluxes are first scaled by ``apply_beam_to_skycomponent`` (``sky_component.py``: the
+    reference's function with the SIN projection written out instead of astropy; another
+    implementation can be passed as ``apply_beam_to_skycomponent=``)."""
     comps = skymodel.components
     if skymodel.mask is not None or pb is not None:
         comps = list(skymodel.components)
         if len(comps) > 0:
             apply_beam = kwargs.get("apply_beam_to_skycomponent")
             if apply_beam is None:
-                try:
-                    from ska_sdp_func_python.sky_component import (
-                        apply_beam_to_skycomponent as apply_beam,
-                    )
-                except ImportError as err:
-                    raise NotImplementedError(
-                        "components with a mask / primary beam need apply_beam_to_skycomponent "
-                        "(reference sky_component package); pass it as "
-                        "apply_beam_to_skycomponent=") from err
+                from .sky_component import apply_beam_to_skycomponent as apply_beam
             if skymodel.mask is not None:
                 comps = apply_beam(comps, skymodel.mask)
             if pb is not None:

@@ -129,3 +129,24 @@ def test_plan_residual_identity(mods, prec, eps, algo, tol):
         assert np.abs(r_dev.cpu().numpy() - ref).max() < tol * scale
         assert np.abs(ms_d.cpu().numpy() - (ms - pred)).max() < tol * np.abs(ms).max()
         assert plan.info()["launches_last_call"] >= 4
+
+
+def test_components_with_mask_use_builtin_apply_beam(mods):
+    """Components combined with a mask (skymodel_imaging.py:22-45): fluxes scaled by the mask value at
+    their pixel through sky_component.apply_beam_to_skycomponent, then the DFT; equal to doing the two
+    steps by hand."""
+    imaging, sm, _ = mods
+    from ska_sdp_func_python_b200 import dft
+    from ska_sdp_func_python_b200.sky_component import apply_beam_to_skycomponent
+    g, mm, vis, model, mask, pb, comps = _load()
+    mask["pixels"].data[:] = np.random.default_rng(1).uniform(0.3, 1.0, mask["pixels"].data.shape)
+    sky = mm.SkyModel(image=model, components=comps, mask=mask)
+    got = sm.skymodel_predict_calibrate(vis, sky, context="ng", epsilon=1e-12)
+    zero = vis.copy(deep=True, zero=True)
+    want = dft.dft_skycomponent_visibility(zero, apply_beam_to_skycomponent(comps, mask))
+    masked = model.copy(deep=True)
+    masked["pixels"].data *= mask["pixels"].data
+    want["vis"].data += imaging.predict_ng(vis.copy(deep=True, zero=True), masked, epsilon=1e-12)["vis"].data
+    assert rel_max(got["vis"].data, want["vis"].data) < 1e-10
+    scaled = apply_beam_to_skycomponent(comps, mask)
+    assert any(not np.array_equal(a.flux, b.flux) for a, b in zip(scaled, comps))
