@@ -15,7 +15,7 @@ import numpy
 from .dft import dft_skycomponent_visibility
 from .imaging import invert_visibility, predict_visibility, residual_ng
 
-__all__ = ["skymodel_predict_calibrate", "skymodel_calibrate_invert", "skymodel_residual"]
+__all__ = ["skymodel_predict_calibrate", "skymodel_calibrate_invert", "skymodel_residual", "subtract_visibility"]
 
 
 def _time_slices(v):
@@ -182,3 +182,18 @@ def skymodel_residual(bvis, skymodel, context="ng", normalise=True, **kwargs):
     if skymodel.mask is not None:
         result[0]["pixels"].data *= skymodel.mask["pixels"].data
     return result
+
+
+def subtract_visibility(vis, model_vis, inplace=False):
+    """vis - model_vis as a new Visibility, or in place (visibility/operations.py:86-105).  This is
+    the stand-alone host form for callers that already hold both cubes in host memory; inside the
+    major cycle the subtraction is fused into the degridder (``skymodel_residual`` /
+    ``imaging.residual_ng``) and never leaves the device."""
+    assert vis.vis.shape == model_vis.vis.shape, (
+        f"Observed {vis.vis.shape} and model visibilities {model_vis.vis.shape} have different shapes.")
+    if inplace:
+        vis["vis"].data = vis["vis"].data - model_vis["vis"].data
+        return vis
+    residual_vis = vis.copy(deep=True)
+    residual_vis["vis"].data = residual_vis["vis"].data - model_vis["vis"].data
+    return residual_vis

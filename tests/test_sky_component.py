@@ -59,3 +59,21 @@ def test_non_sin_raster_uses_the_phase_centre():
     beam.image_acc.wcs.wcs.ctype[0] = "AZELGEO long"
     got = apply_beam_to_skycomponent([c], beam, phasecentre=pc)[0].flux
     assert np.array_equal(got, want)
+
+
+def test_subtract_visibility():
+    from ska_sdp_func_python_b200.skymodel_imaging import subtract_visibility
+    rng = np.random.default_rng(2)
+    shape = (2, 3, 4, 1)
+    mk = lambda: mm.Visibility(rng.normal(size=shape) + 1j * rng.normal(size=shape), rng.normal(size=(2, 3, 3)),  # noqa: E731
+                               1e8 + 1e6 * np.arange(4), mm.SkyCoord.from_deg(0, -30), mm.PolarisationFrame("stokesI"))
+    a, b = mk(), mk()
+    a0 = a["vis"].data.copy()
+    r = subtract_visibility(a, b)
+    assert r is not a and np.array_equal(r["vis"].data, a0 - b["vis"].data) and np.array_equal(a["vis"].data, a0)
+    r2 = subtract_visibility(a, b, inplace=True)
+    assert r2 is a and np.array_equal(a["vis"].data, a0 - b["vis"].data)
+    c = mm.Visibility(np.zeros((2, 3, 5, 1), dtype=complex), rng.normal(size=(2, 3, 3)), 1e8 + 1e6 * np.arange(5),
+                      mm.SkyCoord.from_deg(0, -30), mm.PolarisationFrame("stokesI"))
+    with pytest.raises(AssertionError):
+        subtract_visibility(a, c)
