@@ -34,13 +34,16 @@
 #ifndef B2G_MINB_DEGRID
 #define B2G_MINB_DEGRID 6
 #endif
+#ifndef B2G_CHUNK
+#define B2G_CHUNK 256
+#endif
 
 namespace b2g {
 
 namespace {
 
 constexpr int kWarps = 4;        // warps per block
-constexpr int kChunk = 256;      // samples per warp (multiple of 32)
+constexpr int kChunk = B2G_CHUNK;  // samples per warp (multiple of 32)
 constexpr unsigned kFull = 0xffffffffu;
 
 // resident blocks per SM the register allocation is asked to allow (fp32 kernels only; the
