@@ -21,7 +21,12 @@ def main():
     ap.add_argument("--reps", type=int, default=4)
     ap.add_argument("--pageable", action="store_true")
     ap.add_argument("--verbosity", type=int, default=0)
+    ap.add_argument("--chunk-log2", type=int, default=0,
+                    help="samples per host-streaming chunk = 2^this (default: the library's 2^24)")
     a = ap.parse_args()
+    if a.chunk_log2:
+        from ska_sdp_func_python_b200 import _lib
+        _lib.check(_lib.lib().b2g_set_host_chunk_samples(1 << a.chunk_log2))
     obs = simulate.observation(a.config, nchan=a.nchan)
     uvw = simulate.flip_for_gridder(obs["uvw"])
     freq = obs["freq"]
