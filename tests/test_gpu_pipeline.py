@@ -71,7 +71,7 @@ def test_image_clean_predict_residual_restore(scene, algorithm, extra):
     beam = restored.attrs["clean_beam"]
     assert 0 < beam["bmin"] <= beam["bmaj"]
     m["restored_err"] = max(abs(r[iy, ix] - flux) / flux for ix, iy, flux in pix)
-    limits = {"flux_err": 0.05, "resid_all": 0.03, "resid_inner": 0.01, "vis_err": 0.08,
+    limits = {"flux_err": 0.08, "resid_all": 0.03, "resid_inner": 0.01, "vis_err": 0.08,
               "resid2_inner": 0.02, "resid2_vs_clean": 0.02, "restored_err": 0.06}
     # measured on B200: hogbom flux 1.6 %, residual 1.4 % (0.5 % inner), vis 3.9 %, restored 0.6 %;
     # msclean flux 4.7 % (5 x 5 box against a 3-pixel scale), restored 3.7 %
