@@ -154,6 +154,13 @@ int b2g_sumwt(const void *wgt, int dtype, int space, int64_t n, double *out, voi
  * Default 2^24; 0 disables chunking.  Process-wide setting, applies to plans created later. */
 int b2g_set_host_chunk_samples(int64_t nsamples);
 
+/* Upper limit on the number of origin w-planes a plan grids per slab (0 = default: sized from
+ * free device memory, at most 8 once the planes no longer fit at once).  With a small limit a
+ * small problem runs the multi-slab ring-buffer path (slabs of `nplanes` origin planes in a
+ * wrapping ring of nplanes + W - 1 slots) that the 8192^2 / 16384^2 configurations take; the
+ * parity tests use it.  Process-wide setting, applies to plans created later. */
+int b2g_set_max_slab_planes(int nplanes);
+
 /* Host-side kernel mathematics, exported so that tests can check them without a GPU.
  * b2g_kernel_select: choose (W, sigma) for epsilon; returns 0 and fills
  *   out = {W, sigma, beta, e0, eps_kernel}.

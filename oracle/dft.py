@@ -108,6 +108,27 @@ def dirty2ms_samples(uvw, freq, dirty, wgt, pixsize_x, pixsize_y, do_wstacking, 
     return out
 
 
+def dirty2ms_samples_sparse(uvw, freq, px, py, flux, npix_x, npix_y, pixsize_x, pixsize_y,
+                             do_wstacking, rows, chans):
+    """ms[rows[k], chans[k]] of a model image that is zero except dirty[px[j], py[j]] += flux[j]
+    (same sum as oracle_dirty2ms_samples restricted to the non-zero pixels; for images too large
+    to scan per sample).  numpy, fp64, phase reduced to [-1/2, 1/2] turns."""
+    uvw = np.asarray(uvw, dtype=np.float64)
+    fl = np.asarray(freq, dtype=np.float64)[np.asarray(chans)] / C_M_S
+    x = (np.asarray(px, dtype=np.float64) - npix_x // 2) * pixsize_x
+    y = (np.asarray(py, dtype=np.float64) - npix_y // 2) * pixsize_y
+    r2 = x * x + y * y
+    if do_wstacking:
+        nm1 = -r2 / (np.sqrt(1.0 - r2) + 1.0)
+    else:
+        nm1 = np.zeros_like(r2)
+    n = nm1 + 1.0
+    u, v, w = (uvw[np.asarray(rows), i] * fl for i in range(3))
+    ph = u[:, None] * x[None, :] + v[:, None] * y[None, :] - w[:, None] * nm1[None, :]
+    ph -= np.rint(ph)
+    return np.sum((np.asarray(flux) / n)[None, :] * np.exp(-2j * np.pi * ph), axis=1)
+
+
 def dirty2ms(uvw, freq, dirty, wgt, pixsize_x, pixsize_y, do_wstacking):
     """Full ms [nrow, nchan] by direct summation."""
     nrow, nchan = uvw.shape[0], np.asarray(freq).shape[0]

@@ -36,6 +36,9 @@ thread_local std::string g_err;
 // of about this many samples, overlapped with gridding / degridding (0 disables chunking).
 std::atomic<long long> g_host_chunk_samples{1ll << 24};
 constexpr int kMaxChunks = 32;
+// Upper limit on the origin w-planes per slab (0 = sized from free memory): lets a small
+// geometry run the multi-slab ring-buffer path that the large configurations take.
+std::atomic<int> g_max_slab_planes{0};
 
 int fail(const char *fmt, ...)
 {
@@ -632,6 +635,7 @@ extern "C" int b2g_plan_create_sel(b2g_plan **plan, int64_t nrow, int64_t nchan,
         const int all = p->nplanes - p->W + 1;
         gs = (all <= 24 && gs >= all) ? all : std::max(1, std::min(gs, 8));
         gs = std::min(gs, all);
+        if (const int cap = g_max_slab_planes.load(); cap > 0) gs = std::min(gs, cap);
         p->gs = gs;
         p->nslots = gs + p->W - 1;
         p->nslabs = (p->nplanes - p->W + 1 + gs - 1) / gs;
@@ -1359,6 +1363,13 @@ extern "C" int b2g_set_host_chunk_samples(int64_t nsamples)
 {
     g_err.clear();
     g_host_chunk_samples.store(nsamples > 0 ? (long long)nsamples : 0ll);
+    return 0;
+}
+
+extern "C" int b2g_set_max_slab_planes(int nplanes)
+{
+    g_err.clear();
+    g_max_slab_planes.store(nplanes > 0 ? nplanes : 0);
     return 0;
 }
 

@@ -1,0 +1,246 @@
+"""Parity on the geometries of every BASELINE.json configuration (C1 .. C5) and on
+the multi-slab ring-buffer path that the wide-field ones take.
+
+C1 runs at its full size; C3 / C4 / C5 keep the configuration's layout, image size, w-range
+(C4: the w rescale to 128 reference planes), epsilon and precision but a subset of times / channels,
+so that the exact-DFT oracle finishes in seconds.  The bound is north_star's: max-abs error
+<= 10 * epsilon of the image / visibility peak in fp32, <= 1e-10 of the peak in fp64 (the oracle is
+evaluated at sampled pixels / samples incl. the image corners, where the w term and the gridding
+correction are largest).  The reference analogue: tests/imaging/test_imaging_ng.py:20-57 (LOWBD2,
+256^2) and tests/conftest.py:70-110.
+"""
+import numpy as np
+import pytest
+
+from conftest import make_case, rel_l2, rel_max
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def wg(built):
+    import torch
+    assert torch.cuda.is_available(), "the gpu-marked tests need a CUDA device"
+    from ska_sdp_func_python_b200 import wgridder
+    return wgridder
+
+
+@pytest.fixture()
+def slab_cap(built):
+    """Sets the process-wide cap on origin planes per slab; always restored."""
+    def set_cap(n):
+        assert built.b2g_set_max_slab_planes(int(n)) == 0
+    yield set_cap
+    built.b2g_set_max_slab_planes(0)
+
+
+# ---------------------------------------------------------------------------------------------
+# multi-slab ring buffer (plan.cu: nslabs > 1, wrapping ring of gs + W - 1 slots)
+# ---------------------------------------------------------------------------------------------
+DEEP = (2500, 2, 128, 112, 2.0e-3, 2.2e-3, 2.0)   # ~25 origin planes at sigma 1.5
+_DEEP = {}
+
+
+def _deep():
+    from oracle import dft as odft
+    if not _DEEP:
+        nrow, nchan, npx, npy, psx, psy, wfrac = DEEP
+        uvw, freq, ms, wgt = make_case(211, nrow, nchan, npx, npy, psx, psy, wfrac)
+        rng = np.random.default_rng(17)
+        model = np.zeros((npx, npy))
+        model[rng.integers(0, npx, 40), rng.integers(0, npy, 40)] = rng.uniform(1, 2, 40)
+        model[0, 0], model[npx - 1, npy - 1], model[0, npy - 1] = 1.0, -1.0, 0.5
+        _DEEP.update(uvw=uvw, freq=freq, ms=ms, wgt=wgt, model=model,
+                     d=odft.ms2dirty(uvw, freq, ms, wgt, npx, npy, psx, psy, True),
+                     v=odft.dirty2ms(uvw, freq, model, wgt, psx, psy, True))
+    return _DEEP
+
+
+@pytest.mark.parametrize("cap", [1, 3, 0])
+@pytest.mark.parametrize("prec,eps", [("single", 1e-5), ("double", 1e-7), ("double", 1e-12)])
+@pytest.mark.parametrize("algo", ["simple", "warprun"])
+def test_multi_slab_ring_parity(wg, slab_cap, cap, prec, eps, algo):
+    """invert / predict / residual against the exact DFT with 1 and 3 origin planes per slab
+    (8 .. 25 slabs, the ring wraps many times; W = 16 at eps = 1e-12 runs the multi-pass wide
+    kernels) and with the default sizing."""
+    c = _deep()
+    nrow, nchan, npx, npy, psx, psy, _ = DEEP
+    cdt, rdt = (np.complex128, np.float64) if prec == "double" else (np.complex64, np.float32)
+    slab_cap(cap)
+    code = wg.ALGO_SIMPLE if algo == "simple" else wg.ALGO_WARPRUN
+    with wg.Plan(c["uvw"], c["freq"], npx, npy, psx, psy, eps, True, precision=prec, algo=code) as plan:
+        info = plan.info()
+        norigin = info["nplanes"] - info["W"] + 1
+        assert norigin >= 12, info
+        if cap:
+            assert info["planes_per_slab"] == cap and info["nslabs"] == -(-norigin // cap) >= 3
+        d = plan.invert(c["ms"].astype(cdt), c["wgt"].astype(rdt))
+        v = plan.predict(c["model"].astype(rdt), c["wgt"].astype(rdt))
+        res = plan.residual(c["model"].astype(rdt), c["ms"].astype(cdt), c["wgt"].astype(rdt))
+    assert rel_l2(d, c["d"]) < eps and rel_l2(v, c["v"]) < eps
+    bound = 1e-10 if (prec == "double" and eps <= 1e-12) else 10 * eps
+    assert rel_max(d, c["d"]) < bound and rel_max(v, c["v"]) < bound
+    # residual = invert(ms - predict(model)) in one call; same plan, same slabs
+    from oracle import dft as odft
+    if cap == 3 and algo == "warprun":
+        rref = odft.ms2dirty(c["uvw"], c["freq"], c["ms"] - c["v"] / np.where(c["wgt"] == 0, 1, c["wgt"]),
+                             c["wgt"], npx, npy, psx, psy, True)
+        assert rel_l2(res, rref) < 3 * eps
+
+
+@pytest.mark.parametrize("prec,eps,tol", [("double", 1e-9, 2e-11), ("single", 1e-4, 5e-5)])
+def test_multi_slab_adjointness(wg, slab_cap, prec, eps, tol):
+    c = _deep()
+    nrow, nchan, npx, npy, psx, psy, _ = DEEP
+    rng = np.random.default_rng(3)
+    cdt, rdt = (np.complex128, np.float64) if prec == "double" else (np.complex64, np.float32)
+    x = np.zeros((npx, npy), dtype=rdt)
+    x[npx // 8:-npx // 8, npy // 8:-npy // 8] = rng.normal(size=(npx - 2 * (npx // 8), npy - 2 * (npy // 8)))
+    y = (rng.normal(size=c["ms"].shape) + 1j * rng.normal(size=c["ms"].shape)).astype(cdt)
+    slab_cap(2)
+    with wg.Plan(c["uvw"], c["freq"], npx, npy, psx, psy, eps, True, precision=prec) as plan:
+        assert plan.info()["nslabs"] >= 3
+        Ax, Ahy = plan.predict(x), plan.invert(y)
+    lhs = np.vdot(y.astype(np.complex128), Ax.astype(np.complex128)).real
+    rhs = np.vdot(Ahy.astype(np.float64), x.astype(np.float64))
+    assert abs(lhs - rhs) < tol * max(abs(lhs), abs(rhs))
+
+
+# ---------------------------------------------------------------------------------------------
+# the BASELINE.json configurations
+# ---------------------------------------------------------------------------------------------
+def _sample_pixels(rng, npix, extra):
+    """Sampled pixels: all four corners, the centre, the rim mid-points and random ones."""
+    fixed = [(0, 0), (0, npix - 1), (npix - 1, 0), (npix - 1, npix - 1), (npix // 2, npix // 2),
+             (0, npix // 2), (npix // 2, npix - 1)]
+    px = np.concatenate([[a for a, _ in fixed], rng.integers(0, npix, extra)])
+    py = np.concatenate([[b for _, b in fixed], rng.integers(0, npix, extra)])
+    return px.astype(np.int64), py.astype(np.int64)
+
+
+def _sparse_model(rng, npix, nsrc):
+    ix = rng.integers(npix // 16, npix - npix // 16, nsrc)
+    iy = rng.integers(npix // 16, npix - npix // 16, nsrc)
+    ix[0], iy[0] = npix // 2, npix // 2
+    ix[1], iy[1] = 3, npix - 5            # next to a corner: largest w term and correction
+    flux = rng.uniform(0.5, 2.0, nsrc)
+    return ix, iy, flux
+
+
+def _check_config(wg, obs, prec, eps, ws, bound, nplanes_min=0, nslabs_min=1, npts=57, nsamp=300):
+    """invert of random samples at sampled pixels and predict of a sparse model at sampled
+    (row, chan), both against the exact DFT; returns the plan info."""
+    from oracle import dft as odft
+    from ska_sdp_func_python_b200 import simulate
+    uvw = simulate.flip_for_gridder(obs["uvw"])
+    freq, npix, cell = obs["freq"], obs["npix"], obs["cellsize"]
+    nrow, nchan = uvw.shape[0], len(freq)
+    rng = np.random.default_rng(23)
+    cdt, rdt = (np.complex128, np.float64) if prec == "double" else (np.complex64, np.float32)
+    ms = (rng.standard_normal((nrow, nchan)) + 1j * rng.standard_normal((nrow, nchan))).astype(cdt)
+    wgt = np.ones((nrow, nchan), dtype=rdt)
+    wgt[obs["auto"]] = 0
+    ix, iy, flux = _sparse_model(rng, npix, 12)
+    model = np.zeros((npix, npix), dtype=rdt)
+    np.add.at(model, (ix, iy), flux.astype(rdt))
+    with wg.Plan(uvw, freq, npix, npix, cell, cell, eps, ws, precision=prec) as p:
+        info = p.info()
+        assert info["nplanes"] >= nplanes_min and info["nslabs"] >= nslabs_min, info
+        d = p.invert(ms, wgt)
+        v = p.predict(model)
+    px, py = _sample_pixels(rng, npix, npts - 7)
+    dref = odft.ms2dirty_points(uvw, freq, ms, wgt.astype(np.float64), npix, npix, cell, cell, ws, px, py)
+    # the image peak of random samples is not among the sampled pixels: use the (larger) exact
+    # rms-based scale only through the sampled maximum, which makes the bound tighter, not looser
+    assert np.abs(d[px, py] - dref).max() < bound * np.abs(dref).max(), info
+    rows = rng.integers(0, nrow, nsamp)
+    chans = rng.integers(0, nchan, nsamp)
+    vref = odft.dirty2ms_samples_sparse(uvw, freq, ix, iy, model[ix, iy].astype(np.float64), npix, npix,
+                                        cell, cell, ws, rows, chans)
+    assert np.abs(v[rows, chans] - vref).max() < bound * np.abs(vref).max(), info
+    return info
+
+
+@pytest.mark.parametrize("ws", [False, True])
+def test_c1_full_size(wg, ws):
+    """C1 (LOW-core, 2 times, 5 channels, 512^2, cellsize 5e-4, fp64, eps = 1e-12), whole workload;
+    the invert side is checked on a dense 48 x 48 block + corners + 2000 random pixels, the predict
+    side on 2000 samples of a dense (every pixel non-zero) 512^2 model."""
+    from oracle import dft as odft
+    from ska_sdp_func_python_b200 import simulate
+    obs = simulate.observation("C1")
+    uvw = simulate.flip_for_gridder(obs["uvw"])
+    freq, npix, cell = obs["freq"], obs["npix"], obs["cellsize"]
+    nrow, nchan = uvw.shape[0], len(freq)
+    assert (npix, nchan, nrow) == (512, 5, 27722) and cell == 5e-4
+    rng = np.random.default_rng(31)
+    ms = rng.standard_normal((nrow, nchan)) + 1j * rng.standard_normal((nrow, nchan))
+    wgt = rng.uniform(0.5, 1.5, (nrow, nchan))
+    wgt[obs["auto"]] = 0
+    model = rng.standard_normal((npix, npix))
+    with wg.Plan(uvw, freq, npix, npix, cell, cell, 1e-12, ws, precision="double") as p:
+        d, v = p.invert(ms, wgt), p.predict(model, wgt)
+    bx, by = np.meshgrid(np.arange(232, 280), np.arange(10, 58), indexing="ij")
+    px, py = _sample_pixels(rng, npix, 2000)
+    px, py = np.concatenate([px, bx.ravel()]), np.concatenate([py, by.ravel()])
+    dref = odft.ms2dirty_points(uvw, freq, ms, wgt, npix, npix, cell, cell, ws, px, py)
+    assert rel_l2(d[px, py], dref) < 1e-12
+    assert np.abs(d[px, py] - dref).max() < 1e-10 * np.abs(dref).max()
+    rows, chans = rng.integers(0, nrow, 2000), rng.integers(0, nchan, 2000)
+    vref = odft.dirty2ms_samples(uvw, freq, model, wgt, cell, cell, ws, rows, chans)
+    assert rel_l2(v[rows, chans], vref) < 1e-12
+    assert np.abs(v[rows, chans] - vref).max() < 1e-10 * np.abs(vref).max()
+
+
+def test_c3_mid_geometry(wg):
+    """C3: MID layout, 950-1050 MHz, 4096^2, fp32 eps = 1e-5 (6 of 120 times, 8 of 256 channels)."""
+    from ska_sdp_func_python_b200 import simulate
+    obs = simulate.observation("C3", nchan=8, ntimes=6)
+    assert obs["npix"] == 4096
+    _check_config(wg, obs, "single", 1e-5, True, 1e-4)
+
+
+def test_c4_wide_field_geometry(wg):
+    """C4: LOW-full, 120-180 MHz, 8192^2 with the w rescale to 128 reference planes, fp32
+    eps = 1e-5 (2 of 30 times, 12 of 1024 channels spanning the whole band): the plan needs more
+    than 24 origin planes, i.e. the multi-slab ring path with its default sizing."""
+    from ska_sdp_func_python_b200 import simulate
+    obs = simulate.observation("C4", nchan=12, ntimes=2)
+    assert obs["npix"] == 8192 and obs["nplanes"] == 128
+    info = _check_config(wg, obs, "single", 1e-5, True, 1e-4, nplanes_min=100, nslabs_min=3)
+    assert info["nu"] >= 12288 * 0.9
+
+
+def test_c5_psf_fp64(wg):
+    """C5: 16384^2, fp64, eps = 1e-10, dopsf-style unit visibilities with natural weights (2 of 30
+    times, 2 of 64 channels): PSF peak == sumwt to 1e-9, the peak is the image maximum, sampled
+    pixels and predicted samples within 1e-9 (10 eps) of the exact DFT."""
+    from oracle import dft as odft
+    from ska_sdp_func_python_b200 import simulate
+    obs = simulate.observation("C5", nchan=2, ntimes=2)
+    uvw = simulate.flip_for_gridder(obs["uvw"])
+    freq, npix, cell = obs["freq"], obs["npix"], obs["cellsize"]
+    assert npix == 16384
+    nrow, nchan = uvw.shape[0], len(freq)
+    wgt = np.ones((nrow, nchan))
+    wgt[obs["auto"]] = 0
+    ones = np.ones((nrow, nchan), dtype=np.complex128)
+    rng = np.random.default_rng(41)
+    ix, iy, flux = _sparse_model(rng, npix, 12)
+    with wg.Plan(uvw, freq, npix, npix, cell, cell, 1e-10, True, precision="double") as p:
+        info = p.info()
+        assert info["nslabs"] >= 3, info
+        psf = p.invert(ones, wgt)
+        model = np.zeros((npix, npix))
+        np.add.at(model, (ix, iy), flux)
+        v = p.predict(model)
+        del model
+    sumwt = float(wgt.sum())
+    assert abs(psf[npix // 2, npix // 2] / sumwt - 1.0) < 1e-9
+    assert psf.max() == psf[npix // 2, npix // 2]
+    px, py = _sample_pixels(rng, npix, 41)
+    dref = odft.ms2dirty_points(uvw, freq, ones, wgt, npix, npix, cell, cell, True, px, py)
+    assert np.abs(psf[px, py] - dref).max() < 1e-9 * sumwt
+    rows, chans = rng.integers(0, nrow, 300), rng.integers(0, nchan, 300)
+    vref = odft.dirty2ms_samples_sparse(uvw, freq, ix, iy, flux, npix, npix, cell, cell, True, rows, chans)
+    assert np.abs(v[rows, chans] - vref).max() < 1e-9 * np.abs(vref).max()
