@@ -5,12 +5,27 @@
     python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
     python bench.py --impl reference --gpus N --steps K ...  # CPU arm (oracle port), rank 0 only
 
-One *step* = one invert (ms2dirty, gridding) + one predict (dirty2ms, degridding) of one
-polarisation plane over the rank's whole sample set.  Workload at N=1: BASELINE.json
-configs[1] ("C2": SKA-LOW full array, 64 channels, npixel=2048, do_wstacking=True,
-epsilon=1e-5, fp32).  At N>1 every rank holds its own 64-channel block of an N*64-channel band
-(weak scaling, channel sharding) and the step contains the one NCCL all-reduce of the dirty
-image + sumwt (invert) and the broadcast of the model image (predict).
+One *step* = one invert (ms2dirty: gridding, per-plane FFT, w-screens, correction) + one predict
+(dirty2ms, the adjoint) of one polarisation plane over the WHOLE observation.
+
+Workload (default): BASELINE.json configs[3] = SURVEY.md 8(d) "C4", the headline: SKA-LOW full
+array, 30 times x 131 328 baselines x 1024 channels 120-180 MHz = 4.03e9 samples, npixel = 8192,
+w rescaled to 128 reference planes, MFS, epsilon = 1e-5, fp32.  It fits one B200 (about 150 of
+180 GB).  `--config C2` (configs[1]: 64 channels, npixel 2048) is the small dense workload.
+
+  N = 1 : one plan over all samples.
+  N > 1 : STRONG scaling of the same observation by w-plane sharding (SURVEY.md 8e option 2,
+          distributed.py): rank r owns the samples of its |w| interval (cost-balanced thresholds,
+          re-balanced once from measured stage times inside the warm-up), builds a plan over that
+          selection only, and the step is local gridding -> ONE NCCL all-reduce of the dirty image
+          + sumwt -> normalise -> local degridding of the (now replicated) image.
+
+`value` = samples of the observation / max-over-ranks device time per step, inputs resident in
+HBM, plan (sort) reused across steps.  `e2e` = the same metric through the drop-in API,
+imaging.invert_ng + imaging.predict_ng on Visibility / Image objects holding PAGEABLE complex128 /
+float64 / int arrays as the reference's ng.py receives them, all host<->device copies, the plan and
+the result download inside the timed region (N > 1: every rank holds its own channel block and
+calls invert_ng(shard="channel") / predict_ng(shard="channel")).
 
 Prints ONE JSON line (rank 0).  Keys: see DESIGN.md "Measurement".
 """
@@ -29,6 +44,7 @@ sys.path.insert(0, ROOT)
 
 METRIC = "visibilities/sec (invert_ng+predict_ng)"
 UNIT = "vis/s"
+KERNEL_FILE = os.path.join(ROOT, "profiles", "plan_kernels.json")
 
 
 def _peaks():
@@ -106,104 +122,168 @@ def _env_ranks():
             int(os.environ.get("WORLD_SIZE", "1")))
 
 
-def make_geometry(config, world, rank, nchan_per_rank=None):
-    """uvw (flipped to the gridder convention), the rank's frequency block, auto mask."""
+def make_geometry(config):
+    """The observation of `config`: uvw flipped to the gridder convention, frequencies, auto mask."""
     from ska_sdp_func_python_b200 import simulate
-    from ska_sdp_func_python_b200.distributed import shard_bounds
-    base = simulate.CONFIGS[config]
-    ncr = nchan_per_rank or base["nchan"]
-    obs = simulate.observation(config, nchan=ncr * world)
-    lo, hi = shard_bounds(ncr * world, world, rank)
+    obs = simulate.observation(config)
     uvw = simulate.flip_for_gridder(obs["uvw"])
-    return dict(obs=obs, uvw=uvw, freq=np.ascontiguousarray(obs["freq"][lo:hi]),
-                auto=obs["auto"], chan_lo=lo, chan_hi=hi, nchan_total=ncr * world)
+    return dict(obs=obs, uvw=uvw, freq=np.ascontiguousarray(obs["freq"]), auto=obs["auto"])
 
 
 def alg_bytes_launch(direction, nsamp, nrow, nchan, nplanes_launch, nu, nv, csize):
-    """Algorithmic HBM bytes of one gridding / degridding launch (DESIGN.md "Kernels"):
-    every sample (+ weight for gridding) once, uvw rows once, the w-planes of the launch once."""
+    """Algorithmic HBM bytes of the gridding / degridding launches of one direction (DESIGN.md
+    "Kernels"): every sample (+ weight for gridding) once, uvw rows once, every w-plane once."""
     rsize = csize // 2
     b_in = nsamp * (csize + (rsize if direction == "grid" else 0)) + nrow * 24 + nchan * 8
     return b_in + nplanes_launch * nu * nv * csize
 
 
+def alg_bytes_planes(nplanes, npix, nu, nv, csize):
+    """SURVEY.md 8(d) B_grid: per w-plane one grid write, two FFT passes (read + write each), the
+    cropped read by the screen and the read-modify-write of the image accumulator."""
+    rsize = csize // 2
+    return nplanes * (nu * nv * csize * (5 + (npix / nu) * (npix / nv)) + 2 * npix * npix * rsize)
+
+
 def alg_bytes_step(nsamp, nrow, nchan, npix, nplanes, nu, nv, csize):
     """SURVEY.md section 8(d) B_alg for invert + predict of one polarisation plane."""
     rsize = csize // 2
-    b_grid = nplanes * (nu * nv * csize * (5 + (npix / nu) * (npix / nv)) + 2 * npix * npix * rsize)
+    b_grid = alg_bytes_planes(nplanes, npix, nu, nv, csize)
     inv = nsamp * (csize + rsize) + nrow * 24 + nchan * 8 + npix * npix * rsize + b_grid
     pre = nsamp * csize + nrow * 24 + nchan * 8 + npix * npix * rsize + b_grid
     return inv + pre
 
 
+def workload_name(config):
+    from ska_sdp_func_python_b200 import simulate
+    c = simulate.CONFIGS[config]
+    planes = f", w rescaled to {c['nplanes']} reference planes" if c.get("nplanes") else ""
+    return (f"{config}: SKA-{c['layout']} synthetic, {c['ntimes']} times, {c['nchan']} channels "
+            f"{c['f0'] / 1e6:.0f}-{c['f1'] / 1e6:.0f} MHz, npixel={c['npix']}{planes}, MFS, "
+            f"do_wstacking=True, epsilon={c['epsilon']:g}, {c['precision']} precision")
+
+
 # --------------------------------------------------------------------------------------
 # CPU arm: the oracle port (oracle/wgridder_cpu.*) on the host cores, bounded sample
 # --------------------------------------------------------------------------------------
+def plan_kernel(config):
+    """(W, sigma, beta, e0) the GPU plan uses for `config`, as recorded by the GPU arm in
+    profiles/plan_kernels.json (so that the CPU arm needs nothing of the product library); None
+    lets the port choose its own."""
+    try:
+        with open(KERNEL_FILE) as fh:
+            k = json.load(fh).get(config)
+        return dict(W=int(k["W"]), sigma=float(k["sigma"]), beta=float(k["beta"]), e0=float(k["e0"]))
+    except Exception:  # noqa: BLE001
+        return None
+
+
 def cpu_arm(geo, epsilon, kernel, target_seconds, steps=1, warmup=0, log=None):
-    """Times invert + predict of the CPU restatement on every k-th row of the workload.
-    Returns (vis_per_s, seconds_per_step, description, cores)."""
+    """Times invert + predict of the CPU restatement on a BOUNDED SAMPLE of the workload: every
+    `rs`-th row (all channels) and every `ps`-th w-plane, sized by two pilots so that one step
+    takes about `target_seconds`.  The throughput of the full workload is extrapolated with the
+    two-component model the pilots measure,
+        t_full = t_rows * rs + [A * nplanes + (t_planes - A * k) * rs * nplanes / k] + t_fixed
+    (t_rows: bucket pass + final weighting, proportional to rows; A: image-side time per plane,
+    FFT + w-screen, independent of the samples; the rest of the plane loop is gridding /
+    degridding, proportional to the samples that touch the k processed planes; t_fixed: the
+    gridding-correction image).  With rs = ps = 1 (small workloads) nothing is extrapolated.
+    Returns (vis_per_s, seconds_per_step actually spent, description, cores, details)."""
     from oracle import wgridder_cpu as wc
     cores = os.cpu_count() or 1
     obs = geo["obs"]
     uvw, freq = geo["uvw"], geo["freq"]
     npix, cell = obs["npix"], obs["cellsize"]
-    nrow = uvw.shape[0]
+    nrow, nchan = uvw.shape[0], len(freq)
     rng = np.random.default_rng(7)
+    say = log or (lambda s: None)
 
-    def run(stride, reps):
-        u = np.ascontiguousarray(uvw[::stride])
-        auto = geo["auto"][::stride]
+    def run(rs, ps, off=0):
+        u = np.ascontiguousarray(uvw[off::rs])
+        auto = geo["auto"][off::rs]
         n = u.shape[0]
-        ms = (rng.standard_normal((n, len(freq))) + 1j * rng.standard_normal((n, len(freq))))
-        wgt = np.ones((n, len(freq)))
+        ms = np.empty((n, nchan), dtype=np.complex128)
+        ms.real = rng.standard_normal((n, nchan), dtype=np.float32)
+        ms.imag = rng.standard_normal((n, nchan), dtype=np.float32)
+        wgt = np.ones((n, nchan))
         wgt[auto] = 0.0
-        best = None
-        for _ in range(reps):
-            t0 = time.perf_counter()
-            plan = wc.CpuPlan(u, freq, npix, npix, cell, cell, epsilon, True, nthreads=cores,
-                              kernel=kernel)
-            dirty = plan.invert(ms, wgt)
-            plan.predict(dirty, None)
-            plan.close()
-            dt = time.perf_counter() - t0
-            best = dt if best is None else min(best, dt)
-        return n * len(freq), best
+        t0 = time.perf_counter()
+        plan = wc.CpuPlan(u, freq, npix, npix, cell, cell, epsilon, True, nthreads=cores,
+                          kernel=kernel)
+        planes = list(range(min(ps // 2, plan.nplanes - 1), plan.nplanes, ps))
+        tb0 = time.perf_counter()
+        plan._bucket((ms != 0) & (wgt != 0))
+        t_rows = time.perf_counter() - tb0
+        tc0 = time.perf_counter()
+        plan.correction()
+        t_fixed = time.perf_counter() - tc0 + (tb0 - t0)
+        dirty = plan.invert(ms, wgt, planes=planes)
+        plan.predict(dirty, None, planes=planes)
+        t_all = time.perf_counter() - t0
+        nplanes = plan.nplanes
+        plan.close()
+        # invert / predict repeat the bucket pass themselves (3 in total: count them as rows work)
+        t_rows *= 3.0
+        t_planes = max(t_all - t_rows - t_fixed, 0.0)
+        return dict(n=n * nchan, t=t_all, t_rows=t_rows, t_planes=t_planes, t_fixed=t_fixed,
+                    k=len(planes), nplanes=nplanes)
 
-    # pilot on a thin sample to size the real one
-    stride = max(1, nrow // 20000)
-    ns, dt = run(stride, 1)
-    if log:
-        log(f"cpu pilot: stride {stride}, {ns} samples, {dt:.2f} s")
-    # time ~ fixed (FFT, planes) + per-sample part; second pilot separates the two
-    stride2 = max(1, stride // 4)
-    ns2, dt2 = run(stride2, 1)
-    per = max((dt2 - dt) / max(ns2 - ns, 1), 1e-12)
-    fixed = max(dt - per * ns, 0.0)
-    want = max(target_seconds - fixed, 0.2 * target_seconds) / per
-    stride3 = int(max(1, np.floor(nrow * len(freq) / want)))
-    stride3 = min(stride3, stride2)
+    # pilot 1: very thin rows, one plane -> A (image-side time per plane: FFT + w-screen)
+    rs0 = max(1, nrow // 4000)
+    p1 = run(rs0, 10 ** 9)
+    A = p1["t_planes"]
+    nplanes = p1["nplanes"]
+    say(f"cpu pilot 1: rows/{rs0}, 1 of {nplanes} planes: {p1['t']:.2f} s, plane {A:.2f} s")
+    # planes: at most half of the budget on the image side
+    k = int(max(1, min(nplanes, np.floor(0.5 * target_seconds / max(A, 1e-3)))))
+    ps = int(max(1, np.ceil(nplanes / k)))
+    # pilot 2: thin rows over those planes -> first estimate of the per-sample costs
+    rs1 = max(1, nrow // 40000)
+    p2 = run(rs1, ps)
+    per_rows = p2["t_rows"] / max(p2["n"], 1)
+    per_samp = max(p2["t_planes"] - A * p2["k"], 1e-9) / max(p2["n"], 1)
+    say(f"cpu pilot 2: rows/{rs1}, planes/{ps} ({p2['k']}): {p2['t']:.2f} s")
+    budget = max(target_seconds - A * p2["k"] - p2["t_fixed"], 0.25 * target_seconds)
+    want = budget / (per_rows + per_samp)
+    rs = int(max(1, np.ceil(nrow * nchan / max(want, 1.0))))
+    # pilot 3: a quarter of the step's rows over the same planes: with the timed steps it gives the
+    # MARGINAL cost per sample (per-plane overheads such as tile set-up stay in the intercept)
+    p3 = run(4 * rs, ps) if rs * 4 < rs1 else p2
     for _ in range(warmup):
-        run(stride3, 1)
-    tot_n, tot_t = 0, 0.0
-    for _ in range(max(1, steps)):
-        n3, t3 = run(stride3, 1)
-        tot_n += n3
-        tot_t += t3
-    desc = (f"every {stride3}th row of the workload ({tot_n // max(1, steps)} of "
-            f"{nrow * len(freq)} samples), all channels, fp64, same (W, sigma) as the GPU plan, "
-            f"plan+invert+predict per step, {cores} threads")
-    return tot_n / tot_t, tot_t / max(1, steps), desc, cores
-
-
-def default_kernel(epsilon, precision):
-    """(W, sigma, beta, e0) the GPU plan picks for C2-like work, without needing a GPU: ask the
-    host-side selector of the C ABI (b2g_kernel_select)."""
-    import ctypes
-    from ska_sdp_func_python_b200 import _lib
-    out = (ctypes.c_double * 5)()
-    _lib.check(_lib.lib().b2g_kernel_select(float(epsilon), 1, _lib.F32 if precision == "single"
-                                            else _lib.F64, 2048, 2048, 2.5e8, out))
-    return dict(W=int(out[0]), sigma=out[1], beta=out[2], e0=out[3])
+        run(rs, ps)
+    acc = dict(n=0, t=0.0, t_rows=0.0, t_planes=0.0, t_fixed=0.0)
+    kk = 0
+    for i in range(max(1, steps)):
+        r = run(rs, ps, off=i % rs)
+        for key in acc:
+            acc[key] += r[key]
+        kk = r["k"]
+        nplanes = r["nplanes"]
+    m = max(1, steps)
+    n_sub = acc["n"] / m
+    t_rows, t_planes, t_fixed = acc["t_rows"] / m, acc["t_planes"] / m, acc["t_fixed"] / m
+    nfull = nrow * nchan
+    extrap = rs > 1 or ps > 1
+    if extrap and n_sub > 1.5 * p3["n"]:
+        marginal = max(t_planes - p3["t_planes"], 0.0) / (n_sub - p3["n"])   # s per sample, kk planes
+        per_plane = max(t_planes - marginal * n_sub, 0.0) / kk               # s per plane, no samples
+    else:
+        marginal = max(t_planes - A * kk, 0.0) / n_sub
+        per_plane = A
+    t_full = (t_rows * nfull / n_sub + per_plane * nplanes + marginal * nfull * nplanes / kk + t_fixed
+              if extrap else acc["t"] / m)
+    desc = (f"every {rs}th row (all {nchan} channels: {int(n_sub)} of {nfull} samples) and "
+            f"every {ps}th w-plane ({kk} of {nplanes}) of the workload per step, fp64, "
+            f"{'same (W, sigma) as the GPU plan' if kernel else 'kernel chosen by the port'}, "
+            f"plan + invert + predict per step, {cores} threads; "
+            + ("EXTRAPOLATED to the full workload: t_full = t_rows*N/n + per_plane*nplanes + "
+               "marginal*N*nplanes/k + t_fixed, marginal = d t_planes / d n between a quarter-"
+               "density pilot and the timed steps" if extrap else "whole workload, nothing extrapolated"))
+    details = dict(extrapolated=extrap, row_stride=rs, plane_stride=ps, planes_timed=kk,
+                   nplanes=nplanes, seconds_per_plane_image_side=A, seconds_per_plane_fit=per_plane,
+                   marginal_s_per_sample_per_plane_set=marginal, t_rows_s=t_rows,
+                   t_planes_s=t_planes, t_fixed_s=t_fixed, t_full_estimate_s=t_full)
+    return nfull / t_full, acc["t"] / m, desc, cores, details
 
 
 def run_reference(args):
@@ -212,22 +292,23 @@ def run_reference(args):
         return 0
     from ska_sdp_func_python_b200 import simulate
     cfg = simulate.CONFIGS[args.config]
-    geo = make_geometry(args.config, 1, 0)
-    try:
-        kernel = default_kernel(cfg["epsilon"], cfg["precision"])
-    except Exception:  # noqa: BLE001  (library not built: let the port choose)
-        kernel = None
-    v, t, desc, cores = cpu_arm(geo, cfg["epsilon"], kernel, args.cpu_seconds, steps=args.steps,
-                                warmup=min(args.warmup, 1),
-                                log=lambda s: sys.stderr.write(s + "\n"))
+    geo = make_geometry(args.config)
+    kernel = plan_kernel(args.config)
+    # the whole --steps/--warmup run stays within a few minutes
+    per_step = min(args.cpu_seconds, 300.0 / max(1, args.steps + min(args.warmup, 1)))
+    v, t, desc, cores, det = cpu_arm(geo, cfg["epsilon"], kernel, per_step, steps=args.steps,
+                                     warmup=min(args.warmup, 1),
+                                     log=lambda s: sys.stderr.write(s + "\n"))
     line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * t,
-        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic",
-        "config": {"workload": workload_name(args.config, 1), "note":
+        "config": {"workload": workload_name(args.config), "note":
                    "reference CPU path = ducc0.wgridder (not installable here); timed arm is the "
-                   "oracle port oracle/wgridder_cpu (OpenMP C + scipy/pocketfft FFT)"},
+                   "oracle port oracle/wgridder_cpu (OpenMP C + scipy/pocketfft FFT); ms_per_step "
+                   "is the time actually spent per bounded-sample step, value the throughput "
+                   "of the full workload it extrapolates to", **det},
         "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc},
         "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
     }
@@ -235,18 +316,106 @@ def run_reference(args):
     return 0
 
 
-def workload_name(config, world):
-    from ska_sdp_func_python_b200 import simulate
-    c = simulate.CONFIGS[config]
-    return (f"{config}: SKA-{c['layout']} synthetic, {c['ntimes']} times, {c['nchan']} channels"
-            f"{' per GPU' if world > 1 else ''} {c['f0'] / 1e6:.0f}-{c['f1'] / 1e6:.0f} MHz, "
-            f"npixel={c['npix']}, MFS, do_wstacking=True, epsilon={c['epsilon']:g}, "
-            f"{c['precision']} precision")
-
-
 # --------------------------------------------------------------------------------------
 # GPU arm
 # --------------------------------------------------------------------------------------
+def _e2e_leg(args, torch, dist, dev, rank, world, geo, cfg, barrier):
+    """invert_ng + predict_ng on Visibility / Image objects with pageable host arrays."""
+    from ska_sdp_func_python_b200 import imaging, simulate
+    from ska_sdp_func_python_b200 import minimal_models as mm
+    from ska_sdp_func_python_b200.distributed import shard_bounds
+    obs = geo["obs"]
+    npix, cell = obs["npix"], obs["cellsize"]
+    nt, nbl = obs["ntimes"], obs["nbaselines"]
+    freq_all = geo["freq"]
+    lo, hi = shard_bounds(len(freq_all), world, rank)
+    # host memory bound: the Visibility (c128 vis, f64 weight + imaging_weight, int64 flags) and
+    # predict's fresh copy need ~100 bytes per sample; cut the channel block if the box is small
+    try:
+        avail = os.sysconf("SC_AVPHYS_PAGES") * os.sysconf("SC_PAGE_SIZE")
+    except (ValueError, OSError):
+        avail = 64 << 30
+    per_chan = nt * nbl * 104.0
+    fit = int(max(1, (0.7 * avail / max(1, min(world, 8))) // per_chan))
+    cut = None
+    if hi - lo > fit:
+        cut = (hi - lo, fit)
+        hi = lo + fit
+    freq = np.ascontiguousarray(freq_all[lo:hi])
+    nchan = len(freq)
+    shape = (nt, nbl, nchan, 1)
+    rng = np.random.default_rng(simulate.SEED + 11 + rank)
+    vis = np.empty(shape, dtype=np.complex128)                    # pageable, as ng.py gets it
+    # unit-variance complex Gaussian samples: one random time slice, rolled for the others (the
+    # values only have to be non-zero; drawing 8e9 normals on one host thread would take minutes)
+    one = np.empty((nbl, nchan, 1), dtype=np.complex128)
+    one.real = rng.standard_normal(one.shape, dtype=np.float32)
+    one.imag = rng.standard_normal(one.shape, dtype=np.float32)
+    for t in range(nt):
+        k = (t * 7919) % nbl
+        vis[t, :nbl - k] = one[k:]
+        vis[t, nbl - k:] = one[:k]
+    del one
+    weight = np.ones(shape)
+    weight.reshape(nt * nbl, nchan)[geo["auto"]] = 0.0
+    flags = np.zeros(shape, dtype=np.int64)
+    pc = mm.SkyCoord.from_deg(15.0, -35.0)
+    bvis = mm.Visibility(vis, obs["uvw"].reshape(nt, nbl, 3), freq, pc,
+                         mm.PolarisationFrame("stokesI"), weight=weight, imaging_weight=weight,
+                         flags=flags)
+    model = mm.create_image(npix, cell, pc, frequency=[float(freq_all.mean())], nchan=1,
+                            channel_bandwidth=float(freq_all[-1] - freq_all[0]) or 1e6)
+    kw = dict(epsilon=cfg["epsilon"], do_wstacking=True, precision=cfg["precision"])
+    if world > 1:
+        kw["shard"] = "channel"
+
+    def e2e_step():
+        dirty, sumwt = imaging.invert_ng(bvis, model, dopsf=False, normalise=True, **kw)
+        out = imaging.predict_ng(bvis, dirty, **kw)
+        return float(out["vis"].data[0, 1, 0, 0].real) + float(sumwt[0, 0])
+
+    for _ in range(1):
+        e2e_step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(args.e2e_steps):
+        e2e_step()
+    barrier()
+    dt = (time.perf_counter() - t0) / args.e2e_steps
+    tt = torch.tensor([dt, float(nt * nbl * nchan)], device=dev, dtype=torch.float64)
+    if world > 1:
+        t_max = tt[:1].clone()
+        dist.all_reduce(t_max, op=dist.ReduceOp.MAX)
+        n_all = tt[1:].clone()
+        dist.all_reduce(n_all, op=dist.ReduceOp.SUM)
+        dt, nsamp_all = float(t_max.item()), float(n_all.item())
+    else:
+        nsamp_all = float(nt * nbl * nchan)
+    nloc = nt * nbl * nchan
+    single = cfg["precision"] == "single"
+    # bytes this rank moves per step: vis (c64 after the staging conversion for a single-
+    # precision plan, else c128), imaging weights f64, uvw twice, the model image; back: the
+    # dirty image (f64) and the predicted cube (c128)
+    h2d = nloc * ((8 if single else 16) + 8) + 2 * nt * nbl * 24 + npix * npix * 8
+    d2h = npix * npix * 8 + nloc * 16
+    res = {"value": nsamp_all / dt, "unit": UNIT, "ms_per_step": 1e3 * dt,
+           "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
+           "samples_per_step": int(nsamp_all),
+           "path": "imaging.invert_ng(bvis, model, normalise=True) + imaging.predict_ng(bvis, dirty) "
+                   "on minimal_models.Visibility / Image holding pageable complex128 vis, float64 "
+                   "weights, int64 flags; uvw upload, plan (uv/w sort), pinned staging, polarisation "
+                   "/ flag marshalling kernels, result download and the fresh output objects all "
+                   "inside the timed region" + ("; N > 1: every rank owns a channel block, "
+                                                "shard='channel' (one NCCL all-reduce of image + "
+                                                "sumwt, one broadcast of the model)" if world > 1 else "")}
+    if cut:
+        res["note"] = (f"host memory of this box holds {cut[1]} of the rank's {cut[0]} channels "
+                       f"through the data-model API (about 100 B of host memory per sample): the "
+                       f"e2e leg ran on that channel block of the same observation")
+    del bvis, vis, weight, flags
+    return res
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
@@ -259,53 +428,83 @@ def run_b200(args):
                          "use --impl reference for the CPU arm)")
     torch.cuda.set_device(local_rank)
     dev = torch.device("cuda", local_rank)
-    # several ranks per node: keep each rank's pinned buffers and host copies on its GPU's socket
-    from ska_sdp_func_python_b200 import _xfer
-    affinity = _xfer.bind_host_to_gpu(torch, local_rank) if world > 1 else "unchanged (one rank)"
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     cfg = simulate.CONFIGS[args.config]
-    geo = make_geometry(args.config, world, rank)
+    geo = make_geometry(args.config)
     obs, uvw, freq = geo["obs"], geo["uvw"], geo["freq"]
     nrow, nchan, npix, cell = uvw.shape[0], len(freq), obs["npix"], obs["cellsize"]
     eps, prec = cfg["epsilon"], cfg["precision"]
     csize = 8 if prec == "single" else 16
     cdt = torch.complex64 if prec == "single" else torch.complex128
     rdt = torch.float32 if prec == "single" else torch.float64
-
-    # synthetic samples: unit-variance complex Gaussian, natural weights (autos 0)
+    nsamp = nrow * nchan
+    uvw_d = torch.as_tensor(uvw, device=dev)
+    auto_d = torch.as_tensor(geo["auto"], device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
     gen = torch.Generator(device=dev)
     gen.manual_seed(simulate.SEED + 1 + rank)
-    ms_d = torch.view_as_complex(torch.randn((nrow, nchan, 2), device=dev, dtype=rdt, generator=gen))
-    wgt_d = torch.ones((nrow, nchan), device=dev, dtype=rdt)
-    wgt_d[torch.as_tensor(geo["auto"], device=dev)] = 0
-    nsamp = nrow * nchan
-    nsamp_weighted = int((wgt_d != 0).sum().item())
-    sumwt_local = float(wgt_d.sum(dtype=torch.float64).item())
-    uvw_d = torch.as_tensor(uvw, device=dev)
-    stream = torch.cuda.current_stream().cuda_stream
 
-    plan = wgridder.Plan(uvw_d, freq, npix, npix, cell, cell, eps, True, precision=prec,
-                         stream=stream)
-    info = plan.info()
+    state = {}
+
+    def build(thresholds):
+        """(Re)build this rank's sample arrays and plan.  N = 1: the whole observation."""
+        for k in ("plan", "ms", "wgt", "vis"):
+            if k in state:
+                if k == "plan":
+                    state[k].close()
+                del state[k]
+        torch.cuda.empty_cache()
+        if world > 1:
+            sel = b2dist.wplane_selection(uvw_d, freq, world, rank, npix, cell, precision=prec,
+                                          thresholds=thresholds)
+            nloc = int(sel.numel())
+            shape = (nloc,)
+            wgt = torch.ones(shape, device=dev, dtype=rdt)
+            wgt[auto_d[sel // nchan]] = 0
+        else:
+            sel, nloc, shape = None, nsamp, (nrow, nchan)
+            wgt = torch.ones(shape, device=dev, dtype=rdt)
+            wgt[auto_d] = 0
+        # synthetic samples: unit-variance complex Gaussian, natural weights (autos 0)
+        ms = torch.view_as_complex(torch.randn(shape + (2,), device=dev, dtype=rdt, generator=gen))
+        plan = wgridder.Plan(uvw_d, freq, npix, npix, cell, cell, eps, True, precision=prec,
+                             stream=stream, sel=sel)
+        del sel
+        torch.cuda.empty_cache()
+        state.update(plan=plan, ms=ms, wgt=wgt, nloc=nloc, info=plan.info(),
+                     vis=torch.empty(shape, device=dev, dtype=cdt),
+                     sumwt=float(wgt.sum(dtype=torch.float64).item()),
+                     nweighted=int((wgt != 0).sum().item()))
+        tot = torch.tensor([state["sumwt"]], device=dev, dtype=torch.float64)
+        if world > 1:
+            dist.all_reduce(tot)
+        state["sumwt_total"] = float(tot.item())     # constant over the steps: no sync per step
+
+    thr = (b2dist.wplane_thresholds(uvw_d, freq, world, npix, cell, precision=prec)
+           if world > 1 else None)
+    build(thr)
     dirty_d = torch.empty((npix, npix), device=dev, dtype=rdt)
-    vis_d = torch.empty((nrow, nchan), device=dev, dtype=cdt)
+    sw_d = torch.zeros(1, device=dev, dtype=torch.float64)
 
-    t_grid, t_degrid, launches, stage_sum = [], [], 0, {}
+    t_grid, t_degrid, stage_sum = [], [], {}
+    launches = [0]
 
     def step(record):
-        nonlocal launches
-        b2dist.invert_sharded(lambda m, w: plan.invert(m, w, out=dirty_d), ms_d, wgt_d,
-                              sumwt_local, normalise_result=True)
+        plan = state["plan"]
+        plan.invert(state["ms"], state["wgt"], out=dirty_d)
         ti = plan.timings()
         li = plan.info()["launches_last_call"]
-        b2dist.predict_sharded(lambda im: plan.predict(im, out=vis_d), dirty_d)
+        sw_d[0] = state["sumwt"]
+        b2dist.allreduce_image_sumwt(dirty_d, sw_d)       # the one collective of the step
+        b2dist.normalise(dirty_d, state["sumwt_total"])
+        plan.predict(dirty_d, out=state["vis"])
         tp = plan.timings()
         lp = plan.info()["launches_last_call"]
         if record:
             t_grid.append(ti["vis"])
             t_degrid.append(tp["vis"])
-            launches += li + lp
+            launches[0] += li + lp
             for k in ti:
                 stage_sum[k] = stage_sum.get(k, 0.0) + ti[k] + tp[k]
 
@@ -315,7 +514,31 @@ def run_b200(args):
             dist.barrier()
             torch.cuda.synchronize()
 
-    for _ in range(args.warmup):
+    rebalance = None
+    nwarm = args.warmup
+    if world > 1 and not args.no_rebalance:
+        # measured re-balancing, inside the warm-up: one recorded step under the a-priori
+        # thresholds -> per-rank gridding cost per sample and image-side cost per plane -> new
+        # thresholds, selection and plan (amortised over the major cycles that reuse the plan)
+        step(False)
+        step(True)
+        barrier()
+        t0 = time.time()
+        loc = {"n": state["nloc"], "vis": stage_sum["vis"], "planes": state["info"]["nplanes"],
+               "img": stage_sum["fft"] + stage_sum["screen"] + stage_sum["prep"]}
+        allm = [None] * world
+        dist.all_gather_object(allm, loc)
+        plane_ms = sum(m["img"] for m in allm) / max(1, sum(m["planes"] for m in allm))
+        thr = b2dist.wplane_rebalance(uvw_d, freq, world, npix, cell, thr,
+                                      [m["n"] for m in allm], [m["vis"] for m in allm], plane_ms)
+        build(thr)
+        barrier()
+        rebalance = {"seconds": time.time() - t0, "before_vis_ms": [m["vis"] for m in allm],
+                     "before_samples": [m["n"] for m in allm]}
+        t_grid.clear(), t_degrid.clear(), stage_sum.clear()
+        launches[0] = 0
+        nwarm = max(3, args.warmup - 2)
+    for _ in range(nwarm):
         step(False)
     sampler = ClockSampler(local_rank)
     if rank == 0:
@@ -327,123 +550,56 @@ def run_b200(args):
         step(True)
     e1.record()
     barrier()
-    ms_total = e0.elapsed_time(e1)
-    tt = torch.tensor([ms_total], device=dev, dtype=torch.float64)
+    ms_local = e0.elapsed_time(e1)
+    tt = torch.tensor([ms_local], device=dev, dtype=torch.float64)
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    ms_total = float(tt.item())
-    ms_step = ms_total / args.steps
-    value = nsamp * world / (ms_step * 1e-3)
-
-    # ---- end to end: host buffers through the public Plan API (C ABI, host pointers) ----
-    e2e = None
-    if not args.no_e2e:
-        ms_h = torch.empty((nrow, nchan), dtype=cdt, pin_memory=True)
-        wgt_h = torch.empty((nrow, nchan), dtype=rdt, pin_memory=True)
-        ms_h.copy_(ms_d)
-        wgt_h.copy_(wgt_d)
-        dirty_h = torch.empty((npix, npix), dtype=rdt, pin_memory=True)
-        vis_h = torch.empty((nrow, nchan), dtype=cdt, pin_memory=True)
-        ms_np, wgt_np, dirty_np, vis_np = (ms_h.numpy(), wgt_h.numpy(), dirty_h.numpy(),
-                                           vis_h.numpy())
-        freq_np = np.ascontiguousarray(freq)
-        uvw_h = torch.empty(uvw.shape, dtype=torch.float64, pin_memory=True)
-        uvw_h.copy_(torch.from_numpy(uvw))
-        uvw_np = uvw_h.numpy()
-
-        def e2e_step():
-            # what a caller of ducc0.wgridder does per major-cycle half, on host arrays:
-            # plan (uvw upload + sort) + ms2dirty, then dirty2ms; results back on the host
-            with wgridder.Plan(uvw_np, freq_np, npix, npix, cell, cell, eps, True, precision=prec,
-                               stream=stream) as p2:
-                p2.invert(ms_np, wgt_np, out=dirty_np)
-                if world > 1:
-                    tmp = torch.as_tensor(dirty_np, device=dev)
-                    sw = torch.tensor([sumwt_local], device=dev, dtype=torch.float64)
-                    b2dist.allreduce_image_sumwt(tmp, sw)
-                    dirty_h.copy_(tmp)
-                    torch.cuda.synchronize()
-                p2.predict(dirty_np, out=vis_np)
-            return float(dirty_np[npix // 2, npix // 2])
-
-        for _ in range(min(args.warmup, 2)):
-            e2e_step()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(args.e2e_steps):
-            e2e_step()
-        barrier()
-        dt = (time.perf_counter() - t0) / args.e2e_steps
-        tt = torch.tensor([dt], device=dev, dtype=torch.float64)
-        if world > 1:
-            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-        dt = float(tt.item())
-        h2d = nrow * 24 + nchan * 8 + nsamp * (csize + csize // 2) + npix * npix * (csize // 2)
-        d2h = npix * npix * (csize // 2) + nsamp * csize
-        # context for the number above: what this box's PCIe link moves from / to pinned memory
-        # (the e2e step cannot be shorter than h2d / up + d2h / down: invert's uploads and
-        # predict's downloads do not overlap each other)
-        pcie = {}
-        try:
-            nb = min(ms_h.numel() * ms_h.element_size(), 1 << 30)
-            hbuf = ms_h.view(torch.uint8).reshape(-1)[:nb]
-            dbuf = torch.empty(nb, dtype=torch.uint8, device=dev)
-            ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
-            dbuf.copy_(hbuf, non_blocking=True)
-            torch.cuda.synchronize()
-            ev[0].record()
-            dbuf.copy_(hbuf, non_blocking=True)
-            ev[1].record()
-            vis_h.view(torch.uint8).reshape(-1)[:nb].copy_(dbuf, non_blocking=True)
-            ev[2].record()
-            torch.cuda.synchronize()
-            up, down = nb / (ev[0].elapsed_time(ev[1]) * 1e-3), nb / (ev[1].elapsed_time(ev[2]) * 1e-3)
-            pcie = {"h2d_GBs": up / 1e9, "d2h_GBs": down / 1e9,
-                    "floor_ms_per_step": 1e3 * (h2d / up + d2h / down)}
-            import pynvml
-            pynvml.nvmlInit()
-            hnd = pynvml.nvmlDeviceGetHandleByIndex(local_rank)
-            pcie["link"] = "gen%d x%d" % (pynvml.nvmlDeviceGetCurrPcieLinkGeneration(hnd),
-                                          pynvml.nvmlDeviceGetCurrPcieLinkWidth(hnd))
-        except Exception as exc:  # context only: never fail the bench over it
-            pcie["note"] = type(exc).__name__
-        e2e = {"value": nsamp * world / dt, "unit": UNIT, "ms_per_step": 1e3 * dt,
-               "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(d2h),
-               "host_affinity": affinity, "pcie": pcie,
-               "path": "Plan(host uvw) + Plan.invert(host ms, wgt) + Plan.predict(host image) "
-                       "through the C ABI with pinned host buffers; plan creation (uvw upload, "
-                       "uv/w sort) inside the timed region every step; sample arrays streamed "
-                       "over PCIe in row chunks overlapped with gridding / degridding"}
+    ms_step = float(tt.item()) / args.steps
+    value = nsamp / (ms_step * 1e-3)
     clocks = sampler.stop() if rank == 0 else None
 
-    # ---- roofline of the dominant kernel -------------------------------------------------
+    info = state["info"]
+    mine = {"rank": rank, "samples": state["nloc"], "nplanes": info["nplanes"],
+            "nslabs": info["nslabs"], "ms_per_step": ms_local / args.steps,
+            "stage_ms": {k: v / args.steps for k, v in stage_sum.items()},
+            "wlo": thr[rank] if thr else 0.0,
+            "hbm_used_GiB": (torch.cuda.mem_get_info(dev)[1] - torch.cuda.mem_get_info(dev)[0]) / 2 ** 30}
+    allr = [mine]
+    if world > 1:
+        allr = [None] * world
+        dist.all_gather_object(allr, mine)
+
+    # ---- roofline ----------------------------------------------------------------------------
     peak, peak_src = _peaks()
     tg, td = float(np.mean(t_grid)), float(np.mean(t_degrid))
-    nlaunch = max(1, info["nslabs"])
     if td >= tg:
         kname, kms, kdir = "degrid_warprun_kernel", td, "degrid"
     else:
         kname, kms, kdir = "grid_warprun_kernel", tg, "grid"
     if info["algo"] == 0:
         kname = kname.replace("warprun", "simple")
-    b_launches = alg_bytes_launch(kdir, nsamp, nrow, nchan, info["nplanes"], info["nu"],
+    b_launches = alg_bytes_launch(kdir, state["nloc"], nrow, nchan, info["nplanes"], info["nu"],
                                   info["nv"], csize)
     achieved = b_launches / (kms * 1e-3) / 1e9
-    b_step = alg_bytes_step(nsamp, nrow, nchan, npix, info["nplanes"], info["nu"], info["nv"], csize)
+    # whole step, all ranks: SURVEY 8(d) B_alg with every rank's own (samples, planes)
+    b_step = sum(alg_bytes_step(r["samples"], nrow, nchan, npix, r["nplanes"], info["nu"], info["nv"],
+                                csize) for r in allr)
+    step_ach = b_step / (ms_step * 1e-3) / 1e9 / world
     roofline = {
         "bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
         "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-        "launches_per_step": nlaunch, "kernel_ms_per_step": kms,
-        "kernel_share_of_step": kms / ms_step,
+        "launches_per_step": max(1, info["nslabs"]), "kernel_ms_per_step": kms,
+        "kernel_share_of_step": kms / (ms_local / args.steps),
         "alg_bytes_per_step_launches": int(b_launches),
-        "step": {"alg_bytes": int(b_step), "achieved": b_step / (ms_step * 1e-3) / 1e9,
-                 "frac": b_step / (ms_step * 1e-3) / 1e9 / peak},
-        "note": "the visibility-side kernels are FP32-issue bound, not HBM bound (DESIGN.md); "
-                "the HBM fraction is reported because the metric asks for it",
+        "step": {"alg_bytes_all_ranks": int(b_step), "achieved_per_gpu": step_ach,
+                 "frac": step_ach / peak,
+                 "definition": "SURVEY.md 8(d): B_alg(invert + predict) with each rank's own "
+                               "(samples, w-planes) and the plan's (nu, nv), / (max-over-ranks step "
+                               "time x n_gpus x measured HBM peak)"},
+        "note": "dominant kernel of rank 0's step; the visibility-side kernels are FP32-issue "
+                "bound, not HBM bound (DESIGN.md), the image side (per-plane FFT + w-screen) is HBM "
+                "bound; see config.stage_ms_per_step",
     }
-    # context for the note: the kernel's algorithmic FP32 rate against the FP32 FMA peak
-    # (W^2 footprint cells x Wp w-planes x (re, im) FMAs per sample; kernel-value evaluation,
-    # index work and the 15 of 64 idle lane slots at W = 7 earn no credit)
     Wk = info["W"]
     fma_per_sample = Wk * Wk * (Wk if info["nplanes"] > 1 else 1) * 2
     try:
@@ -451,49 +607,87 @@ def run_b200(args):
     except Exception:  # noqa: BLE001
         sm_count = 148
     fp32_peak = sm_count * 128 * 2 * 1.965e9 / 1e12
-    fp32_ach = nsamp * fma_per_sample * 2 / (kms * 1e-3) / 1e12
+    fp32_ach = state["nloc"] * fma_per_sample * 2 / (kms * 1e-3) / 1e12
     roofline["compute_context"] = {
         "fp32_tflops_algorithmic": fp32_ach, "fp32_peak_tflops_nominal": fp32_peak,
-        "frac": fp32_ach / fp32_peak, "fma_per_sample": fma_per_sample,
-        "ncu": "profiles/r01_d_warprun_c2_full.csv: FMA pipe 59-62 % busy, issue slots 65 %, "
-               "shared-memory wavefronts 60-66 %, DRAM 2.6-4.2 %"}
+        "frac": fp32_ach / fp32_peak, "fma_per_sample": fma_per_sample}
     traffic_file = os.path.join(ROOT, "profiles", "traffic.json")
     if os.path.exists(traffic_file):
         try:
             with open(traffic_file) as fh:
-                roofline["traffic"] = json.load(fh).get(kname)
+                tr = json.load(fh)
+            roofline["traffic"] = tr.get(f"{args.config}:{kname}", tr.get(kname))
         except Exception:  # noqa: BLE001
             pass
+
+    # the kernel parameters of this workload's plan, for the CPU arm (it must not load the
+    # product library): refreshed on every GPU run, committed under profiles/
+    if rank == 0:
+        try:
+            db = {}
+            if os.path.exists(KERNEL_FILE):
+                with open(KERNEL_FILE) as fh:
+                    db = json.load(fh)
+            db[args.config] = dict(W=info["W"], sigma=info["sigma"], beta=info["beta"], e0=info["e0"])
+            with open(KERNEL_FILE, "w") as fh:
+                json.dump(db, fh, indent=1, sort_keys=True)
+        except OSError:
+            pass
+
+    # free the device-resident job before the host-driven legs
+    kernel = dict(W=info["W"], sigma=info["sigma"], beta=info["beta"], e0=info["e0"])
+    plan_ms = info["t_plan_ms"]
+    state["plan"].close()
+    state.clear()
+    del dirty_d
+    torch.cuda.empty_cache()
+
+    # ---- secondary figure: the small dense workload (C2) on this rank's GPU, N = 1 only -------
+    secondary = None
+    if world == 1 and args.config != "C2" and not args.no_secondary:
+        secondary = _secondary_c2(torch, wgridder, simulate, dev, stream)
+
+    e2e = None
+    if not args.no_e2e:
+        e2e = _e2e_leg(args, torch, dist, dev, rank, world, geo, cfg, barrier)
 
     # ---- CPU baseline beside it (rank 0, N=1 only) ---------------------------------------
     cpu = None
     if rank == 0 and world == 1 and not args.no_cpu:
-        kernel = dict(W=info["W"], sigma=info["sigma"], beta=info["beta"], e0=info["e0"])
-        plan.close()
-        del ms_d, wgt_d, vis_d
-        v, t, desc, cores = cpu_arm(geo, eps, kernel, args.cpu_seconds)
-        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc}
+        v, t, desc, cores, det = cpu_arm(geo, eps, kernel, args.cpu_seconds)
+        cpu = {"value": v, "unit": UNIT, "cores": cores, "kind": "port", "sample": desc, **det}
 
     if rank == 0:
+        inputs_gb = nsamp * (csize + csize // 2) / 1e9
         line = {
             "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": ms_step, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "f32" if prec == "single" else "f64",
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32" if prec == "single" else "f64",
             "data": "synthetic",
             "config": {
-                "workload": workload_name(args.config, world),
-                "samples_per_step_per_gpu": nsamp, "samples_nonzero_weight": nsamp_weighted,
-                "nrow": nrow, "nchan_per_gpu": nchan, "parallelism": f"channel-shard x{world}",
+                "workload": workload_name(args.config),
+                "samples_per_step": nsamp, "samples_nonzero_weight_rank0": allr[0].get("samples"),
+                "nrow": nrow, "nchan": nchan,
+                "parallelism": ("one plan, one GPU" if world == 1 else
+                                f"w-plane shard x{world}: per-rank plans over |w| intervals, one NCCL "
+                                f"all-reduce of the {npix}x{npix} image + sumwt per step"),
+                "collective": None if world == 1 else "NCCL all_reduce(SUM)",
                 "kernel_W": info["W"], "sigma": info["sigma"], "grid": [info["nu"], info["nv"]],
-                "nplanes": info["nplanes"], "plan_ms": info["t_plan_ms"],
-                "l2": "inputs (3 GB per step) exceed the 126 MB L2; no explicit flush",
-                "value_definition": "samples (row x channel) of the observation per second "
-                                    "through one invert + one predict; plan (sort) reused "
-                                    "across steps for `value`, rebuilt every step for `e2e`",
-                "stage_ms_per_step": {k: v / args.steps for k, v in stage_sum.items()},
+                "nplanes": [r["nplanes"] for r in allr] if world > 1 else info["nplanes"],
+                "plan_ms": plan_ms, "rebalance": rebalance,
+                "l2": f"inputs ({inputs_gb:.1f} GB of samples + weights per step, "
+                      f"{info['nu'] * info['nv'] * csize / 1e6:.0f} MB per w-plane) exceed the 126 MB "
+                      "L2; no explicit flush",
+                "value_definition": "samples (row x channel) of the observation per second through "
+                                    "one invert + one predict; plan (sort) reused across steps for "
+                                    "`value`, rebuilt every step for `e2e`",
+                "stage_ms_per_step": allr[0]["stage_ms"],
+                "ranks": allr if world > 1 else None,
+                "hbm_used_GiB": allr[0]["hbm_used_GiB"],
+                "secondary": secondary,
             },
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
-            "clocks": clocks,
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e,
+            "gpu_launches": int(launches[0]), "clocks": clocks,
         }
         print(json.dumps(line), flush=True)
     if world > 1:
@@ -501,17 +695,55 @@ def run_b200(args):
     return 0
 
 
+def _secondary_c2(torch, wgridder, simulate, dev, stream, steps=5):
+    """C2 (BASELINE.json configs[1]: 64 channels, npixel 2048, 9 w-planes) on one GPU, device
+    resident: the dense regime, bound by the visibility kernels' instruction issue."""
+    obs = simulate.observation("C2")
+    uvw = torch.as_tensor(simulate.flip_for_gridder(obs["uvw"]), device=dev)
+    nrow, nchan, npix, cell = uvw.shape[0], len(obs["freq"]), obs["npix"], obs["cellsize"]
+    gen = torch.Generator(device=dev)
+    gen.manual_seed(simulate.SEED + 2)
+    ms = torch.view_as_complex(torch.randn((nrow, nchan, 2), device=dev, dtype=torch.float32, generator=gen))
+    wgt = torch.ones((nrow, nchan), device=dev, dtype=torch.float32)
+    wgt[torch.as_tensor(obs["auto"], device=dev)] = 0
+    dirty = torch.empty((npix, npix), device=dev, dtype=torch.float32)
+    vis = torch.empty((nrow, nchan), device=dev, dtype=torch.complex64)
+    tg, td = [], []
+    with wgridder.Plan(uvw, obs["freq"], npix, npix, cell, cell, 1e-5, True, precision="single",
+                       stream=stream) as plan:
+        info = plan.info()
+        for i in range(3 + steps):
+            if i == 3:
+                torch.cuda.synchronize()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+            plan.invert(ms, wgt, out=dirty)
+            ti = plan.timings()["vis"]
+            plan.predict(dirty, out=vis)
+            if i >= 3:
+                tg.append(ti)
+                td.append(plan.timings()["vis"])
+        e1.record()
+        torch.cuda.synchronize()
+        t = e0.elapsed_time(e1) / steps
+    return {"workload": workload_name("C2"), "value": nrow * nchan / (t * 1e-3), "unit": UNIT,
+            "ms_per_step": t, "grid_ms": float(np.mean(tg)), "degrid_ms": float(np.mean(td)),
+            "nplanes": info["nplanes"], "grid": [info["nu"], info["nv"]], "kernel_W": info["W"]}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--config", default="C2")
-    ap.add_argument("--e2e-steps", type=int, default=3)
+    ap.add_argument("--config", default="C4")
+    ap.add_argument("--e2e-steps", type=int, default=1)
     ap.add_argument("--cpu-seconds", type=float, default=20.0)
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true")
+    ap.add_argument("--no-rebalance", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "b200" else args.warmup
     # stdout carries exactly one JSON line: whatever libraries print while the job runs

@@ -207,7 +207,9 @@ class CpuPlan:
         self._corr = corr
         return corr
 
-    def invert(self, ms, wgt=None):
+    def invert(self, ms, wgt=None, planes=None):
+        """``planes``: iterable of w-plane indices to process (default all).  A subset gives a
+        partial image; bench.py uses it to time a bounded sample of a many-plane workload."""
         ms = np.ascontiguousarray(ms, dtype=np.complex128)
         wgt = None if wgt is None else np.ascontiguousarray(wgt, dtype=np.float64)
         keep = (ms != 0) if wgt is None else ((ms != 0) & (wgt != 0))
@@ -215,7 +217,7 @@ class CpuPlan:
         nt = self.nthreads
         grid = np.empty((self.nu, self.nv), dtype=np.complex128)
         acc = np.zeros((self.npix_x, self.npix_y))
-        for p in range(self.nplanes):
+        for p in (range(self.nplanes) if planes is None else planes):
             self.L.wg_grid_plane(self.ctx, p, ms.ctypes.data,
                                  None if wgt is None else wgt.ctypes.data, grid.ctypes.data, nt)
             f = scipy.fft.ifft2(grid, norm="forward", workers=nt, overwrite_x=True)
@@ -223,7 +225,7 @@ class CpuPlan:
                                         self.w0 + p * self.dw, acc.ctypes.data, nt)
         return acc * self.correction()
 
-    def predict(self, dirty, wgt=None):
+    def predict(self, dirty, wgt=None, planes=None):
         dirty = np.ascontiguousarray(dirty, dtype=np.float64)
         wgt = None if wgt is None else np.ascontiguousarray(wgt, dtype=np.float64)
         self._bucket(None if wgt is None else (wgt != 0))
@@ -231,7 +233,7 @@ class CpuPlan:
         pre = np.ascontiguousarray(dirty * self.correction())
         grid = np.empty((self.nu, self.nv), dtype=np.complex128)
         out = np.zeros((self.nrow, self.nchan), dtype=np.complex128)
-        for p in range(self.nplanes):
+        for p in (range(self.nplanes) if planes is None else planes):
             self.L.wg_screen_apply(self.ctx, pre.ctypes.data, self.npix_x, self.npix_y,
                                    self.w0 + p * self.dw, grid.ctypes.data, nt)
             f = scipy.fft.fft2(grid, norm="backward", workers=nt, overwrite_x=True)

@@ -60,10 +60,19 @@ def invert_sharded(local_invert, ms, wgt, sumwt_local, normalise_result=True, gr
     dirty = local_invert(ms, wgt)
     sw = torch.as_tensor(np.atleast_1d(np.asarray(sumwt_local, dtype=np.float64)),
                          device=dirty.device)
+    sw = sw.reshape(np.shape(sumwt_local)) if np.ndim(sumwt_local) > 1 else sw
     allreduce_image_sumwt(dirty, sw, group)
-    total = float(sw.sum().item()) if sw.numel() == 1 else None
-    if normalise_result and total is not None:
-        normalise(dirty, total)
+    if normalise_result:
+        if sw.numel() == 1:
+            normalise(dirty, float(sw.item()))
+        elif dirty.dim() > 2 and sw.numel() == int(np.prod(dirty.shape[:-2])):
+            # one sumwt per leading (chan, pol) plane: normalise_sumwt's 2-D branch
+            planes = dirty.reshape((-1,) + tuple(dirty.shape[-2:]))
+            for k, w in enumerate(sw.reshape(-1).tolist()):
+                normalise(planes[k], w)
+        else:
+            raise ValueError(f"normalise_result=True needs one sumwt per image plane: image "
+                             f"{tuple(dirty.shape)}, sumwt {tuple(sw.shape)}")
     return dirty, sw.cpu().numpy()
 
 

@@ -12,7 +12,10 @@ degridding runs in the CUDA library behind include/b200_wgridder.h.  There is no
 
 New optional kwargs (absent in the reference): ``precision`` ("double" default as the reference
 forces fp64, ng.py:198/:203; "single" is the fp32 opt-in for epsilon >= 2e-6), ``nthreads``
-(alias of ``threads``; both ignored on the GPU), ``sumwt_on_device`` (default None = automatic, see ``_invert``; False: sumwt is
+(alias of ``threads``; both ignored on the GPU), ``shard`` / ``group`` / ``src`` (multi-GPU: "channel" or
+"row" = ``bvis`` is this rank's block of the observation, "wplane" = every rank holds the observation
+and works on its own |w| interval; one all-reduce of the un-normalised image + sumwt in invert, one
+broadcast of the model image in predict; see ``_shard_mode``), ``sumwt_on_device`` (default None = automatic, see ``_invert``; False: sumwt is
 computed with the reference's own numpy expression so that it is bit-exact).
 
 The ``Visibility`` / ``Image`` arguments are used through the attributes the reference touches
@@ -110,7 +113,37 @@ def _options(kwargs):
         verbosity=kwargs.get("verbosity", 0),
         precision=kwargs.get("precision", "double"),
         sumwt_on_device=kwargs.get("sumwt_on_device", None),
+        shard=_shard_mode(kwargs.get("shard", None)),
+        group=kwargs.get("group", None),
+        src=kwargs.get("src", 0),
     )
+
+
+def _shard_mode(shard):
+    """Multi-GPU mode of one call (opt-in kwarg, never a positional; absent in the reference):
+    None = this process alone; "channel" / "row" = ``bvis`` is this rank's own block of frequency
+    channels / rows of the observation; "wplane" = every rank holds the whole observation and
+    processes the samples of its own |w| interval (distributed.wplane_selection).  Needs an
+    initialised ``torch.distributed`` process group (NCCL, one process per GPU)."""
+    if shard in (None, False, "none"):
+        return None
+    if shard not in ("channel", "row", "wplane"):
+        raise ValueError(f"unknown shard mode {shard!r} (channel, row, wplane or None)")
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        raise wgridder.WgridderError(
+            f"shard={shard!r} needs an initialised torch.distributed process group")
+    return shard
+
+
+def _wplane_sel(D, freq, npix, pixsize, opt):
+    """This rank's sample selection under w-plane sharding (identical thresholds on all ranks,
+    computed without communication from the replicated uvw / freq)."""
+    import torch.distributed as dist
+    from . import distributed as b2dist
+    world, rank = dist.get_world_size(opt["group"]), dist.get_rank(opt["group"])
+    prec = "single" if wgridder._prec_code(opt["precision"]) == _lib.F32 else "double"
+    return b2dist.wplane_selection(D.uvw, freq, world, rank, npix, pixsize, precision=prec)
 
 
 def _pixsize(im):
@@ -179,7 +212,11 @@ def _rows_per_chunk(nchan, npol, bytes_per_elem):
 
 def _prepare(D, vis, flags, weight, M, shift, dopsf, prec_code, npol_out):
     """Upload the Visibility cube in row chunks and run the prepare kernel.
-    Returns planar device tensors ms [npol_out, nrow, nchan] complex, wgt (same, real)."""
+    Returns planar device tensors ms [npol_out, nrow, nchan] complex, wgt (same, real), the
+    [npol_out, nchan] mask of (pol, chan) planes holding a non-zero visibility (ng.py:238, :267)
+    and the largest |imaging weight| if every one of them is an integer below 2^24 (the device
+    sum of the flagged weights is then exact in any order and in either precision as long as
+    count * max stays below 2^53), else None."""
     torch = D.torch
     nrow, nchan, npol_in = vis.shape
     cdt = torch.complex64 if prec_code == _lib.F32 else torch.complex128
@@ -201,30 +238,40 @@ def _prepare(D, vis, flags, weight, M, shift, dopsf, prec_code, npol_out):
         lmn = numpy.array([-shift[0], shift[1], -shift[2]], dtype=numpy.float64)
     L = _lib.lib()
     step = _rows_per_chunk(nchan, npol_in, vis.dtype.itemsize + weight.dtype.itemsize + 8)
-    # staging through pinned buffers (_xfer.Stager); a single-precision plan takes its inputs as
-    # complex64 / float32 (converted during the staging copy: half the PCIe bytes), integer flags
-    # travel as uint8 when their values allow it
+    # staging through pinned buffers (_xfer.Stager); a single-precision plan takes its samples as
+    # complex64 (converted during the staging copy: half the PCIe bytes); the weights travel in
+    # their own type, so that the integrality test below sees the caller's values; integer flags
+    # travel as uint8 when their values allow it and not at all when nothing is flagged
     stage = D.stager()
-    vdt = wdt = None
+    vdt = None
     if prec_code == _lib.F32:
-        vdt, wdt = torch.complex64, torch.float32
-        vcode = wcode = _lib.F32
+        vdt = torch.complex64
+        vcode = _lib.F32
     fdt = None
-    if flags is not None and flags.dtype.kind in "iub" and flags.dtype.itemsize > 1:
-        lo, hi = torch.from_numpy(flags.reshape(-1)).aminmax()
-        if int(lo) >= 0 and int(hi) <= 255:
+    if flags is not None and flags.dtype.kind in "iub":
+        lo, hi = (int(x) for x in torch.from_numpy(flags.reshape(-1)).aminmax())
+        if lo == 0 and hi == 0:
+            flags, fcode = None, _lib.FLAG_NONE
+        elif flags.dtype.itemsize > 1 and lo >= 0 and hi <= 255:
             fdt, fcode = torch.uint8, _lib.FLAG_U8
+    nonzero = torch.zeros((npol_out, nchan), device=D.dev, dtype=torch.bool)
+    integral = torch.ones((), device=D.dev, dtype=torch.bool)
+    wmax = torch.zeros((), device=D.dev, dtype=torch.float64)
     for r0 in range(0, nrow, step):
         r1 = min(nrow, r0 + step)
         dv = stage.put(vis[r0:r1], vdt)
-        dw = stage.put(weight[r0:r1], wdt)
+        dw = stage.put(weight[r0:r1])
         df = stage.put(flags[r0:r1], fdt) if flags is not None else None
         _lib.check(L.b2g_vis_prepare(
             r1 - r0, nchan, npol_in, npol_out, _ptr(dv), vcode, _ptr(df), fcode, _ptr(dw), wcode,
             _dptr(polmat), _dptr(lmn), _ptr(D.uvw), _ptr(D.fscale), r0, nrow, int(bool(dopsf)),
             _ptr(ms), _ptr(wg), prec_code, ctypes.c_void_p(D.stream)))
+        integral &= (dw == dw.round()).all()
+        wmax = torch.maximum(wmax, dw.abs().amax().to(torch.float64)) if dw.numel() else wmax
+        nonzero |= torch.view_as_real(ms[:, r0:r1]).ne(0).any(dim=3).any(dim=1)
         del dv, dw, df
-    return ms, wg
+    wmax = float(wmax.item())
+    return ms, wg, nonzero.cpu().numpy(), (wmax if bool(integral.item()) and wmax < 2.0 ** 24 else None)
 
 
 def _flagged_weight_host(bvis, nrow, vnchan, vnpol):
@@ -299,7 +346,7 @@ def _invert(bvis, model, dopsf, normalise, subtract_model, kwargs):
 
     D = _Device(uvw, freq)
     torch = D.torch
-    ms, wg = _prepare(D, vis, flags, weight, M, shift, dopsf, prec, npol)
+    ms, wg, nonzero, wmax_int = _prepare(D, vis, flags, weight, M, shift, dopsf, prec, npol)
     mpix = None
     if subtract_model:
         assert npol == vnpol  # predict_ng's own requirement (ng.py:78)
@@ -309,12 +356,11 @@ def _invert(bvis, model, dopsf, normalise, subtract_model, kwargs):
     sumwt = numpy.zeros([nchan, npol])
     on_device = opt["sumwt_on_device"]
     if on_device is None:
-        # integer-valued weights (natural weighting: 0 / 1) sum exactly in any order as long as the
-        # total stays below 2^53 (2^24 for a single-precision plan): the device sum then IS the
-        # reference's numpy sum, bit for bit, without a host pass over the weight cube
-        big = 2.0 ** 24 if prec == _lib.F32 else 2.0 ** 53   # each weight exact in the plan's type
-        on_device = bool(((wg == wg.round()).all() & (wg.abs().amax() < big)
-                          & (wg.abs().sum(dtype=torch.float64) < 2.0 ** 53)).item()) if wg.numel() else True
+        # integer-valued weights (natural weighting: 0 / 1) below 2^24 are exact in either plan
+        # precision and sum exactly in any order while the total stays below 2^53: the device sum
+        # of the flagged weights then IS the reference's numpy sum, bit for bit, without a host
+        # pass over the weight cube (the test runs on the caller's fp64 values, chunk by chunk)
+        on_device = wmax_int is not None and wmax_int * nrow * vnchan < 2.0 ** 53
     if on_device:
         wsum = wg.sum(dim=1, dtype=torch.float64).cpu().numpy()  # [npol, vnchan]
         for pol in range(npol):
@@ -334,7 +380,6 @@ def _invert(bvis, model, dopsf, normalise, subtract_model, kwargs):
 
     rdt = torch.float32 if prec == _lib.F32 else torch.float64
     pix = torch.zeros((nchan, npol, ny, nx), device=D.dev, dtype=torch.float64)
-    nonzero = (ms.abs().amax(dim=1) > 0).cpu().numpy()  # [npol, vnchan]: ng.py:238, :267
     if subtract_model:
         nonzero[...] = True  # a zero visibility still has a residual
 
@@ -346,7 +391,22 @@ def _invert(bvis, model, dopsf, normalise, subtract_model, kwargs):
     common = dict(epsilon=opt["epsilon"], do_wstacking=opt["do_wstacking"], precision=prec,
                   verbosity=opt["verbosity"], stream=D.stream)
     dirty = torch.empty((nx, ny), device=D.dev, dtype=rdt)
-    if mfs:
+    if opt["shard"] == "wplane":
+        # every rank holds the observation; it grids the samples of its own |w| interval only and
+        # its plan spans only their w-planes (the per-plane FFT work divides with the samples)
+        if not mfs:
+            raise ValueError("shard='wplane' is for MFS imaging (image nchan == 1); shard a "
+                             "spectral cube by 'channel'")
+        sel = _wplane_sel(D, freq, nx, pixsize, opt)
+        sumwt[...] = 0.0
+        with wgridder.Plan(D.uvw, freq, nx, ny, pixsize, pixsize, sel=sel, **common) as plan:
+            for pol in range(npol):
+                w_sel = wg[pol].reshape(-1)[sel]
+                sumwt[0, pol] = float(w_sel.sum(dtype=torch.float64).item())
+                if nonzero[pol].any():
+                    run(plan, 0, pol, ms[pol].reshape(-1)[sel], w_sel)
+                    pix[0, pol] += dirty.t()
+    elif mfs:
         with wgridder.Plan(D.uvw, freq, nx, ny, pixsize, pixsize, **common) as plan:
             for pol in range(npol):
                 if nonzero[pol].any():
@@ -368,6 +428,13 @@ def _invert(bvis, model, dopsf, normalise, subtract_model, kwargs):
                         run(plan, ichan, pol, ms[pol].index_select(1, tsel).contiguous(),
                             wg[pol].index_select(1, tsel).contiguous())
                         pix[ichan, pol] += dirty.t()
+    if opt["shard"] is not None:
+        # the one exchange step of invert: un-normalised images and sumwt add over the ranks
+        # (imaging_helpers.py:25-58 sum_invert_results), normalised once below
+        from . import distributed as b2dist
+        sw = torch.from_numpy(sumwt).to(D.dev)
+        b2dist.allreduce_image_sumwt(pix, sw, opt["group"])
+        sumwt = sw.cpu().numpy()
     if normalise:
         # normalise_sumwt, 2-D sumwt branch (imaging/base.py:117-128)
         for chan in range(nchan):
@@ -408,10 +475,23 @@ def predict_ng(bvis, model, **kwargs):
     cdt = torch.complex64 if prec == _lib.F32 else torch.complex128
     rdt = torch.float32 if prec == _lib.F32 else torch.float64
     pixels = D.up(numpy.asarray(model["pixels"].data, dtype=numpy.float64))
+    if opt["shard"] is not None:
+        # the one exchange step of predict: every rank degrids the same model image
+        import torch.distributed as dist
+        dist.broadcast(pixels, src=opt["src"], group=opt["group"])
     vist = torch.zeros((vnpol, nrow, vnchan), device=D.dev, dtype=cdt)
     common = dict(epsilon=opt["epsilon"], do_wstacking=opt["do_wstacking"], precision=prec,
                   verbosity=opt["verbosity"], stream=D.stream)
-    if mfs:
+    if opt["shard"] == "wplane":
+        # the rank predicts the samples of its own |w| interval; the others stay zero, so the
+        # ranks' outputs are disjoint and add up to the full prediction (imaging_helpers.py:75-93)
+        if not mfs:
+            raise ValueError("shard='wplane' is for MFS imaging (image nchan == 1)")
+        sel = _wplane_sel(D, freq, nx, pixsize, opt)
+        with wgridder.Plan(D.uvw, freq, nx, ny, pixsize, pixsize, sel=sel, **common) as plan:
+            for vpol in range(vnpol):
+                vist[vpol].reshape(-1)[sel] = plan.predict(pixels[0, vpol].t().contiguous().to(rdt))
+    elif mfs:
         with wgridder.Plan(D.uvw, freq, nx, ny, pixsize, pixsize, **common) as plan:
             for vpol in range(vnpol):
                 plan.predict(pixels[0, vpol].t().contiguous().to(rdt), out=vist[vpol])
