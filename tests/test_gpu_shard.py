@@ -50,7 +50,10 @@ def test_sharded_invert_predict(built, tmp_path, mode, world):
     for o in outs:
         # every rank ends with the same, fully normalised image and the total sumwt
         assert rel_max(o["dirty"], g["dirty_norm"]) < 1e-9
-        assert np.array_equal(o["sumwt"], g["sumwt"])
+        if world == 1 and mode == "channel":
+            assert np.array_equal(o["sumwt"], g["sumwt"])     # same sum, same order: bit-exact
+        else:   # partial sums added by the all-reduce: the same value up to summation order
+            assert np.allclose(o["sumwt"], g["sumwt"], rtol=1e-13, atol=0)
         if mode == "channel":
             pred[:, :, int(o["lo"]):int(o["hi"])] = o["vis"]
         else:
