@@ -123,7 +123,8 @@ int b2g_plan_residual(b2g_plan *plan, const void *model, int dirty_dtype, int di
 
 /* Plan introspection: fills up to n entries of
  *   iinfo = {W, nu, nv, nplanes, nslabs, planes_per_slab, algo_used, poly_degree,
- *            nvis_sorted, key_bits, launches_last_call}
+ *            nvis_sorted, key_bits, launches_last_call, hand_fft (1: the per-plane transform is
+ *            the hand-written pruned FFT fused with the w-screen, 0: cuFFT + screen kernels)}
  *   dinfo = {sigma, eps_kernel, dw, wmin, wmax, beta, e0, t_plan_ms, t_last_ms} */
 int b2g_plan_info(const b2g_plan *plan, int64_t *iinfo, int ni, double *dinfo, int nd);
 

@@ -99,6 +99,23 @@ template <typename T>
 int launch_screen_apply(const ImgGeo &g, const T *pre, cplx<T> *ring, int pfirst, int np,
                         cudaStream_t s);
 
+// ---- hand-written pruned 2-D FFT of fp32 w-planes, fused with the w-screen (fft_planes.cu) -----
+// With it the image accumulator is kept TRANSPOSED: accT[npix_y][npix_x].
+struct HandFft;
+// 0: ready; < 0: geometry not supported (the caller keeps cuFFT); > 0: a cudaError_t
+int hfft_create(HandFft **out, const ImgGeo &g, cudaStream_t s);
+void hfft_destroy(HandFft *h, cudaStream_t s);
+void hfft_describe(const HandFft *h, char *buf, int n);
+// accT += Re( FFT^-1(plane) on the image * exp(-2 pi i w (n-1)) )
+int hfft_invert_plane(HandFft *h, const cplx<float> *plane, double w, float *accT, cudaStream_t s);
+// plane = FFT( preT * exp(+2 pi i w (n-1)), zero-padded )
+int hfft_predict_plane(HandFft *h, const float *preT, double w, cplx<float> *plane, cudaStream_t s);
+// out[a][b] = accT[b][a] * correction(a, b);  preT[b][a] = dirty[a][b] * correction(a, b)
+template <typename Tout>
+int hfft_correct(const ImgGeo &g, const float *accT, Tout *out, cudaStream_t s);
+template <typename Tin>
+int hfft_precorrect(const ImgGeo &g, const Tin *dirty, float *preT, cudaStream_t s);
+
 // dtype conversion helpers (n real elements)
 template <typename Tin, typename Tout>
 int launch_convert(const Tin *in, Tout *out, long long n, cudaStream_t s);

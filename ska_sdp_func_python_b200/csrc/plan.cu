@@ -182,13 +182,9 @@ struct b2g_plan {
     double *d_scratch = nullptr;  // small scratch (sums)
     cufftHandle fft = 0;
     bool fft_ok = false;
-    // pruned 2-D FFT (fft_mode != 0): batched 1-D transforms along v (contiguous rows) and along u
-    // (strided columns); the pass over lines that hold no image pixel is restricted to the
-    // image's lines.  fft_mode 1: column pass pruned; 2: row pass pruned.
-    int fft_mode = 0;
-    cufftHandle fft_rows = 0, fft_cols = 0;
-    bool fft_rows_ok = false, fft_cols_ok = false;
-    long long fft_half = 0;  // lines per half range of the pruned pass (ceil(npix / 2))
+    // fp32 plans whose grid lines fit shared memory: hand-written two-pass pruned FFT fused with
+    // the w-screen (fft_planes.cu); d_acc then holds the TRANSPOSED accumulator [npix_y][npix_x]
+    HandFft *hfft = nullptr;
     void *d_fftwork = nullptr;
     int key_bits = 0;
     double t_plan_ms = -1, t_last_ms = 0;
@@ -262,10 +258,9 @@ struct b2g_plan {
         if (d_acc) cudaFreeAsync(d_acc, stream);
         if (d_scratch) cudaFreeAsync(d_scratch, stream);
         if (d_fftwork) cudaFreeAsync(d_fftwork, stream);
+        if (hfft) hfft_destroy(hfft, stream);
+        hfft = nullptr;
         if (fft_ok) cufftDestroy(fft);
-        if (fft_rows_ok) cufftDestroy(fft_rows);
-        if (fft_cols_ok) cufftDestroy(fft_cols);
-        fft_rows_ok = fft_cols_ok = false;
         for (auto e : chunk_ev) cudaEventDestroy(e);
         chunk_ev.clear();
         if (ev_a) cudaEventDestroy(ev_a);
@@ -679,46 +674,20 @@ extern "C" int b2g_plan_create_sel(b2g_plan **plan, int64_t nrow, int64_t nchan,
     B2G_OK(build_tables(p));
     lap("tables");
 
+    // per-plane transform: the hand-written pruned FFT where it applies, else cuFFT
+    if (precision == B2G_F32) {
+        const int hrc = hfft_create(&p->hfft, p->img_geo(), p->stream);
+        if (hrc > 0) return fail("hand FFT set-up failed: %s", cudaGetErrorString((cudaError_t)hrc));
+    }
+    size_t work = 0;
+    if (!p->hfft) {
     // FFT plan (own work area so that memory use is explicit)
     FFT_OK(cufftCreate(&p->fft));
     p->fft_ok = true;
     FFT_OK(cufftSetAutoAllocation(p->fft, 0));
-    size_t work = 0;
     FFT_OK(cufftMakePlan2d(p->fft, (int)p->nu, (int)p->nv,
                            precision == B2G_F32 ? CUFFT_C2C : CUFFT_Z2Z, &work));
     FFT_OK(cufftSetStream(p->fft, p->stream));
-    // Only the image's npix_x x npix_y corner blocks of the transformed plane are read (invert) or
-    // non-zero (predict), so one of the two 1-D passes can skip the lines outside them: with
-    // sigma = 1.55 that pass shrinks to 0.65 of its size.  EXPERIMENT SWITCH, off by default:
-    // composed from cuFFT's batched 1-D plans the pruned transform is SLOWER than cuFFT's own 2-D
-    // plan (measured on B200, 12800^2 c2c, 264 plane FFTs: 2-D 473 ms, B2G_FFT=cols 682 ms,
-    // B2G_FFT=rows 845 ms), so pruning only pays with a hand-written large-FFT kernel.
-    {
-        const char *mode = std::getenv("B2G_FFT");
-        p->fft_mode = 0;
-        if (mode && std::strcmp(mode, "cols") == 0) p->fft_mode = 1;
-        if (mode && std::strcmp(mode, "rows") == 0) p->fft_mode = 2;
-        if (npix_y > 0.9 * p->nv || npix_x > 0.9 * p->nu || p->nu < 64 || p->nv < 64) p->fft_mode = 0;
-    }
-    if (p->fft_mode != 0) {
-        const cufftType type = precision == B2G_F32 ? CUFFT_C2C : CUFFT_Z2Z;
-        const long long ha = npix_x - npix_x / 2, hb = npix_y - npix_y / 2;
-        p->fft_half = p->fft_mode == 1 ? hb : ha;
-        size_t w1 = 0, w2 = 0;
-        int n_rows[1] = {(int)p->nv}, n_cols[1] = {(int)p->nu};
-        FFT_OK(cufftCreate(&p->fft_rows));
-        p->fft_rows_ok = true;
-        FFT_OK(cufftSetAutoAllocation(p->fft_rows, 0));
-        FFT_OK(cufftMakePlanMany(p->fft_rows, 1, n_rows, n_rows, 1, (int)p->nv, n_rows, 1, (int)p->nv,
-                                 type, p->fft_mode == 1 ? (int)p->nu : (int)ha, &w1));
-        FFT_OK(cufftSetStream(p->fft_rows, p->stream));
-        FFT_OK(cufftCreate(&p->fft_cols));
-        p->fft_cols_ok = true;
-        FFT_OK(cufftSetAutoAllocation(p->fft_cols, 0));
-        FFT_OK(cufftMakePlanMany(p->fft_cols, 1, n_cols, n_cols, (int)p->nv, 1, n_cols, (int)p->nv, 1,
-                                 type, p->fft_mode == 1 ? (int)hb : (int)p->nv, &w2));
-        FFT_OK(cufftSetStream(p->fft_cols, p->stream));
-        work = std::max(work, std::max(w1, w2));
     }
     lap("cufft plan");
 
@@ -726,11 +695,7 @@ extern "C" int b2g_plan_create_sel(b2g_plan **plan, int64_t nrow, int64_t nchan,
     // so the caller's next call (e.g. the H2D copies of b2g_plan_invert) overlaps with it
     B2G_OK(build_sort(p));
     if (work > 0) CUDA_OK(cudaMallocAsync(&p->d_fftwork, work, p->stream));
-    FFT_OK(cufftSetWorkArea(p->fft, p->d_fftwork));
-    if (p->fft_mode != 0) {
-        FFT_OK(cufftSetWorkArea(p->fft_rows, p->d_fftwork));
-        FFT_OK(cufftSetWorkArea(p->fft_cols, p->d_fftwork));
-    }
+    if (p->fft_ok) FFT_OK(cufftSetWorkArea(p->fft, p->d_fftwork));
     CUDA_OK(cudaMallocAsync(&p->d_ring, p->plane_bytes * size_t(p->nslots), p->stream));
     CUDA_OK(cudaMallocAsync(&p->d_acc, size_t(npix_x) * size_t(npix_y) * real_size(precision), p->stream));
     CUDA_OK(cudaEventRecord(p->ev_plan1, p->stream));
@@ -742,6 +707,11 @@ extern "C" int b2g_plan_create_sel(b2g_plan **plan, int64_t nrow, int64_t nchan,
                 (long long)p->nvis, p->W, p->sigma, (long long)p->nu, (long long)p->nv, p->nplanes,
                 p->gs, p->nslabs, p->dw, p->wmin, p->wmax, p->algo, p->key_bits, p->nchunks,
                 work / 1048576.0, p->plan_ms());
+    if (verbosity > 0 && p->hfft) {
+        char buf[256];
+        hfft_describe(p->hfft, buf, sizeof(buf));
+        fprintf(stderr, "[b2g] plane transform: hand-written pruned FFT + fused w-screen (%s)\n", buf);
+    }
     guard.p = nullptr;
     *plan = p;
     return 0;
@@ -899,40 +869,9 @@ template <typename T> cplx<T> *slot_ptr(b2g_plan *p, int plane)
     return static_cast<cplx<T> *>(p->d_ring) + (size_t)(plane % p->nslots) * size_t(p->nu) * size_t(p->nv);
 }
 
-template <typename T> int fft_exec(cufftHandle h, cplx<T> *d, int direction)
-{
-    if (sizeof(T) == 4)
-        FFT_OK(cufftExecC2C(h, reinterpret_cast<cufftComplex *>(d), reinterpret_cast<cufftComplex *>(d),
-                            direction));
-    else
-        FFT_OK(cufftExecZ2Z(h, reinterpret_cast<cufftDoubleComplex *>(d),
-                            reinterpret_cast<cufftDoubleComplex *>(d), direction));
-    return 0;
-}
-
 template <typename T> int fft_plane(b2g_plan *p, int plane, int direction)
 {
     cplx<T> *d = slot_ptr<T>(p, plane);
-    if (p->fft_mode != 0) {
-        // full pass over every line of one axis, pruned pass over the image's lines of the other:
-        // gridding (inverse) transforms everything first and prunes the second pass to the lines
-        // that are read; degridding (forward) starts with the only non-zero lines
-        const long long h = p->fft_half;
-        cufftHandle full = p->fft_mode == 1 ? p->fft_rows : p->fft_cols;
-        cufftHandle part = p->fft_mode == 1 ? p->fft_cols : p->fft_rows;
-        // second half range: columns [nv - h, nv) or rows [nu - h, nu)
-        cplx<T> *hi = p->fft_mode == 1 ? d + (p->nv - h) : d + (p->nu - h) * p->nv;
-        if (direction == CUFFT_INVERSE) {
-            B2G_OK(fft_exec<T>(full, d, direction));
-            B2G_OK(fft_exec<T>(part, d, direction));
-            B2G_OK(fft_exec<T>(part, hi, direction));
-        } else {
-            B2G_OK(fft_exec<T>(part, d, direction));
-            B2G_OK(fft_exec<T>(part, hi, direction));
-            B2G_OK(fft_exec<T>(full, d, direction));
-        }
-        return 0;
-    }
     if (sizeof(T) == 4)
         FFT_OK(cufftExecC2C(p->fft, reinterpret_cast<cufftComplex *>(d),
                             reinterpret_cast<cufftComplex *>(d), direction));
@@ -940,6 +879,48 @@ template <typename T> int fft_plane(b2g_plan *p, int plane, int direction)
         FFT_OK(cufftExecZ2Z(p->fft, reinterpret_cast<cufftDoubleComplex *>(d),
                             reinterpret_cast<cufftDoubleComplex *>(d), direction));
     return 0;
+}
+
+// fp32 plans with the hand-written FFT: per-plane fused transform + w-screen
+template <typename T> int hfft_planes_invert(b2g_plan *, int, int) { return -1; }
+template <> int hfft_planes_invert<float>(b2g_plan *p, int first, int count)
+{
+    for (int q = 0; q < count; ++q) {
+        const double w = p->w0 + double(first + q) * p->dw;
+        KERNEL_OK(hfft_invert_plane(p->hfft, slot_ptr<float>(p, first + q), w,
+                                    static_cast<float *>(p->d_acc), p->stream));
+        p->launches_last += 2;
+    }
+    return 0;
+}
+template <typename T> int hfft_planes_predict(b2g_plan *, int, int) { return -1; }
+template <> int hfft_planes_predict<float>(b2g_plan *p, int first, int count)
+{
+    for (int q = 0; q < count; ++q) {
+        const double w = p->w0 + double(first + q) * p->dw;
+        KERNEL_OK(hfft_predict_plane(p->hfft, static_cast<const float *>(p->d_acc), w,
+                                     slot_ptr<float>(p, first + q), p->stream));
+        p->launches_last += 2;
+    }
+    return 0;
+}
+template <typename T, typename Tout> int hfft_correct_any(b2g_plan *, const ImgGeo &, Tout *) { return -1; }
+template <> int hfft_correct_any<float, float>(b2g_plan *p, const ImgGeo &g, float *out)
+{
+    return hfft_correct<float>(g, static_cast<const float *>(p->d_acc), out, p->stream);
+}
+template <> int hfft_correct_any<float, double>(b2g_plan *p, const ImgGeo &g, double *out)
+{
+    return hfft_correct<double>(g, static_cast<const float *>(p->d_acc), out, p->stream);
+}
+template <typename T, typename Tin> int hfft_precorrect_any(b2g_plan *, const ImgGeo &, const Tin *) { return -1; }
+template <> int hfft_precorrect_any<float, float>(b2g_plan *p, const ImgGeo &g, const float *in)
+{
+    return hfft_precorrect<float>(g, in, static_cast<float *>(p->d_acc), p->stream);
+}
+template <> int hfft_precorrect_any<float, double>(b2g_plan *p, const ImgGeo &g, const double *in)
+{
+    return hfft_precorrect<double>(g, in, static_cast<float *>(p->d_acc), p->stream);
 }
 
 // planes finished by slab s (invert) : [first, first+count)
@@ -1009,6 +990,8 @@ int invert_impl(b2g_plan *p, const void *ms, const void *wgt, int vis_dtype, int
 
     tm.begin(S_PREP);
     CUDA_OK(cudaMemsetAsync(p->d_ring, 0, p->plane_bytes * size_t(p->nslots), s));
+    if (p->hfft)   // the fused column pass accumulates into the (transposed) image from plane 0 on
+        CUDA_OK(cudaMemsetAsync(p->d_acc, 0, size_t(p->npix_x) * size_t(p->npix_y) * sizeof(T), s));
     tm.end();
 
     const ImgGeo ig = p->img_geo();
@@ -1033,14 +1016,20 @@ int invert_impl(b2g_plan *p, const void *ms, const void *wgt, int vis_dtype, int
         tm.end();
         int first, count;
         slab_planes_done(p, sl, &first, &count);
-        tm.begin(S_FFT);
-        for (int q = 0; q < count; ++q) B2G_OK(fft_plane<T>(p, first + q, CUFFT_INVERSE));
-        tm.end();
-        tm.begin(S_SCREEN);
-        KERNEL_OK(launch_screen_accumulate<T>(ig, static_cast<const cplx<T> *>(p->d_ring), first,
-                                              count, static_cast<T *>(p->d_acc), sl == 0, s));
-        p->launches_last++;
-        tm.end();
+        if (p->hfft) {
+            tm.begin(S_FFT);
+            B2G_OK(hfft_planes_invert<T>(p, first, count));
+            tm.end();
+        } else {
+            tm.begin(S_FFT);
+            for (int q = 0; q < count; ++q) B2G_OK(fft_plane<T>(p, first + q, CUFFT_INVERSE));
+            tm.end();
+            tm.begin(S_SCREEN);
+            KERNEL_OK(launch_screen_accumulate<T>(ig, static_cast<const cplx<T> *>(p->d_ring), first,
+                                                  count, static_cast<T *>(p->d_acc), sl == 0, s));
+            p->launches_last++;
+            tm.end();
+        }
         if (sl + 1 < p->nslabs) {
             tm.begin(S_PREP);
             for (int q = 0; q < count; ++q)
@@ -1053,7 +1042,10 @@ int invert_impl(b2g_plan *p, const void *ms, const void *wgt, int vis_dtype, int
     void *d_out = dirty;
     const long long npx = p->npix_x * p->npix_y;
     if (dirty_space != B2G_DEVICE) CUDA_OK(cudaMallocAsync(&d_out, real_size(dirty_dtype) * npx, s));
-    if (dirty_dtype == B2G_F64)
+    if (p->hfft) {
+        if (dirty_dtype == B2G_F64) KERNEL_OK((hfft_correct_any<T, double>(p, ig, static_cast<double *>(d_out))));
+        else KERNEL_OK((hfft_correct_any<T, float>(p, ig, static_cast<float *>(d_out))));
+    } else if (dirty_dtype == B2G_F64)
         KERNEL_OK((launch_correct<T, double>(ig, static_cast<const T *>(p->d_acc), static_cast<double *>(d_out), s)));
     else
         KERNEL_OK((launch_correct<T, float>(ig, static_cast<const T *>(p->d_acc), static_cast<float *>(d_out), s)));
@@ -1103,7 +1095,10 @@ int predict_impl(b2g_plan *p, const void *dirty, int dirty_dtype, int dirty_spac
     tm.end();
 
     tm.begin(S_CORRECT);
-    if (dirty_dtype == B2G_F64)
+    if (p->hfft) {
+        if (dirty_dtype == B2G_F64) KERNEL_OK((hfft_precorrect_any<T, double>(p, ig, static_cast<const double *>(d_dirty))));
+        else KERNEL_OK((hfft_precorrect_any<T, float>(p, ig, static_cast<const float *>(d_dirty))));
+    } else if (dirty_dtype == B2G_F64)
         KERNEL_OK((launch_precorrect<T, double>(ig, static_cast<const double *>(d_dirty), static_cast<T *>(p->d_acc), s)));
     else
         KERNEL_OK((launch_precorrect<T, float>(ig, static_cast<const float *>(d_dirty), static_cast<T *>(p->d_acc), s)));
@@ -1123,7 +1118,11 @@ int predict_impl(b2g_plan *p, const void *dirty, int dirty_dtype, int dirty_spac
     for (int sl = 0; sl < p->nslabs; ++sl) {
         int first, count;
         slab_planes_new(p, sl, &first, &count);
-        if (count > 0) {
+        if (count > 0 && p->hfft) {
+            tm.begin(S_FFT);
+            B2G_OK(hfft_planes_predict<T>(p, first, count));
+            tm.end();
+        } else if (count > 0) {
             tm.begin(S_SCREEN);
             KERNEL_OK(launch_screen_apply<T>(ig, static_cast<const T *>(p->d_acc),
                                              static_cast<cplx<T> *>(p->d_ring), first, count, s));
@@ -1282,11 +1281,12 @@ extern "C" int b2g_plan_info(const b2g_plan *p, int64_t *iinfo, int ni, double *
     g_err.clear();
     if (!p) return fail("plan is NULL");
     const_cast<b2g_plan *>(p)->plan_ms();
-    const int64_t iv[11] = {p->W, p->nu, p->nv, p->nplanes, p->nslabs, p->gs, p->algo,
-                            poly_degree(p->W), p->nvis, p->key_bits, p->launches_last};
+    const int64_t iv[12] = {p->W, p->nu, p->nv, p->nplanes, p->nslabs, p->gs, p->algo,
+                            poly_degree(p->W), p->nvis, p->key_bits, p->launches_last,
+                            p->hfft ? 1 : 0};
     const double dv[9] = {p->sigma, p->eps_kernel, p->dw, p->wmin, p->wmax, p->beta, p->e0,
                           p->t_plan_ms, p->t_last_ms};
-    for (int i = 0; i < ni && i < 11; ++i) iinfo[i] = iv[i];
+    for (int i = 0; i < ni && i < 12; ++i) iinfo[i] = iv[i];
     for (int i = 0; i < nd && i < 9; ++i) dinfo[i] = dv[i];
     return 0;
 }

@@ -259,11 +259,11 @@ class Plan:
 
     # -- introspection --------------------------------------------------------------
     def info(self):
-        ii = (ctypes.c_int64 * 11)()
+        ii = (ctypes.c_int64 * 12)()
         dd = (ctypes.c_double * 9)()
-        _lib.check(self._L.b2g_plan_info(self._h, ii, 11, dd, 9))
+        _lib.check(self._L.b2g_plan_info(self._h, ii, 12, dd, 9))
         keys_i = ("W", "nu", "nv", "nplanes", "nslabs", "planes_per_slab", "algo",
-                  "poly_degree", "nvis", "key_bits", "launches_last_call")
+                  "poly_degree", "nvis", "key_bits", "launches_last_call", "hand_fft")
         keys_d = ("sigma", "eps_kernel", "dw", "wmin", "wmax", "beta", "e0", "t_plan_ms",
                   "t_last_ms")
         res = {k: int(v) for k, v in zip(keys_i, ii)}

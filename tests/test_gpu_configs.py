@@ -244,3 +244,47 @@ def test_c5_psf_fp64(wg):
     rows, chans = rng.integers(0, nrow, 300), rng.integers(0, nchan, 300)
     vref = odft.dirty2ms_samples_sparse(uvw, freq, ix, iy, flux, npix, npix, cell, cell, True, rows, chans)
     assert np.abs(v[rows, chans] - vref).max() < 1e-9 * np.abs(vref).max()
+
+
+# ---------------------------------------------------------------------------------------------
+# hand-written pruned plane FFT (fp32 plans) against the cuFFT + screen-kernel path
+# ---------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("ws", [True, False])
+@pytest.mark.parametrize("shape", [(256, 192, 2.0e-4, 2.5e-4, 0.05), (384, 512, 1.5e-3, 1.2e-3, 1.0)])
+def test_hand_fft_equals_cufft_path(wg, slab_cap, monkeypatch, ws, shape):
+    """Same plan, same samples through the fused TMA-staged plane transform (info hand_fft = 1)
+    and through cuFFT + screen kernels (B2G_NO_HFFT=1): both within epsilon of the exact DFT and
+    equal to each other to fp32 rounding; also with a wrapping multi-slab ring."""
+    from oracle import dft as odft
+    npx, npy, psx, psy, wfrac = shape
+    uvw, freq, ms, wgt = make_case(77, 3000, 3, npx, npy, psx, psy, wfrac)
+    rng = np.random.default_rng(5)
+    model = np.zeros((npx, npy), dtype=np.float32)
+    model[rng.integers(0, npx, 60), rng.integers(0, npy, 60)] = rng.uniform(1, 2, 60)
+    model[0, 0], model[npx - 1, npy - 1], model[0, npy - 1] = 1.0, -1.0, 0.5
+    eps = 1e-5
+    res = {}
+    for name, env, cap in (("hand", None, 0), ("hand_slabs", None, 2), ("cufft", "1", 0)):
+        if env:
+            monkeypatch.setenv("B2G_NO_HFFT", env)
+        else:
+            monkeypatch.delenv("B2G_NO_HFFT", raising=False)
+        slab_cap(cap)
+        with wg.Plan(uvw, freq, npx, npy, psx, psy, eps, ws, precision="single") as p:
+            info = p.info()
+            assert info["hand_fft"] == (0 if env else 1), info
+            res[name] = (p.invert(ms.astype(np.complex64), wgt.astype(np.float32)),
+                         p.predict(model, wgt.astype(np.float32)),
+                         p.invert(ms.astype(np.complex64), wgt.astype(np.float32), out_dtype=np.float64))
+    px = np.concatenate([[0, 0, npx - 1, npx - 1, npx // 2], rng.integers(0, npx, 200)])
+    py = np.concatenate([[0, npy - 1, 0, npy - 1, npy // 2], rng.integers(0, npy, 200)])
+    dref = odft.ms2dirty_points(uvw, freq, ms, wgt, npx, npy, psx, psy, ws, px, py)
+    rows, chans = rng.integers(0, 3000, 300), rng.integers(0, 3, 300)
+    vref = odft.dirty2ms_samples(uvw, freq, model.astype(np.float64), wgt, psx, psy, ws, rows, chans)
+    for name, (d, v, d64) in res.items():
+        assert rel_l2(d[px, py], dref) < eps and rel_l2(v[rows, chans], vref) < eps, name
+        assert np.abs(d[px, py] - dref).max() < 10 * eps * np.abs(dref).max(), name
+        assert d64.dtype == np.float64 and rel_l2(d64, d) < 1e-6
+    for name in ("hand", "hand_slabs"):
+        assert rel_l2(res[name][0], res["cufft"][0]) < 3e-6
+        assert rel_l2(res[name][1], res["cufft"][1]) < 3e-6
