@@ -16,7 +16,6 @@ import numpy
 from . import _lib
 from .imaging import (_Device, _dptr, _is_image, _ptr, _radec, _rows_per_chunk, image_centre_radec,
                       separation, skycoord_to_lmn)
-from .skymodel_imaging import _normalise_sumwt_image
 
 log = logging.getLogger("func-python-logger")
 
@@ -90,6 +89,27 @@ def shift_vis_to_image(vis, im, tangent=True, inverse=False):
     return vis
 
 
+def _normalise_by_weight_image(im, sumwt, min_weight, flat_sky):
+    """The Image-valued ``sumwt`` case (imaging/base.py:129-149) as whole-cube expressions; both
+    arguments are updated in place like the reference does.  Its per-plane loop takes the square
+    root of the WHOLE weight cube once per (chan, pol) plane, so plane j of K (loop order) leaves as
+    (W_j^(2^-j) / max W)^(2^-(K-j)); with ``flat_sky`` the weights are left alone."""
+    w = sumwt["pixels"].data
+    pix = im["pixels"].data
+    maxwt = numpy.max(w)
+    nchan, npol, ny, nx = w.shape
+    if flat_sky:
+        norm = numpy.sqrt(w[:, :, ny // 2:ny // 2 + 1, nx // 2:nx // 2 + 1] * w)
+        good = norm > min_weight * maxwt
+        pix[...] = numpy.where(good, pix / numpy.where(good, norm, 1.0), pix / maxwt)
+        return im
+    k = nchan * npol
+    j = numpy.arange(k, dtype=float).reshape(nchan, npol, 1, 1)
+    pix /= maxwt
+    sumwt["pixels"].data = (w ** (0.5 ** j) / maxwt) ** (0.5 ** (k - j))
+    return im
+
+
 def normalise_sumwt(im, sumwt, min_weight=0.1, flat_sky=False):
     """Divide out the sum of weights (imaging/base.py:95-156): per (channel, polarisation) for a
     2-D ``sumwt`` (planes with sumwt <= 0 are zeroed), pixel by pixel / by its maximum for an Image."""
@@ -107,5 +127,5 @@ def normalise_sumwt(im, sumwt, min_weight=0.1, flat_sky=False):
                     pix[chan, pol, :, :] = 0.0
         return im
     if _is_image(sumwt) and im["pixels"].data.shape == sumwt["pixels"].data.shape:
-        return _normalise_sumwt_image(im, sumwt, min_weight=min_weight, flat_sky=flat_sky)
+        return _normalise_by_weight_image(im, sumwt, min_weight, flat_sky)
     raise ValueError("sumwt is not a 2D or 4D array - cannot perform normalisation")

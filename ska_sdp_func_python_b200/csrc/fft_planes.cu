@@ -332,6 +332,7 @@ hfft_rows_fwd_kernel(PlaneGeo g, LinePlan lp, const float2 *__restrict__ tw,
         float2 *target = lastread == first ? second : first;
         int calls = 0;
         auto sync = [&]() {
+            fence_proxy_async();     // generic accesses to `target` ordered before the TMA writes
             __syncthreads();
             if (++calls == lp.nstage - 1 && un < g.nu) fetch(un, target);
         };

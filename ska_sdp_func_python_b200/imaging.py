@@ -443,6 +443,9 @@ def _invert(bvis, model, dopsf, normalise, subtract_model, kwargs):
                     pix[chan, pol] /= float(sumwt[chan, pol])
                 else:
                     pix[chan, pol] = 0.0
+    if kwargs.get("_device_result", False):
+        # callers that keep accumulating on the device (skymodel_imaging.py): fp64 CUDA tensor
+        return pix, sumwt
     im["pixels"].data[...] = pix.cpu().numpy()
     return im, sumwt
 

@@ -1,7 +1,8 @@
 """Major-cycle glue on a B200: drop-ins for
 ``skymodel_predict_calibrate`` and ``skymodel_calibrate_invert``
 (/root/reference/src/ska_sdp_func_python/sky_model/skymodel_imaging.py:70-151, :154-235) built on
-the CUDA component DFT (dft.py), degridder and gridder (imaging.py), plus ``skymodel_residual``:
+the CUDA component DFT (dft.py), degridder and gridder (imaging.py) -- the primary-beam-weighted
+sums over time slices and their normalisation stay on the device -- plus ``skymodel_residual``:
 the residual image of a SkyModel in one pass with the samples resident on the device
 (imaging.residual_ng -> b2g_plan_residual), which is what a major cycle actually needs.
 
@@ -40,25 +41,30 @@ def _no_calibration(docal, skymodel):
             "imaging path: apply the gain table with the reference before / after this call")
 
 
-def _normalise_sumwt_image(im, sumwt, min_weight=0.1, flat_sky=False):
-    """normalise_sumwt for a sum of weights that is an Image (primary-beam case), statement by
-    statement as imaging/base.py:129-149 -- including its in-place updates of ``sumwt``."""
-    maxwt = numpy.max(sumwt["pixels"].data)
-    minwt = min_weight * maxwt
-    nchan, npol, ny, nx = sumwt["pixels"].data.shape
-    cx, cy = nx // 2, ny // 2
-    for chan in range(nchan):
-        for pol in range(npol):
-            if flat_sky:
-                norm = numpy.sqrt(sumwt["pixels"].data[chan, pol, cy, cx]
-                                  * sumwt["pixels"].data[chan, pol, :, :])
-                im["pixels"].data[chan, pol, :, :][norm > minwt] /= norm[norm > minwt]
-                im["pixels"].data[chan, pol, :, :][norm <= minwt] /= maxwt
-            else:
-                im["pixels"].data[chan, pol, :, :] /= maxwt
-                sumwt["pixels"].data[chan, pol, :, :] /= maxwt
-                sumwt["pixels"].data = numpy.sqrt(sumwt["pixels"].data)
-    return im
+def _normalise_weighted(sum_dirty, sum_flat, min_weight=0.1, flat_sky=False):
+    """Primary-beam-weighted normalisation on the device: what ``normalise_sumwt`` does when the
+    sum of weights is an Image (imaging/base.py:129-149) followed by the caller's final square root
+    of the weights (skymodel_imaging.py:226-227), written as whole-cube tensor expressions.
+
+    sum_dirty, sum_flat: CUDA tensors [nchan, npol, ny, nx].  Returns (image, sensitivity).
+      flat_sky : image / sqrt(W_centre * W) where that exceeds min_weight * max(W), else image /
+                 max(W); sensitivity = sqrt(W).
+      otherwise: image / max(W).  The reference takes the square root of the WHOLE weight cube once
+                 per (chan, pol) plane of its loop, so plane j (of K, in loop order) ends up as
+                 (W_j^(2^-j) / max(W))^(2^-(K-j+1)) -- (W / max(W))^(1/4) for a single plane.  Kept,
+                 because callers of the reference see exactly these numbers."""
+    import torch
+    maxwt = sum_flat.max()
+    nchan, npol, ny, nx = sum_flat.shape
+    if flat_sky:
+        centre = sum_flat[:, :, ny // 2:ny // 2 + 1, nx // 2:nx // 2 + 1]
+        norm = torch.sqrt(centre * sum_flat)
+        image = torch.where(norm > min_weight * maxwt, sum_dirty / norm, sum_dirty / maxwt)
+        return image, torch.sqrt(sum_flat)
+    k = nchan * npol
+    j = torch.arange(k, device=sum_flat.device, dtype=torch.float64).reshape(nchan, npol, 1, 1)
+    sens = (sum_flat ** (0.5 ** j) / maxwt) ** (0.5 ** (k - j + 1))
+    return sum_dirty / maxwt, sens
 
 
 def _dft_sky_component(vis_slice, skymodel, pb=None, **kwargs):
@@ -128,28 +134,40 @@ def skymodel_calibrate_invert(bvis, skymodel, context="ng", docal=False, get_pb=
     if skymodel.image is None:
         raise ValueError("skymodel image is None")
     _no_calibration(docal, skymodel)
-    bvis_cal = bvis.copy(deep=True)
     if get_pb is not None:
-        sum_flats = skymodel.image.copy(deep=True)
-        sum_flats["pixels"].data[...] = 0.0
-        sum_dirtys = skymodel.image.copy(deep=True)
-        sum_dirtys["pixels"].data[...] = 0.0
-        for _, vis_slice in _time_slices(bvis_cal):
+        # one gridding per time slice (each has its own primary beam); the beam-weighted image
+        # sum_t flat_t * dirty_t and the weight image sum_t flat_t^2 * sumwt_t stay on the device
+        # until the single normalisation at the end
+        import torch
+        sum_dirty = sum_flat = None
+        mask = None
+        for _, vis_slice in _time_slices(bvis):
             pb = get_pb(vis_slice, skymodel.image)
-            result = invert_visibility(vis_slice, skymodel.image, context=context, normalise=False,
-                                       **kwargs)
-            flat = numpy.ones_like(result[0]["pixels"].data)
-            if skymodel.mask is not None:
-                flat *= skymodel.mask["pixels"].data
+            pix, sumwt = invert_visibility(vis_slice, skymodel.image, context=context, normalise=False,
+                                           _device_result=True, **kwargs)
+            if sum_dirty is None:
+                sum_dirty, sum_flat = torch.zeros_like(pix), torch.zeros_like(pix)
+                if skymodel.mask is not None:
+                    mask = torch.as_tensor(numpy.asarray(skymodel.mask["pixels"].data, dtype=float),
+                                           device=pix.device)
+            flat = None if mask is None else mask
             if pb is not None:
-                flat *= pb["pixels"].data
-            sum_dirtys["pixels"].data += flat * result[0]["pixels"].data
-            sum_flats["pixels"].data += flat * flat * result[1][:, :, numpy.newaxis, numpy.newaxis]
+                beam = torch.as_tensor(numpy.asarray(pb["pixels"].data, dtype=float), device=pix.device)
+                flat = beam if flat is None else flat * beam
+            wt = torch.as_tensor(sumwt, device=pix.device)[:, :, None, None]
+            if flat is None:
+                sum_dirty += pix
+                sum_flat += wt
+            else:
+                sum_dirty.addcmul_(flat, pix)
+                sum_flat.addcmul_(flat * flat, wt.expand_as(flat))
         if normalise:
-            sum_dirtys = _normalise_sumwt_image(sum_dirtys, sum_flats, flat_sky=flat_sky)
-            sum_flats["pixels"].data = numpy.sqrt(sum_flats["pixels"].data)
-        return sum_dirtys, sum_flats
-    result = invert_visibility(bvis_cal, skymodel.image, context=context, **kwargs)
+            sum_dirty, sum_flat = _normalise_weighted(sum_dirty, sum_flat, flat_sky=flat_sky)
+        dirty_im, flat_im = skymodel.image.copy(deep=True), skymodel.image.copy(deep=True)
+        dirty_im["pixels"].data[...] = sum_dirty.cpu().numpy()
+        flat_im["pixels"].data[...] = sum_flat.cpu().numpy()
+        return dirty_im, flat_im
+    result = invert_visibility(bvis, skymodel.image, context=context, **kwargs)
     if skymodel.mask is not None:
         result[0]["pixels"].data *= skymodel.mask["pixels"].data
     return result

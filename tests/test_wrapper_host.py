@@ -110,3 +110,45 @@ def test_inputs_are_not_mutated_by_standin_copy():
     assert np.array_equal(c["uvw"].data, vis["uvw"].data)
     c["uvw"].data[...] = 0
     assert np.any(vis["uvw"].data != 0)
+
+
+# ---- pins that do not go through the repo's own tables / formulas ------------------------------
+def test_pol_matrices_on_a_typed_in_stokes_vector():
+    """Thompson, Moran & Swenson eq. 4.58 / 4.59 as ska_sdp_datamodels applies them, on the Stokes
+    vector (I, Q, U, V) = (1.0, 0.3, -0.2, 0.1) with the expected correlations typed in by hand:
+    XX = I + Q, XY = U + iV, YX = U - iV, YY = I - Q;  RR = I + V, RL = -iQ + U, LR = -iQ - U,
+    LL = I - V.  Independent of polarisation.py's tables."""
+    from ska_sdp_func_python_b200.polarisation import pol_matrix_table
+    stokes = np.array([1.0, 0.3, -0.2, 0.1], dtype=complex)
+    linear = np.array([1.3, -0.2 + 0.1j, -0.2 - 0.1j, 0.7])
+    circular = np.array([1.1, -0.2 - 0.3j, 0.2 - 0.3j, 0.9])
+    assert np.allclose(pol_matrix_table("stokesIQUV", "linear") @ stokes, linear, atol=1e-15)
+    assert np.allclose(pol_matrix_table("stokesIQUV", "circular") @ stokes, circular, atol=1e-15)
+    assert np.allclose(pol_matrix_table("linear", "stokesIQUV") @ linear, stokes, atol=1e-15)
+    assert np.allclose(pol_matrix_table("circular", "stokesIQUV") @ circular, stokes, atol=1e-15)
+    # two-product frames: (XX, YY) = (I + Q, I - Q), (RR, LL) = (I + V, I - V)
+    assert np.allclose(pol_matrix_table("stokesIQ", "linearnp") @ np.array([1.0, 0.3]), [1.3, 0.7])
+    assert np.allclose(pol_matrix_table("stokesIV", "circularnp") @ np.array([1.0, 0.1]), [1.1, 0.9])
+    assert np.allclose(pol_matrix_table("linearnp", "stokesIQ") @ np.array([1.3, 0.7]), [1.0, 0.3])
+    assert np.allclose(pol_matrix_table("circularnp", "stokesIV") @ np.array([1.1, 0.9]), [1.0, 0.1])
+    assert np.array_equal(pol_matrix_table("stokesI", "stokesI"), np.eye(1))
+
+
+def test_geometry_against_typed_in_closed_form_values():
+    """SIN deprojection of an off-centre FFT-centre pixel and (l, m, n-1) of a sky position, against
+    values computed independently with 30-digit arithmetic from the rotation of the tangent-plane
+    unit vector into equatorial coordinates (x = n cos d0 - m sin d0, y = l, z = n sin d0 + m cos d0;
+    ra = ra0 + atan2(y, x), dec = asin z) and typed in here."""
+    from ska_sdp_func_python_b200 import imaging
+    from ska_sdp_func_python_b200 import minimal_models as mm
+    # image 64 x 64, reference pixel moved so that the FFT centre (33, 33 one-based) sits at
+    # (dx, dy) = (+3, -2) pixels from crpix; cdelt = (-0.01, +0.01) deg; crval = (15, -35) deg
+    wcs = mm.WCS(crval=[15.0, -35.0, 1.0, 1e8], crpix=[30.0, 35.0, 1.0, 1.0], cdelt=[-0.01, 0.01, 1.0, 1e6])
+    im = mm.Image(np.zeros((1, 1, 64, 64)), wcs, mm.PolarisationFrame("stokesI"))
+    ra, dec = imaging.image_centre_radec(im)
+    assert abs(ra - 0.261160035410117501731) < 1e-15
+    assert abs(dec - (-0.611214208049086070517)) < 1e-15
+    l, m, nm1 = imaging.skycoord_to_lmn(np.radians(15.5), np.radians(-34.2), np.radians(15.0), np.radians(-35.0))
+    assert abs(l - 0.00721754799142246370904) < 1e-16
+    assert abs(m - 0.0139441168719772890360) < 1e-16
+    assert abs(nm1 - (-0.000123273295326594406871)) < 2e-16
