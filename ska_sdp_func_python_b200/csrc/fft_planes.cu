@@ -1,24 +1,29 @@
 // fft_planes.cu -- hand-written pruned 2-D FFT of one fp32 w-plane, fused with the w-screen.
 //
-// Replaces, for single-precision plans whose grid lines fit shared memory (nu, nv <= 14000), the
-// per-plane  cuFFT C2C (four passes over the padded plane for 12800^2)  +  w-screen kernel  +
-// cropping  that sit between gridding and the dirty image inside what the reference runs as
-// ducc0.wgridder.ms2dirty / dirty2ms (/root/reference/src/ska_sdp_func_python/imaging/ng.py:240-256,
-// :99-112).  Two passes per plane, each line transformed once in shared memory (fft_lines.cuh):
+// Replaces, for single-precision plans whose grid sides have a static line plan (fft_inplace.cuh:
+// 1600, 3200, 6400, 12800), the per-plane  cuFFT C2C (four passes over the padded plane for
+// 12800^2)  +  w-screen kernel  +  cropping  that sit between gridding and the dirty image inside
+// what the reference runs as ducc0.wgridder.ms2dirty / dirty2ms
+// (/root/reference/src/ska_sdp_func_python/imaging/ng.py:240-256, :99-112).  Two passes per plane,
+// every line transformed once, in place, in shared memory:
 //
 //   invert (grid plane -> image):
-//     rows : FFT along v of every grid row u; only the npix_y outputs that fall on the image are
-//            kept and go to the intermediate T[npix_y/2][nu][2] (pairs of image columns, so that a
-//            row's outputs are 16-byte pieces at a stride of nu*16 bytes) by TMA tensor stores
-//            (cp.async.bulk.tensor.3d) straight out of the line buffer;
-//     cols : FFT along u of every kept column; each of the npix_x kept outputs is multiplied by the
-//            w-screen exp(-2 pi i w (n-1)) in registers and its real part is accumulated into the
-//            transposed image accumulator accT[npix_y][npix_x].
+//     rows : persistent blocks; TMA bulk loads (cp.async.bulk + mbarrier) bring row u+1 into the
+//            second line buffer while row u is transformed along v; only the npix_y outputs that
+//            fall on the image are kept and leave as 16-byte pieces (two adjacent image columns)
+//            through TMA tensor stores into T[npix_y/2][nu][2];
+//     cols : one TMA bulk load per PAIR of image columns (its nu 16-byte pieces are contiguous in
+//            T); the first stage splits the pieces into the two line buffers, each column is
+//            transformed along u, the npix_x kept outputs are multiplied by the w-screen
+//            exp(-2 pi i w (n-1)) in registers and their real parts accumulated into the
+//            transposed image accumulator accT[npix_y][npix_x]; the next pair's load is issued as
+//            soon as the last stage of the second column has read its buffer.
 //   predict (image -> grid plane) is the adjoint:
-//     cols : pre-corrected image column * exp(+2 pi i w (n-1)), zero-padded to nu, FFT along u,
-//            written to T;
-//     rows : TMA tensor loads gather a row's 16-byte pieces into the (zero-padded) line buffer,
-//            FFT along v, whole row written to the plane.
+//     cols : pre-corrected image column * exp(+2 pi i w (n-1)), zero-padded to nu (the screen and
+//            the padding happen in the first stage's loads), both columns of a pair transformed,
+//            then written to T as whole 16-byte pieces;
+//     rows : TMA tensor loads gather row u+1's pieces while row u is transformed (the rows between
+//            the two kept ranges read as zero in the first stage); whole rows written to the plane.
 //
 // Per plane this moves nu*nv*8 + 2*nu*npix*8 + 2*npix^2*4 bytes instead of cuFFT's 8 passes over
 // nu*nv*8 plus the screen kernel's cropped read.
@@ -29,16 +34,12 @@
 #include <cstdlib>
 #include <vector>
 
-#include "fft_lines.cuh"
+#include "fft_inplace.cuh"
 #include "kernels.h"
 
 namespace b2g {
 
-using hfft::LinePlan;
-
 namespace {
-
-constexpr int kThreads = 512;
 
 // ---- PTX helpers (TMA, mbarrier) ----------------------------------------------------------
 __device__ __forceinline__ uint32_t smem_u32(const void *p)
@@ -49,16 +50,6 @@ __device__ __forceinline__ void fence_proxy_async()
 {
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
-__device__ __forceinline__ void tma_store_3d(const CUtensorMap *map, const void *smem, int c0, int c1,
-                                             int c2)
-{
-    asm volatile("cp.async.bulk.tensor.3d.global.shared::cta.bulk_group [%0, {%2, %3, %4}], [%1];"
-                 ::"l"(reinterpret_cast<uint64_t>(map)), "r"(smem_u32(smem)), "r"(c0), "r"(c1), "r"(c2)
-                 : "memory");
-}
-__device__ __forceinline__ void tma_commit() { asm volatile("cp.async.bulk.commit_group;" ::: "memory"); }
-__device__ __forceinline__ void tma_wait_read() { asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory"); }
-__device__ __forceinline__ void tma_wait_all() { asm volatile("cp.async.bulk.wait_group 0;" ::: "memory"); }
 __device__ __forceinline__ void tma_load_3d(void *smem, const CUtensorMap *map, uint64_t *bar, int c0,
                                             int c1, int c2)
 {
@@ -68,9 +59,19 @@ __device__ __forceinline__ void tma_load_3d(void *smem, const CUtensorMap *map, 
                  "r"(c1), "r"(c2)
                  : "memory");
 }
+// contiguous global -> shared bulk copy (bytes: multiple of 16, both addresses 16-byte aligned)
+__device__ __forceinline__ void bulk_load(void *smem, const void *gmem, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_u32(smem)), "l"(reinterpret_cast<uint64_t>(gmem)), "r"(bytes), "r"(smem_u32(bar))
+                 : "memory");
+}
 __device__ __forceinline__ void mbar_init(uint64_t *bar, int count)
 {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init()
+{
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
 }
 __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
@@ -78,18 +79,27 @@ __device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes)
                  : "memory");
 }
-__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity)
 {
+    uint32_t ok;
     asm volatile(
         "{\n"
         ".reg .pred p;\n"
-        "WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra DONE_%=;\n"
-        "bra WAIT_%=;\n"
-        "DONE_%=:\n"
-        "}\n" ::"r"(smem_u32(bar)), "r"(parity)
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity)
         : "memory");
+    return ok != 0;
+}
+// A transfer that never completes (a bad descriptor) must not hang the device: trap after ~2 s.
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    if (mbar_try_wait(bar, parity)) return;
+    const long long t0 = clock64();
+    while (!mbar_try_wait(bar, parity))
+        if (clock64() - t0 > 4000000000LL) __trap();
 }
 
 // ---- w-screen -----------------------------------------------------------------------------
@@ -123,228 +133,376 @@ __device__ __forceinline__ int image_index(int k, int n, int npix, int h)
     return k < npix - h ? k + h : (k >= n - h ? k - (n - h) : -1);
 }
 
-struct Smem {
-    float2 *a, *b, *t0, *t1;
-    uint64_t *bar;
+// ---- shared-memory carve-up ---------------------------------------------------------------------
+// [X0 | X1 | twiddle tables | two mbarriers]; line buffers rounded to 128 B so that both are valid
+// TMA bases
+template <class P> struct SmemLayout {
+    static constexpr int NPADA = (P::NPAD + 15) & ~15;
+    static constexpr size_t X_BYTES = size_t(NPADA) * 8;
+    static constexpr size_t TW_OFF = 2 * X_BYTES;
+    static constexpr size_t BAR_OFF = TW_OFF + ((size_t(P::TW_ENTRIES) * 8 + 15) & ~size_t(15));
+    static constexpr size_t BYTES = BAR_OFF + 16;
+    static_assert(2 * X_BYTES >= size_t(P::N) * 16, "a pair block of 16-byte pieces must fit the two buffers");
 };
-__device__ __forceinline__ Smem carve(unsigned char *raw, int nline, int n_hi)
+
+template <class P> constexpr int min_blocks() { return P::T >= 320 ? 1 : (P::T >= 160 ? 2 : 4); }
+
+template <class P>
+__device__ __forceinline__ void load_tables(float2 *tws, const float2 *__restrict__ tw, int tid)
 {
-    Smem s;
-    s.a = reinterpret_cast<float2 *>(raw);
-    s.b = s.a + nline;
-    s.t0 = s.b + nline;
-    s.t1 = s.t0 + hfft::kTwLow;
-    s.bar = reinterpret_cast<uint64_t *>(s.t1 + ((n_hi + 1) & ~1));
-    return s;
-}
-inline size_t smem_bytes(const LinePlan &p)
-{
-    // line buffers padded to 128 B so that both are valid TMA box bases
-    const size_t nline = (size_t(p.n) + 15) & ~size_t(15);
-    return 2 * nline * 8 + hfft::kTwLow * 8 + ((p.n_hi + 1) & ~1) * 8 + 16;
+    for (int i = tid; i < P::TW_ENTRIES; i += P::THREADS) tws[i] = tw[i];
 }
 
-struct SyncThreads {
-    __device__ __forceinline__ void operator()() const { __syncthreads(); }
+// barrier between the phases of the line transform, with a hook after a chosen call
+template <class Hook> struct HookSync {
+    int calls, at;
+    Hook hook;
+    __device__ __forceinline__ void operator()()
+    {
+        fence_proxy_async();     // generic accesses of the buffers ordered before later TMA writes
+        __syncthreads();
+        if (++calls == at) hook();
+    }
+};
+struct NoHook {
+    __device__ __forceinline__ void operator()() const {}
 };
 
 // ---- invert, rows: plane[u][:] -> T[:, u, :] (kept columns) ----------------------------------
-// tw: {t0, t1} of the +1 transform along v.  Boxes of `pb` column pairs.
-__global__ void __launch_bounds__(kThreads, 1)
-hfft_rows_inv_kernel(PlaneGeo g, LinePlan lp, const float2 *__restrict__ tw,
-                     const float2 *__restrict__ plane, const __grid_constant__ CUtensorMap tmap, int pb)
+// tw: tables of the +1 transform along v.  The last stage's outputs stay in registers: lanes
+// 2m / 2m+1 hold adjacent columns, one exchange builds the 16-byte piece (two adjacent image
+// columns of row u) that goes to T[pair][u] with one vector store -- no staging buffer, so the line
+// buffer is free (and refilled by TMA) as soon as the last stage has read it.
+template <class P>
+__global__ void __launch_bounds__(P::THREADS, min_blocks<P>())
+hfft_rows_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *__restrict__ plane,
+                     float4 *__restrict__ T4)
 {
     extern __shared__ __align__(128) unsigned char raw[];
-    const int nline = (lp.n + 15) & ~15;
-    Smem sm = carve(raw, nline, lp.n_hi);
+    using L = SmemLayout<P>;
+    using LS = hfft::LastStage<P>;
+    static_assert(LS::C == 1 && LS::NS % 2 == 0 && LS::R % 2 == 0, "pair exchange layout");
+    float2 *X0 = reinterpret_cast<float2 *>(raw);
+    float2 *tws = reinterpret_cast<float2 *>(raw + L::TW_OFF);
+    uint64_t *bar = reinterpret_cast<uint64_t *>(raw + L::BAR_OFF);
     const int tid = threadIdx.x;
-    for (int i = tid; i < hfft::kTwLow; i += kThreads) sm.t0[i] = tw[i];
-    for (int i = tid; i < lp.n_hi; i += kThreads) sm.t1[i] = tw[hfft::kTwLow + i];
+    load_tables<P>(tws, tw, tid);
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        mbar_init(bar + 1, 1);
+        mbar_fence_init();
+    }
     __syncthreads();
-    float2 *first = sm.a, *second = sm.b;
-    const int nv = g.nv, hy = g.hy, half_pairs = hy / 2;
-    bool pending = false;      // a TMA store may still be reading the buffer it was issued from
-    for (int u = blockIdx.x; u < g.nu; u += gridDim.x) {
-        const float2 *row = plane + (size_t)u * nv;
-        // the last stage writes buffer `outb` (stage s writes `first` if s is even)
-        float2 *outb = ((lp.nstage - 1) & 1) ? second : first;
-        auto load = [row](int i) { return __ldg(row + i); };
-        auto store = [outb](int k, float2 v) { outb[k] = v; };
-        int calls = 0;
-        auto sync = [&]() {
-            // stage 0 wrote `first`, which the previous row's store never reads (see the swap
-            // below); every later stage may write the buffer that store is still reading
-            if (calls++ == 0 && pending) {
-                if (tid == 0) tma_wait_read();
-                pending = false;
+    constexpr int nv = P::N;
+    constexpr uint32_t row_bytes = uint32_t(P::N) * 8u;
+    const int hy = g.hy, half_pairs = hy / 2;
+    const bool active = tid < P::T;
+    if (tid == 0) {
+        for (int b = 0; b < 2; ++b) {
+            const int u = blockIdx.x + b * gridDim.x;
+            if (u < g.nu) {
+                mbar_expect_tx(bar + b, row_bytes);
+                bulk_load(X0 + b * L::NPADA, plane + (size_t)u * nv, row_bytes, bar + b);
             }
-            __syncthreads();
-        };
-        if (lp.nstage == 1 && pending) {
-            if (tid == 0) tma_wait_read();
-            pending = false;
-            __syncthreads();
-        }
-        hfft::fft_line<1>(lp, first, second, sm.t0, sm.t1, tid, kThreads, load, store, sync);
-        fence_proxy_async();         // the line written by generic stores -> visible to the TMA
-        __syncthreads();
-        if (tid == 0) {
-            // image columns b >= hy come from k = b - hy in [0, hy); b < hy from k = nv - hy + b
-            for (int q = 0; q < half_pairs; q += pb) {
-                tma_store_3d(&tmap, outb + 2 * q, 0, u, half_pairs + q);
-                tma_store_3d(&tmap, outb + (nv - hy) + 2 * q, 0, u, q);
-            }
-            tma_commit();
-        }
-        pending = true;
-        // next row: its stage 0 must not write `outb`
-        if (outb == first) {
-            float2 *t = first;
-            first = second;
-            second = t;
         }
     }
-    if (tid == 0) tma_wait_all();
+    int it = 0;
+    for (int u = blockIdx.x; u < g.nu; u += gridDim.x, ++it) {
+        const int b = it & 1;
+        float2 *X = X0 + b * L::NPADA;
+        mbar_wait(bar + b, (uint32_t)(it >> 1) & 1u);
+        auto rd0 = [X](int i) { return X[i]; };                 // linear, as the bulk load left it
+        const int un = u + 2 * gridDim.x;
+        auto hook = [&]() {
+            // the last stage has read X: refill it with the row after next
+            if (tid == 0 && un < g.nu) {
+                mbar_expect_tx(bar + b, row_bytes);
+                bulk_load(X, plane + (size_t)un * nv, row_bytes, bar + b);
+            }
+        };
+        HookSync<NoHook> sync0{0, -1, NoHook()};
+        hfft::line_stage0<P, 1>(tid, X, tws, rd0, sync0);
+        HookSync<decltype(hook)> sync{0, 2 * P::NSTAGE - 3, hook};
+        float2 v[1][LS::R];
+        hfft::line_rest_open<P, 1>(tid, X, tws, v, sync);
+        if (active) hfft::stage_compute<P, 1, LS::R, 1, LS::NS>(tid, v, tws + LS::TW_OFF);
+        // v[0][r] is column k = tid + r * NS of row u
+        const bool odd = tid & 1;
+        const int kb0 = tid & ~1;
+#pragma unroll
+        for (int r = 0; r < LS::R; r += 2) {
+            const float2 send = odd ? v[0][r] : v[0][r + 1];
+            float2 recv;
+            recv.x = __shfl_xor_sync(0xffffffffu, send.x, 1);
+            recv.y = __shfl_xor_sync(0xffffffffu, send.y, 1);
+            const int kb = kb0 + (odd ? r + 1 : r) * LS::NS;      // first column of this lane's piece
+            const float4 piece = odd ? make_float4(recv.x, recv.y, v[0][r + 1].x, v[0][r + 1].y)
+                                     : make_float4(v[0][r].x, v[0][r].y, recv.x, recv.y);
+            // image columns b >= hy come from k = b - hy in [0, hy); b < hy from k = nv - hy + b
+            int pair = -1;
+            if (kb < hy) pair = half_pairs + (kb >> 1);
+            else if (kb >= nv - hy) pair = (kb - (nv - hy)) >> 1;
+            if (active && pair >= 0) T4[(size_t)pair * g.nu + u] = piece;
+        }
+    }
 }
 
-// ---- invert, columns: T[b/2][:][b&1] -> accT[b][:] (+)= Re(F * screen) --------------------------
-__global__ void __launch_bounds__(kThreads, 1)
-hfft_cols_inv_kernel(PlaneGeo g, LinePlan lp, const float2 *__restrict__ tw,
-                     const float2 *__restrict__ T, double w, float *__restrict__ accT)
+__device__ __forceinline__ void red_add_v4(float *addr, float a, float b, float c, float d)
+{
+    asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};" ::"l"(addr), "f"(a), "f"(b), "f"(c), "f"(d)
+                 : "memory");
+}
+
+// ---- invert, columns: T[b/2][:][b&1] -> accT[b][:] += Re(F * screen) ----------------------------
+// The kept outputs are multiplied by the w-screen in registers; a 4 x 4 lane transpose gives every
+// lane four consecutive image pixels, which are added to the accumulator with one vector reduction
+// (no read-modify-write round trip; every pixel receives exactly one addition per plane, so the
+// result does not depend on any ordering).
+template <class P>
+__global__ void __launch_bounds__(P::THREADS, min_blocks<P>())
+hfft_cols_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *__restrict__ T, double w,
+                     float *__restrict__ accT)
 {
     extern __shared__ __align__(128) unsigned char raw[];
-    const int nline = (lp.n + 15) & ~15;
-    Smem sm = carve(raw, nline, lp.n_hi);
+    using L = SmemLayout<P>;
+    using LS = hfft::LastStage<P>;
+    static_assert(LS::C == 1 && LS::NS % 4 == 0 && LS::R % 4 == 0, "quad exchange layout");
+    float2 *X0 = reinterpret_cast<float2 *>(raw);
+    float2 *X1 = X0 + L::NPADA;
+    const float4 *P4 = reinterpret_cast<const float4 *>(raw);      // the pair block as loaded
+    float2 *tws = reinterpret_cast<float2 *>(raw + L::TW_OFF);
+    uint64_t *bar = reinterpret_cast<uint64_t *>(raw + L::BAR_OFF);
     const int tid = threadIdx.x;
-    for (int i = tid; i < hfft::kTwLow; i += kThreads) sm.t0[i] = tw[i];
-    for (int i = tid; i < lp.n_hi; i += kThreads) sm.t1[i] = tw[hfft::kTwLow + i];
+    load_tables<P>(tws, tw, tid);
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        mbar_fence_init();
+    }
     __syncthreads();
-    const int nu = g.nu, npx = g.npix_x, hx = g.hx;
-    for (int pair = blockIdx.x; pair < g.npix_y / 2; pair += gridDim.x) {
+    constexpr int nu = P::N;
+    constexpr uint32_t pair_bytes = uint32_t(P::N) * 16u;
+    const int npx = g.npix_x, hx = g.hx, npairs = g.npix_y / 2;
+    const bool active = tid < P::T;
+    if (tid == 0 && (int)blockIdx.x < npairs) {
+        mbar_expect_tx(bar, pair_bytes);
+        bulk_load(raw, T + (size_t)blockIdx.x * nu * 2, pair_bytes, bar);
+    }
+    int it = 0;
+    for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x, ++it) {
+        mbar_wait(bar, (uint32_t)it & 1u);
+        {
+            // stage 0 of both columns: the 16-byte pieces split into the two line buffers
+            float2 v0[P::C0][P::R0], v1[P::C0][P::R0];
+            constexpr int q = P::N / P::R0;
+            if (active) {
+#pragma unroll
+                for (int c = 0; c < P::C0; ++c)
+#pragma unroll
+                    for (int t = 0; t < P::R0; ++t) {
+                        const float4 p = P4[tid + c * P::T + t * q];
+                        v0[c][t] = make_float2(p.x, p.y);
+                        v1[c][t] = make_float2(p.z, p.w);
+                    }
+            }
+            __syncthreads();
+            if (active) {
+                auto wr0 = [X0](int i, float2 val) { X0[hfft::padded<P>(i)] = val; };
+                auto wr1 = [X1](int i, float2 val) { X1[hfft::padded<P>(i)] = val; };
+                hfft::stage_write<P, 1, P::R0, P::C0, 1>(tid, v0, tws, wr0);
+                hfft::stage_write<P, 1, P::R0, P::C0, 1>(tid, v1, tws, wr1);
+            }
+            __syncthreads();
+        }
+        const int pn = pair + gridDim.x;
+#pragma unroll 1
         for (int c = 0; c < 2; ++c) {
             const int b = 2 * pair + c;
-            const float2 *src = T + (size_t)pair * nu * 2 + c;
+            float2 *X = c ? X1 : X0;
+            // after the last stage of the SECOND column has read its buffer both are free: the
+            // next pair's load runs under that stage's arithmetic and the epilogue
+            auto hook = [=]() {
+                if (c == 1 && tid == 0 && pn < npairs) {
+                    mbar_expect_tx(bar, pair_bytes);
+                    bulk_load(raw, T + (size_t)pn * nu * 2, pair_bytes, bar);
+                }
+            };
+            HookSync<decltype(hook)> sync{0, 2 * P::NSTAGE - 3, hook};
+            float2 v[1][LS::R];
+            hfft::line_rest_open<P, 1>(tid, X, tws, v, sync);
+            if (active) hfft::stage_compute<P, 1, LS::R, 1, LS::NS>(tid, v, tws + LS::TW_OFF);
+            // v[0][r] is image row index k = tid + r * NS of column b: screen, keep the real part
             const double y = (double)(b - g.hy) * g.psy;
             const double y2 = y * y;
-            float *dst = accT + (size_t)b * npx;
-            auto load = [src](int i) { return __ldg(src + 2 * i); };
-            auto store = [=](int k, float2 v) {
-                const int a = image_index(k, nu, npx, hx);
-                if (a < 0) return;
-                float val = v.x;
-                if (g.wstack) {
-                    const double x = (double)(a - hx) * g.psx;
-                    float s, co;
-                    if (!screen_sincos(fma(x, x, y2), -w, s, co)) return;
-                    val = v.x * co - v.y * s;
+            float val[LS::R];
+#pragma unroll
+            for (int r = 0; r < LS::R; ++r) {
+                val[r] = 0.f;
+                const int a = image_index(tid + r * LS::NS, nu, npx, hx);
+                if (active && a >= 0) {
+                    if (g.wstack) {
+                        const double x = (double)(a - hx) * g.psx;
+                        float s, co;
+                        if (screen_sincos(fma(x, x, y2), -w, s, co)) val[r] = v[0][r].x * co - v[0][r].y * s;
+                    } else {
+                        val[r] = v[0][r].x;
+                    }
                 }
-                dst[a] += val;
-            };
-            hfft::fft_line<1>(lp, sm.a, sm.b, sm.t0, sm.t1, tid, kThreads, load, store, SyncThreads());
-            __syncthreads();
+            }
+            float *dst = accT + (size_t)b * npx;
+            const int l4 = tid & 3;
+            const bool hi2 = l4 & 2, hi1 = l4 & 1;
+#pragma unroll
+            for (int r = 0; r < LS::R; r += 4) {
+                // 4 x 4 transpose over lanes (l4) x outputs (r .. r+3)
+                const float s0 = hi2 ? val[r] : val[r + 2], s1 = hi2 ? val[r + 1] : val[r + 3];
+                const float t0 = __shfl_xor_sync(0xffffffffu, s0, 2), t1 = __shfl_xor_sync(0xffffffffu, s1, 2);
+                const float a0 = hi2 ? t0 : val[r], a1 = hi2 ? t1 : val[r + 1];
+                const float b0 = hi2 ? val[r + 2] : t0, b1 = hi2 ? val[r + 3] : t1;
+                const float u0 = hi1 ? a0 : a1, u1 = hi1 ? b0 : b1;
+                const float w0 = __shfl_xor_sync(0xffffffffu, u0, 1), w1 = __shfl_xor_sync(0xffffffffu, u1, 1);
+                // this lane now holds output r + l4 of the four lanes 4m .. 4m+3
+                const float f0 = hi1 ? w0 : a0, f1 = hi1 ? a1 : w0, f2 = hi1 ? w1 : b0, f3 = hi1 ? b1 : w1;
+                const int kb = (tid & ~3) + (r + l4) * LS::NS;
+                const int a = image_index(kb, nu, npx, hx);
+                if (active && a >= 0) red_add_v4(dst + a, f0, f1, f2, f3);
+            }
         }
     }
 }
 
 // ---- predict, columns: preT[b][:] * screen, zero-padded -> T[b/2][:][b&1] -------------------------
-__global__ void __launch_bounds__(kThreads, 1)
-hfft_cols_fwd_kernel(PlaneGeo g, LinePlan lp, const float2 *__restrict__ tw,
-                     const float *__restrict__ preT, double w, float2 *__restrict__ T)
+template <class P>
+__global__ void __launch_bounds__(P::THREADS, min_blocks<P>())
+hfft_cols_fwd_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float *__restrict__ preT, double w,
+                     float2 *__restrict__ T)
 {
     extern __shared__ __align__(128) unsigned char raw[];
-    const int nline = (lp.n + 15) & ~15;
-    Smem sm = carve(raw, nline, lp.n_hi);
+    using L = SmemLayout<P>;
+    float2 *X0 = reinterpret_cast<float2 *>(raw);
+    float2 *X1 = X0 + L::NPADA;
+    float2 *tws = reinterpret_cast<float2 *>(raw + L::TW_OFF);
     const int tid = threadIdx.x;
-    for (int i = tid; i < hfft::kTwLow; i += kThreads) sm.t0[i] = tw[i];
-    for (int i = tid; i < lp.n_hi; i += kThreads) sm.t1[i] = tw[hfft::kTwLow + i];
+    load_tables<P>(tws, tw, tid);
     __syncthreads();
-    const int nu = g.nu, npx = g.npix_x, hx = g.hx;
-    for (int pair = blockIdx.x; pair < g.npix_y / 2; pair += gridDim.x) {
+    constexpr int nu = P::N;
+    const int npx = g.npix_x, hx = g.hx, npairs = g.npix_y / 2;
+    const bool active = tid < P::T;
+    float4 *T4 = reinterpret_cast<float4 *>(T);
+    for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
+#pragma unroll 1
         for (int c = 0; c < 2; ++c) {
             const int b = 2 * pair + c;
+            float2 *X = c ? X1 : X0;
             const float *src = preT + (size_t)b * npx;
-            float2 *dst = T + (size_t)pair * nu * 2 + c;
             const double y = (double)(b - g.hy) * g.psy;
             const double y2 = y * y;
-            auto load = [=](int i) {
-                const int a = image_index(i, nu, npx, hx);
-                if (a < 0) return make_float2(0.f, 0.f);
-                const float val = __ldg(src + a);
-                if (val == 0.f) return make_float2(0.f, 0.f);
-                if (!g.wstack) return make_float2(val, 0.f);
-                const double x = (double)(a - hx) * g.psx;
-                float s, co;
-                if (!screen_sincos(fma(x, x, y2), w, s, co)) return make_float2(0.f, 0.f);
-                return make_float2(val * co, val * s);
-            };
-            auto store = [dst](int k, float2 v) { dst[2 * k] = v; };
-            hfft::fft_line<-1>(lp, sm.a, sm.b, sm.t0, sm.t1, tid, kThreads, load, store, SyncThreads());
-            __syncthreads();
+            auto wr = [X](int k, float2 v) { X[k] = v; };         // linear, for the piece copy below
+            HookSync<NoHook> sync{0, -1, NoHook()};
+            {
+                // stage 0: all of the thread's image pixels are requested before the first screen
+                // is evaluated (40 independent loads in flight), zero-padding by predication
+                float2 v[P::C0][P::R0];
+                constexpr int q = P::N / P::R0;
+                if (active) {
+                    float in[P::C0][P::R0];
+#pragma unroll
+                    for (int cc = 0; cc < P::C0; ++cc)
+#pragma unroll
+                        for (int t = 0; t < P::R0; ++t) {
+                            const int a = image_index(tid + cc * P::T + t * q, nu, npx, hx);
+                            in[cc][t] = a >= 0 ? __ldg(src + a) : 0.f;
+                        }
+#pragma unroll
+                    for (int cc = 0; cc < P::C0; ++cc)
+#pragma unroll
+                        for (int t = 0; t < P::R0; ++t) {
+                            const float val = in[cc][t];
+                            float2 z = make_float2(val, 0.f);
+                            if (g.wstack && val != 0.f) {
+                                const int a = image_index(tid + cc * P::T + t * q, nu, npx, hx);
+                                const double x = (double)(a - hx) * g.psx;
+                                float s, co;
+                                z = screen_sincos(fma(x, x, y2), w, s, co) ? make_float2(val * co, val * s)
+                                                                            : make_float2(0.f, 0.f);
+                            }
+                            v[cc][t] = z;
+                        }
+                }
+                sync();
+                if (active) {
+                    auto wrX = [X](int i, float2 val) { X[hfft::padded<P>(i)] = val; };
+                    hfft::stage_write<P, -1, P::R0, P::C0, 1>(tid, v, tws, wrX);
+                }
+                sync();
+            }
+            hfft::line_rest<P, -1>(tid, X, tws, wr, sync);
         }
+        __syncthreads();
+        float4 *dst = T4 + (size_t)pair * nu;
+        for (int i = tid; i < nu; i += P::THREADS) {
+            const float2 a = X0[i], bb = X1[i];
+            dst[i] = make_float4(a.x, a.y, bb.x, bb.y);
+        }
+        __syncthreads();
     }
 }
 
 // ---- predict, rows: T[:, u, :] (kept columns, zero elsewhere) -> plane[u][:] ---------------------
-__global__ void __launch_bounds__(kThreads, 1)
-hfft_rows_fwd_kernel(PlaneGeo g, LinePlan lp, const float2 *__restrict__ tw,
-                     const __grid_constant__ CUtensorMap tmap, int pb, float2 *__restrict__ plane)
+template <class P>
+__global__ void __launch_bounds__(P::THREADS, min_blocks<P>())
+hfft_rows_fwd_kernel(PlaneGeo g, const float2 *__restrict__ tw, const __grid_constant__ CUtensorMap tmap,
+                     int pb, float2 *__restrict__ plane)
 {
     extern __shared__ __align__(128) unsigned char raw[];
-    const int nline = (lp.n + 15) & ~15;
-    Smem sm = carve(raw, nline, lp.n_hi);
+    using L = SmemLayout<P>;
+    float2 *X0 = reinterpret_cast<float2 *>(raw);
+    float2 *tws = reinterpret_cast<float2 *>(raw + L::TW_OFF);
+    uint64_t *bar = reinterpret_cast<uint64_t *>(raw + L::BAR_OFF);
     const int tid = threadIdx.x;
-    for (int i = tid; i < hfft::kTwLow; i += kThreads) sm.t0[i] = tw[i];
-    for (int i = tid; i < lp.n_hi; i += kThreads) sm.t1[i] = tw[hfft::kTwLow + i];
-    if (tid == 0) mbar_init(sm.bar, 1);
+    load_tables<P>(tws, tw, tid);
+    if (tid == 0) {
+        mbar_init(bar, 1);
+        mbar_init(bar + 1, 1);
+        mbar_fence_init();
+    }
     __syncthreads();
-    const int nv = g.nv, hy = g.hy, half_pairs = hy / 2;
+    constexpr int nv = P::N;
+    const int hy = g.hy, half_pairs = hy / 2;
     const uint32_t row_bytes = (uint32_t)g.npix_y * 8u;
-    // `inb` receives the row (TMA + zero fill); stage 0 reads it and writes `first` = the other one
-    float2 *inb = sm.b, *first = sm.a;
-    uint32_t parity = 0;
-    auto fetch = [&](int u, float2 *buf) {
-        // zero the lines between the two kept ranges (generic stores, ordered by the barriers of
-        // the FFT stages / the one below), then gather the kept ones
-        for (int i = hy + tid; i < nv - hy; i += kThreads) buf[i] = make_float2(0.f, 0.f);
-        if (tid == 0) {
-            mbar_expect_tx(sm.bar, row_bytes);
-            for (int q = 0; q < half_pairs; q += pb) {
-                tma_load_3d(buf + 2 * q, &tmap, sm.bar, 0, u, half_pairs + q);
-                tma_load_3d(buf + (nv - hy) + 2 * q, &tmap, sm.bar, 0, u, q);
-            }
+    // gather the kept columns of row u (16-byte pieces at a stride of nu * 16 bytes) into buf
+    auto fetch = [&](int u, float2 *buf, uint64_t *mb) {
+        mbar_expect_tx(mb, row_bytes);
+        for (int q = 0; q < half_pairs; q += pb) {
+            tma_load_3d(buf + 2 * q, &tmap, mb, 0, u, half_pairs + q);
+            tma_load_3d(buf + (nv - hy) + 2 * q, &tmap, mb, 0, u, q);
         }
     };
-    int u = blockIdx.x;
-    if (u < g.nu) fetch(u, inb);
-    for (; u < g.nu; u += gridDim.x) {
-        mbar_wait(sm.bar, parity);
-        parity ^= 1u;
-        __syncthreads();             // zero fill by all threads complete
+    if (tid == 0) {
+        for (int b = 0; b < 2; ++b) {
+            const int u = blockIdx.x + b * gridDim.x;
+            if (u < g.nu) fetch(u, X0 + b * L::NPADA, bar + b);
+        }
+    }
+    int it = 0;
+    for (int u = blockIdx.x; u < g.nu; u += gridDim.x, ++it) {
+        const int b = it & 1;
+        float2 *X = X0 + b * L::NPADA;
+        mbar_wait(bar + b, (uint32_t)(it >> 1) & 1u);
         float2 *row = plane + (size_t)u * nv;
-        const float2 *in = inb;
-        float2 *second = inb;
-        auto load = [in](int i) { return in[i]; };
-        auto store = [row](int k, float2 v) { row[k] = v; };
-        // the buffer the last stage does not read is free from the barrier before it: prefetch
-        // the next row into it while the last stage runs
-        const int un = u + gridDim.x;
-        float2 *lastread = lp.nstage == 1 ? inb : (((lp.nstage - 2) & 1) ? second : first);
-        float2 *target = lastread == first ? second : first;
-        int calls = 0;
-        auto sync = [&]() {
-            fence_proxy_async();     // generic accesses to `target` ordered before the TMA writes
-            __syncthreads();
-            if (++calls == lp.nstage - 1 && un < g.nu) fetch(un, target);
+        auto rd0 = [X, hy](int i) {
+            return (i < hy || i >= nv - hy) ? X[i] : make_float2(0.f, 0.f);
         };
-        if (lp.nstage == 1 && un < g.nu) fetch(un, target);
-        hfft::fft_line<-1>(lp, first, second, sm.t0, sm.t1, tid, kThreads, load, store, sync);
-        __syncthreads();
-        // next row: input sits in `target`
-        inb = target;
-        first = (target == sm.a) ? sm.b : sm.a;
+        auto wr = [row](int k, float2 v) { row[k] = v; };
+        const int un = u + 2 * gridDim.x;
+        // X is free once the last stage has read it: prefetch the row after next under that
+        // stage's arithmetic and stores
+        auto hook = [&]() {
+            if (tid == 0 && un < g.nu) fetch(un, X, bar + b);
+        };
+        HookSync<decltype(hook)> sync{0, 2 * P::NSTAGE - 1, hook};
+        hfft::line_inplace<P, -1>(tid, X, tws, rd0, wr, sync);
     }
 }
-
 // ---- image <-> transposed accumulator ----------------------------------------------------------
 __device__ __forceinline__ double nm1_exact(double r2) { return -r2 / (sqrt(1.0 - r2) + 1.0); }
 
@@ -410,6 +568,7 @@ precorrect_t_kernel(ImgGeo g, const Tin *__restrict__ dirty, float *__restrict__
     }
 }
 
+
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *,
                                   const cuuint64_t *, const cuuint64_t *, const cuuint32_t *,
                                   const cuuint32_t *, CUtensorMapInterleave, CUtensorMapSwizzle,
@@ -428,18 +587,51 @@ EncodeTiledFn encode_fn()
     return fn;
 }
 
+// ---- per-plan launch tables ----------------------------------------------------------------------
+struct LineOps {
+    int n = 0, threads = 0, tw_entries = 0;
+    size_t smem = 0;
+    void (*build_tw)(int sign, float2 *tw) = nullptr;
+    const void *rows_inv = nullptr, *cols_inv = nullptr, *cols_fwd = nullptr, *rows_fwd = nullptr;
+};
+
+template <class P> LineOps make_ops()
+{
+    LineOps o;
+    o.n = P::N;
+    o.threads = P::THREADS;
+    o.tw_entries = P::TW_ENTRIES;
+    o.smem = SmemLayout<P>::BYTES;
+    o.build_tw = &hfft::build_twiddles<P>;
+    o.rows_inv = reinterpret_cast<const void *>(&hfft_rows_inv_kernel<P>);
+    o.cols_inv = reinterpret_cast<const void *>(&hfft_cols_inv_kernel<P>);
+    o.cols_fwd = reinterpret_cast<const void *>(&hfft_cols_fwd_kernel<P>);
+    o.rows_fwd = reinterpret_cast<const void *>(&hfft_rows_fwd_kernel<P>);
+    return o;
+}
+
+bool ops_for(int n, LineOps *o)
+{
+    switch (n) {
+    case 1600: *o = make_ops<hfft::Plan1600>(); return true;
+    case 3200: *o = make_ops<hfft::Plan3200>(); return true;
+    case 6400: *o = make_ops<hfft::Plan6400>(); return true;
+    case 12800: *o = make_ops<hfft::Plan12800>(); return true;
+    default: return false;
+    }
+}
+
 }  // namespace
 
 struct HandFft {
     PlaneGeo g;
-    LinePlan lu, lv;
-    float2 *d_tw = nullptr;       // [u+ | u- | v+ | v-], each kTwLow + n_hi entries
+    LineOps ou, ov;               // lines along u (columns pass), along v (rows pass)
+    float2 *d_tw = nullptr;       // [u+ | u- | v+ | v-]
     size_t off_up = 0, off_um = 0, off_vp = 0, off_vm = 0;
     float2 *d_T = nullptr;        // [npix_y/2][nu][2]
     CUtensorMap tmap;
     int pb = 0;
-    int nsm = 148;
-    size_t smem_u = 0, smem_v = 0;
+    int grid_rows_inv = 0, grid_rows_fwd = 0, grid_cols_inv = 0, grid_cols_fwd = 0;
 };
 
 int hfft_create(HandFft **out, const ImgGeo &ig, cudaStream_t s)
@@ -450,8 +642,8 @@ int hfft_create(HandFft **out, const ImgGeo &ig, cudaStream_t s)
     if (std::getenv("B2G_NO_HFFT")) return -1;
     if (npy % 4 != 0 || npx % 2 != 0 || npx > nu || npy > nv) return -1;
     if ((nv - hy) % 16 != 0 || hy % 16 != 0) return -1;   // TMA box bases: 128-byte aligned
-    LinePlan lu, lv;
-    if (hfft::plan_line(nu, &lu) || hfft::plan_line(nv, &lv)) return -1;
+    LineOps ou, ov;
+    if (!ops_for(nu, &ou) || !ops_for(nv, &ov)) return -1;
     int pb = 0;
     for (int d = 256; d >= 8; d -= 8)
         if ((hy / 2) % d == 0) {
@@ -465,27 +657,22 @@ int hfft_create(HandFft **out, const ImgGeo &ig, cudaStream_t s)
     cudaGetDevice(&dev);
     cudaDeviceGetAttribute(&max_smem, cudaDevAttrMaxSharedMemoryPerBlockOptin, dev);
     cudaDeviceGetAttribute(&nsm, cudaDevAttrMultiProcessorCount, dev);
-    const size_t su = smem_bytes(lu), sv = smem_bytes(lv);
-    if ((int)su > max_smem || (int)sv > max_smem) return -1;
+    if ((int)ou.smem > max_smem || (int)ov.smem > max_smem) return -1;
 
     HandFft *h = new HandFft();
     h->g = PlaneGeo{nu, nv, npx, npy, hx, hy, ig.pixsize_x, ig.pixsize_y, ig.wstack};
-    h->lu = lu;
-    h->lv = lv;
+    h->ou = ou;
+    h->ov = ov;
     h->pb = pb;
-    h->nsm = nsm;
-    h->smem_u = su;
-    h->smem_v = sv;
-    const size_t nu_tw = hfft::kTwLow + lu.n_hi, nv_tw = hfft::kTwLow + lv.n_hi;
     h->off_up = 0;
-    h->off_um = nu_tw;
-    h->off_vp = 2 * nu_tw;
-    h->off_vm = 2 * nu_tw + nv_tw;
-    std::vector<float2> tw(2 * nu_tw + 2 * nv_tw);
-    hfft::build_twiddles(lu, +1, tw.data() + h->off_up, tw.data() + h->off_up + hfft::kTwLow);
-    hfft::build_twiddles(lu, -1, tw.data() + h->off_um, tw.data() + h->off_um + hfft::kTwLow);
-    hfft::build_twiddles(lv, +1, tw.data() + h->off_vp, tw.data() + h->off_vp + hfft::kTwLow);
-    hfft::build_twiddles(lv, -1, tw.data() + h->off_vm, tw.data() + h->off_vm + hfft::kTwLow);
+    h->off_um = ou.tw_entries;
+    h->off_vp = 2 * size_t(ou.tw_entries);
+    h->off_vm = 2 * size_t(ou.tw_entries) + ov.tw_entries;
+    std::vector<float2> tw(2 * size_t(ou.tw_entries) + 2 * size_t(ov.tw_entries));
+    ou.build_tw(+1, tw.data() + h->off_up);
+    ou.build_tw(-1, tw.data() + h->off_um);
+    ov.build_tw(+1, tw.data() + h->off_vp);
+    ov.build_tw(-1, tw.data() + h->off_vm);
     cudaError_t e = cudaMallocAsync(&h->d_tw, tw.size() * sizeof(float2), s);
     if (e == cudaSuccess)
         e = cudaMemcpyAsync(h->d_tw, tw.data(), tw.size() * sizeof(float2), cudaMemcpyHostToDevice, s);
@@ -506,13 +693,27 @@ int hfft_create(HandFft **out, const ImgGeo &ig, cudaStream_t s)
         hfft_destroy(h, s);
         return -1;
     }
-    cudaFuncSetAttribute(hfft_rows_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sv);
-    cudaFuncSetAttribute(hfft_rows_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sv);
-    cudaFuncSetAttribute(hfft_cols_inv_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)su);
-    cudaFuncSetAttribute(hfft_cols_fwd_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)su);
-    if (cudaGetLastError() != cudaSuccess) {
-        hfft_destroy(h, s);
-        return -1;
+    // persistent grids: as many blocks as fit the device at once
+    struct K {
+        const void *fn;
+        const LineOps *o;
+        int *grid;
+        int lines;
+    } ks[4] = {{ov.rows_inv, &h->ov, &h->grid_rows_inv, nu},
+               {ov.rows_fwd, &h->ov, &h->grid_rows_fwd, nu},
+               {ou.cols_inv, &h->ou, &h->grid_cols_inv, npy / 2},
+               {ou.cols_fwd, &h->ou, &h->grid_cols_fwd, npy / 2}};
+    for (auto &k : ks) {
+        int per_sm = 0;
+        if (cudaFuncSetAttribute(k.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k.o->smem) != cudaSuccess ||
+            cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k.fn, k.o->threads, k.o->smem) != cudaSuccess ||
+            per_sm < 1) {
+            cudaGetLastError();
+            hfft_destroy(h, s);
+            return -1;
+        }
+        const long resident = (long)per_sm * nsm;
+        *k.grid = (int)(k.lines < resident ? k.lines : resident);
     }
     *out = h;
     return 0;
@@ -528,35 +729,41 @@ void hfft_destroy(HandFft *h, cudaStream_t s)
 
 void hfft_describe(const HandFft *h, char *buf, int n)
 {
-    int o = snprintf(buf, n, "u:%d=", h->lu.n);
-    for (int i = 0; i < h->lu.nstage; ++i) o += snprintf(buf + o, n - o, "%s%d", i ? "x" : "", h->lu.radix[i]);
-    o += snprintf(buf + o, n - o, " v:%d=", h->lv.n);
-    for (int i = 0; i < h->lv.nstage; ++i) o += snprintf(buf + o, n - o, "%s%d", i ? "x" : "", h->lv.radix[i]);
-    snprintf(buf + o, n - o, " box=%d pairs", h->pb);
+    snprintf(buf, n, "u:%d (%d threads, %zu B smem, grids %d/%d) v:%d (%d threads, %zu B smem, grids %d/%d) box=%d pairs",
+             h->ou.n, h->ou.threads, h->ou.smem, h->grid_cols_inv, h->grid_cols_fwd, h->ov.n, h->ov.threads,
+             h->ov.smem, h->grid_rows_inv, h->grid_rows_fwd, h->pb);
 }
 
 int hfft_invert_plane(HandFft *h, const cplx<float> *plane, double w, float *accT, cudaStream_t s)
 {
-    const PlaneGeo &g = h->g;
-    const int grid_r = g.nu < h->nsm ? g.nu : h->nsm;
-    const int grid_c = g.npix_y / 2 < h->nsm ? g.npix_y / 2 : h->nsm;
-    hfft_rows_inv_kernel<<<grid_r, kThreads, h->smem_v, s>>>(
-        g, h->lv, h->d_tw + h->off_vp, reinterpret_cast<const float2 *>(plane), h->tmap, h->pb);
-    hfft_cols_inv_kernel<<<grid_c, kThreads, h->smem_u, s>>>(g, h->lu, h->d_tw + h->off_up, h->d_T, w,
-                                                            accT);
-    return (int)cudaGetLastError();
+    PlaneGeo g = h->g;
+    const float2 *twv = h->d_tw + h->off_vp, *twu = h->d_tw + h->off_up;
+    const float2 *pl = reinterpret_cast<const float2 *>(plane);
+    const float2 *T = h->d_T;
+    float4 *T4 = reinterpret_cast<float4 *>(h->d_T);
+    void *a_rows[] = {&g, &twv, &pl, &T4};
+    cudaError_t e = cudaLaunchKernel(h->ov.rows_inv, dim3(h->grid_rows_inv), dim3(h->ov.threads), a_rows,
+                                     h->ov.smem, s);
+    if (e != cudaSuccess) return (int)e;
+    void *a_cols[] = {&g, &twu, &T, &w, &accT};
+    e = cudaLaunchKernel(h->ou.cols_inv, dim3(h->grid_cols_inv), dim3(h->ou.threads), a_cols, h->ou.smem, s);
+    return (int)e;
 }
 
 int hfft_predict_plane(HandFft *h, const float *preT, double w, cplx<float> *plane, cudaStream_t s)
 {
-    const PlaneGeo &g = h->g;
-    const int grid_r = g.nu < h->nsm ? g.nu : h->nsm;
-    const int grid_c = g.npix_y / 2 < h->nsm ? g.npix_y / 2 : h->nsm;
-    hfft_cols_fwd_kernel<<<grid_c, kThreads, h->smem_u, s>>>(g, h->lu, h->d_tw + h->off_um, preT, w,
-                                                            h->d_T);
-    hfft_rows_fwd_kernel<<<grid_r, kThreads, h->smem_v, s>>>(g, h->lv, h->d_tw + h->off_vm, h->tmap,
-                                                            h->pb, reinterpret_cast<float2 *>(plane));
-    return (int)cudaGetLastError();
+    PlaneGeo g = h->g;
+    const float2 *twv = h->d_tw + h->off_vm, *twu = h->d_tw + h->off_um;
+    float2 *pl = reinterpret_cast<float2 *>(plane);
+    float2 *T = h->d_T;
+    int pb = h->pb;
+    void *a_cols[] = {&g, &twu, &preT, &w, &T};
+    cudaError_t e = cudaLaunchKernel(h->ou.cols_fwd, dim3(h->grid_cols_fwd), dim3(h->ou.threads), a_cols,
+                                     h->ou.smem, s);
+    if (e != cudaSuccess) return (int)e;
+    void *a_rows[] = {&g, &twv, &h->tmap, &pb, &pl};
+    e = cudaLaunchKernel(h->ov.rows_fwd, dim3(h->grid_rows_fwd), dim3(h->ov.threads), a_rows, h->ov.smem, s);
+    return (int)e;
 }
 
 template <typename Tout>

@@ -322,7 +322,9 @@ def _invert(bvis, model, dopsf, normalise, subtract_model, kwargs):
         raise ValueError("invert_ng: the reference supports square images only (npixdirty = nx)")
     pixsize = _pixsize(im)
     vis_to_im = _vis_to_im(model, freq)
-    mfs = nchan == 1 and vnchan > 1
+    # (ng.py:228) -- a rank of a channel-sharded MFS inversion may own a single channel of the
+    # band: it still images into the one MFS plane
+    mfs = nchan == 1 and (vnchan > 1 or opt["shard"] == "channel")
     prec = wgridder._prec_code(opt["precision"])
 
     vis = _raw(bvis, "vis")

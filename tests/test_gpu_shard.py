@@ -35,8 +35,9 @@ def _launch(mode, world, out):
                                        str(out)], env=env, stdout=subprocess.PIPE,
                                       stderr=subprocess.STDOUT, text=True))
     logs = [p.communicate(timeout=600)[0] for p in procs]
-    for p, log in zip(procs, logs):
-        assert p.returncode == 0, log[-3000:]
+    failed = [f"--- rank {r} (exit {p.returncode}) ---\n{log[-2500:]}"
+              for r, (p, log) in enumerate(zip(procs, logs)) if p.returncode != 0]
+    assert not failed, "\n".join(failed)
 
 
 @pytest.mark.timeout(900)

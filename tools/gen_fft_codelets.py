@@ -12,7 +12,7 @@ Composite sizes use Cooley-Tukey on registers with literal twiddle constants (tr
 import math
 import os
 
-SIZES = [2, 3, 4, 5, 8, 9, 15, 16, 25, 32]
+SIZES = [2, 3, 4, 5, 8, 9, 10, 15, 16, 20, 25, 32, 40]
 
 
 class Gen:
