@@ -19,7 +19,7 @@ EXPORTS = (
     "b2g_last_error", "b2g_version", "b2g_plan_create", "b2g_plan_destroy",
     "b2g_plan_invert", "b2g_plan_predict", "b2g_plan_info", "b2g_plan_timings",
     "b2g_ms2dirty", "b2g_dirty2ms", "b2g_sumwt", "b2g_kernel_select", "b2g_kernel_eval",
-    "b2g_kernel_corr", "b2g_vis_prepare", "b2g_vis_finish", "b2g_set_host_chunk_samples", "b2g_set_max_slab_planes", "b2g_plan_create_sel",
+    "b2g_kernel_corr", "b2g_vis_prepare", "b2g_vis_finish", "b2g_set_host_chunk_samples", "b2g_set_max_slab_planes", "b2g_set_tc_mode", "b2g_plan_create_sel",
     "b2g_weight_grid", "b2g_weight_apply", "b2g_weight_taper", "b2g_dft_predict",
     "b2g_plan_residual", "b2g_hogbom", "b2g_image_peak", "b2g_dft_invert", "b2g_msclean", "b2g_msmfsclean", "b2g_hogbom_complex",
 )
@@ -76,6 +76,8 @@ def lib():
     L.b2g_set_host_chunk_samples.argtypes = [i64]
     L.b2g_set_max_slab_planes.restype = ci
     L.b2g_set_max_slab_planes.argtypes = [ci]
+    L.b2g_set_tc_mode.restype = ci
+    L.b2g_set_tc_mode.argtypes = [ci]
     L.b2g_kernel_select.restype = ci
     L.b2g_kernel_select.argtypes = [dbl, ci, ci, i64, i64, dbl, pd]
     L.b2g_kernel_eval.restype = ci

@@ -111,14 +111,11 @@ __device__ __forceinline__ void locate_axis(double cyc, int n, double halfW, int
 
 // The same function is used by key generation and by the gridding kernels, so the
 // sort key always describes the origin the kernels recompute.
-__device__ __forceinline__ Located locate(const VisGeo &g, int W, uint32_t row, uint32_t chan)
+// (u, v, w) in wavelengths -> footprint origin and offsets
+__device__ __forceinline__ Located locate_uvw(const VisGeo &g, int W, double u, double v, double w)
 {
     Located L;
     const double halfW = 0.5 * (double)W;
-    const double fs = __ldg(g.fscale + chan);
-    double u = __ldg(g.uvw + 3ull * row + 0) * fs;
-    double v = __ldg(g.uvw + 3ull * row + 1) * fs;
-    double w = __ldg(g.uvw + 3ull * row + 2) * fs;
     L.flip = false;
     L.p0 = 0;
     L.dw = 0.0;
@@ -138,6 +135,15 @@ __device__ __forceinline__ Located locate(const VisGeo &g, int W, uint32_t row, 
     locate_axis(u * g.su, g.nu, halfW, L.iu0, L.du);
     locate_axis(v * g.sv, g.nv, halfW, L.iv0, L.dv);
     return L;
+}
+
+__device__ __forceinline__ Located locate(const VisGeo &g, int W, uint32_t row, uint32_t chan)
+{
+    const double fs = __ldg(g.fscale + chan);
+    const double u = __ldg(g.uvw + 3ull * row + 0) * fs;
+    const double v = __ldg(g.uvw + 3ull * row + 1) * fs;
+    const double w = __ldg(g.uvw + 3ull * row + 2) * fs;
+    return locate_uvw(g, W, u, v, w);
 }
 
 // All W kernel values along one axis for offset delta in [0,1): out[s] = P_s(2*delta - 1).

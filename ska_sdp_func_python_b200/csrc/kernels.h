@@ -24,6 +24,9 @@ template <typename T> struct VisLaunch {
     const cplx<T> *sub_from = nullptr;  // degridding: ms_out = sub_from - model (residual), may alias ms_out
     cplx<T> *ring;          // [nslots][nu][nv]
     cudaStream_t stream;
+    // degridding, warp-run kernel: chunks of 1024 samples of [begin, end) to leave out (they were
+    // degridded by the tensor-core kernel, vis_tc.cu); NULL = none
+    const unsigned char *skip_chunks = nullptr;
 };
 
 // host table [W][W+4] (highest power first, exactly mirror-symmetric: es_kernel.h) -> the
@@ -47,6 +50,13 @@ template <typename T, int W> inline KernelTab<T, W> make_tab(const double *coef)
 
 template <typename T> int launch_grid_simple(const VisLaunch<T> &L);
 template <typename T> int launch_degrid_simple(const VisLaunch<T> &L);
+
+// tensor-core degridder (fp32, w-stacking, W <= 7): degrids the chunks of 1024 sorted samples whose
+// runs of equal footprint origin are long (at most max_runs runs per chunk) and records them in
+// dense_scratch (one byte per chunk) for the warp-run launch to skip; dense_scratch == NULL: all
+bool tc_supported(int W, bool wstack);
+long long tc_chunks(long long nvis);
+int launch_degrid_tc(const VisLaunch<float> &L, unsigned char *dense_scratch, int max_runs);
 
 template <typename T> bool warprun_supported(int W, bool wstack);
 template <typename T> int launch_grid_warprun(const VisLaunch<T> &L);

@@ -39,6 +39,10 @@ constexpr int kMaxChunks = 32;
 // Upper limit on the origin w-planes per slab (0 = sized from free memory): lets a small
 // geometry run the multi-slab ring-buffer path that the large configurations take.
 std::atomic<int> g_max_slab_planes{0};
+// Tensor-core degridder (vis_tc.cu): 0 = off, 1 = chunks of the sorted sample list with long runs
+// (the rest stays with the warp-run kernel), 2 = every chunk (tests).
+std::atomic<int> g_tc_mode{0};
+constexpr int kTcMaxRuns = 32;     // a chunk of 1024 samples is "dense" with at most this many runs
 
 int fail(const char *fmt, ...)
 {
@@ -186,6 +190,9 @@ struct b2g_plan {
     // the w-screen (fft_planes.cu); d_acc then holds the TRANSPOSED accumulator [npix_y][npix_x]
     HandFft *hfft = nullptr;
     void *d_fftwork = nullptr;
+    unsigned char *d_dense = nullptr;   // per-launch chunk classification of the tensor-core degridder
+    long long dense_cap = 0;
+    int tc_mode = 0;
     int key_bits = 0;
     double t_plan_ms = -1, t_last_ms = 0;
     // device time of plan creation; the sort of a single-slab plan is left running on the
@@ -258,6 +265,8 @@ struct b2g_plan {
         if (d_acc) cudaFreeAsync(d_acc, stream);
         if (d_scratch) cudaFreeAsync(d_scratch, stream);
         if (d_fftwork) cudaFreeAsync(d_fftwork, stream);
+        if (d_dense) cudaFreeAsync(d_dense, stream);
+        d_dense = nullptr;
         if (hfft) hfft_destroy(hfft, stream);
         hfft = nullptr;
         if (fft_ok) cufftDestroy(fft);
@@ -669,6 +678,7 @@ extern "C" int b2g_plan_create_sel(b2g_plan **plan, int64_t nrow, int64_t nchan,
                     precision == B2G_F32 ? "f32" : "f64", p->wstack);
     if (algo != B2G_ALGO_SIMPLE && algo != B2G_ALGO_WARPRUN) return fail("bad algo code %d", algo);
     p->algo = algo;
+    p->tc_mode = g_tc_mode.load();
 
     lap("setup");
     B2G_OK(build_tables(p));
@@ -841,6 +851,44 @@ int stage_out(const T *src, void *dst, int dtype, int space, long long n, cudaSt
         }
         CUDA_OK(cudaFreeAsync(tmp, s));
     }
+    return 0;
+}
+
+// degridding of one launch range with the plan's kernel family
+template <typename T> int degrid_dispatch(b2g_plan *p, VisLaunch<T> &L)
+{
+    if (p->algo == B2G_ALGO_WARPRUN) KERNEL_OK(launch_degrid_warprun<T>(L));
+    else KERNEL_OK(launch_degrid_simple<T>(L));
+    p->launches_last++;
+    return 0;
+}
+// fp32: chunks with long runs go to the tensor-core kernel, the rest to the warp-run kernel
+template <> int degrid_dispatch<float>(b2g_plan *p, VisLaunch<float> &L)
+{
+    if (p->algo == B2G_ALGO_WARPRUN && p->tc_mode > 0 && tc_supported(p->W, p->wstack != 0)) {
+        unsigned char *dense = nullptr;
+        if (p->tc_mode == 1) {
+            const long long need = tc_chunks(L.end - L.begin);
+            if (need > p->dense_cap) {
+                if (p->d_dense) CUDA_OK(cudaFreeAsync(p->d_dense, p->stream));
+                p->d_dense = nullptr;
+                CUDA_OK(cudaMallocAsync(&p->d_dense, (size_t)need, p->stream));
+                p->dense_cap = need;
+            }
+            dense = p->d_dense;
+        }
+        KERNEL_OK(launch_degrid_tc(L, dense, kTcMaxRuns));
+        p->launches_last += dense ? 2 : 1;
+        if (!dense) return 0;
+        L.skip_chunks = dense;
+        KERNEL_OK(launch_degrid_warprun<float>(L));
+        L.skip_chunks = nullptr;
+        p->launches_last++;
+        return 0;
+    }
+    if (p->algo == B2G_ALGO_WARPRUN) KERNEL_OK(launch_degrid_warprun<float>(L));
+    else KERNEL_OK(launch_degrid_simple<float>(L));
+    p->launches_last++;
     return 0;
 }
 
@@ -1142,11 +1190,7 @@ int predict_impl(b2g_plan *p, const void *dirty, int dirty_dtype, int dirty_spac
                 L.begin = std::min<long long>(p->nrow, c * p->rows_per_chunk) * p->nchan;
                 L.end = std::min<long long>(p->nrow, (c + 1) * p->rows_per_chunk) * p->nchan;
             }
-            if (L.end > L.begin) {
-                if (p->algo == B2G_ALGO_WARPRUN) KERNEL_OK(launch_degrid_warprun<T>(L));
-                else KERNEL_OK(launch_degrid_simple<T>(L));
-                p->launches_last++;
-            }
+            if (L.end > L.begin) B2G_OK(degrid_dispatch<T>(p, L));
             if (stream_out && L.end > L.begin) {
                 CUDA_OK(cudaEventRecord(p->chunk_ev[c], s));
                 CUDA_OK(cudaStreamWaitEvent(p->copy_stream, p->chunk_ev[c], 0));
@@ -1370,6 +1414,14 @@ extern "C" int b2g_set_max_slab_planes(int nplanes)
 {
     g_err.clear();
     g_max_slab_planes.store(nplanes > 0 ? nplanes : 0);
+    return 0;
+}
+
+extern "C" int b2g_set_tc_mode(int mode)
+{
+    g_err.clear();
+    if (mode < 0 || mode > 2) return fail("tensor-core mode must be 0 (off), 1 (dense chunks) or 2 (all chunks)");
+    g_tc_mode.store(mode);
     return 0;
 }
 
