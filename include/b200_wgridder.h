@@ -164,7 +164,7 @@ int b2g_set_max_slab_planes(int nplanes);
 
 /* Tensor-core degridder (tcgen05 / TMEM, fp32 w-stacking plans with W <= 7): 0 = off, 1 = the
  * chunks of 1024 sorted samples whose runs of equal footprint origin are long (the sparse rest
- * stays with the warp-run kernel), 2 = every chunk (parity tests).  Same results within fp32
+ * stays with the warp-run kernel; the default), 2 = every chunk (parity tests).  Same results within fp32
  * rounding (3 x TF32 split).  Process-wide setting, applies to plans created later. */
 int b2g_set_tc_mode(int mode);
 

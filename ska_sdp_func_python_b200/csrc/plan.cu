@@ -41,8 +41,8 @@ constexpr int kMaxChunks = 32;
 std::atomic<int> g_max_slab_planes{0};
 // Tensor-core degridder (vis_tc.cu): 0 = off, 1 = chunks of the sorted sample list with long runs
 // (the rest stays with the warp-run kernel), 2 = every chunk (tests).
-std::atomic<int> g_tc_mode{0};
-constexpr int kTcMaxRuns = 32;     // a chunk of 1024 samples is "dense" with at most this many runs
+std::atomic<int> g_tc_mode{1};
+constexpr int kTcMaxRuns = 16;     // a chunk of 1024 samples is "dense" with at most this many runs
 
 int fail(const char *fmt, ...)
 {
@@ -877,7 +877,11 @@ template <> int degrid_dispatch<float>(b2g_plan *p, VisLaunch<float> &L)
             }
             dense = p->d_dense;
         }
-        KERNEL_OK(launch_degrid_tc(L, dense, kTcMaxRuns));
+        static const int max_runs = [] {
+            const char *e = std::getenv("B2G_TC_MAX_RUNS");
+            return e ? std::atoi(e) : kTcMaxRuns;
+        }();
+        KERNEL_OK(launch_degrid_tc(L, dense, max_runs));
         p->launches_last += dense ? 2 : 1;
         if (!dense) return 0;
         L.skip_chunks = dense;

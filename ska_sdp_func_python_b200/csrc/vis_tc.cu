@@ -15,20 +15,24 @@
 //     products ku[a] kv[b] and writes them straight from registers into its TMEM lane
 //     (tcgen05.st) -- no shared-memory staging and no cross-lane reduction; the w-kernel stays in
 //     the thread's registers for the W-term epilogue on its own accumulator row (tcgen05.ld);
-//   * every WARP runs its own pipeline on its quadrant of the 128 TMEM lanes: tiles of up to 32
-//     samples of one run, MMAs issued by its lane 0 with the other three quadrants masked off
-//     (disable-output-lane), completion through its own mbarrier (tcgen05.commit) -- no block
-//     barrier anywhere in the loop;
-//   * B = the W^2 x 2W block of grid cells under the run's footprint, loaded once per run into the
-//     warp's shared-memory block in the K-major core-matrix layout;
+//   * a tile = up to 128 consecutive sorted samples of one run = the 128 TMEM lanes of the block;
+//     thread 0 issues the MMAs, completion comes back through an mbarrier (tcgen05.commit);
+//   * B = the W^2 x 2W block of grid cells under the run's footprint, loaded once per run into
+//     shared memory in the K-major core-matrix layout (the next run's block is loaded while the
+//     current tile's MMAs run);
 //   * fp32 accuracy from TF32 tensor cores: A = A_hi + A_lo, B = B_hi + B_lo (11 + 11 mantissa
 //     bits each), three MMAs per K-step (hi*hi, lo*hi, hi*lo), fp32 accumulation: measured
 //     1.1e-6 of the row maximum against fp64 (tools/probe/tc_probe.cu), against 8e-4 for plain
 //     TF32;
-//   * a warp works through 256 sorted samples (a block through a chunk of 1024): a lane-parallel
-//     first phase locates all of them (fp64, as the sort key did) into shared memory, then the
-//     tiles follow each other.  Chunks whose runs are short (sparse outer uv-plane) are left to
-//     the warp-run kernel (vis_warprun.cu), which costs less per run.
+//   * persistent blocks work through chunks of 1024 sorted samples: a lane-parallel first phase
+//     locates all of them (fp64, as the sort key did) into shared memory, then the tiles follow
+//     each other.  Chunks whose runs are short (sparse outer uv-plane) are left to the warp-run
+//     kernel (vis_warprun.cu), which costs less per run.
+//
+// Measured alternative (same file, earlier revision): every warp running its own 32-row tiles in
+// its TMEM lane quadrant with the other quadrants masked off (disable-output-lane) needs no block
+// barrier, but the 21 MMA issues per tile (about 11 instructions each: operands moved to uniform
+// registers) are then paid per 27 samples instead of per 73, and it measured 13 % slower.
 #include <cuda_runtime.h>
 
 #include "kernels.h"
@@ -53,19 +57,14 @@ template <int W> struct TcCfg {
     static constexpr int B_FLOATS = KS * 128;        // one operand copy (hi or lo) of one buffer
 };
 
-constexpr int kTcWarpChunk = kTcChunk / 4;            // sorted samples per warp (== B2G_CHUNK)
-
-// per-warp working set: the located samples of the warp's 256-sample stretch and one B block
-template <int W> struct TcWarpSmem {
-    float wt[kTcWarpChunk];
-    int oxy[kTcWarpChunk];        // iu0 << 16 | iv0
-    int oz[kTcWarpChunk];         // p0 | flip << 31
-    float du[kTcWarpChunk], dv[kTcWarpChunk], dw[kTcWarpChunk];
-    alignas(128) float B[2][TcCfg<W>::B_FLOATS];      // [hi, lo]
-    alignas(8) unsigned long long bar;
-};
 template <int W> struct TcSmem {
-    TcWarpSmem<W> w[4];
+    uint32_t idx[kTcChunk];
+    float wt[kTcChunk];
+    int oxy[kTcChunk];        // iu0 << 16 | iv0
+    int oz[kTcChunk];         // p0 | flip << 31
+    float du[kTcChunk], dv[kTcChunk], dw[kTcChunk];
+    alignas(128) float B[2][2][TcCfg<W>::B_FLOATS];   // [buffer][hi, lo]
+    alignas(8) unsigned long long bar;
     uint32_t tm_base;
 };
 
@@ -127,15 +126,16 @@ __device__ __forceinline__ int b_off(int n, int k)
 }
 
 // The W x W x W block of grid cells under the footprint with origin (oxy, p0), split in hi / lo
-// TF32 parts, into the warp's B block.  Lane = (plane c = lane / 4, cell k mod 4): all loads are
-// issued before the first store; the pad rows (k >= W^2) and columns (n >= 2 W) stay zero from
-// the initial clear.
+// TF32 parts, into one B buffer, by the whole block.  Lane = (plane c = lane / 4, cell k mod 4),
+// the four warps take every fourth group of four cells; the pad rows (k >= W^2) and columns
+// (n >= 2 W) stay zero from the initial clear.
 template <int W>
 __device__ __forceinline__ void load_B(const VisGeo &g, const cplx<float> *__restrict__ ring, int plane0,
-                                       int slot0, int oxy, int p0, float *Bhi, float *Blo, int lane)
+                                       int slot0, int oxy, int p0, float *Bhi, float *Blo, int tid)
 {
     using C = TcCfg<W>;
-    constexpr int ROUNDS = (C::K + 3) / 4;
+    constexpr int ROUNDS = (C::K + 15) / 16;
+    const int lane = tid & 31, warp = tid >> 5;
     const int c = lane >> 2;
     if (c >= W) return;
     const int iu0 = oxy >> 16, iv0 = oxy & 0xffff;
@@ -143,7 +143,7 @@ __device__ __forceinline__ void load_B(const VisGeo &g, const cplx<float> *__res
     cplx<float> v[ROUNDS];
 #pragma unroll
     for (int r = 0; r < ROUNDS; ++r) {
-        const int k = 4 * r + (lane & 3);
+        const int k = 4 * (warp + 4 * r) + (lane & 3);
         v[r] = cplx<float>{0.f, 0.f};
         if (k < C::K) {
             const int a = k / W, b = k - a * W;
@@ -152,7 +152,7 @@ __device__ __forceinline__ void load_B(const VisGeo &g, const cplx<float> *__res
     }
 #pragma unroll
     for (int r = 0; r < ROUNDS; ++r) {
-        const int k = 4 * r + (lane & 3);
+        const int k = 4 * (warp + 4 * r) + (lane & 3);
         if (k < C::K) {
             const int o = b_off(2 * c, k);
             const float hr = tf32_hi(v[r].re), hi = tf32_hi(v[r].im);
@@ -175,18 +175,17 @@ degrid_tc_kernel(VisGeo g, KernelTab<float, W> tab, const uint32_t *__restrict__
     extern __shared__ __align__(128) unsigned char smem_raw[];
     TcSmem<W> &sm = *reinterpret_cast<TcSmem<W> *>(smem_raw);
     const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-    TcWarpSmem<W> &ws = sm.w[warp];
     if (warp == 0) {
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&sm.tm_base)),
                      "r"(kTmCols)
                      : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
-    if (lane == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&ws.bar)) : "memory");
+    if (tid == 0) {
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&sm.bar)) : "memory");
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
-    for (int i = lane; i < 2 * C::B_FLOATS; i += 32) (&ws.B[0][0])[i] = 0.f;
+    for (int i = tid; i < 4 * C::B_FLOATS; i += kTcThreads) (&sm.B[0][0][0])[i] = 0.f;
     asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
     __syncthreads();
     asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
@@ -195,150 +194,176 @@ degrid_tc_kernel(VisGeo g, KernelTab<float, W> tab, const uint32_t *__restrict__
     // instruction descriptor: D fp32, A / B tf32, both K-major, N = 16, M = 128
     const uint32_t idesc = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(kN >> 3) << 17) | ((128u >> 4) << 24);
     const uint64_t dbase = (uint64_t(128 >> 4) << 16) | (uint64_t(256 >> 4) << 32) | (1ull << 46);
-    const uint32_t m0 = warp == 0 ? 0u : ~0u, m1 = warp == 1 ? 0u : ~0u, m2 = warp == 2 ? 0u : ~0u,
-                   m3 = warp == 3 ? 0u : ~0u;
-    // shared-memory descriptors of the first K-step of B_hi / B_lo; the next steps are 512 B
-    // (32 units of 16 B) further on
-    const uint64_t bh_desc = dbase | (uint64_t)((smem_u32(ws.B[0]) >> 4) & 0x3fff);
-    const uint64_t bl_desc = dbase | (uint64_t)((smem_u32(ws.B[1]) >> 4) & 0x3fff);
 
-    int cur_xy = -1, cur_z = -1;          // origin whose cells the B block holds
+    int bb = 0;                           // B buffer of the current tile
+    int cur_xy = -1, cur_z = -1;          // origin whose cells buffer bb holds
+    int oth_xy = -1, oth_z = -1;          // ... and buffer bb ^ 1
     uint32_t parity = 0;
-    // persistent warps: stretch = 256 sorted samples; stretches are dealt out round-robin
-    const long long nstretch = (end - begin + kTcWarpChunk - 1) / kTcWarpChunk;
-    for (long long st = (long long)blockIdx.x * 4 + warp; st < nstretch; st += (long long)gridDim.x * 4) {
-    if (dense && !dense[st >> 2]) continue;           // sparse chunk: the warp-run kernel's
-    const long long wbeg = begin + st * kTcWarpChunk;
-    const int nw = (int)((end - wbeg < kTcWarpChunk) ? end - wbeg : kTcWarpChunk);
+    // persistent blocks: chunk = 1024 sorted samples, dealt out round-robin
+    const long long nchunk = (end - begin + kTcChunk - 1) / kTcChunk;
+    for (long long ch = blockIdx.x; ch < nchunk; ch += gridDim.x) {
+        if (dense && !dense[ch]) continue;            // sparse chunk: the warp-run kernel's
+        const long long cbeg = begin + ch * kTcChunk;
+        const int n = (int)((end - cbeg < kTcChunk) ? end - cbeg : kTcChunk);
+        __syncthreads();                              // the previous chunk's arrays are no longer read
 
-    // ---- phase 1: locate every sample of the stretch (one sample per lane and round); the loads
-    // of four rounds are in flight together ---------------------------------------------------
+        // ---- phase 1: locate every sample of the chunk (one sample per thread and round); the
+        // loads of four rounds are in flight together ------------------------------------------
 #pragma unroll
-    for (int r0 = 0; r0 < kTcWarpChunk / 32; r0 += 4) {
-        uint32_t idx[4];
-        double uu[4], vv[4], ww[4], fs[4];
-        float wt[4];
+        for (int r0 = 0; r0 < kTcPer; r0 += 4) {
+            uint32_t idx[4];
+            double uu[4], vv[4], ww[4], fs[4];
+            float wt[4];
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            const int s = lane + 32 * (r0 + r);
-            idx[r] = s < nw ? __ldg(sidx + wbeg + s) : 0u;
-        }
+            for (int r = 0; r < 4; ++r) {
+                const int s = tid + kTcThreads * (r0 + r);
+                idx[r] = s < n ? __ldg(sidx + cbeg + s) : 0u;
+            }
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            const int s = lane + 32 * (r0 + r);
-            uint32_t row = 0, chan = 0;
-            if (s < nw) g.split(idx[r], row, chan);
-            fs[r] = __ldg(g.fscale + chan);
-            uu[r] = __ldg(g.uvw + 3ull * row + 0);
-            vv[r] = __ldg(g.uvw + 3ull * row + 1);
-            ww[r] = __ldg(g.uvw + 3ull * row + 2);
-            wt[r] = (wgt && s < nw) ? __ldg(wgt + idx[r]) : 1.f;
-        }
+            for (int r = 0; r < 4; ++r) {
+                const int s = tid + kTcThreads * (r0 + r);
+                uint32_t row = 0, chan = 0;
+                if (s < n) g.split(idx[r], row, chan);
+                fs[r] = __ldg(g.fscale + chan);
+                uu[r] = __ldg(g.uvw + 3ull * row + 0);
+                vv[r] = __ldg(g.uvw + 3ull * row + 1);
+                ww[r] = __ldg(g.uvw + 3ull * row + 2);
+                wt[r] = (wgt && s < n) ? __ldg(wgt + idx[r]) : 1.f;
+            }
 #pragma unroll
-        for (int r = 0; r < 4; ++r) {
-            const int s = lane + 32 * (r0 + r);
-            if (s < nw) {
-                const Located L = locate_uvw(g, W, uu[r] * fs[r], vv[r] * fs[r], ww[r] * fs[r]);
-                ws.wt[s] = wt[r];
-                ws.oxy[s] = (L.iu0 << 16) | L.iv0;
-                ws.oz[s] = L.p0 | (L.flip ? (int)0x80000000 : 0);
-                ws.du[s] = (float)L.du;
-                ws.dv[s] = (float)L.dv;
-                ws.dw[s] = (float)L.dw;
+            for (int r = 0; r < 4; ++r) {
+                const int s = tid + kTcThreads * (r0 + r);
+                if (s < n) {
+                    const Located L = locate_uvw(g, W, uu[r] * fs[r], vv[r] * fs[r], ww[r] * fs[r]);
+                    sm.idx[s] = idx[r];
+                    sm.wt[s] = wt[r];
+                    sm.oxy[s] = (L.iu0 << 16) | L.iv0;
+                    sm.oz[s] = L.p0 | (L.flip ? (int)0x80000000 : 0);
+                    sm.du[s] = (float)L.du;
+                    sm.dv[s] = (float)L.dv;
+                    sm.dw[s] = (float)L.dw;
+                }
             }
         }
-    }
-    __syncwarp();
-    int pos = 0;
-    while (pos < nw) {                    // warp-uniform
-        const int s = pos + lane;
-        const int oxy0 = ws.oxy[pos], oz0 = ws.oz[pos] & 0x7fffffff;
-        const bool match = s < nw && ws.oxy[s] == oxy0 && (ws.oz[s] & 0x7fffffff) == oz0;
-        // the samples sharing the first one's origin are a prefix of the sorted window
-        const int tile_len = __popc(__ballot_sync(0xffffffffu, match));
-        const uint32_t idx = match ? __ldg(sidx + wbeg + s) : 0u;     // for the epilogue
-        const float my_w = match ? ws.wt[s] : 0.f;
-        const bool active = match && my_w != 0.f;
+        __syncthreads();
 
-        // ---- B: the grid cells of this run (the previous tile's MMAs have completed) -----------
-        if (cur_xy != oxy0 || cur_z != oz0) {
-            load_B<W>(g, ring, plane0, slot0, oxy0, oz0, ws.B[0], ws.B[1], lane);
-            cur_xy = oxy0;
-            cur_z = oz0;
-            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // stores -> tensor core reads
-        }
+        int pos = 0;
+        while (pos < n) {                 // block-uniform
+            const int s = pos + tid;
+            const int oxy0 = sm.oxy[pos], oz0 = sm.oz[pos] & 0x7fffffff;
+            const bool match = s < n && sm.oxy[s] == oxy0 && (sm.oz[s] & 0x7fffffff) == oz0;
+            // the samples sharing the first one's origin are a prefix of the sorted window
+            const int tile_len = __syncthreads_count(match);
+            const float my_w = match ? sm.wt[s] : 0.f;
+            const bool active = match && my_w != 0.f;
+            const bool warp_on = __any_sync(0xffffffffu, match);
 
-        // ---- A: this lane's row = ku (x) kv, hi and lo parts, registers -> TMEM -----------------
-        float ku[W], kv[W], kw[W];
-        if (active) {
-            kernel_values<float, W>(tab, ws.du[s], ku);
-            kernel_values<float, W>(tab, ws.dv[s], kv);
-            kernel_values<float, W>(tab, ws.dw[s], kw);
-        } else {
-#pragma unroll
-            for (int i = 0; i < W; ++i) ku[i] = kv[i] = kw[i] = 0.f;
-        }
-#pragma unroll
-        for (int c0 = 0; c0 < C::KP; c0 += 8) {
-            float hi[8], lo[8];
-#pragma unroll
-            for (int i = 0; i < 8; ++i) {
-                const int k = c0 + i;
-                float p = 0.f;
-                if (k < C::K) p = ku[k / W] * kv[k % W];
-                hi[i] = p;                      // the tensor core reads the upper 19 bits
-                lo[i] = p - tf32_hi(p);
+            // ---- B: the grid cells of this run (usually prefetched during the previous tile) ----
+            if (cur_xy != oxy0 || cur_z != oz0) {
+                if (oth_xy == oxy0 && oth_z == oz0) {
+                    bb ^= 1;
+                    oth_xy = cur_xy;
+                    oth_z = cur_z;
+                } else {
+                    load_B<W>(g, ring, plane0, slot0, oxy0, oz0, sm.B[bb][0], sm.B[bb][1], tid);
+                }
+                cur_xy = oxy0;
+                cur_z = oz0;
             }
-            tm_st8(lane_base + c0, hi);
-            tm_st8(lane_base + C::COL_ALO + c0, lo);
-        }
-        asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        __syncwarp();
-        if (lane == 0) {
+
+            // ---- A: this thread's row = ku (x) kv, hi and lo parts, registers -> TMEM ------------
+            float kw[W];
+            if (warp_on) {
+                float ku[W], kv[W];
+                if (active) {
+                    kernel_values<float, W>(tab, sm.du[s], ku);
+                    kernel_values<float, W>(tab, sm.dv[s], kv);
+                    kernel_values<float, W>(tab, sm.dw[s], kw);
+                } else {
+#pragma unroll
+                    for (int i = 0; i < W; ++i) ku[i] = kv[i] = kw[i] = 0.f;
+                }
+#pragma unroll
+                for (int c0 = 0; c0 < C::KP; c0 += 8) {
+                    float hi[8], lo[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        const int k = c0 + i;
+                        float p = 0.f;
+                        if (k < C::K) p = ku[k / W] * kv[k % W];
+                        hi[i] = p;                      // the tensor core reads the upper 19 bits
+                        lo[i] = p - tf32_hi(p);
+                    }
+                    tm_st8(lane_base + c0, hi);
+                    tm_st8(lane_base + C::COL_ALO + c0, lo);
+                }
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+            }
+            asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // B stores -> tensor core reads
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            __syncthreads();
+            if (tid == 0) {
+                asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
+                const uint64_t bh_desc = dbase | (uint64_t)((smem_u32(sm.B[bb][0]) >> 4) & 0x3fff);
+                const uint64_t bl_desc = dbase | (uint64_t)((smem_u32(sm.B[bb][1]) >> 4) & 0x3fff);
+#pragma unroll
+                for (int ks = 0; ks < C::KS; ++ks) {
+                    const uint64_t bh = bh_desc + (uint64_t)(ks * 32), bl = bl_desc + (uint64_t)(ks * 32);
+                    mma_ts(tm + C::COL_D, tm + ks * 8, bh, idesc, ks > 0, 0u, 0u, 0u, 0u);
+                    mma_ts(tm + C::COL_D, tm + C::COL_ALO + ks * 8, bh, idesc, 1, 0u, 0u, 0u, 0u);
+                    mma_ts(tm + C::COL_D, tm + ks * 8, bl, idesc, 1, 0u, 0u, 0u, 0u);
+                }
+                asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
+                                 smem_u32(&sm.bar))
+                             : "memory");
+            }
+            // ---- while the MMAs run: the next run's cells into the other buffer ------------------
+            const int npos = pos + tile_len;
+            if (npos < n) {
+                const int nxy = sm.oxy[npos], nz = sm.oz[npos] & 0x7fffffff;
+                if ((nxy != oxy0 || nz != oz0) && (oth_xy != nxy || oth_z != nz)) {
+                    load_B<W>(g, ring, plane0, slot0, nxy, nz, sm.B[bb ^ 1][0], sm.B[bb ^ 1][1], tid);
+                    oth_xy = nxy;
+                    oth_z = nz;
+                }
+            }
+            if (lane == 0) {              // one poller per warp
+                const long long t0 = clock64();
+                while (!mbar_try(&sm.bar, parity))
+                    if (clock64() - t0 > 4000000000LL) __trap();    // never hang the device
+            }
+            __syncwarp();
+            parity ^= 1u;
             asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
-#pragma unroll
-            for (int ks = 0; ks < C::KS; ++ks) {
-                const uint64_t bh = bh_desc + (uint64_t)(ks * 32), bl = bl_desc + (uint64_t)(ks * 32);
-                mma_ts(tm + C::COL_D, tm + ks * 8, bh, idesc, ks > 0, m0, m1, m2, m3);
-                mma_ts(tm + C::COL_D, tm + C::COL_ALO + ks * 8, bh, idesc, 1, m0, m1, m2, m3);
-                mma_ts(tm + C::COL_D, tm + ks * 8, bl, idesc, 1, m0, m1, m2, m3);
-            }
-            asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
-                             smem_u32(&ws.bar))
-                         : "memory");
-            const long long t0 = clock64();
-            while (!mbar_try(&ws.bar, parity))
-                if (clock64() - t0 > 4000000000LL) __trap();    // never hang the device
-        }
-        __syncwarp();
-        parity ^= 1u;
-        asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
 
-        // ---- epilogue: this lane's accumulator row, W-term w-kernel sum, store ------------------
-        float d[16];
-        tm_ld16(lane_base + C::COL_D, d);
-        if (match) {
-            float re = 0.f, im = 0.f;
+            // ---- epilogue: this thread's accumulator row, W-term w-kernel sum, store -------------
+            if (warp_on) {
+                float d[16];
+                tm_ld16(lane_base + C::COL_D, d);
+                if (match) {
+                    float re = 0.f, im = 0.f;
+                    if (active) {
 #pragma unroll
-            for (int c = 0; c < W; ++c) {
-                re = fmaf(kw[c], d[2 * c], re);
-                im = fmaf(kw[c], d[2 * c + 1], im);
+                        for (int c = 0; c < W; ++c) {
+                            re = fmaf(kw[c], d[2 * c], re);
+                            im = fmaf(kw[c], d[2 * c + 1], im);
+                        }
+                        if (sm.oz[s] < 0) im = -im;   // flipped sample: conjugate
+                    }
+                    const uint32_t idx = sm.idx[s];
+                    cplx<float> r{re * my_w, im * my_w};
+                    if (sub_from) {                   // residual mode: data - model
+                        const cplx<float> prev = sub_from[idx];
+                        r.re = prev.re - r.re;
+                        r.im = prev.im - r.im;
+                    }
+                    out[idx] = r;
+                }
             }
-            if (ws.oz[s] < 0) im = -im;           // flipped sample: conjugate
-            cplx<float> r{active ? re * my_w : 0.f, active ? im * my_w : 0.f};
-            if (sub_from) {                       // residual mode: data - model
-                const cplx<float> prev = sub_from[idx];
-                r.re = prev.re - r.re;
-                r.im = prev.im - r.im;
-            }
-            out[idx] = r;
+            asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
+            pos = npos;
         }
-        asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
-        pos += tile_len;
     }
-    __syncwarp();
-    }   // stretches
     __syncthreads();
     if (warp == 0)
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tm), "r"(kTmCols) : "memory");

@@ -29,7 +29,7 @@ def tc_mode(built):
     def set_mode(m):
         assert built.b2g_set_tc_mode(int(m)) == 0
     yield set_mode
-    built.b2g_set_tc_mode(0)
+    built.b2g_set_tc_mode(1)     # the library default
 
 
 @pytest.fixture()
