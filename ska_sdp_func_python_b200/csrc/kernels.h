@@ -53,7 +53,8 @@ template <typename T> int launch_degrid_simple(const VisLaunch<T> &L);
 
 // tensor-core degridder (fp32, w-stacking, W <= 7): degrids the chunks of 1024 sorted samples whose
 // runs of equal footprint origin are long (at most max_runs runs per chunk) and records them in
-// dense_scratch (one byte per chunk) for the warp-run launch to skip; dense_scratch == NULL: all
+// dense_scratch (one byte per chunk) for the warp-run launch to skip (max_runs < 0: the table is
+// already filled); dense_scratch == NULL: all chunks
 bool tc_supported(int W, bool wstack);
 long long tc_chunks(long long nvis);
 int launch_degrid_tc(const VisLaunch<float> &L, unsigned char *dense_scratch, int max_runs);

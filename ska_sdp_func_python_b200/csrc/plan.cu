@@ -18,6 +18,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/b200_wgridder.h"
@@ -190,8 +191,12 @@ struct b2g_plan {
     // the w-screen (fft_planes.cu); d_acc then holds the TRANSPOSED accumulator [npix_y][npix_x]
     HandFft *hfft = nullptr;
     void *d_fftwork = nullptr;
-    unsigned char *d_dense = nullptr;   // per-launch chunk classification of the tensor-core degridder
-    long long dense_cap = 0;
+    // chunk classification of the tensor-core degridder: one byte per chunk of 1024 samples of
+    // every launch range seen so far (ranges are fixed per plan: slabs x host chunks), filled by
+    // the first predict that degrids the range
+    unsigned char *d_dense = nullptr;
+    long long dense_cap = 0, dense_used = 0;
+    std::vector<std::pair<std::pair<long long, long long>, long long>> dense_ranges;   // (begin, end) -> offset
     int tc_mode = 0;
     int key_bits = 0;
     double t_plan_ms = -1, t_last_ms = 0;
@@ -867,22 +872,31 @@ template <> int degrid_dispatch<float>(b2g_plan *p, VisLaunch<float> &L)
 {
     if (p->algo == B2G_ALGO_WARPRUN && p->tc_mode > 0 && tc_supported(p->W, p->wstack != 0)) {
         unsigned char *dense = nullptr;
+        bool classify = false;
         if (p->tc_mode == 1) {
-            const long long need = tc_chunks(L.end - L.begin);
-            if (need > p->dense_cap) {
-                if (p->d_dense) CUDA_OK(cudaFreeAsync(p->d_dense, p->stream));
-                p->d_dense = nullptr;
-                CUDA_OK(cudaMallocAsync(&p->d_dense, (size_t)need, p->stream));
-                p->dense_cap = need;
+            if (!p->d_dense) {
+                p->dense_cap = tc_chunks(p->nvis) + 4 * (long long)(p->nslabs + 1) * std::max(1, p->nchunks) + 64;
+                CUDA_OK(cudaMallocAsync(&p->d_dense, (size_t)p->dense_cap, p->stream));
             }
-            dense = p->d_dense;
+            long long off = -1;
+            for (const auto &r : p->dense_ranges)
+                if (r.first.first == L.begin && r.first.second == L.end) off = r.second;
+            if (off < 0) {
+                const long long need = tc_chunks(L.end - L.begin);
+                if (p->dense_used + need > p->dense_cap) return fail("tensor-core chunk table overflow");
+                off = p->dense_used;
+                p->dense_used += need;
+                p->dense_ranges.push_back({{L.begin, L.end}, off});
+                classify = true;
+            }
+            dense = p->d_dense + off;
         }
         static const int max_runs = [] {
             const char *e = std::getenv("B2G_TC_MAX_RUNS");
             return e ? std::atoi(e) : kTcMaxRuns;
         }();
-        KERNEL_OK(launch_degrid_tc(L, dense, max_runs));
-        p->launches_last += dense ? 2 : 1;
+        KERNEL_OK(launch_degrid_tc(L, dense, classify ? max_runs : -1));
+        p->launches_last += classify ? 2 : 1;
         if (!dense) return 0;
         L.skip_chunks = dense;
         KERNEL_OK(launch_degrid_warprun<float>(L));

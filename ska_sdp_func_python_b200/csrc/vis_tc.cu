@@ -409,7 +409,7 @@ template <int W> int degrid_tc_inst(const VisLaunch<float> &L, unsigned char *de
     const size_t smem = sizeof(TcSmem<W>);
     cudaError_t e = cudaFuncSetAttribute(degrid_tc_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
-    if (dense_scratch) {
+    if (dense_scratch && max_runs >= 0) {
         tc_classify_kernel<W><<<nblk, 256, 0, L.stream>>>(L.geo, L.sidx, L.begin, L.end, max_runs, dense_scratch);
         if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;
     }
@@ -433,9 +433,10 @@ bool tc_supported(int W, bool wstack) { return wstack && W >= 4 && W <= 7; }
 
 long long tc_chunks(long long nvis) { return (nvis + kTcChunk - 1) / kTcChunk; }
 
-// Degrids the dense chunks of [begin, end) (all chunks if dense_scratch is null); when
-// dense_scratch is given it is first filled with the classification (one byte per chunk of 1024
-// samples of the range), which the warp-run launch then uses to skip those chunks.
+// Degrids the dense chunks of [begin, end) (all chunks if dense_scratch is null).  dense_scratch
+// holds the classification (one byte per chunk of 1024 samples of the range), which the warp-run
+// launch then uses to skip those chunks; it is (re)computed first unless max_runs < 0 (the
+// caller has kept it from an earlier call on the same range of the same plan).
 int launch_degrid_tc(const VisLaunch<float> &L, unsigned char *dense_scratch, int max_runs)
 {
     switch (L.W) {

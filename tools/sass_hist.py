@@ -32,7 +32,7 @@ def main():
         if a.match and a.match not in name:
             continue
         total = sum(h.values())
-        short = re.sub(r"\(.*", "", name)
+        short = re.sub(r"\(.*", "", name.replace("(anonymous namespace)::", ""))
         print(f"== {short}  ({total} instructions)")
         special = {k: v for k, v in h.items() if re.match(r"UBLKCP|UTMA|SYNCS|UTC|LDTM|STTM|FFMA2|FMUL2|FADD2|REDG|RED|LDGSTS|BAR|UCGABAR", k)}
         if special:
