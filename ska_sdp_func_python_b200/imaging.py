@@ -460,12 +460,17 @@ def predict_ng(bvis, model, **kwargs):
     assert _is_image(model), model
     assert model.image_acc.is_canonical()
     opt = _options(kwargs)
-    newbvis = bvis.copy(deep=True, zero=True)
+    # the result container (ng.py:63: a deep copy with a zeroed cube) is built by a helper thread
+    # while the GPU degrids: copying the weights and flags is pure host-memory traffic
+    import concurrent.futures
+    pool = concurrent.futures.ThreadPoolExecutor(max_workers=1)
+    newbvis_f = pool.submit(bvis.copy, deep=True, zero=True)
+    pool.shutdown(wait=False)
 
     freq = numpy.asarray(bvis.frequency.data)
     nrows, nbaselines, vnchan, vnpol = bvis.vis.shape
     nrow = nrows * nbaselines
-    uvw = numpy.nan_to_num(numpy.array(newbvis.uvw.data, dtype=numpy.float64).reshape(nrow, 3))
+    uvw = numpy.nan_to_num(numpy.array(bvis.uvw.data, dtype=numpy.float64).reshape(nrow, 3))
     m_nchan, m_npol, ny, nx = model["pixels"].data.shape
     assert m_npol == vnpol
     uvw[:, 0] *= -1.0
@@ -513,6 +518,7 @@ def predict_ng(bvis, model, **kwargs):
 
     # image frame -> visibility frame, interleave, inverse phase rotation (ng.py:131-143)
     M = pol_matrix(model.image_acc.polarisation_frame, bvis.visibility_acc.polarisation_frame)
+    newbvis = newbvis_f.result()
     shift, update_pc = _shift_vector(newbvis, model)
     lmn = None
     if shift is not None:
@@ -522,12 +528,15 @@ def predict_ng(bvis, model, **kwargs):
     step = max(1, _rows_per_chunk(vnchan, vnpol, 16) // 2)
     L = _lib.lib()
     stage = D.stager()
+    # a single-precision plan's samples cross PCIe as complex64 (half the bytes); the staging
+    # ring widens them to the reference's complex128 on the way into the result cube
+    odt, ocode = (torch.complex64, _lib.F32) if prec == _lib.F32 else (torch.complex128, _lib.F64)
     for r0 in range(0, nrow, step):
         r1 = min(nrow, r0 + step)
-        chunk = torch.empty((r1 - r0, vnchan, vnpol), device=D.dev, dtype=torch.complex128)
+        chunk = torch.empty((r1 - r0, vnchan, vnpol), device=D.dev, dtype=odt)
         _lib.check(L.b2g_vis_finish(
             r1 - r0, vnchan, m_npol, vnpol, _ptr(vist), prec, _dptr(Mh.view(numpy.float64)),
-            _dptr(lmn), _ptr(D.uvw), _ptr(D.fscale), r0, nrow, _ptr(chunk), _lib.F64,
+            _dptr(lmn), _ptr(D.uvw), _ptr(D.fscale), r0, nrow, _ptr(chunk), ocode,
             ctypes.c_void_p(D.stream)))
         stage.get(chunk, vis[r0:r1])   # D2H into pinned memory while the next chunk is finished
     stage.finish()

@@ -196,7 +196,9 @@ class _Dataset:
     def _copy_vars(self, zero_keys=()):
         out = {}
         for k, v in self._vars.items():
-            out[k] = numpy.zeros_like(v.data) if k in zero_keys else _deep_copy(v.data)
+            # numpy.zeros maps untouched zero pages (calloc); zeros_like would write all of them
+            out[k] = (numpy.zeros(numpy.shape(v.data), dtype=numpy.asarray(v.data).dtype) if k in zero_keys
+                      else _deep_copy(v.data))
         return out
 
 
