@@ -123,9 +123,9 @@ int hfft_invert_plane(HandFft *h, const cplx<float> *plane, double w, float *acc
 int hfft_predict_plane(HandFft *h, const float *preT, double w, cplx<float> *plane, cudaStream_t s);
 // out[a][b] = accT[b][a] * correction(a, b);  preT[b][a] = dirty[a][b] * correction(a, b)
 template <typename Tout>
-int hfft_correct(const ImgGeo &g, const float *accT, Tout *out, cudaStream_t s);
+int hfft_correct(HandFft *h, const ImgGeo &g, const float *accT, Tout *out, cudaStream_t s);
 template <typename Tin>
-int hfft_precorrect(const ImgGeo &g, const Tin *dirty, float *preT, cudaStream_t s);
+int hfft_precorrect(HandFft *h, const ImgGeo &g, const Tin *dirty, float *preT, cudaStream_t s);
 
 // dtype conversion helpers (n real elements)
 template <typename Tin, typename Tout>

@@ -973,20 +973,20 @@ template <> int hfft_planes_predict<float>(b2g_plan *p, int first, int count)
 template <typename T, typename Tout> int hfft_correct_any(b2g_plan *, const ImgGeo &, Tout *) { return -1; }
 template <> int hfft_correct_any<float, float>(b2g_plan *p, const ImgGeo &g, float *out)
 {
-    return hfft_correct<float>(g, static_cast<const float *>(p->d_acc), out, p->stream);
+    return hfft_correct<float>(p->hfft, g, static_cast<const float *>(p->d_acc), out, p->stream);
 }
 template <> int hfft_correct_any<float, double>(b2g_plan *p, const ImgGeo &g, double *out)
 {
-    return hfft_correct<double>(g, static_cast<const float *>(p->d_acc), out, p->stream);
+    return hfft_correct<double>(p->hfft, g, static_cast<const float *>(p->d_acc), out, p->stream);
 }
 template <typename T, typename Tin> int hfft_precorrect_any(b2g_plan *, const ImgGeo &, const Tin *) { return -1; }
 template <> int hfft_precorrect_any<float, float>(b2g_plan *p, const ImgGeo &g, const float *in)
 {
-    return hfft_precorrect<float>(g, in, static_cast<float *>(p->d_acc), p->stream);
+    return hfft_precorrect<float>(p->hfft, g, in, static_cast<float *>(p->d_acc), p->stream);
 }
 template <> int hfft_precorrect_any<float, double>(b2g_plan *p, const ImgGeo &g, const double *in)
 {
-    return hfft_precorrect<double>(g, in, static_cast<float *>(p->d_acc), p->stream);
+    return hfft_precorrect<double>(p->hfft, g, in, static_cast<float *>(p->d_acc), p->stream);
 }
 
 // planes finished by slab s (invert) : [first, first+count)
