@@ -2,8 +2,8 @@
 fuse into their device kernels, for callers that use them
 on their own:
 
-* ``shift_vis_to_image`` / ``phaserotate_visibility`` (imaging/base.py:48-92, visibility/base.py:27-125,
-  tangent-plane case): vis *= conj(phasor) (or phasor for ``inverse``), phasor =
+* ``shift_vis_to_image`` / ``phaserotate_visibility`` (imaging/base.py:48-92, visibility/base.py:27-125):
+  vis *= conj(phasor) (or phasor for ``inverse``), phasor =
   exp(-2 pi i uvw_lambda . [l, m, sqrt(1 - l^2 - m^2) - 1]), on the device through ``b2g_vis_finish``
   (exact range reduction of the phase, ``sincospi``);
 * ``normalise_sumwt`` (imaging/base.py:95-156).
@@ -55,7 +55,21 @@ def _rotate(vis, lmn, inverse):
     return out.reshape(data.shape)
 
 
-def _phaserotate(vis, ra_n, dec_n, inverse):
+def _reproject_matrix(ra_old, dec_old, ra_new, dec_new):
+    """The 3 x 3 rotation uvw(old phase centre) -> uvw(new phase centre): out of the old frame
+    into earth coordinates (hour angle -ra_old, declination dec_old) and into the new one, as the
+    reference's uvw_to_xyz followed by xyz_to_uvw (util/coordinate_support.py:335-393) -- two
+    rotations each, about the z axis by the hour angle and about the u axis by 90 deg - dec."""
+    def to_xyz(ha, dec):      # rows: x, y, z as combinations of (u, v, w)
+        sh, ch, sd, cd = numpy.sin(ha), numpy.cos(ha), numpy.sin(dec), numpy.cos(dec)
+        return numpy.array([[ch, sh * sd, -sh * cd],
+                            [-sh, ch * sd, -ch * cd],
+                            [0.0, cd, sd]])
+    # xyz_to_uvw is the inverse rotation, i.e. the transpose
+    return to_xyz(-ra_new, dec_new).T @ to_xyz(-ra_old, dec_old)
+
+
+def _phaserotate(vis, ra_n, dec_n, inverse, tangent=True):
     ra_v, dec_v = _radec(vis.phasecentre)
     l, m, nm1 = skycoord_to_lmn(ra_n, dec_n, ra_v, dec_v)
     if abs(nm1) < 1e-15:                                   # "no significant change", visibility/base.py:78
@@ -63,17 +77,25 @@ def _phaserotate(vis, ra_n, dec_n, inverse):
     newvis = vis.copy(deep=True)
     s = (l, m, float(numpy.sqrt(1.0 - l * l - m * m) - 1.0))
     newvis["vis"].data = _rotate(newvis, s, inverse)
+    if not tangent:
+        # leave the tangent plane: re-project the baselines onto the new phase centre and move the
+        # phase centre there (visibility/base.py:98-125; the reference rotates the same way for
+        # both values of ``inverse``); uvw_lambda follows from uvw and frequency on demand
+        uvw = numpy.asarray(newvis["uvw"].data, dtype=numpy.float64)
+        R = _reproject_matrix(ra_v, dec_v, ra_n, dec_n)
+        newvis["uvw"].data[...] = (uvw.reshape(-1, 3) @ R.T).reshape(uvw.shape)
     return newvis
 
 
 def phaserotate_visibility(vis, newphasecentre, tangent=True, inverse=False):
-    """Phase rotate to a new phase centre on the same tangent plane (visibility/base.py:60-125).
-    Returns ``vis`` itself when the change is insignificant, else a rotated deep copy.  The
-    ``tangent=False`` branch (uvw re-projection) is outside the imaging path and not built."""
-    if not tangent:
-        raise NotImplementedError("phaserotate_visibility: tangent=False (uvw re-projection) is not built")
+    """Phase rotate to a new phase centre (visibility/base.py:60-125).  Returns ``vis`` itself when
+    the change is insignificant, else a rotated deep copy; with ``tangent=False`` the uvw are
+    re-projected onto the new phase centre and ``attrs["phasecentre"]`` moves there."""
     ra_n, dec_n = _radec(newphasecentre)
-    return _phaserotate(vis, ra_n, dec_n, inverse)
+    out = _phaserotate(vis, ra_n, dec_n, inverse, tangent)
+    if not tangent and out is not vis:
+        out.attrs["phasecentre"] = newphasecentre
+    return out
 
 
 def shift_vis_to_image(vis, im, tangent=True, inverse=False):
@@ -82,9 +104,7 @@ def shift_vis_to_image(vis, im, tangent=True, inverse=False):
     ra_i, dec_i = image_centre_radec(im)
     ra_v, dec_v = _radec(vis.phasecentre)
     if separation(ra_v, dec_v, ra_i, dec_i) > 1e-15:
-        if not tangent:
-            raise NotImplementedError("shift_vis_to_image: tangent=False (uvw re-projection) is not built")
-        vis = _phaserotate(vis, ra_i, dec_i, inverse)
+        vis = _phaserotate(vis, ra_i, dec_i, inverse, tangent)
         vis.attrs["phasecentre"] = im.image_acc.phasecentre
     return vis
 

@@ -48,8 +48,36 @@ def test_shift_vis_to_image_both_directions(mods, npol):
     assert fwd.attrs["phasecentre"].separation(im.image_acc.phasecentre).rad < 1e-15
     back = base.phaserotate_visibility(fwd_like(mm, vis, fwd), mm.SkyCoord(ra_i, dec_i), inverse=True)
     assert np.abs(back["vis"].data - v0).max() < 1e-12
-    with pytest.raises(NotImplementedError):
-        base.phaserotate_visibility(vis, mm.SkyCoord(ra_i, dec_i), tangent=False)
+
+
+def test_phaserotate_off_the_tangent_plane(mods):
+    """tangent=False (visibility/base.py:98-125): same phasor, uvw re-projected onto the new phase
+    centre, phase centre moved.  Checked against the geometry itself: the new w of a baseline is
+    its projection on the new direction, u stays perpendicular to the new direction and to the
+    celestial pole, lengths are preserved, and rotating back returns the original uvw."""
+    base, mm = mods
+    from ska_sdp_func_python_b200.imaging import skycoord_to_lmn
+    vis = make_vis(mm, 1)
+    new = mm.SkyCoord.from_deg(17.5, -33.0)
+    ra0, dec0 = vis.phasecentre.ra.rad, vis.phasecentre.dec.rad
+    l, m, nm1 = skycoord_to_lmn(new.ra.rad, new.dec.rad, ra0, dec0)
+    out = base.phaserotate_visibility(vis, new, tangent=False)
+    same = base.phaserotate_visibility(vis, new, tangent=True)
+    assert np.array_equal(out["vis"].data, same["vis"].data)                 # identical phasor
+    assert out.attrs["phasecentre"].separation(new).rad < 1e-15
+    assert same.attrs["phasecentre"].separation(vis.phasecentre).rad < 1e-15
+    uvw0, uvw1 = vis["uvw"].data.reshape(-1, 3), out["uvw"].data.reshape(-1, 3)
+    assert np.allclose(np.linalg.norm(uvw1, axis=1), np.linalg.norm(uvw0, axis=1), rtol=1e-13)
+    # w' = b . s_new, with s_new = (l, m, n) in the old frame
+    assert np.allclose(uvw1[:, 2], uvw0 @ np.array([l, m, nm1 + 1.0]), rtol=0, atol=1e-9)
+    # typed-in check of one rotation: phase centre (0, 0) -> (90 deg, 0): the old w axis (towards
+    # ra 0) becomes -u, the old u axis (east at ra 0 = towards ra 90 deg) becomes w, v stays north
+    R = base._reproject_matrix(0.0, 0.0, np.pi / 2, 0.0)
+    assert np.allclose(R, [[0.0, 0.0, -1.0], [0.0, 1.0, 0.0], [1.0, 0.0, 0.0]], atol=1e-15)
+    back = base.phaserotate_visibility(out, vis.phasecentre, tangent=False)
+    assert np.allclose(back["uvw"].data, vis["uvw"].data, rtol=0, atol=1e-9)
+    assert np.abs(out.visibility_acc.uvw_lambda.data[1, 2, 3]
+                  - out["uvw"].data[1, 2] * vis.frequency.data[3] / C).max() < 1e-9
 
 
 def fwd_like(mm, vis, fwd):

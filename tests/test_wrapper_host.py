@@ -152,3 +152,35 @@ def test_geometry_against_typed_in_closed_form_values():
     assert abs(l - 0.00721754799142246370904) < 1e-16
     assert abs(m - 0.0139441168719772890360) < 1e-16
     assert abs(nm1 - (-0.000123273295326594406871)) < 2e-16
+
+
+def test_uvw_reprojection_matrix_equals_the_two_step_rotation():
+    """phaserotate_visibility(tangent=False): base._reproject_matrix against the reference's two
+    steps written out (uvw -> earth xyz at hour angle -ra_old, xyz -> uvw at -ra_new;
+    util/coordinate_support.py:335-393), plus a typed-in case."""
+    from ska_sdp_func_python_b200 import base
+
+    def uvw_to_xyz(uvw, ha, dec):
+        u, v, w = uvw
+        v0 = v * np.sin(dec) - w * np.cos(dec)
+        z = v * np.cos(dec) + w * np.sin(dec)
+        return np.array([u * np.cos(ha) + v0 * np.sin(ha), -u * np.sin(ha) + v0 * np.cos(ha), z])
+
+    def xyz_to_uvw(xyz, ha, dec):
+        x, y, z = xyz
+        v0 = x * np.sin(ha) + y * np.cos(ha)
+        return np.array([x * np.cos(ha) - y * np.sin(ha), z * np.cos(dec) + v0 * np.sin(dec),
+                         z * np.sin(dec) - v0 * np.cos(dec)])
+
+    rng = np.random.default_rng(4)
+    for _ in range(10):
+        ra0, dec0, ra1, dec1 = rng.uniform(-1.4, 1.4, 4)
+        b = rng.normal(size=3) * 1e3
+        want = xyz_to_uvw(uvw_to_xyz(b, -ra0, dec0), -ra1, dec1)
+        R = base._reproject_matrix(ra0, dec0, ra1, dec1)
+        assert np.abs(R @ b - want).max() < 1e-12
+        assert np.abs(R @ R.T - np.eye(3)).max() < 1e-15
+    # phase centre (ra 0, dec 0) -> (ra 90 deg, dec 0): old w (towards ra 0) becomes -u, old u
+    # (east at ra 0, i.e. towards ra 90 deg) becomes w, v keeps pointing north
+    R = base._reproject_matrix(0.0, 0.0, np.pi / 2, 0.0)
+    assert np.allclose(R, [[0.0, 0.0, -1.0], [0.0, 1.0, 0.0], [1.0, 0.0, 0.0]], atol=1e-15)
