@@ -24,9 +24,10 @@ template <typename T> struct VisLaunch {
     const cplx<T> *sub_from = nullptr;  // degridding: ms_out = sub_from - model (residual), may alias ms_out
     cplx<T> *ring;          // [nslots][nu][nv]
     cudaStream_t stream;
-    // degridding, warp-run kernel: chunks of 1024 samples of [begin, end) to leave out (they were
-    // degridded by the tensor-core kernel, vis_tc.cu); NULL = none
-    const unsigned char *skip_chunks = nullptr;
+    // degridding: class of every chunk of 1024 sorted samples of [begin, end) (vis_tc.cu:
+    // tc_classify_kernel) -- 0: warp-run kernel, 1: tensor-core kernel (long runs), 2: one thread
+    // per sample (hardly any two samples share a footprint).  NULL: the launched kernel takes all.
+    const unsigned char *chunk_class = nullptr;
 };
 
 // host table [W][W+4] (highest power first, exactly mirror-symmetric: es_kernel.h) -> the
@@ -52,12 +53,13 @@ template <typename T> int launch_grid_simple(const VisLaunch<T> &L);
 template <typename T> int launch_degrid_simple(const VisLaunch<T> &L);
 
 // tensor-core degridder (fp32, w-stacking, W <= 7): degrids the chunks of 1024 sorted samples whose
-// runs of equal footprint origin are long (at most max_runs runs per chunk) and records them in
-// dense_scratch (one byte per chunk) for the warp-run launch to skip (max_runs < 0: the table is
-// already filled); dense_scratch == NULL: all chunks
+// runs of equal footprint origin are long (at most max_runs runs per chunk: class 1) and records
+// the class of every chunk in chunk_class (one byte per chunk; class 2 = at least sparse_runs runs)
+// for the other launches (max_runs < 0: the table is already filled); chunk_class == NULL: all
+// chunks go through this kernel
 bool tc_supported(int W, bool wstack);
 long long tc_chunks(long long nvis);
-int launch_degrid_tc(const VisLaunch<float> &L, unsigned char *dense_scratch, int max_runs);
+int launch_degrid_tc(const VisLaunch<float> &L, unsigned char *chunk_class, int max_runs, int sparse_runs);
 
 template <typename T> bool warprun_supported(int W, bool wstack);
 template <typename T> int launch_grid_warprun(const VisLaunch<T> &L);

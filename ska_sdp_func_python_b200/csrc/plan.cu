@@ -44,6 +44,7 @@ std::atomic<int> g_max_slab_planes{0};
 // (the rest stays with the warp-run kernel), 2 = every chunk (tests).
 std::atomic<int> g_tc_mode{1};
 constexpr int kTcMaxRuns = 16;     // a chunk of 1024 samples is "dense" with at most this many runs
+constexpr int kSparseRuns = 384;   // ... and "sparse" (one thread per sample) with at least this many
 
 int fail(const char *fmt, ...)
 {
@@ -895,13 +896,20 @@ template <> int degrid_dispatch<float>(b2g_plan *p, VisLaunch<float> &L)
             const char *e = std::getenv("B2G_TC_MAX_RUNS");
             return e ? std::atoi(e) : kTcMaxRuns;
         }();
-        KERNEL_OK(launch_degrid_tc(L, dense, classify ? max_runs : -1));
+        static const int sparse_runs = [] {
+            const char *e = std::getenv("B2G_SPARSE_RUNS");
+            return e ? std::atoi(e) : kSparseRuns;
+        }();
+        KERNEL_OK(launch_degrid_tc(L, dense, classify ? max_runs : -1, sparse_runs));
         p->launches_last += classify ? 2 : 1;
         if (!dense) return 0;
-        L.skip_chunks = dense;
+        // the chunks the tensor-core kernel left: hardly any shared footprints -> one thread per
+        // sample; the rest -> warp-run
+        L.chunk_class = dense;
         KERNEL_OK(launch_degrid_warprun<float>(L));
-        L.skip_chunks = nullptr;
-        p->launches_last++;
+        KERNEL_OK(launch_degrid_simple<float>(L));
+        L.chunk_class = nullptr;
+        p->launches_last += 2;
         return 0;
     }
     if (p->algo == B2G_ALGO_WARPRUN) KERNEL_OK(launch_degrid_warprun<float>(L));

@@ -59,9 +59,13 @@ __global__ void __launch_bounds__(128)
 degrid_simple_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ sidx,
                      long long begin, long long end, int plane0, int slot0,
                      const T *__restrict__ wgt, cplx<T> *out, const cplx<T> *sub_from,
-                     const cplx<T> *__restrict__ ring)
+                     const cplx<T> *__restrict__ ring, const unsigned char *__restrict__ chunk_class)
 {
     constexpr int PW = WS ? W : 1;
+    // with a chunk table: only the chunks of 1024 samples of class 2 (hardly any shared
+    // footprints: one thread per sample beats the warp-run kernel there); blocks of 128 samples
+    // never straddle a chunk
+    if (chunk_class && chunk_class[blockIdx.x >> 3] != 2) return;
     long long i = begin + (long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= end) return;
     const uint32_t idx = sidx[i];
@@ -131,7 +135,7 @@ template <typename T, int W, bool WS> static int degrid_simple_inst(const VisLau
     unsigned blocks = (unsigned)((n + 127) / 128);
     degrid_simple_kernel<T, W, WS><<<blocks, 128, 0, L.stream>>>(
         L.geo, make_tab<T, W>(L.coef), L.sidx, L.begin, L.end, L.plane0, L.slot0, L.wgt, L.ms_out,
-        L.sub_from, L.ring);
+        L.sub_from, L.ring, L.chunk_class);
     return (int)cudaGetLastError();
 }
 

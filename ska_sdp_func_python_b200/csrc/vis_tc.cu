@@ -202,7 +202,7 @@ degrid_tc_kernel(VisGeo g, KernelTab<float, W> tab, const uint32_t *__restrict__
     // persistent blocks: chunk = 1024 sorted samples, dealt out round-robin
     const long long nchunk = (end - begin + kTcChunk - 1) / kTcChunk;
     for (long long ch = blockIdx.x; ch < nchunk; ch += gridDim.x) {
-        if (dense && !dense[ch]) continue;            // sparse chunk: the warp-run kernel's
+        if (dense && dense[ch] != 1) continue;        // not a long-run chunk: another kernel's
         const long long cbeg = begin + ch * kTcChunk;
         const int n = (int)((end - cbeg < kTcChunk) ? end - cbeg : kTcChunk);
         __syncthreads();                              // the previous chunk's arrays are no longer read
@@ -369,11 +369,12 @@ degrid_tc_kernel(VisGeo g, KernelTab<float, W> tab, const uint32_t *__restrict__
         asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tm), "r"(kTmCols) : "memory");
 }
 
-// dense[c] = 1 if chunk c of [begin, end) has at most `max_runs` runs of equal footprint origin
+// class of chunk c of [begin, end): 1 = at most `max_runs` runs of equal footprint origin, 2 = at
+// least `sparse_runs` runs, else 0 (and 0 for the ragged last chunk)
 template <int W>
 __global__ void __launch_bounds__(256)
 tc_classify_kernel(VisGeo g, const uint32_t *__restrict__ sidx, long long begin, long long end, int max_runs,
-                   unsigned char *__restrict__ dense)
+                   int sparse_runs, unsigned char *__restrict__ dense)
 {
     __shared__ int s_count;
     const long long cbeg = begin + (long long)blockIdx.x * kTcChunk;
@@ -398,10 +399,12 @@ tc_classify_kernel(VisGeo g, const uint32_t *__restrict__ sidx, long long begin,
     }
     atomicAdd(&s_count, changes);
     __syncthreads();
-    if (threadIdx.x == 0) dense[blockIdx.x] = (s_count <= max_runs && n == kTcChunk) ? 1 : 0;
+    if (threadIdx.x == 0)
+        dense[blockIdx.x] = n != kTcChunk ? 0 : (s_count <= max_runs ? 1 : (s_count >= sparse_runs ? 2 : 0));
 }
 
-template <int W> int degrid_tc_inst(const VisLaunch<float> &L, unsigned char *dense_scratch, int max_runs)
+template <int W> int degrid_tc_inst(const VisLaunch<float> &L, unsigned char *dense_scratch, int max_runs,
+                                   int sparse_runs)
 {
     const long long nvis = L.end - L.begin;
     if (nvis <= 0) return 0;
@@ -410,7 +413,8 @@ template <int W> int degrid_tc_inst(const VisLaunch<float> &L, unsigned char *de
     cudaError_t e = cudaFuncSetAttribute(degrid_tc_kernel<W>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return (int)e;
     if (dense_scratch && max_runs >= 0) {
-        tc_classify_kernel<W><<<nblk, 256, 0, L.stream>>>(L.geo, L.sidx, L.begin, L.end, max_runs, dense_scratch);
+        tc_classify_kernel<W><<<nblk, 256, 0, L.stream>>>(L.geo, L.sidx, L.begin, L.end, max_runs, sparse_runs,
+                                                          dense_scratch);
         if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;
     }
     // persistent warps: as many blocks as are resident at once (4 per SM: 128 TMEM columns each)
@@ -437,13 +441,13 @@ long long tc_chunks(long long nvis) { return (nvis + kTcChunk - 1) / kTcChunk; }
 // holds the classification (one byte per chunk of 1024 samples of the range), which the warp-run
 // launch then uses to skip those chunks; it is (re)computed first unless max_runs < 0 (the
 // caller has kept it from an earlier call on the same range of the same plan).
-int launch_degrid_tc(const VisLaunch<float> &L, unsigned char *dense_scratch, int max_runs)
+int launch_degrid_tc(const VisLaunch<float> &L, unsigned char *dense_scratch, int max_runs, int sparse_runs)
 {
     switch (L.W) {
-    case 4: return degrid_tc_inst<4>(L, dense_scratch, max_runs);
-    case 5: return degrid_tc_inst<5>(L, dense_scratch, max_runs);
-    case 6: return degrid_tc_inst<6>(L, dense_scratch, max_runs);
-    case 7: return degrid_tc_inst<7>(L, dense_scratch, max_runs);
+    case 4: return degrid_tc_inst<4>(L, dense_scratch, max_runs, sparse_runs);
+    case 5: return degrid_tc_inst<5>(L, dense_scratch, max_runs, sparse_runs);
+    case 6: return degrid_tc_inst<6>(L, dense_scratch, max_runs, sparse_runs);
+    case 7: return degrid_tc_inst<7>(L, dense_scratch, max_runs, sparse_runs);
     default: return -1;
     }
 }

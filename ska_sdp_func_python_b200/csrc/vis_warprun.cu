@@ -376,7 +376,7 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
 {
     using C = Cfg<T, W, PWB, false>;
     static_assert(kWarps * kChunk == 1024, "skip flags are per chunk of 1024 samples (vis_tc.cu)");
-    if (skip && skip[blockIdx.x]) return;   // degridded by the tensor-core kernel
+    if (skip && skip[blockIdx.x]) return;   // another kernel's chunk (vis_tc.cu classes 1, 2)
     using S = Stage<T, W, PWB, false>;
     using P = typename V2<T>::type;
     constexpr int PW = C::PW, IPL = C::IPL;
@@ -573,7 +573,7 @@ template <typename T, int W, int PWB> static int degrid_inst(const VisLaunch<T> 
     for (int q0 = 0; q0 < (PWB > 0 ? W : 1); q0 += (PWB > 0 ? PWB : 1)) {
         degrid_warprun_kernel<T, W, PWB><<<nblocks_for(n), 32 * kWarps, smem, L.stream>>>(
             L.geo, make_tab<T, W>(L.coef), L.sidx, L.begin, L.end, L.plane0, L.slot0, q0, L.wgt,
-            L.ms_out, L.sub_from, L.ring, L.skip_chunks);
+            L.ms_out, L.sub_from, L.ring, L.chunk_class);
         if ((e = cudaGetLastError()) != cudaSuccess) return (int)e;
     }
     return 0;
