@@ -86,18 +86,29 @@ template <typename T> struct Partials {
     typename V2<T>::type p[16 * 33];
 };
 
-// Lane-parallel preparation of one sample (lane `lane` of the warp).  `val` is the (weighted)
-// visibility for gridding.  Returns the packed origin (iu0 << 16 | iv0, p0).
+// (u, v, w) of sample idx in wavelengths: loaded one batch ahead of their use (the loads depend on
+// the sorted index, so they cannot be issued any earlier than that)
+__device__ __forceinline__ void fetch_uvw(const VisGeo &g, uint32_t idx, double &ul, double &vl, double &wl)
+{
+    uint32_t row, chan;
+    g.split(idx, row, chan);
+    const double fs = __ldg(g.fscale + chan);
+    ul = __ldg(g.uvw + 3ull * row + 0) * fs;
+    vl = __ldg(g.uvw + 3ull * row + 1) * fs;
+    wl = __ldg(g.uvw + 3ull * row + 2) * fs;
+}
+
+// Lane-parallel preparation of one sample (lane `lane` of the warp), located from its (u, v, w) in
+// wavelengths.  `val` is the (weighted) visibility for gridding.  Returns the packed origin
+// (iu0 << 16 | iv0, p0).
 template <typename T, int W, int PWB, bool GRID>
-__device__ __forceinline__ void prepare(const VisGeo &g, const KernelTab<T, W> &tab, uint32_t idx,
-                                        int lane, Stage<T, W, PWB, GRID> &st, cplx<T> val, int q0,
-                                        bool &flip, int &oxy, int &oz)
+__device__ __forceinline__ void prepare(const VisGeo &g, const KernelTab<T, W> &tab, double ul, double vl,
+                                        double wl, int lane, Stage<T, W, PWB, GRID> &st, cplx<T> val,
+                                        int q0, bool &flip, int &oxy, int &oz)
 {
     using C = Cfg<T, W, PWB, GRID>;
     constexpr bool WS = C::WS;
-    uint32_t row, chan;
-    g.split(idx, row, chan);
-    const Located L = locate(g, W, row, chan);
+    const Located L = locate_uvw(g, W, ul, vl, wl);
     flip = L.flip;
     oxy = (L.iu0 << 16) | L.iv0;
     oz = L.p0;
@@ -268,6 +279,8 @@ grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ 
 
     // software pipeline: the next batch's index / sample / weight are in flight while the
     // current batch is accumulated
+    // (the (u, v, w) loads are NOT issued a batch ahead here, unlike in the degridder: measured,
+    // the six extra live registers cost this kernel more than the hidden latency gains)
     uint32_t nidx = 0;
     cplx<T> nval{T(0), T(0)};
     if (cbeg + lane < cend) {
@@ -297,7 +310,9 @@ grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ 
         int oxy = 0, oz = 0;
         if (active) {
             bool flip;
-            prepare<T, W, PWB, true>(g, tab, idx, lane, st, val, q0, flip, oxy, oz);
+            double ul, vl, wl;
+            fetch_uvw(g, idx, ul, vl, wl);
+            prepare<T, W, PWB, true>(g, tab, ul, vl, wl, lane, st, val, q0, flip, oxy, oz);
         }
         const unsigned act = __ballot_sync(kFull, active);
         const unsigned mov = moved_mask(active, oxy, oz, lane, act, carry_xy, carry_z);
@@ -428,24 +443,28 @@ degrid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict_
 
     uint32_t nidx = 0;
     T nw = T(1);
+    double nul = 0.0, nvl = 0.0, nwl = 0.0;
     if (cbeg + lane < cend) {
         nidx = sidx[cbeg + lane];
         if (wgt) nw = wgt[nidx];
+        fetch_uvw(g, nidx, nul, nvl, nwl);
     }
 
     for (long long b0 = cbeg; b0 < cend; b0 += 32) {
         const int n = (int)((cend - b0 < 32) ? cend - b0 : 32);
         const uint32_t my_idx = nidx;
         const T my_w = nw;
+        const double ul = nul, vl = nvl, wl = nwl;
         if (b0 + 32 + lane < cend) {
             nidx = sidx[b0 + 32 + lane];
             if (wgt) nw = wgt[nidx];
+            fetch_uvw(g, nidx, nul, nvl, nwl);
         }
         const bool active = lane < n && my_w != T(0);
         bool my_flip = false;
         int oxy = 0, oz = 0;
         if (active)
-            prepare<T, W, PWB, false>(g, tab, my_idx, lane, st, cplx<T>{T(1), T(1)}, q0, my_flip, oxy, oz);
+            prepare<T, W, PWB, false>(g, tab, ul, vl, wl, lane, st, cplx<T>{T(1), T(1)}, q0, my_flip, oxy, oz);
         const unsigned act = __ballot_sync(kFull, active);
         const unsigned mov = moved_mask(active, oxy, oz, lane, act, carry_xy, carry_z);
         __syncwarp();
