@@ -430,6 +430,10 @@ def run_b200(args):
     dev = torch.device("cuda", local_rank)
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
+        # torchrun exports OMP_NUM_THREADS=1, which would make the staging copies of the e2e leg
+        # (complex128 -> complex64 into pinned memory, the deep copy of the result container)
+        # single-threaded: give every rank its share of the host cores instead
+        torch.set_num_threads(max(1, (os.cpu_count() or 1) // world))
     cfg = simulate.CONFIGS[args.config]
     geo = make_geometry(args.config)
     obs, uvw, freq = geo["obs"], geo["uvw"], geo["freq"]
