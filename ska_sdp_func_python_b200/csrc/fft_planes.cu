@@ -30,6 +30,7 @@
 #include <cuda.h>
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <vector>
@@ -119,6 +120,47 @@ __device__ __forceinline__ bool screen_sincos(double r2, double w_signed, float 
     ph -= rint(ph);
     sincospif(2.0f * (float)ph, &s, &c);
     return true;
+}
+
+// Per-plane screen constants.  phase [cycles] = w (n - 1) = -w r2 / 2 - w q^2 / 2 with r2 = x^2 + y^2
+// and q = r2 / (1 + sqrt(1 - r2)) = -(n - 1).  The first term is tens of cycles and linear in the
+// INTEGERS (a - hx)^2, (b - hy)^2: its fractional part comes exactly out of a 64-bit fixed-point
+// product; the second is a fraction of a cycle and fp32 is enough for it.  `fast` is set per plane
+// when that holds (|w| q_max^2 / 2 < 1/2 cycle); otherwise the fp64 evaluation above is used.
+struct Screen {
+    double w;                      // signed: -w for invert, +w for predict
+    unsigned long long cx, cy;     // frac(-w psx^2 / 2), frac(-w psy^2 / 2) as 0.64 fixed point
+    float k3;                      // -w / 2
+    float psx, psy;
+    int fast;
+};
+
+__device__ __forceinline__ float frac_fixed(unsigned long long c, int d)
+{
+    // frac(c * d^2) as a signed fraction in [-1/2, 1/2)
+    const unsigned long long p = c * (unsigned long long)((unsigned)(d * d));
+    return (float)(int)(unsigned)(p >> 32) * 2.3283064365386963e-10f;
+}
+
+// (sin, cos) of 2 pi * phase at pixel offset ax = a - hx of the line with fy = frac_fixed(cy, b - hy),
+// y2f = y^2 (fp32), y2d = y^2 (fp64); false beyond the horizon
+template <bool FAST>
+__device__ __forceinline__ bool screen_eval(const Screen &S, double psx, int ax, float fy, float y2f,
+                                            double y2d, float &s, float &c)
+{
+    if (FAST) {
+        const float xf = (float)ax * S.psx;
+        const float r2 = fmaf(xf, xf, y2f);
+        if (!(r2 < 1.f)) return false;
+        const float z = 1.f - r2;
+        const float q = __fdividef(r2, fmaf(z, rsqrtf(z), 1.f));      // r2 / (1 + sqrt(1 - r2))
+        float ph = frac_fixed(S.cx, ax) + fy + S.k3 * q * q;
+        ph -= rintf(ph);
+        __sincosf(6.283185307179586f * ph, &s, &c);
+        return true;
+    }
+    const double x = (double)ax * psx;
+    return screen_sincos(fma(x, x, y2d), S.w, s, c);
 }
 
 struct PlaneGeo {
@@ -258,9 +300,9 @@ __device__ __forceinline__ void red_add_v4(float *addr, float a, float b, float 
 // lane four consecutive image pixels, which are added to the accumulator with one vector reduction
 // (no read-modify-write round trip; every pixel receives exactly one addition per plane, so the
 // result does not depend on any ordering).
-template <class P>
+template <class P, bool FAST>
 __global__ void __launch_bounds__(P::THREADS, min_blocks<P>())
-hfft_cols_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *__restrict__ T, double w,
+hfft_cols_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *__restrict__ T, Screen S,
                      float *__restrict__ accT)
 {
     extern __shared__ __align__(128) unsigned char raw[];
@@ -333,6 +375,7 @@ hfft_cols_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *__
             // v[0][r] is image row index k = tid + r * NS of column b: screen, keep the real part
             const double y = (double)(b - g.hy) * g.psy;
             const double y2 = y * y;
+            const float y2f = (float)y2, fy = frac_fixed(S.cy, b - g.hy);
             float val[LS::R];
 #pragma unroll
             for (int r = 0; r < LS::R; ++r) {
@@ -340,9 +383,8 @@ hfft_cols_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *__
                 const int a = image_index(tid + r * LS::NS, nu, npx, hx);
                 if (active && a >= 0) {
                     if (g.wstack) {
-                        const double x = (double)(a - hx) * g.psx;
                         float s, co;
-                        if (screen_sincos(fma(x, x, y2), -w, s, co)) val[r] = v[0][r].x * co - v[0][r].y * s;
+                        if (screen_eval<FAST>(S, g.psx, a - hx, fy, y2f, y2, s, co)) val[r] = v[0][r].x * co - v[0][r].y * s;
                     } else {
                         val[r] = v[0][r].x;
                     }
@@ -371,9 +413,9 @@ hfft_cols_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *__
 }
 
 // ---- predict, columns: preT[b][:] * screen, zero-padded -> T[b/2][:][b&1] -------------------------
-template <class P>
+template <class P, bool FAST>
 __global__ void __launch_bounds__(P::THREADS, min_blocks<P>())
-hfft_cols_fwd_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float *__restrict__ preT, double w,
+hfft_cols_fwd_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float *__restrict__ preT, Screen S,
                      float2 *__restrict__ T)
 {
     extern __shared__ __align__(128) unsigned char raw[];
@@ -396,6 +438,7 @@ hfft_cols_fwd_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float *__r
             const float *src = preT + (size_t)b * npx;
             const double y = (double)(b - g.hy) * g.psy;
             const double y2 = y * y;
+            const float y2f = (float)y2, fy = frac_fixed(S.cy, b - g.hy);
             auto wr = [X](int k, float2 v) { X[k] = v; };         // linear, for the piece copy below
             HookSync<NoHook> sync{0, -1, NoHook()};
             {
@@ -420,10 +463,9 @@ hfft_cols_fwd_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float *__r
                             float2 z = make_float2(val, 0.f);
                             if (g.wstack && val != 0.f) {
                                 const int a = image_index(tid + cc * P::T + t * q, nu, npx, hx);
-                                const double x = (double)(a - hx) * g.psx;
                                 float s, co;
-                                z = screen_sincos(fma(x, x, y2), w, s, co) ? make_float2(val * co, val * s)
-                                                                            : make_float2(0.f, 0.f);
+                                z = screen_eval<FAST>(S, g.psx, a - hx, fy, y2f, y2, s, co) ? make_float2(val * co, val * s)
+                                                                                       : make_float2(0.f, 0.f);
                             }
                             v[cc][t] = z;
                         }
@@ -604,6 +646,7 @@ struct LineOps {
     size_t smem = 0;
     void (*build_tw)(int sign, float2 *tw) = nullptr;
     const void *rows_inv = nullptr, *cols_inv = nullptr, *cols_fwd = nullptr, *rows_fwd = nullptr;
+    const void *cols_inv_fast = nullptr, *cols_fwd_fast = nullptr;   // fixed-point / fp32 screen
 };
 
 template <class P> LineOps make_ops()
@@ -615,8 +658,10 @@ template <class P> LineOps make_ops()
     o.smem = SmemLayout<P>::BYTES;
     o.build_tw = &hfft::build_twiddles<P>;
     o.rows_inv = reinterpret_cast<const void *>(&hfft_rows_inv_kernel<P>);
-    o.cols_inv = reinterpret_cast<const void *>(&hfft_cols_inv_kernel<P>);
-    o.cols_fwd = reinterpret_cast<const void *>(&hfft_cols_fwd_kernel<P>);
+    o.cols_inv = reinterpret_cast<const void *>(&hfft_cols_inv_kernel<P, false>);
+    o.cols_fwd = reinterpret_cast<const void *>(&hfft_cols_fwd_kernel<P, false>);
+    o.cols_inv_fast = reinterpret_cast<const void *>(&hfft_cols_inv_kernel<P, true>);
+    o.cols_fwd_fast = reinterpret_cast<const void *>(&hfft_cols_fwd_kernel<P, true>);
     o.rows_fwd = reinterpret_cast<const void *>(&hfft_rows_fwd_kernel<P>);
     return o;
 }
@@ -711,10 +756,12 @@ int hfft_create(HandFft **out, const ImgGeo &ig, cudaStream_t s)
         const LineOps *o;
         int *grid;
         int lines;
-    } ks[4] = {{ov.rows_inv, &h->ov, &h->grid_rows_inv, nu},
+    } ks[6] = {{ov.rows_inv, &h->ov, &h->grid_rows_inv, nu},
                {ov.rows_fwd, &h->ov, &h->grid_rows_fwd, nu},
                {ou.cols_inv, &h->ou, &h->grid_cols_inv, npy / 2},
-               {ou.cols_fwd, &h->ou, &h->grid_cols_fwd, npy / 2}};
+               {ou.cols_fwd, &h->ou, &h->grid_cols_fwd, npy / 2},
+               {ou.cols_inv_fast, &h->ou, &h->grid_cols_inv, npy / 2},
+               {ou.cols_fwd_fast, &h->ou, &h->grid_cols_fwd, npy / 2}};
     for (auto &k : ks) {
         int per_sm = 0;
         if (cudaFuncSetAttribute(k.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k.o->smem) != cudaSuccess ||
@@ -747,9 +794,37 @@ void hfft_describe(const HandFft *h, char *buf, int n)
              h->ov.smem, h->grid_rows_inv, h->grid_rows_fwd, h->pb);
 }
 
+namespace {
+// the per-plane screen constants for signed w (see struct Screen)
+Screen make_screen(const HandFft *h, double w_signed)
+{
+    const PlaneGeo &g = h->g;
+    Screen S;
+    S.w = w_signed;
+    auto fixed = [](double v) {
+        double f = v - std::floor(v);                      // [0, 1)
+        if (!(f >= 0.0) || f >= 1.0) f = 0.0;
+        return (unsigned long long)std::ldexp(f, 64 - 11) << 11;   // 53 significant bits
+    };
+    S.cx = fixed(-0.5 * w_signed * g.psx * g.psx);
+    S.cy = fixed(-0.5 * w_signed * g.psy * g.psy);
+    S.k3 = (float)(-0.5 * w_signed);
+    S.psx = (float)g.psx;
+    S.psy = (float)g.psy;
+    // the fp32 remainder term must stay a fraction of a cycle (its relative error is ~1e-6), and
+    // the squared pixel offsets must fit 32 bits
+    const double xm = g.psx * g.hx, ym = g.psy * g.hy, r2 = xm * xm + ym * ym;
+    const double q = r2 < 1.0 ? r2 / (1.0 + std::sqrt(1.0 - r2)) : 1.0;
+    S.fast = (r2 < 0.5 && 0.5 * std::fabs(w_signed) * q * q < 0.5 && g.hx < 46000 && g.hy < 46000 &&
+              !std::getenv("B2G_SCREEN_FP64")) ? 1 : 0;
+    return S;
+}
+}  // namespace
+
 int hfft_invert_plane(HandFft *h, const cplx<float> *plane, double w, float *accT, cudaStream_t s)
 {
     PlaneGeo g = h->g;
+    Screen S = make_screen(h, -w);
     const float2 *twv = h->d_tw + h->off_vp, *twu = h->d_tw + h->off_up;
     const float2 *pl = reinterpret_cast<const float2 *>(plane);
     const float2 *T = h->d_T;
@@ -758,21 +833,23 @@ int hfft_invert_plane(HandFft *h, const cplx<float> *plane, double w, float *acc
     cudaError_t e = cudaLaunchKernel(h->ov.rows_inv, dim3(h->grid_rows_inv), dim3(h->ov.threads), a_rows,
                                      h->ov.smem, s);
     if (e != cudaSuccess) return (int)e;
-    void *a_cols[] = {&g, &twu, &T, &w, &accT};
-    e = cudaLaunchKernel(h->ou.cols_inv, dim3(h->grid_cols_inv), dim3(h->ou.threads), a_cols, h->ou.smem, s);
+    void *a_cols[] = {&g, &twu, &T, &S, &accT};
+    e = cudaLaunchKernel(S.fast ? h->ou.cols_inv_fast : h->ou.cols_inv, dim3(h->grid_cols_inv),
+                         dim3(h->ou.threads), a_cols, h->ou.smem, s);
     return (int)e;
 }
 
 int hfft_predict_plane(HandFft *h, const float *preT, double w, cplx<float> *plane, cudaStream_t s)
 {
     PlaneGeo g = h->g;
+    Screen S = make_screen(h, w);
     const float2 *twv = h->d_tw + h->off_vm, *twu = h->d_tw + h->off_um;
     float2 *pl = reinterpret_cast<float2 *>(plane);
     float2 *T = h->d_T;
     int pb = h->pb;
-    void *a_cols[] = {&g, &twu, &preT, &w, &T};
-    cudaError_t e = cudaLaunchKernel(h->ou.cols_fwd, dim3(h->grid_cols_fwd), dim3(h->ou.threads), a_cols,
-                                     h->ou.smem, s);
+    void *a_cols[] = {&g, &twu, &preT, &S, &T};
+    cudaError_t e = cudaLaunchKernel(S.fast ? h->ou.cols_fwd_fast : h->ou.cols_fwd, dim3(h->grid_cols_fwd),
+                                     dim3(h->ou.threads), a_cols, h->ou.smem, s);
     if (e != cudaSuccess) return (int)e;
     void *a_rows[] = {&g, &twv, &h->tmap, &pb, &pl};
     e = cudaLaunchKernel(h->ov.rows_fwd, dim3(h->grid_rows_fwd), dim3(h->ov.threads), a_rows, h->ov.smem, s);
