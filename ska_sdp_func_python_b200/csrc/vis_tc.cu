@@ -182,7 +182,8 @@ degrid_tc_kernel(VisGeo g, KernelTab<float, W> tab, const uint32_t *__restrict__
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     if (tid == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&sm.bar)) : "memory");
+        // four arrivals per tile: lane 0 of every warp issues a share of the MMAs and commits
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], 4;" ::"r"(smem_u32(&sm.bar)) : "memory");
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     for (int i = tid; i < 4 * C::B_FLOATS; i += kTcThreads) (&sm.B[0][0][0])[i] = 0.f;
@@ -297,21 +298,32 @@ degrid_tc_kernel(VisGeo g, KernelTab<float, W> tab, const uint32_t *__restrict__
                     tm_st8(lane_base + c0, hi);
                     tm_st8(lane_base + C::COL_ALO + c0, lo);
                 }
+                // every MMA of the tile accumulates (they are issued by four threads, in no
+                // particular order): the accumulator rows start from zero
+                const float zero[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+                tm_st8(lane_base + C::COL_D, zero);
+                tm_st8(lane_base + C::COL_D + 8, zero);
                 asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
             }
             asm volatile("fence.proxy.async.shared::cta;" ::: "memory");   // B stores -> tensor core reads
             asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory");
             __syncthreads();
-            if (tid == 0) {
+            if (lane == 0) {
+                // K-steps warp, warp + 4, ...: the ~11 instructions of operand set-up per MMA are the
+                // serial part of a tile, so they are spread over the four warps (measured safe:
+                // tools/probe/tc_probe.cu mode 3)
                 asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory");
                 const uint64_t bh_desc = dbase | (uint64_t)((smem_u32(sm.B[bb][0]) >> 4) & 0x3fff);
                 const uint64_t bl_desc = dbase | (uint64_t)((smem_u32(sm.B[bb][1]) >> 4) & 0x3fff);
 #pragma unroll
-                for (int ks = 0; ks < C::KS; ++ks) {
-                    const uint64_t bh = bh_desc + (uint64_t)(ks * 32), bl = bl_desc + (uint64_t)(ks * 32);
-                    mma_ts(tm + C::COL_D, tm + ks * 8, bh, idesc, ks > 0, 0u, 0u, 0u, 0u);
-                    mma_ts(tm + C::COL_D, tm + C::COL_ALO + ks * 8, bh, idesc, 1, 0u, 0u, 0u, 0u);
-                    mma_ts(tm + C::COL_D, tm + ks * 8, bl, idesc, 1, 0u, 0u, 0u, 0u);
+                for (int k0 = 0; k0 < C::KS; k0 += 4) {
+                    const int ks = k0 + warp;
+                    if (ks < C::KS) {
+                        const uint64_t bh = bh_desc + (uint64_t)(ks * 32), bl = bl_desc + (uint64_t)(ks * 32);
+                        mma_ts(tm + C::COL_D, tm + ks * 8, bh, idesc, 1, 0u, 0u, 0u, 0u);
+                        mma_ts(tm + C::COL_D, tm + C::COL_ALO + ks * 8, bh, idesc, 1, 0u, 0u, 0u, 0u);
+                        mma_ts(tm + C::COL_D, tm + ks * 8, bl, idesc, 1, 0u, 0u, 0u, 0u);
+                    }
                 }
                 asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(
                                  smem_u32(&sm.bar))
