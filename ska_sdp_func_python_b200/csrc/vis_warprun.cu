@@ -277,35 +277,32 @@ grid_warprun_kernel(VisGeo g, KernelTab<T, W> tab, const uint32_t *__restrict__ 
         }
     };
 
-    // software pipeline: the next batch's index / sample / weight are in flight while the
-    // current batch is accumulated
+    // software pipeline, two deep: the sorted index is loaded two batches ahead, the sample and
+    // its weight (whose addresses depend on the index) one batch ahead, and nothing is done with a
+    // loaded value before the batch that uses it (the weighting multiply included), so neither
+    // load latency sits in front of the arithmetic
     // (the (u, v, w) loads are NOT issued a batch ahead here, unlike in the degridder: measured,
     // the six extra live registers cost this kernel more than the hidden latency gains)
-    uint32_t nidx = 0;
-    cplx<T> nval{T(0), T(0)};
+    uint32_t idx1 = 0, idx2 = 0;
+    cplx<T> val1{T(0), T(0)};
+    T w1 = T(1);
     if (cbeg + lane < cend) {
-        nidx = sidx[cbeg + lane];
-        nval = ms[nidx];
-        if (wgt) {
-            const T w = wgt[nidx];
-            nval.re *= w;
-            nval.im *= w;
-        }
+        idx1 = sidx[cbeg + lane];
+        val1 = ms[idx1];
+        if (wgt) w1 = wgt[idx1];
     }
+    if (cbeg + 32 + lane < cend) idx2 = sidx[cbeg + 32 + lane];
 
     for (long long b0 = cbeg; b0 < cend; b0 += 32) {
         const int n = (int)((cend - b0 < 32) ? cend - b0 : 32);
-        const uint32_t idx = nidx;
-        const cplx<T> val = nval;
+        const uint32_t idx = idx1;
+        const cplx<T> val{val1.re * w1, val1.im * w1};
+        idx1 = idx2;
         if (b0 + 32 + lane < cend) {
-            nidx = sidx[b0 + 32 + lane];
-            nval = ms[nidx];
-            if (wgt) {
-                const T w = wgt[nidx];
-                nval.re *= w;
-                nval.im *= w;
-            }
+            val1 = ms[idx1];
+            if (wgt) w1 = wgt[idx1];
         }
+        if (b0 + 64 + lane < cend) idx2 = sidx[b0 + 64 + lane];
         const bool active = lane < n && (val.re != T(0) || val.im != T(0));
         int oxy = 0, oz = 0;
         if (active) {

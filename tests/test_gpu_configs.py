@@ -170,3 +170,4 @@ def _check_config(wg, obs, prec, eps, ws, bound, nplanes_min=0, nslabs_min=1, np
     for k in (0, 1):
         assert rel_l2(res["hand"][k], res["cufft"][k]) < 3e-6
         assert rel_l2(res["hand_slabs"][k], res["cufft"][k]) < 3e-6
+        assert rel_l2(res["hand_fp64_screen"][k], res["hand"][k]) < 2e-6
