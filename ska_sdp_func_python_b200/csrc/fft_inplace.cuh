@@ -44,6 +44,25 @@ static inline float2 make_float2(float x, float y) { float2 r; r.x = x; r.y = y;
 namespace b2g {
 namespace hfft {
 
+// complex add / subtract: one packed FADD2 / FFMA2 on the device (sm_100 f32x2 arithmetic; the
+// subtraction is b * (-1, -1) + a, exact like a - b), two scalar operations on the host
+B2G_HD float2 cadd(float2 a, float2 b)
+{
+#if defined(__CUDA_ARCH__)
+    return __fadd2_rn(a, b);
+#else
+    return make_float2(a.x + b.x, a.y + b.y);
+#endif
+}
+B2G_HD float2 csub(float2 a, float2 b)
+{
+#if defined(__CUDA_ARCH__)
+    return __ffma2_rn(b, make_float2(-1.f, -1.f), a);
+#else
+    return make_float2(a.x - b.x, a.y - b.y);
+#endif
+}
+
 #include "fft_codelets.inc"
 
 B2G_HD float2 cmul(float2 a, float2 b)
