@@ -149,6 +149,21 @@ int b2g_dirty2ms(int64_t nrow, int64_t nchan, const double *uvw, const double *f
  * Mirrors numpy.sum(wgt) at ng.py:258, :289. */
 int b2g_sumwt(const void *wgt, int dtype, int space, int64_t n, double *out, void *stream);
 
+/* b2g_sumwt for callers that may not allocate device memory (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * The 1024 block partials of the reduction live in a file-scope
+ * __device__ array of the library (8 KiB, held by every GPU that loads the library until the
+ * process exits; csrc/sum_static.cu) instead of coming from cudaMallocAsync.  The call allocates
+ * nothing, copies nothing and does not synchronise: wgt (dtype B2G_F32 / B2G_F64, n entries) and
+ * out (one double) are DEVICE pointers, and the two kernels are only enqueued on `stream`, on the
+ * current device.  Same reduction tree as b2g_sumwt: the results agree bit for bit.
+ * n > B2G_SUMWT_STATIC_MAX_N is rejected (non-zero return, message in b2g_last_error()).
+ * All calls on one device SHARE the scratch array: calls that overlap on the GPU (different
+ * streams) race; calls on one stream are ordered and safe.  Nothing needs clearing between
+ * calls (every partial and *out are overwritten by each call). */
+#define B2G_SUMWT_STATIC_MAX_N 4294967296ll /* 2^32 weights */
+int b2g_sumwt_static(const void *wgt, int dtype, int64_t n, double *out, void *stream);
+
 /* Plans created from HOST uvw stream the visibility arrays of b2g_plan_invert /
  * b2g_plan_predict over PCIe in row chunks of about `nsamples` samples, overlapped with
  * gridding / degridding (what a caller of ducc0.wgridder with host arrays gets, ng.py:240-256).

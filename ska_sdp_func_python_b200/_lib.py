@@ -22,6 +22,7 @@ EXPORTS = (
     "b2g_kernel_corr", "b2g_vis_prepare", "b2g_vis_finish", "b2g_set_host_chunk_samples", "b2g_set_max_slab_planes", "b2g_set_tc_mode", "b2g_plan_create_sel",
     "b2g_weight_grid", "b2g_weight_apply", "b2g_weight_taper", "b2g_dft_predict",
     "b2g_plan_residual", "b2g_hogbom", "b2g_image_peak", "b2g_dft_invert", "b2g_msclean", "b2g_msmfsclean", "b2g_hogbom_complex",
+    "b2g_sumwt_static",
 )
 FLAG_NONE, FLAG_U8, FLAG_I32, FLAG_I64, FLAG_F64 = 0, 1, 2, 3, 4
 
@@ -72,6 +73,8 @@ def lib():
                                i64, dbl, ci, ci, vp, vp]
     L.b2g_sumwt.restype = ci
     L.b2g_sumwt.argtypes = [vp, ci, ci, i64, pd, vp]
+    L.b2g_sumwt_static.restype = ci
+    L.b2g_sumwt_static.argtypes = [vp, ci, i64, vp, vp]
     L.b2g_set_host_chunk_samples.restype = ci
     L.b2g_set_host_chunk_samples.argtypes = [i64]
     L.b2g_set_max_slab_planes.restype = ci
