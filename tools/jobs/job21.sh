@@ -1,3 +1,4 @@
-timeout 900 python -m pytest tests/test_gpu_configs.py tests/test_gpu_fullsize.py -m gpu -q 2>&1 | tail -3
-timeout 600 python bench.py --steps 3 --warmup 3 --no-e2e --no-cpu --no-secondary 2>/dev/null | python -c "
-import json,sys; d=json.loads(sys.stdin.read()); print('ms', round(d['ms_per_step'],1), {k: round(v,1) for k,v in d['config']['stage_ms_per_step'].items()})"
+# full ncu capture of the four plane-transform kernels of the current build (all stall reasons)
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:hfft_ -s 20 -c 2 -o gpurun_out/r02_d_hfft_inv python tools/wshard_bench.py --config C4 --nchan 8 --steps 1 --warmup 0 > gpurun_out/ncu_hfft.log 2>&1; tail -3 gpurun_out/ncu_hfft.log
+timeout 900 ncu --set full --clock-control none --import-source on -k regex:hfft_.*fwd -s 20 -c 2 -o gpurun_out/r02_d_hfft_fwd python tools/wshard_bench.py --config C4 --nchan 8 --steps 1 --warmup 0 > gpurun_out/ncu_hfft2.log 2>&1; tail -3 gpurun_out/ncu_hfft2.log
+ls -la gpurun_out/*.ncu-rep

@@ -42,6 +42,9 @@ def main():
     rows = list(csv.reader(io.StringIO(raw)))
     hdr, units, data = rows[0], rows[1], rows[2:]
     idx = [(k, hdr.index(k)) for k in KEYS if k in hdr]
+    # every stall reason the capture holds, not only the ones named above
+    idx += [(k, i) for i, k in enumerate(hdr)
+            if "issue_stalled" in k and k.endswith("per_issue_active.ratio") and k not in KEYS]
     with open(out, "w", newline="") as fh:
         w = csv.writer(fh)
         w.writerow(["metric", "unit"] + [f"launch{i}" for i in range(len(data))])
