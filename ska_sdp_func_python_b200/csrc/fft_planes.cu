@@ -217,8 +217,8 @@ struct NoHook {
 // buffer is free (and refilled by TMA) as soon as the last stage has read it.
 template <class P>
 __global__ void __launch_bounds__(P::THREADS, min_blocks<P>())
-hfft_rows_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *__restrict__ plane,
-                     float4 *__restrict__ T4)
+hfft_rows_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *plane, float4 *__restrict__ T4,
+                     float2 *clear_plane)
 {
     extern __shared__ __align__(128) unsigned char raw[];
     using L = SmemLayout<P>;
@@ -234,6 +234,10 @@ hfft_rows_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *__
         mbar_init(bar + 1, 1);
         mbar_fence_init();
     }
+    // clear_plane (= plane, or null): every row is zeroed in global memory once it has arrived in
+    // shared memory, so the ring slot is ready for the gridder's next slab without a separate
+    // memset pass over it (the stores ride in this kernel's unused DRAM bandwidth)
+    static_assert(P::N % (2 * P::T) == 0, "whole 16-byte stores per thread");
     __syncthreads();
     constexpr int nv = P::N;
     constexpr uint32_t row_bytes = uint32_t(P::N) * 8u;
@@ -253,6 +257,13 @@ hfft_rows_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *__
         const int b = it & 1;
         float2 *X = X0 + b * L::NPADA;
         mbar_wait(bar + b, (uint32_t)(it >> 1) & 1u);
+        if (clear_plane && active) {
+            // measured: bulk (TMA) stores from a block of zeros here cost 1.2 ms per plane -- they
+            // queue in front of the next rows' bulk loads; plain vector stores do not
+            float4 *zrow = reinterpret_cast<float4 *>(clear_plane + (size_t)u * nv);
+#pragma unroll
+            for (int i = 0; i < P::N / (2 * P::T); ++i) zrow[tid + i * P::T] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
         auto rd0 = [X](int i) { return X[i]; };                 // linear, as the bulk load left it
         const int un = u + 2 * gridDim.x;
         auto hook = [&]() {
@@ -821,7 +832,7 @@ Screen make_screen(const HandFft *h, double w_signed)
 }
 }  // namespace
 
-int hfft_invert_plane(HandFft *h, const cplx<float> *plane, double w, float *accT, cudaStream_t s)
+int hfft_invert_plane(HandFft *h, cplx<float> *plane, double w, float *accT, bool clear, cudaStream_t s)
 {
     PlaneGeo g = h->g;
     Screen S = make_screen(h, -w);
@@ -829,7 +840,8 @@ int hfft_invert_plane(HandFft *h, const cplx<float> *plane, double w, float *acc
     const float2 *pl = reinterpret_cast<const float2 *>(plane);
     const float2 *T = h->d_T;
     float4 *T4 = reinterpret_cast<float4 *>(h->d_T);
-    void *a_rows[] = {&g, &twv, &pl, &T4};
+    float2 *clr = clear ? reinterpret_cast<float2 *>(plane) : nullptr;
+    void *a_rows[] = {&g, &twv, &pl, &T4, &clr};
     cudaError_t e = cudaLaunchKernel(h->ov.rows_inv, dim3(h->grid_rows_inv), dim3(h->ov.threads), a_rows,
                                      h->ov.smem, s);
     if (e != cudaSuccess) return (int)e;

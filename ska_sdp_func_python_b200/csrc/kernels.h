@@ -119,8 +119,9 @@ struct HandFft;
 int hfft_create(HandFft **out, const ImgGeo &g, cudaStream_t s);
 void hfft_destroy(HandFft *h, cudaStream_t s);
 void hfft_describe(const HandFft *h, char *buf, int n);
-// accT += Re( FFT^-1(plane) on the image * exp(-2 pi i w (n-1)) )
-int hfft_invert_plane(HandFft *h, const cplx<float> *plane, double w, float *accT, cudaStream_t s);
+// accT += Re( FFT^-1(plane) on the image * exp(-2 pi i w (n-1)) ); clear: the plane is left zeroed
+// (every row is cleared by the rows pass once it has loaded it: no separate memset of the ring slot)
+int hfft_invert_plane(HandFft *h, cplx<float> *plane, double w, float *accT, bool clear, cudaStream_t s);
 // plane = FFT( preT * exp(+2 pi i w (n-1)), zero-padded )
 int hfft_predict_plane(HandFft *h, const float *preT, double w, cplx<float> *plane, cudaStream_t s);
 // out[a][b] = accT[b][a] * correction(a, b);  preT[b][a] = dirty[a][b] * correction(a, b)

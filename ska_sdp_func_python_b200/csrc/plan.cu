@@ -956,13 +956,13 @@ template <typename T> int fft_plane(b2g_plan *p, int plane, int direction)
 }
 
 // fp32 plans with the hand-written FFT: per-plane fused transform + w-screen
-template <typename T> int hfft_planes_invert(b2g_plan *, int, int) { return -1; }
-template <> int hfft_planes_invert<float>(b2g_plan *p, int first, int count)
+template <typename T> int hfft_planes_invert(b2g_plan *, int, int, bool) { return -1; }
+template <> int hfft_planes_invert<float>(b2g_plan *p, int first, int count, bool clear)
 {
     for (int q = 0; q < count; ++q) {
         const double w = p->w0 + double(first + q) * p->dw;
         KERNEL_OK(hfft_invert_plane(p->hfft, slot_ptr<float>(p, first + q), w,
-                                    static_cast<float *>(p->d_acc), p->stream));
+                                    static_cast<float *>(p->d_acc), clear, p->stream));
         p->launches_last += 2;
     }
     return 0;
@@ -1092,7 +1092,8 @@ int invert_impl(b2g_plan *p, const void *ms, const void *wgt, int vis_dtype, int
         slab_planes_done(p, sl, &first, &count);
         if (p->hfft) {
             tm.begin(S_FFT);
-            B2G_OK(hfft_planes_invert<T>(p, first, count));
+            // the slots are cleared by the transform itself when a later slab reuses them
+            B2G_OK(hfft_planes_invert<T>(p, first, count, sl + 1 < p->nslabs));
             tm.end();
         } else {
             tm.begin(S_FFT);
@@ -1104,7 +1105,7 @@ int invert_impl(b2g_plan *p, const void *ms, const void *wgt, int vis_dtype, int
             p->launches_last++;
             tm.end();
         }
-        if (sl + 1 < p->nslabs) {
+        if (sl + 1 < p->nslabs && !p->hfft) {
             tm.begin(S_PREP);
             for (int q = 0; q < count; ++q)
                 CUDA_OK(cudaMemsetAsync(slot_ptr<T>(p, first + q), 0, p->plane_bytes, s));
