@@ -448,7 +448,20 @@ def _invert(bvis, model, dopsf, normalise, subtract_model, kwargs):
     if kwargs.get("_device_result", False):
         # callers that keep accumulating on the device (skymodel_imaging.py): fp64 CUDA tensor
         return pix, sumwt
-    im["pixels"].data[...] = pix.cpu().numpy()
+    dst = im["pixels"].data
+    if (isinstance(dst, numpy.ndarray) and dst.flags.c_contiguous and dst.dtype == numpy.float64
+            and dst.shape == tuple(pix.shape)):
+        # through the pinned ring in 64 MB pieces: PCIe speed, and the copy into the image's own
+        # (pageable) array runs while the next piece crosses (a plain .cpu() of an 8192^2 image
+        # costs five times as much)
+        flat_dev, flat_dst = pix.reshape(-1), dst.reshape(-1)
+        stage = D.stager()
+        step = 1 << 23
+        for e0 in range(0, flat_dev.numel(), step):
+            stage.get(flat_dev[e0:e0 + step], flat_dst[e0:e0 + step])
+        stage.finish()
+    else:
+        dst[...] = pix.cpu().numpy()
     return im, sumwt
 
 
@@ -470,7 +483,9 @@ def predict_ng(bvis, model, **kwargs):
     freq = numpy.asarray(bvis.frequency.data)
     nrows, nbaselines, vnchan, vnpol = bvis.vis.shape
     nrow = nrows * nbaselines
-    uvw = numpy.nan_to_num(numpy.array(bvis.uvw.data, dtype=numpy.float64).reshape(nrow, 3))
+    uvw = numpy.array(bvis.uvw.data, dtype=numpy.float64).reshape(nrow, 3)
+    if not numpy.isfinite(uvw).all():      # (nan_to_num itself is ten times the cost of the check)
+        uvw = numpy.nan_to_num(uvw)
     m_nchan, m_npol, ny, nx = model["pixels"].data.shape
     assert m_npol == vnpol
     uvw[:, 0] *= -1.0
@@ -518,8 +533,9 @@ def predict_ng(bvis, model, **kwargs):
 
     # image frame -> visibility frame, interleave, inverse phase rotation (ng.py:131-143)
     M = pol_matrix(model.image_acc.polarisation_frame, bvis.visibility_acc.polarisation_frame)
-    newbvis = newbvis_f.result()
-    shift, update_pc = _shift_vector(newbvis, model)
+    # (the copy has bvis' phase centre; it is only collected once the samples are on the host, so
+    # the helper thread's copying overlaps the download loop as well)
+    shift, update_pc = _shift_vector(bvis, model)
     lmn = None
     if shift is not None:
         lmn = numpy.array([-shift[0], shift[1], -shift[2]], dtype=numpy.float64)
@@ -540,6 +556,7 @@ def predict_ng(bvis, model, **kwargs):
             ctypes.c_void_p(D.stream)))
         stage.get(chunk, vis[r0:r1])   # D2H into pinned memory while the next chunk is finished
     stage.finish()
+    newbvis = newbvis_f.result()
     newbvis["vis"].data = vis.reshape([nrows, nbaselines, vnchan, vnpol])
     if update_pc:
         newbvis.attrs["phasecentre"] = model.image_acc.phasecentre

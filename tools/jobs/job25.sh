@@ -1,1 +1,2 @@
-timeout 900 python -m pytest tests/test_gpu_configs.py -m gpu -q 2>&1 | tail -5 | cut -c1-250
+timeout 600 python tools/sparse_perf.py --config C4 --nchan 256 --world 8 --rank 7
+timeout 600 python tools/sparse_perf.py --config C4 --nchan 256 --world 8 --rank 5
