@@ -1093,8 +1093,19 @@ int invert_impl(b2g_plan *p, const void *ms, const void *wgt, int vis_dtype, int
         if (p->hfft) {
             tm.begin(S_FFT);
             // the slots are cleared by the transform itself when a later slab reuses them
-            B2G_OK(hfft_planes_invert<T>(p, first, count, sl + 1 < p->nslabs));
+            // (B2G_FUSED_CLEAR=0: by memsets after it, for A/B measurements)
+            static const bool fused_clear = [] {
+                const char *e = std::getenv("B2G_FUSED_CLEAR");
+                return !(e && e[0] == '0');
+            }();
+            B2G_OK(hfft_planes_invert<T>(p, first, count, fused_clear && sl + 1 < p->nslabs));
             tm.end();
+            if (!fused_clear && sl + 1 < p->nslabs) {
+                tm.begin(S_PREP);
+                for (int q = 0; q < count; ++q)
+                    CUDA_OK(cudaMemsetAsync(slot_ptr<T>(p, first + q), 0, p->plane_bytes, s));
+                tm.end();
+            }
         } else {
             tm.begin(S_FFT);
             for (int q = 0; q < count; ++q) B2G_OK(fft_plane<T>(p, first + q, CUFFT_INVERSE));
