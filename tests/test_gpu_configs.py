@@ -158,6 +158,151 @@ def _check_config(wg, obs, prec, eps, ws, bound, nplanes_min=0, nslabs_min=1, np
     assert np.abs(d[px, py] - dref).max() < bound * np.abs(dref).max(), info
     rows = rng.integers(0, nrow, nsamp)
     chans = rng.integers(0, nchan, nsamp)
+    vref = odft.dirty2ms_samples_sparse(uvw, freq, ix, iy, model[ix, iy].astype(np.float64), npix, npix,
+                                        cell, cell, ws, rows, chans)
+    assert np.abs(v[rows, chans] - vref).max() < bound * np.abs(vref).max(), info
+    return info
+
+
+@pytest.mark.parametrize("ws", [False, True])
+def test_c1_full_size(wg, ws):
+    """C1 (LOW-core, 2 times, 5 channels, 512^2, cellsize 5e-4, fp64, eps = 1e-12), whole workload;
+    the invert side is checked on a dense 48 x 48 block + corners + 2000 random pixels, the predict
+    side on 2000 samples of a dense (every pixel non-zero) 512^2 model."""
+    from oracle import dft as odft
+    from ska_sdp_func_python_b200 import simulate
+    obs = simulate.observation("C1")
+    uvw = simulate.flip_for_gridder(obs["uvw"])
+    freq, npix, cell = obs["freq"], obs["npix"], obs["cellsize"]
+    nrow, nchan = uvw.shape[0], len(freq)
+    assert (npix, nchan, nrow) == (512, 5, 27722) and cell == 5e-4
+    rng = np.random.default_rng(31)
+    ms = rng.standard_normal((nrow, nchan)) + 1j * rng.standard_normal((nrow, nchan))
+    wgt = rng.uniform(0.5, 1.5, (nrow, nchan))
+    wgt[obs["auto"]] = 0
+    model = rng.standard_normal((npix, npix))
+    with wg.Plan(uvw, freq, npix, npix, cell, cell, 1e-12, ws, precision="double") as p:
+        d, v = p.invert(ms, wgt), p.predict(model, wgt)
+    bx, by = np.meshgrid(np.arange(232, 280), np.arange(10, 58), indexing="ij")
+    px, py = _sample_pixels(rng, npix, 2000)
+    px, py = np.concatenate([px, bx.ravel()]), np.concatenate([py, by.ravel()])
+    dref = odft.ms2dirty_points(uvw, freq, ms, wgt, npix, npix, cell, cell, ws, px, py)
+    assert rel_l2(d[px, py], dref) < 1e-12
+    assert np.abs(d[px, py] - dref).max() < 1e-10 * np.abs(dref).max()
+    rows, chans = rng.integers(0, nrow, 2000), rng.integers(0, nchan, 2000)
+    vref = odft.dirty2ms_samples(uvw, freq, model, wgt, cell, cell, ws, rows, chans)
+    assert rel_l2(v[rows, chans], vref) < 1e-12
+    assert np.abs(v[rows, chans] - vref).max() < 1e-10 * np.abs(vref).max()
+
+
+def test_c3_mid_geometry(wg):
+    """C3: MID layout, 950-1050 MHz, 4096^2, fp32 eps = 1e-5 (6 of 120 times, 8 of 256 channels)."""
+    from ska_sdp_func_python_b200 import simulate
+    obs = simulate.observation("C3", nchan=8, ntimes=6)
+    assert obs["npix"] == 4096
+    _check_config(wg, obs, "single", 1e-5, True, 1e-4)
+
+
+def test_c4_wide_field_geometry(wg):
+    """C4: LOW-full, 120-180 MHz, 8192^2 with the w rescale to 128 reference planes, fp32
+    eps = 1e-5 (2 of 30 times, 12 of 1024 channels spanning the whole band): the plan needs more
+    than 24 origin planes, i.e. the multi-slab ring path with its default sizing."""
+    from ska_sdp_func_python_b200 import simulate
+    obs = simulate.observation("C4", nchan=12, ntimes=2)
+    assert obs["npix"] == 8192 and obs["nplanes"] == 128
+    info = _check_config(wg, obs, "single", 1e-5, True, 1e-4, nplanes_min=100, nslabs_min=3)
+    assert info["nu"] >= 12288 * 0.9
+
+
+def test_c5_psf_fp64(wg):
+    """C5: 16384^2, fp64, eps = 1e-10, dopsf-style unit visibilities with natural weights (2 of 30
+    times, 2 of 64 channels): PSF peak == sumwt to 1e-9, the peak is the image maximum, sampled
+    pixels and predicted samples within 1e-9 (10 eps) of the exact DFT."""
+    from oracle import dft as odft
+    from ska_sdp_func_python_b200 import simulate
+    obs = simulate.observation("C5", nchan=2, ntimes=2)
+    uvw = simulate.flip_for_gridder(obs["uvw"])
+    freq, npix, cell = obs["freq"], obs["npix"], obs["cellsize"]
+    assert npix == 16384
+    nrow, nchan = uvw.shape[0], len(freq)
+    wgt = np.ones((nrow, nchan))
+    wgt[obs["auto"]] = 0
+    ones = np.ones((nrow, nchan), dtype=np.complex128)
+    rng = np.random.default_rng(41)
+    ix, iy, flux = _sparse_model(rng, npix, 12)
+    with wg.Plan(uvw, freq, npix, npix, cell, cell, 1e-10, True, precision="double") as p:
+        info = p.info()
+        assert info["nslabs"] >= 3, info
+        psf = p.invert(ones, wgt)
+        model = np.zeros((npix, npix))
+        np.add.at(model, (ix, iy), flux)
+        v = p.predict(model)
+        del model
+    sumwt = float(wgt.sum())
+    assert abs(psf[npix // 2, npix // 2] / sumwt - 1.0) < 1e-9
+    assert psf.max() == psf[npix // 2, npix // 2]
+    px, py = _sample_pixels(rng, npix, 41)
+    dref = odft.ms2dirty_points(uvw, freq, ones, wgt, npix, npix, cell, cell, True, px, py)
+    assert np.abs(psf[px, py] - dref).max() < 1e-9 * sumwt
+    rows, chans = rng.integers(0, nrow, 300), rng.integers(0, nchan, 300)
+    vref = odft.dirty2ms_samples_sparse(uvw, freq, ix, iy, flux, npix, npix, cell, cell, True, rows, chans)
+    assert np.abs(v[rows, chans] - vref).max() < 1e-9 * np.abs(vref).max()
+
+
+# ---------------------------------------------------------------------------------------------
+# hand-written pruned plane FFT (fp32 plans) against the cuFFT + screen-kernel path
+# ---------------------------------------------------------------------------------------------
+# (npix_x, npix_y, pixsize_x, pixsize_y, w fraction, nu, nv): the hand-written transform has static
+# plans for lines of 1600, 3200, 6400 and 12800 points, so the padded grid is asked for explicitly
+HAND_SHAPES = [(1024, 960, 2.0e-4, 2.5e-4, 0.05, 1600, 1600),      # few planes, both axes 1600
+               (2000, 992, 2.4e-4, 5.0e-4, 0.2, 3200, 1600)]       # > 24 planes, 3200 x 1600
+
+
+@pytest.mark.parametrize("ws", [True, False])
+@pytest.mark.parametrize("shape", HAND_SHAPES)
+def test_hand_fft_equals_cufft_path(wg, slab_cap, monkeypatch, ws, shape):
+    """Same plan, same samples through the fused, TMA-staged plane transform (info hand_fft = 1)
+    and through cuFFT + screen kernels (B2G_NO_HFFT=1): both within epsilon of the exact DFT and
+    equal to each other to fp32 rounding; also with a wrapping multi-slab ring, and with the fp64
+    w-screen (B2G_SCREEN_FP64=1) against the fixed-point / fp32 one."""
+    from oracle import dft as odft
+    npx, npy, psx, psy, wfrac, nu, nv = shape
+    nrow, nchan = 3000, 3
+    uvw, freq, ms, wgt = make_case(77, nrow, nchan, npx, npy, psx, psy, wfrac)
+    rng = np.random.default_rng(5)
+    # a sparse model (the oracle then costs sources x samples): random pixels and three corners
+    ix = np.concatenate([[0, npx - 1, 0], rng.integers(0, npx, 60)])
+    iy = np.concatenate([[0, npy - 1, npy - 1], rng.integers(0, npy, 60)])
+    model = np.zeros((npx, npy), dtype=np.float32)
+    model[ix, iy] = rng.uniform(1, 2, ix.size).astype(np.float32)
+    eps = 1e-5
+    res = {}
+    for name, env, cap in (("hand", None, 0), ("hand_slabs", None, 2), ("hand_fp64_screen", None, 0),
+                           ("cufft", "1", 0)):
+        if env:
+            monkeypatch.setenv("B2G_NO_HFFT", env)
+        else:
+            monkeypatch.delenv("B2G_NO_HFFT", raising=False)
+        # the w-screen of the hand-written transform: fixed-point / fp32 where the field allows it
+        # (decided per plane), fp64 otherwise or when asked for
+        if name == "hand_fp64_screen":
+            monkeypatch.setenv("B2G_SCREEN_FP64", "1")
+        else:
+            monkeypatch.delenv("B2G_SCREEN_FP64", raising=False)
+        slab_cap(cap)
+        with wg.Plan(uvw, freq, npx, npy, psx, psy, eps, ws, precision="single", nu=nu, nv=nv) as p:
+            info = p.info()
+            assert (info["nu"], info["nv"]) == (nu, nv), info
+            assert info["hand_fft"] == (0 if env else 1), info
+            if name == "hand_slabs" and ws:
+                assert info["nslabs"] >= 2, info
+            res[name] = (p.invert(ms.astype(np.complex64), wgt.astype(np.float32)),
+                         p.predict(model, wgt.astype(np.float32)),
+                         p.invert(ms.astype(np.complex64), wgt.astype(np.float32), out_dtype=np.float64))
+    px = np.concatenate([[0, 0, npx - 1, npx - 1, npx // 2], rng.integers(0, npx, 200)])
+    py = np.concatenate([[0, npy - 1, 0, npy - 1, npy // 2], rng.integers(0, npy, 200)])
+    dref = odft.ms2dirty_points(uvw, freq, ms, wgt, npx, npy, psx, psy, ws, px, py)
+    rows, chans = rng.integers(0, nrow, 300), rng.integers(0, nchan, 300)
     # the model pixels may collide: take the accumulated image values once per distinct pixel
     upix = np.unique(np.stack([ix, iy]), axis=1)
     vref = odft.dirty2ms_samples_sparse(uvw, freq, upix[0], upix[1], model[upix[0], upix[1]].astype(np.float64),
@@ -171,3 +316,44 @@ def _check_config(wg, obs, prec, eps, ws, bound, nplanes_min=0, nslabs_min=1, np
         assert rel_l2(res["hand"][k], res["cufft"][k]) < 3e-6
         assert rel_l2(res["hand_slabs"][k], res["cufft"][k]) < 3e-6
         assert rel_l2(res["hand_fp64_screen"][k], res["hand"][k]) < 2e-6
+
+
+_FUSED_CLEAR_SCRIPT = r"""
+import sys
+import numpy as np
+sys.path.insert(0, {tests!r}); sys.path.insert(0, {root!r})
+from conftest import make_case
+from ska_sdp_func_python_b200 import _lib, wgridder
+npx, npy, psx, psy, wfrac, nu, nv = {shape!r}
+uvw, freq, ms, wgt = make_case(77, 3000, 3, npx, npy, psx, psy, wfrac)
+assert _lib.lib().b2g_set_max_slab_planes(2) == 0
+with wgridder.Plan(uvw, freq, npx, npy, psx, psy, 1e-5, True, precision="single", nu=nu, nv=nv) as p:
+    info = p.info()
+    assert info["hand_fft"] == 1 and info["nslabs"] >= 3, info
+    d1 = p.invert(ms.astype(np.complex64), wgt.astype(np.float32))
+    d2 = p.invert(ms.astype(np.complex64), wgt.astype(np.float32))     # the ring as the first call left it
+np.save({out!r}, np.stack([d1, d2]))
+"""
+
+
+def test_fused_ring_clear(wg, slab_cap, tmp_path):
+    """B2G_FUSED_CLEAR=1 (read once per process, hence the child process): the invert rows pass
+    zeroes the plane rows it has loaded instead of a memset per ring slot between slabs.  Same
+    image as the default path on a wrapping multi-slab ring, also on a second call of the plan."""
+    import os
+    import subprocess
+    import sys
+    shape = HAND_SHAPES[1]
+    here = os.path.dirname(os.path.abspath(__file__))
+    out = str(tmp_path / "fused.npy")
+    script = _FUSED_CLEAR_SCRIPT.format(tests=here, root=os.path.dirname(here), shape=shape, out=out)
+    env = dict(os.environ, B2G_FUSED_CLEAR="1")
+    proc = subprocess.run([sys.executable, "-c", script], env=env, capture_output=True, text=True, timeout=600)
+    assert proc.returncode == 0, proc.stderr[-2000:]
+    fused = np.load(out)
+    npx, npy, psx, psy, wfrac, nu, nv = shape
+    uvw, freq, ms, wgt = make_case(77, 3000, 3, npx, npy, psx, psy, wfrac)
+    slab_cap(2)
+    with wg.Plan(uvw, freq, npx, npy, psx, psy, 1e-5, True, precision="single", nu=nu, nv=nv) as p:
+        d = p.invert(ms.astype(np.complex64), wgt.astype(np.float32))
+    assert rel_l2(fused[0], d) < 2e-6 and rel_l2(fused[1], d) < 2e-6
