@@ -202,6 +202,27 @@ B2G_HD void stage_write(int tid, float2 (&v)[CNT][R], const float2 *tw, Wr wr)
     }
 }
 
+// Stage 0 (ns = 1: no twiddles) written into the padded layout with the address algebra spelled
+// out.  Butterfly j writes padded(j R0 + u) = padded(j R0) + u (its R0 outputs do not straddle a
+// padding step when R0 divides 2^PS), and padded((tid + c T) R0) = padded(tid R0) + c padded(T R0)
+// when T R0 is a multiple of 2^PS: one address register and immediates.  Through the generic
+// stage_write the compiler sees C0 R0 = 40 unrelated loop-invariant addresses, keeps them in
+// registers across the line loop and spills them (measured: 35 of them in the predict rows pass,
+// and beside 227 KB of shared memory a spill reload comes from L2).
+template <class P, int S>
+B2G_HD void stage0_write_padded(int tid, float2 (&v)[P::C0][P::R0], const float2 *tw, float2 *X)
+{
+    static_assert((1 << P::PS) % P::R0 == 0, "a butterfly's outputs share one padding step");
+    static_assert((P::T * P::R0) % (1 << P::PS) == 0, "the per-c offset is a constant");
+    stage_compute<P, S, P::R0, P::C0, 1>(tid, v, tw);
+    float2 *base = X + padded<P>(tid * P::R0);
+    constexpr int CST = P::T * P::R0 + ((P::T * P::R0) >> P::PS);
+#pragma unroll
+    for (int c = 0; c < P::C0; ++c)
+#pragma unroll
+        for (int u = 0; u < P::R0; ++u) base[c * CST + u] = v[c][u];
+}
+
 // ---- a whole line ------------------------------------------------------------------------------
 // Stages 1 .. of a line whose stage 0 has left it in X in the padded layout.  `sync` is the block
 // barrier; it is called 2 * NSTAGE - 3 times, the last call being the barrier after the final
@@ -272,11 +293,10 @@ template <class P, int S, class Rd0, class Sync>
 B2G_HD void line_stage0(int tid, float2 *X, const float2 *tw, Rd0 rd0, Sync &sync)
 {
     const bool active = tid < P::T;
-    auto wrX = [X](int i, float2 val) { X[padded<P>(i)] = val; };
     float2 v[P::C0][P::R0];
     if (active) stage_read<P, P::R0, P::C0>(tid, v, rd0);
     sync();
-    if (active) stage_write<P, S, P::R0, P::C0, 1>(tid, v, tw, wrX);
+    if (active) stage0_write_padded<P, S>(tid, v, tw, X);
     sync();
 }
 

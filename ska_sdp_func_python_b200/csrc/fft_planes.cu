@@ -281,21 +281,29 @@ hfft_rows_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *pl
         if (active) hfft::stage_compute<P, 1, LS::R, 1, LS::NS>(tid, v, tws + LS::TW_OFF);
         // v[0][r] is column k = tid + r * NS of row u
         const bool odd = tid & 1;
-        const int kb0 = tid & ~1;
+        // this lane's pieces start at columns kb = kbase + r NS (r = 0, 2, ...).  Image columns
+        // b >= hy come from k = b - hy in [0, hy), b < hy from k = nv - hy + b, so the piece goes to
+        // pair (kb + hy) / 2 of the low range or (kb - (nv - hy)) / 2 of the high one: two running
+        // pointers that advance by NS pairs per step (the 20 pair indices are loop invariants that
+        // the compiler otherwise keeps in registers across the line -- and spills: beside 227 KB of
+        // shared memory a spill reload comes from L2)
+        const int kbase = (tid & ~1) + (odd ? LS::NS : 0);
+        const ptrdiff_t step = (ptrdiff_t)LS::NS * g.nu;
+        float4 *plo = T4 + (ptrdiff_t)(half_pairs + (kbase >> 1)) * g.nu + u;
+        float4 *phi = T4 + (ptrdiff_t)((kbase - (nv - hy)) >> 1) * g.nu + u;
 #pragma unroll
         for (int r = 0; r < LS::R; r += 2) {
             const float2 send = odd ? v[0][r] : v[0][r + 1];
             float2 recv;
             recv.x = __shfl_xor_sync(0xffffffffu, send.x, 1);
             recv.y = __shfl_xor_sync(0xffffffffu, send.y, 1);
-            const int kb = kb0 + (odd ? r + 1 : r) * LS::NS;      // first column of this lane's piece
+            const int kb = kbase + r * LS::NS;                    // first column of this lane's piece
             const float4 piece = odd ? make_float4(recv.x, recv.y, v[0][r + 1].x, v[0][r + 1].y)
                                      : make_float4(v[0][r].x, v[0][r].y, recv.x, recv.y);
-            // image columns b >= hy come from k = b - hy in [0, hy); b < hy from k = nv - hy + b
-            int pair = -1;
-            if (kb < hy) pair = half_pairs + (kb >> 1);
-            else if (kb >= nv - hy) pair = (kb - (nv - hy)) >> 1;
-            if (active && pair >= 0) T4[(size_t)pair * g.nu + u] = piece;
+            if (active && kb < hy) *plo = piece;
+            else if (active && kb >= nv - hy) *phi = piece;
+            plo += step;
+            phi += step;
         }
     }
 }
@@ -359,10 +367,8 @@ hfft_cols_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *__
             }
             __syncthreads();
             if (active) {
-                auto wr0 = [X0](int i, float2 val) { X0[hfft::padded<P>(i)] = val; };
-                auto wr1 = [X1](int i, float2 val) { X1[hfft::padded<P>(i)] = val; };
-                hfft::stage_write<P, 1, P::R0, P::C0, 1>(tid, v0, tws, wr0);
-                hfft::stage_write<P, 1, P::R0, P::C0, 1>(tid, v1, tws, wr1);
+                hfft::stage0_write_padded<P, 1>(tid, v0, tws, X0);
+                hfft::stage0_write_padded<P, 1>(tid, v1, tws, X1);
             }
             __syncthreads();
         }
@@ -482,10 +488,7 @@ hfft_cols_fwd_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float *__r
                         }
                 }
                 sync();
-                if (active) {
-                    auto wrX = [X](int i, float2 val) { X[hfft::padded<P>(i)] = val; };
-                    hfft::stage_write<P, -1, P::R0, P::C0, 1>(tid, v, tws, wrX);
-                }
+                if (active) hfft::stage0_write_padded<P, -1>(tid, v, tws, X);
                 sync();
             }
             hfft::line_rest<P, -1>(tid, X, tws, wr, sync);
