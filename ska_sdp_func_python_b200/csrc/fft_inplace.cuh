@@ -223,6 +223,45 @@ B2G_HD void stage0_write_padded(int tid, float2 (&v)[P::C0][P::R0], const float2
         for (int u = 0; u < P::R0; ++u) base[c * CST + u] = v[c][u];
 }
 
+// The later stages' accesses to the padded buffer, same idea.  Reads: padded(tid + c T + t q) =
+// padded(tid) + c padded(T) + t padded(q) when T and q are multiples of 2^PS.  Writes of a stage
+// with ns | 2^PS: element (j / ns) ns R + j mod ns + u ns lands at
+// [padded((j / ns) ns R) + j mod ns] + [u ns + (u ns >> PS)] when ns R is a multiple of 2^PS.
+// Plans that do not meet the conditions (1600 points: T = 40) take the generic path.
+template <class P, int R, int CNT>
+B2G_HD void stage_read_padded(int tid, float2 (&v)[CNT][R], const float2 *X)
+{
+    constexpr int q = P::N / R, M = 1 << P::PS;
+    if constexpr (q % M == 0 && P::T % M == 0) {
+        const float2 *base = X + padded<P>(tid);
+        constexpr int CT = P::T + (P::T >> P::PS), CQ = q + (q >> P::PS);
+#pragma unroll
+        for (int c = 0; c < CNT; ++c)
+#pragma unroll
+            for (int t = 0; t < R; ++t) v[c][t] = base[c * CT + t * CQ];
+    } else {
+        stage_read<P, R, CNT>(tid, v, [X](int i) { return X[padded<P>(i)]; });
+    }
+}
+
+template <class P, int S, int R, int CNT, int NS>
+B2G_HD void stage_write_padded(int tid, float2 (&v)[CNT][R], const float2 *tw, float2 *X)
+{
+    constexpr int M = 1 << P::PS;
+    if constexpr (M % NS == 0 && (NS * R) % M == 0 && P::T % NS == 0 && (P::T * R) % M == 0) {
+        stage_compute<P, S, R, CNT, NS>(tid, v, tw);
+        const int a0 = (tid / NS) * (NS * R);
+        float2 *base = X + (a0 + (a0 >> P::PS) + tid % NS);
+        constexpr int CC = P::T * R + ((P::T * R) >> P::PS);
+#pragma unroll
+        for (int c = 0; c < CNT; ++c)
+#pragma unroll
+            for (int u = 0; u < R; ++u) base[c * CC + u * NS + ((u * NS) >> P::PS)] = v[c][u];
+    } else {
+        stage_write<P, S, R, CNT, NS>(tid, v, tw, [X](int i, float2 val) { X[padded<P>(i)] = val; });
+    }
+}
+
 // ---- a whole line ------------------------------------------------------------------------------
 // Stages 1 .. of a line whose stage 0 has left it in X in the padded layout.  `sync` is the block
 // barrier; it is called 2 * NSTAGE - 3 times, the last call being the barrier after the final
@@ -231,26 +270,24 @@ template <class P, int S, class WrLast, class Sync>
 B2G_HD void line_rest(int tid, float2 *X, const float2 *tw, WrLast wr_last, Sync &sync)
 {
     const bool active = tid < P::T;
-    auto rdX = [X](int i) { return X[padded<P>(i)]; };
-    auto wrX = [X](int i, float2 val) { X[padded<P>(i)] = val; };
     if (P::NSTAGE == 2) {
         float2 v[P::C1][P::R1];
-        if (active) stage_read<P, P::R1, P::C1>(tid, v, rdX);
+        if (active) stage_read_padded<P, P::R1, P::C1>(tid, v, X);
         sync();
         if (active) stage_write<P, S, P::R1, P::C1, P::NS1>(tid, v, tw, wr_last);
         return;
     }
     {
         float2 v[P::C1][P::R1];
-        if (active) stage_read<P, P::R1, P::C1>(tid, v, rdX);
+        if (active) stage_read_padded<P, P::R1, P::C1>(tid, v, X);
         sync();
-        if (active) stage_write<P, S, P::R1, P::C1, P::NS1>(tid, v, tw, wrX);
+        if (active) stage_write_padded<P, S, P::R1, P::C1, P::NS1>(tid, v, tw, X);
         sync();
     }
     {
         constexpr int R2 = P::R2 > 1 ? P::R2 : 2, C2 = P::C2 > 0 ? P::C2 : 1, NS2 = P::NS2 > 0 ? P::NS2 : 1;
         float2 v[C2][R2];
-        if (active) stage_read<P, R2, C2>(tid, v, rdX);
+        if (active) stage_read_padded<P, R2, C2>(tid, v, X);
         sync();
         if (active) stage_write<P, S, R2, C2, NS2>(tid, v, tw + 3 * P::NS1, wr_last);
     }
@@ -272,16 +309,14 @@ B2G_HD void line_rest_open(int tid, float2 *X, const float2 *tw,
                            float2 (&v)[LastStage<P>::C][LastStage<P>::R], Sync &sync)
 {
     const bool active = tid < P::T;
-    auto rdX = [X](int i) { return X[padded<P>(i)]; };
-    auto wrX = [X](int i, float2 val) { X[padded<P>(i)] = val; };
     if (P::NSTAGE == 3) {
         float2 m[P::C1][P::R1];
-        if (active) stage_read<P, P::R1, P::C1>(tid, m, rdX);
+        if (active) stage_read_padded<P, P::R1, P::C1>(tid, m, X);
         sync();
-        if (active) stage_write<P, S, P::R1, P::C1, P::NS1>(tid, m, tw, wrX);
+        if (active) stage_write_padded<P, S, P::R1, P::C1, P::NS1>(tid, m, tw, X);
         sync();
     }
-    if (active) stage_read<P, LastStage<P>::R, LastStage<P>::C>(tid, v, rdX);
+    if (active) stage_read_padded<P, LastStage<P>::R, LastStage<P>::C>(tid, v, X);
     sync();
 }
 

@@ -21,42 +21,46 @@ struct NoSync {
     void operator()() const {}
 };
 
-// one stage for all threads: reads of every thread first, then the writes
-template <class P, int S, int R, int CNT, int NS, class Rd, class Wr>
-static void stage_all(const float2 *tw, Rd rd, Wr wr)
+// one stage for all threads: the read phase of every thread first, then the write phases -- with the
+// functions the device kernels call (stage0_write_padded, stage_read_padded, stage_write_padded:
+// the padded addressing spelled out as base + immediates)
+template <class P, int R, int CNT, class ReadOne, class WriteOne>
+static void stage_all(ReadOne read_one, WriteOne write_one)
 {
     std::vector<float2> regs((size_t)P::T * CNT * R);
-    for (int tid = 0; tid < P::T; ++tid) {
-        float2(&v)[CNT][R] = *reinterpret_cast<float2(*)[CNT][R]>(&regs[(size_t)tid * CNT * R]);
-        stage_read<P, R, CNT>(tid, v, rd);
-    }
-    for (int tid = 0; tid < P::T; ++tid) {
-        float2(&v)[CNT][R] = *reinterpret_cast<float2(*)[CNT][R]>(&regs[(size_t)tid * CNT * R]);
-        stage_write<P, S, R, CNT, NS>(tid, v, tw, wr);
-    }
+    for (int tid = 0; tid < P::T; ++tid)
+        read_one(tid, *reinterpret_cast<float2(*)[CNT][R]>(&regs[(size_t)tid * CNT * R]));
+    for (int tid = 0; tid < P::T; ++tid)
+        write_one(tid, *reinterpret_cast<float2(*)[CNT][R]>(&regs[(size_t)tid * CNT * R]));
 }
 
 template <class P, int S> static double run(const std::vector<float2> &x)
 {
     const int n = P::N;
-    std::vector<float2> X(P::NPAD), out(n), tw(P::TW_ENTRIES);
-    build_twiddles<P>(S, tw.data());
+    std::vector<float2> X(P::NPAD), out(n), twv(P::TW_ENTRIES);
+    build_twiddles<P>(S, twv.data());
+    const float2 *tw = twv.data();
     // the line arrives LINEAR in X (as the TMA load leaves it); stage 0 reads it linear and writes
     // the padded layout into the same buffer
     for (int i = 0; i < n; ++i) X[i] = x[i];
     float2 *Xp = X.data();
-    auto rd_lin = [Xp](int i) { return Xp[i]; };
-    auto rdX = [Xp](int i) { return Xp[padded<P>(i)]; };
-    auto wrX = [Xp](int i, float2 v) { Xp[padded<P>(i)] = v; };
     float2 *op = out.data();
     auto wr_out = [op](int k, float2 v) { op[k] = v; };
-    stage_all<P, S, P::R0, P::C0, 1>(tw.data(), rd_lin, wrX);
+    stage_all<P, P::R0, P::C0>(
+        [&](int tid, float2(&v)[P::C0][P::R0]) { stage_read<P, P::R0, P::C0>(tid, v, [Xp](int i) { return Xp[i]; }); },
+        [&](int tid, float2(&v)[P::C0][P::R0]) { stage0_write_padded<P, S>(tid, v, tw, Xp); });
     if (P::NSTAGE == 2) {
-        stage_all<P, S, P::R1, P::C1, P::NS1>(tw.data(), rdX, wr_out);
+        stage_all<P, P::R1, P::C1>(
+            [&](int tid, float2(&v)[P::C1][P::R1]) { stage_read_padded<P, P::R1, P::C1>(tid, v, Xp); },
+            [&](int tid, float2(&v)[P::C1][P::R1]) { stage_write<P, S, P::R1, P::C1, P::NS1>(tid, v, tw, wr_out); });
     } else {
-        stage_all<P, S, P::R1, P::C1, P::NS1>(tw.data(), rdX, wrX);
+        stage_all<P, P::R1, P::C1>(
+            [&](int tid, float2(&v)[P::C1][P::R1]) { stage_read_padded<P, P::R1, P::C1>(tid, v, Xp); },
+            [&](int tid, float2(&v)[P::C1][P::R1]) { stage_write_padded<P, S, P::R1, P::C1, P::NS1>(tid, v, tw, Xp); });
         constexpr int R2 = P::R2 > 1 ? P::R2 : 2, C2 = P::C2 > 0 ? P::C2 : 1, NS2 = P::NS2 > 0 ? P::NS2 : 1;
-        stage_all<P, S, R2, C2, NS2>(tw.data() + 3 * P::NS1, rdX, wr_out);
+        stage_all<P, R2, C2>(
+            [&](int tid, float2(&v)[C2][R2]) { stage_read_padded<P, R2, C2>(tid, v, Xp); },
+            [&](int tid, float2(&v)[C2][R2]) { stage_write<P, S, R2, C2, NS2>(tid, v, tw + 3 * P::NS1, wr_out); });
     }
     double num = 0, den = 0;
     const int step = n > 2048 ? n / 400 : 1;
