@@ -167,6 +167,13 @@ struct PlaneGeo {
     int nu, nv, npix_x, npix_y, hx, hy;
     double psx, psy;
     int wstack;
+    // rows (u) of the grid that can hold samples: u < ukeep or u >= nu - ukeep (nu / 2: all).  The
+    // others are identically zero when a plane is transformed to the image and are never read by
+    // the degridder, so the rows passes leave them out
+    int ukeep;
+    __device__ __forceinline__ int nlines() const { return 2 * ukeep; }
+    __device__ __forceinline__ int row_of(int line) const { return line < ukeep ? line : nu - 2 * ukeep + line; }
+    __device__ __forceinline__ bool kept(int u) const { return u < ukeep || u >= nu - ukeep; }
 };
 
 __device__ __forceinline__ int image_index(int k, int n, int npix, int h)
@@ -243,17 +250,19 @@ hfft_rows_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *pl
     constexpr uint32_t row_bytes = uint32_t(P::N) * 8u;
     const int hy = g.hy, half_pairs = hy / 2;
     const bool active = tid < P::T;
+    const int nlines = g.nlines();
     if (tid == 0) {
         for (int b = 0; b < 2; ++b) {
-            const int u = blockIdx.x + b * gridDim.x;
-            if (u < g.nu) {
+            const int line = blockIdx.x + b * gridDim.x;
+            if (line < nlines) {
                 mbar_expect_tx(bar + b, row_bytes);
-                bulk_load(X0 + b * L::NPADA, plane + (size_t)u * nv, row_bytes, bar + b);
+                bulk_load(X0 + b * L::NPADA, plane + (size_t)g.row_of(line) * nv, row_bytes, bar + b);
             }
         }
     }
     int it = 0;
-    for (int u = blockIdx.x; u < g.nu; u += gridDim.x, ++it) {
+    for (int line = blockIdx.x; line < nlines; line += gridDim.x, ++it) {
+        const int u = g.row_of(line);
         const int b = it & 1;
         float2 *X = X0 + b * L::NPADA;
         mbar_wait(bar + b, (uint32_t)(it >> 1) & 1u);
@@ -265,12 +274,12 @@ hfft_rows_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *pl
             for (int i = 0; i < P::N / (2 * P::T); ++i) zrow[tid + i * P::T] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
         auto rd0 = [X](int i) { return X[i]; };                 // linear, as the bulk load left it
-        const int un = u + 2 * gridDim.x;
+        const int ln = line + 2 * gridDim.x;
         auto hook = [&]() {
             // the last stage has read X: refill it with the row after next
-            if (tid == 0 && un < g.nu) {
+            if (tid == 0 && ln < nlines) {
                 mbar_expect_tx(bar + b, row_bytes);
-                bulk_load(X, plane + (size_t)un * nv, row_bytes, bar + b);
+                bulk_load(X, plane + (size_t)g.row_of(ln) * nv, row_bytes, bar + b);
             }
         };
         HookSync<NoHook> sync0{0, -1, NoHook()};
@@ -341,13 +350,19 @@ hfft_cols_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *__
     }
     __syncthreads();
     constexpr int nu = P::N;
-    constexpr uint32_t pair_bytes = uint32_t(P::N) * 16u;
     const int npx = g.npix_x, hx = g.hx, npairs = g.npix_y / 2;
     const bool active = tid < P::T;
-    if (tid == 0 && (int)blockIdx.x < npairs) {
-        mbar_expect_tx(bar, pair_bytes);
-        bulk_load(raw, T + (size_t)blockIdx.x * nu * 2, pair_bytes, bar);
-    }
+    // only the rows of T that the rows pass wrote (the kept rows of the grid) are loaded: the two
+    // ends of the pair block; the first stage reads the others as zero
+    const int ukeep = g.ukeep;
+    const uint32_t end_bytes = (uint32_t)ukeep * 16u;
+    auto fetch = [&](int pr) {
+        const float2 *src = T + (size_t)pr * nu * 2;
+        mbar_expect_tx(bar, 2 * end_bytes);
+        bulk_load(raw, src, end_bytes, bar);
+        bulk_load(raw + (size_t)(nu - ukeep) * 16, src + (size_t)(nu - ukeep) * 2, end_bytes, bar);
+    };
+    if (tid == 0 && (int)blockIdx.x < npairs) fetch(blockIdx.x);
     int it = 0;
     for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x, ++it) {
         mbar_wait(bar, (uint32_t)it & 1u);
@@ -360,7 +375,8 @@ hfft_cols_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *__
                 for (int c = 0; c < P::C0; ++c)
 #pragma unroll
                     for (int t = 0; t < P::R0; ++t) {
-                        const float4 p = P4[tid + c * P::T + t * q];
+                        const int idx = tid + c * P::T + t * q;
+                        const float4 p = g.kept(idx) ? P4[idx] : make_float4(0.f, 0.f, 0.f, 0.f);
                         v0[c][t] = make_float2(p.x, p.y);
                         v1[c][t] = make_float2(p.z, p.w);
                     }
@@ -380,10 +396,7 @@ hfft_cols_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *__
             // after the last stage of the SECOND column has read its buffer both are free: the
             // next pair's load runs under that stage's arithmetic and the epilogue
             auto hook = [=]() {
-                if (c == 1 && tid == 0 && pn < npairs) {
-                    mbar_expect_tx(bar, pair_bytes);
-                    bulk_load(raw, T + (size_t)pn * nu * 2, pair_bytes, bar);
-                }
+                if (c == 1 && tid == 0 && pn < npairs) fetch(pn);
             };
             HookSync<decltype(hook)> sync{0, 2 * P::NSTAGE - 3, hook};
             float2 v[1][LS::R];
@@ -533,14 +546,16 @@ hfft_rows_fwd_kernel(PlaneGeo g, const float2 *__restrict__ tw, const __grid_con
             tma_load_3d(buf + (nv - hy) + 2 * q, &tmap, mb, 0, u, q);
         }
     };
+    const int nlines = g.nlines();
     if (tid == 0) {
         for (int b = 0; b < 2; ++b) {
-            const int u = blockIdx.x + b * gridDim.x;
-            if (u < g.nu) fetch(u, X0 + b * L::NPADA, bar + b);
+            const int line = blockIdx.x + b * gridDim.x;
+            if (line < nlines) fetch(g.row_of(line), X0 + b * L::NPADA, bar + b);
         }
     }
     int it = 0;
-    for (int u = blockIdx.x; u < g.nu; u += gridDim.x, ++it) {
+    for (int line = blockIdx.x; line < nlines; line += gridDim.x, ++it) {
+        const int u = g.row_of(line);
         const int b = it & 1;
         float2 *X = X0 + b * L::NPADA;
         mbar_wait(bar + b, (uint32_t)(it >> 1) & 1u);
@@ -549,11 +564,11 @@ hfft_rows_fwd_kernel(PlaneGeo g, const float2 *__restrict__ tw, const __grid_con
             return (i < hy || i >= nv - hy) ? X[i] : make_float2(0.f, 0.f);
         };
         auto wr = [row](int k, float2 v) { row[k] = v; };
-        const int un = u + 2 * gridDim.x;
+        const int ln = line + 2 * gridDim.x;
         // X is free once the last stage has read it: prefetch the row after next under that
         // stage's arithmetic and stores
         auto hook = [&]() {
-            if (tid == 0 && un < g.nu) fetch(un, X, bar + b);
+            if (tid == 0 && ln < nlines) fetch(g.row_of(ln), X, bar + b);
         };
         HookSync<decltype(hook)> sync{0, 2 * P::NSTAGE - 1, hook};
         hfft::line_inplace<P, -1>(tid, X, tws, rd0, wr, sync);
@@ -705,7 +720,7 @@ struct HandFft {
     int grid_rows_inv = 0, grid_rows_fwd = 0, grid_cols_inv = 0, grid_cols_fwd = 0;
 };
 
-int hfft_create(HandFft **out, const ImgGeo &ig, cudaStream_t s)
+int hfft_create(HandFft **out, const ImgGeo &ig, int ukeep, cudaStream_t s)
 {
     *out = nullptr;
     const int nu = ig.nu, nv = ig.nv, npx = ig.npix_x, npy = ig.npix_y;
@@ -731,7 +746,8 @@ int hfft_create(HandFft **out, const ImgGeo &ig, cudaStream_t s)
     if ((int)ou.smem > max_smem || (int)ov.smem > max_smem) return -1;
 
     HandFft *h = new HandFft();
-    h->g = PlaneGeo{nu, nv, npx, npy, hx, hy, ig.pixsize_x, ig.pixsize_y, ig.wstack};
+    if (ukeep < 1 || 2 * ukeep > nu || std::getenv("B2G_NO_ROW_PRUNING")) ukeep = nu / 2;
+    h->g = PlaneGeo{nu, nv, npx, npy, hx, hy, ig.pixsize_x, ig.pixsize_y, ig.wstack, ukeep};
     h->ou = ou;
     h->ov = ov;
     h->pb = pb;
@@ -770,8 +786,8 @@ int hfft_create(HandFft **out, const ImgGeo &ig, cudaStream_t s)
         const LineOps *o;
         int *grid;
         int lines;
-    } ks[6] = {{ov.rows_inv, &h->ov, &h->grid_rows_inv, nu},
-               {ov.rows_fwd, &h->ov, &h->grid_rows_fwd, nu},
+    } ks[6] = {{ov.rows_inv, &h->ov, &h->grid_rows_inv, 2 * ukeep},
+               {ov.rows_fwd, &h->ov, &h->grid_rows_fwd, 2 * ukeep},
                {ou.cols_inv, &h->ou, &h->grid_cols_inv, npy / 2},
                {ou.cols_fwd, &h->ou, &h->grid_cols_fwd, npy / 2},
                {ou.cols_inv_fast, &h->ou, &h->grid_cols_inv, npy / 2},
@@ -800,6 +816,8 @@ void hfft_destroy(HandFft *h, cudaStream_t s)
     if (h->d_corr) cudaFreeAsync(h->d_corr, s);
     delete h;
 }
+
+int hfft_ukeep(const HandFft *h) { return h ? h->g.ukeep : 0; }
 
 void hfft_describe(const HandFft *h, char *buf, int n)
 {

@@ -116,7 +116,10 @@ int launch_screen_apply(const ImgGeo &g, const T *pre, cplx<T> *ring, int pfirst
 // With it the image accumulator is kept TRANSPOSED: accT[npix_y][npix_x].
 struct HandFft;
 // 0: ready; < 0: geometry not supported (the caller keeps cuFFT); > 0: a cudaError_t
-int hfft_create(HandFft **out, const ImgGeo &g, cudaStream_t s);
+// ukeep: the rows u < ukeep and u >= nu - ukeep of the grid can hold samples, the others are left
+// out of the rows passes (<= 0 or >= nu / 2: all rows)
+int hfft_create(HandFft **out, const ImgGeo &g, int ukeep, cudaStream_t s);
+int hfft_ukeep(const HandFft *h);
 void hfft_destroy(HandFft *h, cudaStream_t s);
 void hfft_describe(const HandFft *h, char *buf, int n);
 // accT += Re( FFT^-1(plane) on the image * exp(-2 pi i w (n-1)) ); clear: the plane is left zeroed

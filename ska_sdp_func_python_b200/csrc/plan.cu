@@ -164,6 +164,7 @@ struct b2g_plan {
     // w-planes
     int nplanes = 1, gs = 1, nslabs = 1, nslots = 1;
     double dw = 0, w0 = 0, wmin = 0, wmax = 0, nm1min = 0;
+    double umax_l = 0, vmax_l = 0;   // max |u|, |v| over all rows and channels, wavelengths
     // device buffers
     double *d_uvw = nullptr;
     bool own_uvw = false;
@@ -572,6 +573,8 @@ extern "C" int b2g_plan_create_sel(b2g_plan **plan, int64_t nrow, int64_t nchan,
         return fail("uvw contains NaN or Inf");
     p->wmin = st[0] * fsmin;
     p->wmax = st[1] * fsmax;
+    p->umax_l = st[2] * fsmax;
+    p->vmax_l = st[3] * fsmax;
     if (sel) {
         // w-plane-sharded plan: the w-range (hence the planes) of the selected samples only
         if (uvw_space == B2G_DEVICE) {
@@ -692,7 +695,12 @@ extern "C" int b2g_plan_create_sel(b2g_plan **plan, int64_t nrow, int64_t nchan,
 
     // per-plane transform: the hand-written pruned FFT where it applies, else cuFFT
     if (precision == B2G_F32) {
-        const int hrc = hfft_create(&p->hfft, p->img_geo(), p->stream);
+        // rows of the grid that a footprint can reach (locate_axis: cells f nu - W/2 .. + W, |f| <=
+        // max |u| pixsize_x, wrapped): beyond them a plane is identically zero / never degridded
+        const double fu = p->umax_l * p->psx;
+        int ukeep = 0;
+        if (fu < 0.49) ukeep = (int)std::ceil(fu * double(p->nu) + 0.5 * p->W) + 3;
+        const int hrc = hfft_create(&p->hfft, p->img_geo(), ukeep, p->stream);
         if (hrc > 0) return fail("hand FFT set-up failed: %s", cudaGetErrorString((cudaError_t)hrc));
     }
     size_t work = 0;

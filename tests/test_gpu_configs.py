@@ -254,8 +254,13 @@ def test_c5_psf_fp64(wg):
 # ---------------------------------------------------------------------------------------------
 # (npix_x, npix_y, pixsize_x, pixsize_y, w fraction, nu, nv): the hand-written transform has static
 # plans for lines of 1600, 3200, 6400 and 12800 points, so the padded grid is asked for explicitly
-HAND_SHAPES = [(1024, 960, 2.0e-4, 2.5e-4, 0.05, 1600, 1600),      # few planes, both axes 1600
-               (2000, 992, 2.4e-4, 5.0e-4, 0.2, 3200, 1600)]       # > 24 planes, 3200 x 1600
+# The last entry is the scale of (u, v): below 1 the samples cover only the middle of the grid (the
+# benchmark configurations: cellsize = 1 / (4 max baseline), i.e. half of each axis) and the rows
+# passes of the hand-written transform leave the empty rows of the grid out.
+HAND_SHAPES = [(1024, 960, 2.0e-4, 2.5e-4, 0.05, 1600, 1600, 1.0),      # few planes, both axes 1600
+               (2000, 992, 2.4e-4, 5.0e-4, 0.2, 3200, 1600, 1.0),       # > 24 planes, 3200 x 1600
+               (2000, 992, 2.4e-4, 5.0e-4, 0.2, 3200, 1600, 0.45),      # ... rows pruned to 45 %
+               (1024, 960, 2.0e-4, 2.5e-4, 0.05, 1600, 1600, 0.1)]      # ... to 10 %
 
 
 @pytest.mark.parametrize("ws", [True, False])
@@ -266,9 +271,10 @@ def test_hand_fft_equals_cufft_path(wg, slab_cap, monkeypatch, ws, shape):
     equal to each other to fp32 rounding; also with a wrapping multi-slab ring, and with the fp64
     w-screen (B2G_SCREEN_FP64=1) against the fixed-point / fp32 one."""
     from oracle import dft as odft
-    npx, npy, psx, psy, wfrac, nu, nv = shape
+    npx, npy, psx, psy, wfrac, nu, nv, uvscale = shape
     nrow, nchan = 3000, 3
     uvw, freq, ms, wgt = make_case(77, nrow, nchan, npx, npy, psx, psy, wfrac)
+    uvw[:, :2] *= uvscale
     rng = np.random.default_rng(5)
     # a sparse model (the oracle then costs sources x samples): random pixels and three corners
     ix = np.concatenate([[0, npx - 1, 0], rng.integers(0, npx, 60)])
@@ -278,7 +284,7 @@ def test_hand_fft_equals_cufft_path(wg, slab_cap, monkeypatch, ws, shape):
     eps = 1e-5
     res = {}
     for name, env, cap in (("hand", None, 0), ("hand_slabs", None, 2), ("hand_fp64_screen", None, 0),
-                           ("cufft", "1", 0)):
+                           ("hand_all_rows", None, 0), ("cufft", "1", 0)):
         if env:
             monkeypatch.setenv("B2G_NO_HFFT", env)
         else:
@@ -289,6 +295,10 @@ def test_hand_fft_equals_cufft_path(wg, slab_cap, monkeypatch, ws, shape):
             monkeypatch.setenv("B2G_SCREEN_FP64", "1")
         else:
             monkeypatch.delenv("B2G_SCREEN_FP64", raising=False)
+        if name == "hand_all_rows":
+            monkeypatch.setenv("B2G_NO_ROW_PRUNING", "1")
+        else:
+            monkeypatch.delenv("B2G_NO_ROW_PRUNING", raising=False)
         slab_cap(cap)
         with wg.Plan(uvw, freq, npx, npy, psx, psy, eps, ws, precision="single", nu=nu, nv=nv) as p:
             info = p.info()
@@ -316,6 +326,8 @@ def test_hand_fft_equals_cufft_path(wg, slab_cap, monkeypatch, ws, shape):
         assert rel_l2(res["hand"][k], res["cufft"][k]) < 3e-6
         assert rel_l2(res["hand_slabs"][k], res["cufft"][k]) < 3e-6
         assert rel_l2(res["hand_fp64_screen"][k], res["hand"][k]) < 2e-6
+        # leaving the empty rows of the grid out changes nothing but rounding order
+        assert rel_l2(res["hand_all_rows"][k], res["hand"][k]) < 1e-6
 
 
 _FUSED_CLEAR_SCRIPT = r"""
@@ -324,8 +336,9 @@ import numpy as np
 sys.path.insert(0, {tests!r}); sys.path.insert(0, {root!r})
 from conftest import make_case
 from ska_sdp_func_python_b200 import _lib, wgridder
-npx, npy, psx, psy, wfrac, nu, nv = {shape!r}
+npx, npy, psx, psy, wfrac, nu, nv, uvscale = {shape!r}
 uvw, freq, ms, wgt = make_case(77, 3000, 3, npx, npy, psx, psy, wfrac)
+uvw[:, :2] *= uvscale
 assert _lib.lib().b2g_set_max_slab_planes(2) == 0
 with wgridder.Plan(uvw, freq, npx, npy, psx, psy, 1e-5, True, precision="single", nu=nu, nv=nv) as p:
     info = p.info()
@@ -343,7 +356,7 @@ def test_fused_ring_clear(wg, slab_cap, tmp_path):
     import os
     import subprocess
     import sys
-    shape = HAND_SHAPES[1]
+    shape = HAND_SHAPES[2]
     here = os.path.dirname(os.path.abspath(__file__))
     out = str(tmp_path / "fused.npy")
     script = _FUSED_CLEAR_SCRIPT.format(tests=here, root=os.path.dirname(here), shape=shape, out=out)
@@ -351,8 +364,9 @@ def test_fused_ring_clear(wg, slab_cap, tmp_path):
     proc = subprocess.run([sys.executable, "-c", script], env=env, capture_output=True, text=True, timeout=600)
     assert proc.returncode == 0, proc.stderr[-2000:]
     fused = np.load(out)
-    npx, npy, psx, psy, wfrac, nu, nv = shape
+    npx, npy, psx, psy, wfrac, nu, nv, uvscale = shape
     uvw, freq, ms, wgt = make_case(77, 3000, 3, npx, npy, psx, psy, wfrac)
+    uvw[:, :2] *= uvscale
     slab_cap(2)
     with wg.Plan(uvw, freq, npx, npy, psx, psy, 1e-5, True, precision="single", nu=nu, nv=nv) as p:
         d = p.invert(ms.astype(np.complex64), wgt.astype(np.float32))
