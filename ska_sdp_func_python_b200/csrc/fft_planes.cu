@@ -508,7 +508,9 @@ hfft_cols_fwd_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float *__r
         }
         __syncthreads();
         float4 *dst = T4 + (size_t)pair * nu;
+        // (only the rows of the grid that the rows pass goes on to transform)
         for (int i = tid; i < nu; i += P::THREADS) {
+            if (!g.kept(i)) continue;
             const float2 a = X0[i], bb = X1[i];
             dst[i] = make_float4(a.x, a.y, bb.x, bb.y);
         }

@@ -951,6 +951,23 @@ template <typename T> cplx<T> *slot_ptr(b2g_plan *p, int plane)
     return static_cast<cplx<T> *>(p->d_ring) + (size_t)(plane % p->nslots) * size_t(p->nu) * size_t(p->nv);
 }
 
+// Zero the ring slot of `plane` for gridding.  With the hand-written transform only the rows of
+// the grid that a footprint can reach are ever read or written (fft_planes.cu: ukeep), so only
+// those are cleared: the two ends of the plane.
+template <typename T> int clear_slot(b2g_plan *p, int plane)
+{
+    cplx<T> *d = slot_ptr<T>(p, plane);
+    const int ukeep = p->hfft ? hfft_ukeep(p->hfft) : 0;
+    if (ukeep > 0 && 2 * (int64_t)ukeep < p->nu) {
+        const size_t rows = size_t(ukeep) * size_t(p->nv);
+        CUDA_OK(cudaMemsetAsync(d, 0, rows * sizeof(cplx<T>), p->stream));
+        CUDA_OK(cudaMemsetAsync(d + size_t(p->nu - ukeep) * size_t(p->nv), 0, rows * sizeof(cplx<T>), p->stream));
+    } else {
+        CUDA_OK(cudaMemsetAsync(d, 0, p->plane_bytes, p->stream));
+    }
+    return 0;
+}
+
 template <typename T> int fft_plane(b2g_plan *p, int plane, int direction)
 {
     cplx<T> *d = slot_ptr<T>(p, plane);
@@ -1071,7 +1088,7 @@ int invert_impl(b2g_plan *p, const void *ms, const void *wgt, int vis_dtype, int
     }
 
     tm.begin(S_PREP);
-    CUDA_OK(cudaMemsetAsync(p->d_ring, 0, p->plane_bytes * size_t(p->nslots), s));
+    for (int q = 0; q < p->nslots; ++q) B2G_OK(clear_slot<T>(p, q));
     if (p->hfft)   // the fused column pass accumulates into the (transposed) image from plane 0 on
         CUDA_OK(cudaMemsetAsync(p->d_acc, 0, size_t(p->npix_x) * size_t(p->npix_y) * sizeof(T), s));
     tm.end();
@@ -1114,7 +1131,7 @@ int invert_impl(b2g_plan *p, const void *ms, const void *wgt, int vis_dtype, int
             if (!fused_clear && sl + 1 < p->nslabs) {
                 tm.begin(S_PREP);
                 for (int q = 0; q < count; ++q)
-                    CUDA_OK(cudaMemsetAsync(slot_ptr<T>(p, first + q), 0, p->plane_bytes, s));
+                    B2G_OK(clear_slot<T>(p, first + q));
                 tm.end();
             }
         } else {
@@ -1130,7 +1147,7 @@ int invert_impl(b2g_plan *p, const void *ms, const void *wgt, int vis_dtype, int
         if (sl + 1 < p->nslabs && !p->hfft) {
             tm.begin(S_PREP);
             for (int q = 0; q < count; ++q)
-                CUDA_OK(cudaMemsetAsync(slot_ptr<T>(p, first + q), 0, p->plane_bytes, s));
+                B2G_OK(clear_slot<T>(p, first + q));
             tm.end();
         }
     }
