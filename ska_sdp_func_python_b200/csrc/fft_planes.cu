@@ -459,7 +459,6 @@ hfft_cols_fwd_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float *__r
     constexpr int nu = P::N;
     const int npx = g.npix_x, hx = g.hx, npairs = g.npix_y / 2;
     const bool active = tid < P::T;
-    float4 *T4 = reinterpret_cast<float4 *>(T);
     for (int pair = blockIdx.x; pair < npairs; pair += gridDim.x) {
 #pragma unroll 1
         for (int c = 0; c < 2; ++c) {
@@ -469,7 +468,13 @@ hfft_cols_fwd_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float *__r
             const double y = (double)(b - g.hy) * g.psy;
             const double y2 = y * y;
             const float y2f = (float)y2, fy = frac_fixed(S.cy, b - g.hy);
-            auto wr = [X](int k, float2 v) { X[k] = v; };         // linear, for the piece copy below
+            // the last stage stores its outputs straight into T: 8-byte halves of the 16-byte
+            // pieces, consecutive lanes consecutive rows (the other half follows with the pair's
+            // second column and meets it in L2); only the rows the rows pass goes on to transform
+            float2 *tcol = T + (size_t)pair * nu * 2 + c;
+            auto wr = [tcol, &g](int k, float2 v) {
+                if (g.kept(k)) tcol[2 * k] = v;
+            };
             HookSync<NoHook> sync{0, -1, NoHook()};
             {
                 // stage 0: all of the thread's image pixels are requested before the first screen
@@ -506,15 +511,7 @@ hfft_cols_fwd_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float *__r
             }
             hfft::line_rest<P, -1>(tid, X, tws, wr, sync);
         }
-        __syncthreads();
-        float4 *dst = T4 + (size_t)pair * nu;
-        // (only the rows of the grid that the rows pass goes on to transform)
-        for (int i = tid; i < nu; i += P::THREADS) {
-            if (!g.kept(i)) continue;
-            const float2 a = X0[i], bb = X1[i];
-            dst[i] = make_float4(a.x, a.y, bb.x, bb.y);
-        }
-        __syncthreads();
+        __syncthreads();     // the second column's last stage has read X1 before the next pair's stage 0 writes
     }
 }
 
