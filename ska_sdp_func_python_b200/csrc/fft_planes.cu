@@ -171,6 +171,10 @@ struct PlaneGeo {
     // others are identically zero when a plane is transformed to the image and are never read by
     // the degridder, so the rows passes leave them out
     int ukeep;
+    // ... and the same along v: columns v < vkeep or v >= nv - vkeep (even; nv / 2: all).  The rows
+    // passes neither load nor store the others
+    int vkeep;
+    __device__ __forceinline__ bool vkept(int v) const { return v < vkeep || v >= nv - vkeep; }
     __device__ __forceinline__ int nlines() const { return 2 * ukeep; }
     __device__ __forceinline__ int row_of(int line) const { return line < ukeep ? line : nu - 2 * ukeep + line; }
     __device__ __forceinline__ bool kept(int u) const { return u < ukeep || u >= nu - ukeep; }
@@ -247,17 +251,22 @@ hfft_rows_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *pl
     static_assert(P::N % (2 * P::T) == 0, "whole 16-byte stores per thread");
     __syncthreads();
     constexpr int nv = P::N;
-    constexpr uint32_t row_bytes = uint32_t(P::N) * 8u;
     const int hy = g.hy, half_pairs = hy / 2;
     const bool active = tid < P::T;
     const int nlines = g.nlines();
+    // a row arrives as its two ends (the columns that can hold samples); stage 0 reads the rest as 0
+    const int vkeep = g.vkeep;
+    const uint32_t end_bytes = (uint32_t)vkeep * 8u;
+    auto fetch = [&](int line, float2 *buf, uint64_t *mb) {
+        const float2 *src = plane + (size_t)g.row_of(line) * nv;
+        mbar_expect_tx(mb, 2 * end_bytes);
+        bulk_load(buf, src, end_bytes, mb);
+        bulk_load(buf + (nv - vkeep), src + (nv - vkeep), end_bytes, mb);
+    };
     if (tid == 0) {
         for (int b = 0; b < 2; ++b) {
             const int line = blockIdx.x + b * gridDim.x;
-            if (line < nlines) {
-                mbar_expect_tx(bar + b, row_bytes);
-                bulk_load(X0 + b * L::NPADA, plane + (size_t)g.row_of(line) * nv, row_bytes, bar + b);
-            }
+            if (line < nlines) fetch(line, X0 + b * L::NPADA, bar + b);
         }
     }
     int it = 0;
@@ -273,14 +282,12 @@ hfft_rows_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *pl
 #pragma unroll
             for (int i = 0; i < P::N / (2 * P::T); ++i) zrow[tid + i * P::T] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        auto rd0 = [X](int i) { return X[i]; };                 // linear, as the bulk load left it
+        // linear, as the bulk loads left it
+        auto rd0 = [X, vkeep](int i) { return (i < vkeep || i >= nv - vkeep) ? X[i] : make_float2(0.f, 0.f); };
         const int ln = line + 2 * gridDim.x;
         auto hook = [&]() {
             // the last stage has read X: refill it with the row after next
-            if (tid == 0 && ln < nlines) {
-                mbar_expect_tx(bar + b, row_bytes);
-                bulk_load(X, plane + (size_t)g.row_of(ln) * nv, row_bytes, bar + b);
-            }
+            if (tid == 0 && ln < nlines) fetch(ln, X, bar + b);
         };
         HookSync<NoHook> sync0{0, -1, NoHook()};
         hfft::line_stage0<P, 1>(tid, X, tws, rd0, sync0);
@@ -562,7 +569,10 @@ hfft_rows_fwd_kernel(PlaneGeo g, const float2 *__restrict__ tw, const __grid_con
         auto rd0 = [X, hy](int i) {
             return (i < hy || i >= nv - hy) ? X[i] : make_float2(0.f, 0.f);
         };
-        auto wr = [row](int k, float2 v) { row[k] = v; };
+        const int vkeep = g.vkeep;
+        auto wr = [row, vkeep](int k, float2 v) {
+            if (k < vkeep || k >= nv - vkeep) row[k] = v;     // only where the degridder can read
+        };
         const int ln = line + 2 * gridDim.x;
         // X is free once the last stage has read it: prefetch the row after next under that
         // stage's arithmetic and stores
@@ -719,7 +729,7 @@ struct HandFft {
     int grid_rows_inv = 0, grid_rows_fwd = 0, grid_cols_inv = 0, grid_cols_fwd = 0;
 };
 
-int hfft_create(HandFft **out, const ImgGeo &ig, int ukeep, cudaStream_t s)
+int hfft_create(HandFft **out, const ImgGeo &ig, int ukeep, int vkeep, cudaStream_t s)
 {
     *out = nullptr;
     const int nu = ig.nu, nv = ig.nv, npx = ig.npix_x, npy = ig.npix_y;
@@ -746,7 +756,9 @@ int hfft_create(HandFft **out, const ImgGeo &ig, int ukeep, cudaStream_t s)
 
     HandFft *h = new HandFft();
     if (ukeep < 1 || 2 * ukeep > nu || std::getenv("B2G_NO_ROW_PRUNING")) ukeep = nu / 2;
-    h->g = PlaneGeo{nu, nv, npx, npy, hx, hy, ig.pixsize_x, ig.pixsize_y, ig.wstack, ukeep};
+    vkeep = (vkeep + 1) & ~1;     // whole 16-byte pieces at both ends of a row
+    if (vkeep < 2 || 2 * vkeep > nv || std::getenv("B2G_NO_ROW_PRUNING")) vkeep = nv / 2;
+    h->g = PlaneGeo{nu, nv, npx, npy, hx, hy, ig.pixsize_x, ig.pixsize_y, ig.wstack, ukeep, vkeep};
     h->ou = ou;
     h->ov = ov;
     h->pb = pb;
@@ -817,6 +829,7 @@ void hfft_destroy(HandFft *h, cudaStream_t s)
 }
 
 int hfft_ukeep(const HandFft *h) { return h ? h->g.ukeep : 0; }
+int hfft_vkeep(const HandFft *h) { return h ? h->g.vkeep : 0; }
 
 void hfft_describe(const HandFft *h, char *buf, int n)
 {

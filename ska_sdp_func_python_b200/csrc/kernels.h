@@ -118,8 +118,10 @@ struct HandFft;
 // 0: ready; < 0: geometry not supported (the caller keeps cuFFT); > 0: a cudaError_t
 // ukeep: the rows u < ukeep and u >= nu - ukeep of the grid can hold samples, the others are left
 // out of the rows passes (<= 0 or >= nu / 2: all rows)
-int hfft_create(HandFft **out, const ImgGeo &g, int ukeep, cudaStream_t s);
+// vkeep: the same along v (the rows passes load / store only the two ends of a row)
+int hfft_create(HandFft **out, const ImgGeo &g, int ukeep, int vkeep, cudaStream_t s);
 int hfft_ukeep(const HandFft *h);
+int hfft_vkeep(const HandFft *h);
 void hfft_destroy(HandFft *h, cudaStream_t s);
 void hfft_describe(const HandFft *h, char *buf, int n);
 // accT += Re( FFT^-1(plane) on the image * exp(-2 pi i w (n-1)) ); clear: the plane is left zeroed

@@ -700,7 +700,10 @@ extern "C" int b2g_plan_create_sel(b2g_plan **plan, int64_t nrow, int64_t nchan,
         const double fu = p->umax_l * p->psx;
         int ukeep = 0;
         if (fu < 0.49) ukeep = (int)std::ceil(fu * double(p->nu) + 0.5 * p->W) + 3;
-        const int hrc = hfft_create(&p->hfft, p->img_geo(), ukeep, p->stream);
+        const double fv = p->vmax_l * p->psy;
+        int vkeep = 0;
+        if (fv < 0.49) vkeep = (int)std::ceil(fv * double(p->nv) + 0.5 * p->W) + 3;
+        const int hrc = hfft_create(&p->hfft, p->img_geo(), ukeep, vkeep, p->stream);
         if (hrc > 0) return fail("hand FFT set-up failed: %s", cudaGetErrorString((cudaError_t)hrc));
     }
     size_t work = 0;
@@ -957,8 +960,16 @@ template <typename T> cplx<T> *slot_ptr(b2g_plan *p, int plane)
 template <typename T> int clear_slot(b2g_plan *p, int plane)
 {
     cplx<T> *d = slot_ptr<T>(p, plane);
-    const int ukeep = p->hfft ? hfft_ukeep(p->hfft) : 0;
-    if (ukeep > 0 && 2 * (int64_t)ukeep < p->nu) {
+    const int ukeep = p->hfft ? hfft_ukeep(p->hfft) : 0, vkeep = p->hfft ? hfft_vkeep(p->hfft) : 0;
+    if (ukeep > 0 && 2 * (int64_t)ukeep < p->nu && vkeep > 0 && 2 * (int64_t)vkeep < p->nv) {
+        // the four corners of the plane (rows and columns both wrap around 0)
+        const size_t pitch = size_t(p->nv) * sizeof(cplx<T>), width = size_t(vkeep) * sizeof(cplx<T>);
+        cplx<T> *hi = d + size_t(p->nu - ukeep) * size_t(p->nv);
+        CUDA_OK(cudaMemset2DAsync(d, pitch, 0, width, ukeep, p->stream));
+        CUDA_OK(cudaMemset2DAsync(d + (p->nv - vkeep), pitch, 0, width, ukeep, p->stream));
+        CUDA_OK(cudaMemset2DAsync(hi, pitch, 0, width, ukeep, p->stream));
+        CUDA_OK(cudaMemset2DAsync(hi + (p->nv - vkeep), pitch, 0, width, ukeep, p->stream));
+    } else if (ukeep > 0 && 2 * (int64_t)ukeep < p->nu) {
         const size_t rows = size_t(ukeep) * size_t(p->nv);
         CUDA_OK(cudaMemsetAsync(d, 0, rows * sizeof(cplx<T>), p->stream));
         CUDA_OK(cudaMemsetAsync(d + size_t(p->nu - ukeep) * size_t(p->nv), 0, rows * sizeof(cplx<T>), p->stream));
