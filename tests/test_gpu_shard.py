@@ -40,9 +40,10 @@ def _launch_once(mode, world, out):
 
 
 def _launch(mode, world, out):
-    """The ranks' processes must exit 0.  One retry if a process dies (seen once in a fresh box's very
-    first rendezvous: the port picked by _free_port can be taken again before rank 0 binds it); the
-    first attempt's log is reported.  The numerical assertions of the test are not retried."""
+    """The ranks' processes must exit 0.  One retry if a process dies: seen once, in the very first
+    launch on a fresh two-GPU box, the log was not captured and the next run of the same build
+    passed (a rendezvous race is possible: _free_port releases the port before rank 0 binds it).
+    The first attempt's log is written to stderr.  The numerical assertions are not retried."""
     failed = _launch_once(mode, world, out)
     if failed:
         sys.stderr.write("first launch failed, retrying once:\n" + "\n".join(failed) + "\n")
