@@ -144,16 +144,25 @@ __device__ __forceinline__ float frac_fixed(unsigned long long c, int d)
 
 // (sin, cos) of 2 pi * phase at pixel offset ax = a - hx of the line with fy = frac_fixed(cy, b - hy),
 // y2f = y^2 (fp32), y2d = y^2 (fp64); false beyond the horizon
-template <bool FAST>
+// FAST: 0 = fp64, 1 = fixed point + fp32, 2 = the same for small fields (r2 <= 0.01 everywhere: no
+// horizon test, and q = r2 / (1 + sqrt(1 - r2)) from its series -- relative error 7 r2^4 / 128 < 1e-9
+// -- instead of a reciprocal square root and a division: the screen is as many instructions of the
+// columns passes as the transform itself)
+template <int FAST>
 __device__ __forceinline__ bool screen_eval(const Screen &S, double psx, int ax, float fy, float y2f,
                                             double y2d, float &s, float &c)
 {
     if (FAST) {
         const float xf = (float)ax * S.psx;
         const float r2 = fmaf(xf, xf, y2f);
-        if (!(r2 < 1.f)) return false;
-        const float z = 1.f - r2;
-        const float q = __fdividef(r2, fmaf(z, rsqrtf(z), 1.f));      // r2 / (1 + sqrt(1 - r2))
+        float q;
+        if (FAST == 2) {
+            q = r2 * fmaf(r2, fmaf(r2, fmaf(r2, 0.0390625f, 0.0625f), 0.125f), 0.5f);
+        } else {
+            if (!(r2 < 1.f)) return false;
+            const float z = 1.f - r2;
+            q = __fdividef(r2, fmaf(z, rsqrtf(z), 1.f));      // r2 / (1 + sqrt(1 - r2))
+        }
         float ph = frac_fixed(S.cx, ax) + fy + S.k3 * q * q;
         ph -= rintf(ph);
         __sincosf(6.283185307179586f * ph, &s, &c);
@@ -335,7 +344,7 @@ __device__ __forceinline__ void red_add_v4(float *addr, float a, float b, float 
 // lane four consecutive image pixels, which are added to the accumulator with one vector reduction
 // (no read-modify-write round trip; every pixel receives exactly one addition per plane, so the
 // result does not depend on any ordering).
-template <class P, bool FAST>
+template <class P, int FAST>
 __global__ void __launch_bounds__(P::THREADS, min_blocks<P>())
 hfft_cols_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *__restrict__ T, Screen S,
                      float *__restrict__ accT)
@@ -450,7 +459,7 @@ hfft_cols_inv_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float2 *__
 }
 
 // ---- predict, columns: preT[b][:] * screen, zero-padded -> T[b/2][:][b&1] -------------------------
-template <class P, bool FAST>
+template <class P, int FAST>
 __global__ void __launch_bounds__(P::THREADS, min_blocks<P>())
 hfft_cols_fwd_kernel(PlaneGeo g, const float2 *__restrict__ tw, const float *__restrict__ preT, Screen S,
                      float2 *__restrict__ T)
@@ -685,6 +694,7 @@ struct LineOps {
     void (*build_tw)(int sign, float2 *tw) = nullptr;
     const void *rows_inv = nullptr, *cols_inv = nullptr, *cols_fwd = nullptr, *rows_fwd = nullptr;
     const void *cols_inv_fast = nullptr, *cols_fwd_fast = nullptr;   // fixed-point / fp32 screen
+    const void *cols_inv_small = nullptr, *cols_fwd_small = nullptr; // ... of a small field
 };
 
 template <class P> LineOps make_ops()
@@ -696,10 +706,12 @@ template <class P> LineOps make_ops()
     o.smem = SmemLayout<P>::BYTES;
     o.build_tw = &hfft::build_twiddles<P>;
     o.rows_inv = reinterpret_cast<const void *>(&hfft_rows_inv_kernel<P>);
-    o.cols_inv = reinterpret_cast<const void *>(&hfft_cols_inv_kernel<P, false>);
-    o.cols_fwd = reinterpret_cast<const void *>(&hfft_cols_fwd_kernel<P, false>);
-    o.cols_inv_fast = reinterpret_cast<const void *>(&hfft_cols_inv_kernel<P, true>);
-    o.cols_fwd_fast = reinterpret_cast<const void *>(&hfft_cols_fwd_kernel<P, true>);
+    o.cols_inv = reinterpret_cast<const void *>(&hfft_cols_inv_kernel<P, 0>);
+    o.cols_fwd = reinterpret_cast<const void *>(&hfft_cols_fwd_kernel<P, 0>);
+    o.cols_inv_fast = reinterpret_cast<const void *>(&hfft_cols_inv_kernel<P, 1>);
+    o.cols_fwd_fast = reinterpret_cast<const void *>(&hfft_cols_fwd_kernel<P, 1>);
+    o.cols_inv_small = reinterpret_cast<const void *>(&hfft_cols_inv_kernel<P, 2>);
+    o.cols_fwd_small = reinterpret_cast<const void *>(&hfft_cols_fwd_kernel<P, 2>);
     o.rows_fwd = reinterpret_cast<const void *>(&hfft_rows_fwd_kernel<P>);
     return o;
 }
@@ -797,12 +809,14 @@ int hfft_create(HandFft **out, const ImgGeo &ig, int ukeep, int vkeep, cudaStrea
         const LineOps *o;
         int *grid;
         int lines;
-    } ks[6] = {{ov.rows_inv, &h->ov, &h->grid_rows_inv, 2 * ukeep},
+    } ks[8] = {{ov.rows_inv, &h->ov, &h->grid_rows_inv, 2 * ukeep},
                {ov.rows_fwd, &h->ov, &h->grid_rows_fwd, 2 * ukeep},
                {ou.cols_inv, &h->ou, &h->grid_cols_inv, npy / 2},
                {ou.cols_fwd, &h->ou, &h->grid_cols_fwd, npy / 2},
                {ou.cols_inv_fast, &h->ou, &h->grid_cols_inv, npy / 2},
-               {ou.cols_fwd_fast, &h->ou, &h->grid_cols_fwd, npy / 2}};
+               {ou.cols_fwd_fast, &h->ou, &h->grid_cols_fwd, npy / 2},
+               {ou.cols_inv_small, &h->ou, &h->grid_cols_inv, npy / 2},
+               {ou.cols_fwd_small, &h->ou, &h->grid_cols_fwd, npy / 2}};
     for (auto &k : ks) {
         int per_sm = 0;
         if (cudaFuncSetAttribute(k.fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)k.o->smem) != cudaSuccess ||
@@ -861,6 +875,8 @@ Screen make_screen(const HandFft *h, double w_signed)
     const double q = r2 < 1.0 ? r2 / (1.0 + std::sqrt(1.0 - r2)) : 1.0;
     S.fast = (r2 < 0.5 && 0.5 * std::fabs(w_signed) * q * q < 0.5 && g.hx < 46000 && g.hy < 46000 &&
               !std::getenv("B2G_SCREEN_FP64")) ? 1 : 0;
+    // small field: the series of q holds to 1e-9 (B2G_SCREEN_GENERAL=1 keeps the general fp32 path)
+    if (S.fast && r2 <= 0.01 && !std::getenv("B2G_SCREEN_GENERAL")) S.fast = 2;
     return S;
 }
 }  // namespace
@@ -879,7 +895,8 @@ int hfft_invert_plane(HandFft *h, cplx<float> *plane, double w, float *accT, boo
                                      h->ov.smem, s);
     if (e != cudaSuccess) return (int)e;
     void *a_cols[] = {&g, &twu, &T, &S, &accT};
-    e = cudaLaunchKernel(S.fast ? h->ou.cols_inv_fast : h->ou.cols_inv, dim3(h->grid_cols_inv),
+    e = cudaLaunchKernel(S.fast == 2 ? h->ou.cols_inv_small : (S.fast ? h->ou.cols_inv_fast : h->ou.cols_inv),
+                         dim3(h->grid_cols_inv),
                          dim3(h->ou.threads), a_cols, h->ou.smem, s);
     return (int)e;
 }
@@ -893,7 +910,8 @@ int hfft_predict_plane(HandFft *h, const float *preT, double w, cplx<float> *pla
     float2 *T = h->d_T;
     int pb = h->pb;
     void *a_cols[] = {&g, &twu, &preT, &S, &T};
-    cudaError_t e = cudaLaunchKernel(S.fast ? h->ou.cols_fwd_fast : h->ou.cols_fwd, dim3(h->grid_cols_fwd),
+    cudaError_t e = cudaLaunchKernel(S.fast == 2 ? h->ou.cols_fwd_small : (S.fast ? h->ou.cols_fwd_fast : h->ou.cols_fwd),
+                                     dim3(h->grid_cols_fwd),
                                      dim3(h->ou.threads), a_cols, h->ou.smem, s);
     if (e != cudaSuccess) return (int)e;
     void *a_rows[] = {&g, &twv, &h->tmap, &pb, &pl};

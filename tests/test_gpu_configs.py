@@ -260,7 +260,9 @@ def test_c5_psf_fp64(wg):
 HAND_SHAPES = [(1024, 960, 2.0e-4, 2.5e-4, 0.05, 1600, 1600, 1.0),      # few planes, both axes 1600
                (2000, 992, 2.4e-4, 5.0e-4, 0.2, 3200, 1600, 1.0),       # > 24 planes, 3200 x 1600
                (2000, 992, 2.4e-4, 5.0e-4, 0.2, 3200, 1600, 0.45),      # ... rows pruned to 45 %
-               (1024, 960, 2.0e-4, 2.5e-4, 0.05, 1600, 1600, 0.1)]      # ... to 10 %
+               (1024, 960, 2.0e-4, 2.5e-4, 0.05, 1600, 1600, 0.1),      # ... to 10 %
+               # a small field (r^2 <= 0.01 everywhere): the w-screen takes q from its series
+               (1024, 960, 5.0e-5, 6.0e-5, 1.0, 1600, 1600, 0.5)]
 
 
 @pytest.mark.parametrize("ws", [True, False])
@@ -284,7 +286,7 @@ def test_hand_fft_equals_cufft_path(wg, slab_cap, monkeypatch, ws, shape):
     eps = 1e-5
     res = {}
     for name, env, cap in (("hand", None, 0), ("hand_slabs", None, 2), ("hand_fp64_screen", None, 0),
-                           ("hand_all_rows", None, 0), ("cufft", "1", 0)):
+                           ("hand_all_rows", None, 0), ("hand_general_screen", None, 0), ("cufft", "1", 0)):
         if env:
             monkeypatch.setenv("B2G_NO_HFFT", env)
         else:
@@ -299,6 +301,10 @@ def test_hand_fft_equals_cufft_path(wg, slab_cap, monkeypatch, ws, shape):
             monkeypatch.setenv("B2G_NO_ROW_PRUNING", "1")
         else:
             monkeypatch.delenv("B2G_NO_ROW_PRUNING", raising=False)
+        if name == "hand_general_screen":      # the fp32 screen without the small-field short cut
+            monkeypatch.setenv("B2G_SCREEN_GENERAL", "1")
+        else:
+            monkeypatch.delenv("B2G_SCREEN_GENERAL", raising=False)
         slab_cap(cap)
         with wg.Plan(uvw, freq, npx, npy, psx, psy, eps, ws, precision="single", nu=nu, nv=nv) as p:
             info = p.info()
@@ -328,6 +334,7 @@ def test_hand_fft_equals_cufft_path(wg, slab_cap, monkeypatch, ws, shape):
         assert rel_l2(res["hand_fp64_screen"][k], res["hand"][k]) < 2e-6
         # leaving the empty rows of the grid out changes nothing but rounding order
         assert rel_l2(res["hand_all_rows"][k], res["hand"][k]) < 1e-6
+        assert rel_l2(res["hand_general_screen"][k], res["hand"][k]) < 2e-6
 
 
 _FUSED_CLEAR_SCRIPT = r"""
