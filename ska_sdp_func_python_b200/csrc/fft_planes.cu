@@ -10,8 +10,8 @@
 //   invert (grid plane -> image):
 //     rows : persistent blocks; TMA bulk loads (cp.async.bulk + mbarrier) bring row u+1 into the
 //            second line buffer while row u is transformed along v; only the npix_y outputs that
-//            fall on the image are kept and leave as 16-byte pieces (two adjacent image columns)
-//            through TMA tensor stores into T[npix_y/2][nu][2];
+//            fall on the image are kept and leave as 16-byte pieces (two adjacent image columns,
+//            built by a lane-pair exchange) into T[npix_y/2][nu][2];
 //     cols : one TMA bulk load per PAIR of image columns (its nu 16-byte pieces are contiguous in
 //            T); the first stage splits the pieces into the two line buffers, each column is
 //            transformed along u, the npix_x kept outputs are multiplied by the w-screen
@@ -21,12 +21,19 @@
 //   predict (image -> grid plane) is the adjoint:
 //     cols : pre-corrected image column * exp(+2 pi i w (n-1)), zero-padded to nu (the screen and
 //            the padding happen in the first stage's loads), both columns of a pair transformed,
-//            then written to T as whole 16-byte pieces;
+//            each stored into T as the 8-byte halves of the pieces;
 //     rows : TMA tensor loads gather row u+1's pieces while row u is transformed (the rows between
 //            the two kept ranges read as zero in the first stage); whole rows written to the plane.
 //
-// Per plane this moves nu*nv*8 + 2*nu*npix*8 + 2*npix^2*4 bytes instead of cuFFT's 8 passes over
-// nu*nv*8 plus the screen kernel's cropped read.
+// Only the part of the grid that a footprint can reach takes part (PlaneGeo::ukeep, vkeep, from the
+// plan's max |u|, |v|): the rows passes run over the rows u < ukeep or u >= nu - ukeep and load /
+// store their two ends in v, the columns passes read / write those rows of T only, and only the
+// four corners of a ring slot are cleared.  All other cells are identically zero on the way to the
+// image and are never read by the degridder, so this is exact; a benchmark configuration
+// (cellsize = 1 / (4 longest baseline)) keeps about half of each axis.
+//
+// Per plane this moves (2 ukeep)(2 vkeep)*8 + 2*(2 ukeep)*npix*8 + 2*npix^2*4 bytes instead of
+// cuFFT's 8 passes over nu*nv*8 plus the screen kernel's cropped read.
 #include <cuda.h>
 #include <cuda_runtime.h>
 
